@@ -1,0 +1,126 @@
+/*
+ * scb200.h — C ABI of the B200-native Gaussian-splatting hot path (libscb200.so).
+ *
+ * Every entry point replaces one call the reference makes into a third-party CUDA
+ * extension (citations are to /root/reference):
+ *
+ *   sc_projection_fwd/bwd      gsplat.fully_fused_projection   street_gaussian/models/street_gaussian_renderer.py:219-232
+ *   sc_isect_count/emit        gsplat.isect_tiles              street_gaussian_renderer.py:243-252
+ *   sc_exclusive_scan_i32      (torch.cumsum inside isect_tiles)
+ *   sc_radix_sort_pairs        (cub::DeviceRadixSort inside isect_tiles)
+ *   sc_isect_offset_encode     gsplat.isect_offset_encode      street_gaussian_renderer.py:253
+ *   sc_sh_fwd/bwd              gsplat.spherical_harmonics      street_gaussian_renderer.py:256-260
+ *   sc_rasterize_fwd/bwd       gsplat.rasterize_to_pixels      street_gaussian_renderer.py:267-280
+ *                              (+ max_hit for diff_point_rasterization.PointRasterizer,
+ *                               data_processor/utils/render_utils.py:150-177)
+ *   sc_knn3_mean_dist2         simple_knn._C.distCUDA2         submodules/simple-knn/spatial.cu:16-25,
+ *                                                              simple_knn.cu:186-222
+ *
+ * Conventions: all pointers are DEVICE pointers unless named host_*; row-major contiguous
+ * fp32 / int32 / int64 arrays; `stream` is a cudaStream_t passed as void*; nothing here
+ * synchronises the stream; every function returns 0 on success or a negative sc_status
+ * (sc_last_error() gives a thread-local message).  No torch types cross this boundary.
+ */
+#ifndef SCB200_H
+#define SCB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum sc_status {
+    SC_OK = 0,
+    SC_ERR_BAD_ARG = -1,
+    SC_ERR_CUDA = -2,
+    SC_ERR_WORKSPACE = -3,
+    SC_ERR_UNSUPPORTED = -4
+};
+
+const char* sc_last_error(void);
+int sc_version(void);
+/* number of kernel launches issued through this library since load (bench.py "gpu_launches") */
+int64_t sc_launch_count(void);
+
+/* ---- A1: fused projection ------------------------------------------------------------ */
+/* means[N,3] quats[N,4](wxyz) scales[N,3] viewmats[C,4,4] Ks[C,3,3] ->
+ * radii[C,N] i32, means2d[C,N,2], depths[C,N], conics[C,N,3], compensations[C,N] (nullable).
+ * Culled Gaussians: radius 0, float outputs 0. */
+int sc_projection_fwd(int64_t N, int C, const float* means, const float* quats, const float* scales,
+                      const float* viewmats, const float* Ks, int width, int height, float eps2d,
+                      float near_plane, float far_plane, float radius_clip, int32_t* radii,
+                      float* means2d, float* depths, float* conics, float* compensations,
+                      void* stream);
+/* v_* inputs [C,N,...] (v_compensations nullable) -> v_means[N,3] v_quats[N,4] v_scales[N,3]
+ * (each nullable; summed over cameras, written not accumulated). */
+int sc_projection_bwd(int64_t N, int C, const float* means, const float* quats, const float* scales,
+                      const float* viewmats, const float* Ks, int width, int height, float eps2d,
+                      const int32_t* radii, const float* v_means2d, const float* v_depths,
+                      const float* v_conics, const float* v_compensations, float* v_means,
+                      float* v_quats, float* v_scales, void* stream);
+
+/* ---- A5: spherical harmonics ----------------------------------------------------------- */
+/* dirs[M,3] (un-normalised), coeffs[M,K,3], masks[M] u8 (nullable) -> colors[M,3]. */
+int sc_sh_fwd(int64_t M, int K, int degree, const float* dirs, const float* coeffs,
+              const uint8_t* masks, float* colors, void* stream);
+/* v_colors[M,3] -> v_coeffs[M,K,3] (fully written, zeros where masked), v_dirs[M,3] (nullable). */
+int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const float* coeffs,
+              const uint8_t* masks, const float* v_colors, float* v_coeffs, float* v_dirs,
+              void* stream);
+
+/* ---- A3/A4: tile intersection ---------------------------------------------------------- */
+int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, int tile_size,
+                   int tile_width, int tile_height, int32_t* tiles_per_gauss, void* stream);
+/* out[i] = sum_{j<i} in[j] (int64 accumulate); total (nullable) receives the grand total.
+ * workspace >= sc_scan_workspace_bytes(n). */
+int64_t sc_scan_workspace_bytes(int64_t n);
+int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out, int64_t* total,
+                          void* workspace, int64_t workspace_bytes, void* stream);
+/* emits, for camera-major then Gaussian order, the row-major tile list of each Gaussian:
+ * isect_ids = cam << (32+tile_n_bits) | tile << 32 | bits(depth); flatten_ids = cam*N + g. */
+int sc_isect_emit(int64_t N, int C, const float* means2d, const int32_t* radii, const float* depths,
+                  const int64_t* cum_tiles, int tile_size, int tile_width, int tile_height,
+                  int tile_n_bits, int64_t n_isects, int64_t* isect_ids, int32_t* flatten_ids,
+                  void* stream);
+/* stable LSD radix sort of (u64 key, u32 value) pairs on key bits [0, end_bit), n < 2^30.
+ * Both buffer pairs are ping-pong storage; RETURNS 0 if the sorted pairs ended in
+ * keys_out/vals_out, 1 if they ended in keys_in/vals_in (even pass count), <0 on error. */
+int64_t sc_sort_workspace_bytes(int64_t n);
+int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
+                        uint32_t* vals_out, int end_bit, void* workspace, int64_t workspace_bytes,
+                        void* stream);
+int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, int tile_width,
+                           int tile_height, int tile_n_bits, int32_t* offsets, void* stream);
+
+/* ---- A7/A8: compositing ---------------------------------------------------------------- */
+/* CH in 1..5; backgrounds[C,CH] nullable; max_hit 0 = unlimited.
+ * render_colors[C,H,W,CH], render_alphas[C,H,W]; saved for backward (nullable):
+ * last_ids[C,H,W] i32 (index into flatten_ids of the last contributing splat, -1 if none),
+ * final_T[C,H,W] (exact final transmittance; 1-render_alpha loses bits near saturation). */
+int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
+                     int tile_size, const float* means2d, const float* conics, const float* colors,
+                     const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
+                     const int32_t* flatten_ids, int max_hit, float* render_colors,
+                     float* render_alphas, int32_t* last_ids, float* final_T, void* stream);
+/* gradient buffers must be ZEROED by the caller; v_means2d_abs nullable. */
+int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
+                     int tile_size, const float* means2d, const float* conics, const float* colors,
+                     const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
+                     const int32_t* flatten_ids, const float* final_T,
+                     const int32_t* last_ids, const float* v_render_colors,
+                     const float* v_render_alphas, float* v_means2d, float* v_means2d_abs,
+                     float* v_conics, float* v_colors, float* v_opacities, void* stream);
+
+/* ---- A10: distCUDA2 -------------------------------------------------------------------- */
+/* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,
+ * as the reference's FLT_MAX placeholders overflow).  Never synchronises (scene bounds stay
+ * on the device, unlike the reference's two blocking cudaMemcpy). */
+int64_t sc_knn_workspace_bytes(int64_t P);
+int sc_knn3_mean_dist2(int64_t P, const float* points, float* mean_dist2, void* workspace,
+                       int64_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCB200_H */

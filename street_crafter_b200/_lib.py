@@ -1,0 +1,74 @@
+"""ctypes binding of libscb200.so (the C ABI declared in include/scb200.h).
+
+There is NO fallback: if the shared library cannot be loaded the import fails loudly, and
+every call raises RuntimeError on a non-zero status.  The library is built in-tree by
+`python -m street_crafter_b200.build` (nvcc, sm_100a)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libscb200.so")
+
+_i64, _i32, _f32, _ptr = C.c_int64, C.c_int, C.c_float, C.c_void_p
+
+# name -> (restype, argtypes); mirrors include/scb200.h one to one
+SIGNATURES = {
+    "sc_last_error": (C.c_char_p, []),
+    "sc_version": (_i32, []),
+    "sc_launch_count": (_i64, []),
+    "sc_projection_fwd": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _f32, _f32, _f32,
+                                 _f32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_projection_bwd": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _f32, _ptr, _ptr,
+                                 _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_sh_fwd": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_sh_bwd": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_isect_count": (_i32, [_i64, _ptr, _ptr, _i32, _i32, _i32, _ptr, _ptr]),
+    "sc_scan_workspace_bytes": (_i64, [_i64]),
+    "sc_exclusive_scan_i32": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
+    "sc_isect_emit": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i64, _ptr, _ptr,
+                             _ptr]),
+    "sc_sort_workspace_bytes": (_i64, [_i64]),
+    "sc_radix_sort_pairs": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _i64, _ptr]),
+    "sc_isect_offset_encode": (_i32, [_i64, _ptr, _i32, _i32, _i32, _i32, _ptr, _ptr]),
+    "sc_rasterize_fwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
+                                _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_rasterize_bwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
+                                _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_knn_workspace_bytes": (_i64, [_i64]),
+    "sc_knn3_mean_dist2": (_i32, [_i64, _ptr, _ptr, _ptr, _i64, _ptr]),
+}
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        # in-tree build (nvcc cross-compiles sm_100a without a GPU); never a CPU fallback
+        from .build import build
+        build()
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing; run `python -m street_crafter_b200.build`")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as e:  # stale build
+            raise ImportError(f"{LIB_PATH} does not export {name}; rebuild with "
+                              f"`python -m street_crafter_b200.build --force`") from e
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+
+
+def check(status: int, what: str) -> int:
+    if status < 0:
+        msg = lib.sc_last_error()
+        raise RuntimeError(f"{what} failed (status {status}): {msg.decode() if msg else ''}")
+    return status
+
+
+def launch_count() -> int:
+    return int(lib.sc_launch_count())

@@ -1,0 +1,385 @@
+// Fused projection (A1) and tile binning (A3/A4) — the integer-feeding chain.
+//
+// THIS FILE IS COMPILED WITH -fmad=false (see build.py): every fp32 operation below is a
+// separately rounded IEEE op in exactly the association order of oracle/gsplat_torch.py, so
+// radii, tile bounds and the depth bits of the sort key are bit-identical to the CPU oracle.
+// The kernels are HBM-bound streaming passes (80 B/Gaussian), so giving up FMA costs nothing.
+//
+// Replaces gsplat.fully_fused_projection / isect_tiles / isect_offset_encode as called at
+// /root/reference/street_gaussian/models/street_gaussian_renderer.py:219-253.
+#include "common.cuh"
+
+namespace {
+
+constexpr int PROJ_THREADS = 256;
+
+struct Cam {
+    float W[3][3];
+    float t[3];
+    float fx, fy, cx, cy;
+};
+
+__device__ __forceinline__ Cam load_cam(const float* __restrict__ viewmat, const float* __restrict__ K) {
+    Cam c;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) c.W[i][j] = __ldg(viewmat + i * 4 + j);
+        c.t[i] = __ldg(viewmat + i * 4 + 3);
+    }
+    c.fx = __ldg(K + 0);
+    c.cx = __ldg(K + 2);
+    c.fy = __ldg(K + 4);
+    c.cy = __ldg(K + 5);
+    return c;
+}
+
+// quat (wxyz, un-normalised) + scale -> 6 unique entries of the world covariance
+__device__ __forceinline__ void quat_scale_to_covar(const float4 q, const float s0, const float s1,
+                                                    const float s2, float S[6]) {
+    float w = q.x, x = q.y, y = q.z, z = q.w;
+    float n2 = ((w * w + x * x) + y * y) + z * z;
+    float nrm = fmaxf(sqrtf(n2), 1e-12f);
+    w = w / nrm; x = x / nrm; y = y / nrm; z = z / nrm;
+    float x2 = x * x, y2 = y * y, z2 = z * z;
+    float xy = x * y, xz = x * z, yz = y * z;
+    float wx = w * x, wy = w * y, wz = w * z;
+    float R[3][3] = {{1.0f - 2.0f * (y2 + z2), 2.0f * (xy - wz), 2.0f * (xz + wy)},
+                     {2.0f * (xy + wz), 1.0f - 2.0f * (x2 + z2), 2.0f * (yz - wx)},
+                     {2.0f * (xz - wy), 2.0f * (yz + wx), 1.0f - 2.0f * (x2 + y2)}};
+    float M[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        M[i][0] = R[i][0] * s0;
+        M[i][1] = R[i][1] * s1;
+        M[i][2] = R[i][2] * s2;
+    }
+    S[0] = (M[0][0] * M[0][0] + M[0][1] * M[0][1]) + M[0][2] * M[0][2];
+    S[1] = (M[0][0] * M[1][0] + M[0][1] * M[1][1]) + M[0][2] * M[1][2];
+    S[2] = (M[0][0] * M[2][0] + M[0][1] * M[2][1]) + M[0][2] * M[2][2];
+    S[3] = (M[1][0] * M[1][0] + M[1][1] * M[1][1]) + M[1][2] * M[1][2];
+    S[4] = (M[1][0] * M[2][0] + M[1][1] * M[2][1]) + M[1][2] * M[2][2];
+    S[5] = (M[2][0] * M[2][0] + M[2][1] * M[2][1]) + M[2][2] * M[2][2];
+}
+
+__global__ void __launch_bounds__(PROJ_THREADS)
+projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* __restrict__ quats,
+                      const float* __restrict__ scales, const float* __restrict__ viewmats,
+                      const float* __restrict__ Ks, int width, int height, float eps2d, float near_plane,
+                      float far_plane, float radius_clip, int32_t* __restrict__ radii,
+                      float* __restrict__ means2d, float* __restrict__ depths,
+                      float* __restrict__ conics, float* __restrict__ comps) {
+    // stage the two 12-byte-stride arrays through shared memory so that global loads are
+    // full-line float4 accesses (AoS [N,3] would otherwise be 3 strided scalar loads)
+    __shared__ float s_means[PROJ_THREADS * 3];
+    __shared__ float s_scales[PROJ_THREADS * 3];
+    __shared__ float s_conics[PROJ_THREADS * 3];
+    const int cam = blockIdx.y;
+    const int64_t base = (int64_t)blockIdx.x * PROJ_THREADS;
+    const int tid = threadIdx.x;
+    const int64_t n_here = min((int64_t)PROJ_THREADS, N - base);
+    {
+        const int64_t f0 = base * 3;           // float offset, multiple of 768 -> 16B aligned
+        const int nf = (int)n_here * 3;
+        const int nf4 = nf >> 2;
+        const float4* m4 = reinterpret_cast<const float4*>(means + f0);
+        const float4* s4 = reinterpret_cast<const float4*>(scales + f0);
+        if (tid < nf4) {
+            reinterpret_cast<float4*>(s_means)[tid] = __ldg(m4 + tid);
+            reinterpret_cast<float4*>(s_scales)[tid] = __ldg(s4 + tid);
+        }
+        const int rem = nf - (nf4 << 2);
+        if (tid < rem) {
+            s_means[(nf4 << 2) + tid] = __ldg(means + f0 + (nf4 << 2) + tid);
+            s_scales[(nf4 << 2) + tid] = __ldg(scales + f0 + (nf4 << 2) + tid);
+        }
+    }
+    __syncthreads();
+    const int64_t g = base + tid;
+    const bool active = g < N;
+    int32_t radius_i = 0;
+    float o_mx = 0.f, o_my = 0.f, o_z = 0.f, o_a = 0.f, o_b = 0.f, o_c = 0.f, o_comp = 0.f;
+    if (active) {
+        const Cam c = load_cam(viewmats + cam * 16, Ks + cam * 9);
+        const float px = s_means[tid * 3 + 0], py = s_means[tid * 3 + 1], pz = s_means[tid * 3 + 2];
+        const float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
+        float S[6];
+        quat_scale_to_covar(q, s_scales[tid * 3 + 0], s_scales[tid * 3 + 1], s_scales[tid * 3 + 2], S);
+        const float Sm[3][3] = {{S[0], S[1], S[2]}, {S[1], S[3], S[4]}, {S[2], S[4], S[5]}};
+        const float xc = ((c.W[0][0] * px + c.W[0][1] * py) + c.W[0][2] * pz) + c.t[0];
+        const float yc = ((c.W[1][0] * px + c.W[1][1] * py) + c.W[1][2] * pz) + c.t[1];
+        const float zc = ((c.W[2][0] * px + c.W[2][1] * py) + c.W[2][2] * pz) + c.t[2];
+        float A[3][3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j)
+                A[i][j] = (c.W[i][0] * Sm[0][j] + c.W[i][1] * Sm[1][j]) + c.W[i][2] * Sm[2][j];
+#define CC(i, j) ((A[i][0] * c.W[j][0] + A[i][1] * c.W[j][1]) + A[i][2] * c.W[j][2])
+        const float c00 = CC(0, 0), c01 = CC(0, 1), c02 = CC(0, 2), c11 = CC(1, 1), c12 = CC(1, 2),
+                    c22 = CC(2, 2);
+#undef CC
+        const float Wf = (float)width, Hf = (float)height;
+        const float tan_fovx = 0.5f * Wf / c.fx;
+        const float tan_fovy = 0.5f * Hf / c.fy;
+        const float lim_x_pos = (Wf - c.cx) / c.fx + SC_JAC_PAD * tan_fovx;
+        const float lim_x_neg = c.cx / c.fx + SC_JAC_PAD * tan_fovx;
+        const float lim_y_pos = (Hf - c.cy) / c.fy + SC_JAC_PAD * tan_fovy;
+        const float lim_y_neg = c.cy / c.fy + SC_JAC_PAD * tan_fovy;
+        const float zs = (zc == 0.0f) ? 1.0f : zc;
+        const float tx = zs * fminf(fmaxf(xc / zs, -lim_x_neg), lim_x_pos);
+        const float ty = zs * fminf(fmaxf(yc / zs, -lim_y_neg), lim_y_pos);
+        const float z2 = zs * zs;
+        const float J00 = c.fx / zs;
+        const float J02 = -(c.fx * tx) / z2;
+        const float J11 = c.fy / zs;
+        const float J12 = -(c.fy * ty) / z2;
+        const float T00 = J00 * c00 + J02 * c02;
+        const float T01 = J00 * c01 + J02 * c12;
+        const float T02 = J00 * c02 + J02 * c22;
+        const float T11 = J11 * c11 + J12 * c12;
+        const float T12 = J11 * c12 + J12 * c22;
+        const float v00 = T00 * J00 + T02 * J02;
+        const float v01 = T01 * J11 + T02 * J12;
+        const float v11 = T11 * J11 + T12 * J12;
+        const float mx = (c.fx * xc) / zs + c.cx;
+        const float my = (c.fy * yc) / zs + c.cy;
+        const float det_orig = v00 * v11 - v01 * v01;
+        const float b00 = v00 + eps2d;
+        const float b11 = v11 + eps2d;
+        const float det = b00 * b11 - v01 * v01;
+        bool valid = (det > 0.0f) && (zc > near_plane) && (zc < far_plane);
+        const float dets = (det > 0.0f) ? det : 1.0f;
+        const float comp = sqrtf(fmaxf(det_orig / dets, 0.0f));
+        const float b = 0.5f * (b00 + b11);
+        const float v1 = b + sqrtf(fmaxf(b * b - det, SC_EIGEN_FLOOR));
+        const float radius = ceilf(3.0f * sqrtf(v1));
+        valid = valid && (radius > radius_clip);
+        const bool inside = (mx + radius > 0.0f) && (mx - radius < Wf) && (my + radius > 0.0f) &&
+                            (my - radius < Hf);
+        valid = valid && inside;
+        if (valid) {
+            radius_i = (int32_t)radius;
+            o_mx = mx; o_my = my; o_z = zc;
+            o_a = b11 / dets; o_b = -v01 / dets; o_c = b00 / dets;
+            o_comp = comp;
+        }
+    }
+    const int64_t o = (int64_t)cam * N + g;
+    if (active) {
+        radii[o] = radius_i;
+        reinterpret_cast<float2*>(means2d)[o] = make_float2(o_mx, o_my);
+        depths[o] = o_z;
+        if (comps) comps[o] = o_comp;
+    }
+    s_conics[tid * 3 + 0] = o_a;
+    s_conics[tid * 3 + 1] = o_b;
+    s_conics[tid * 3 + 2] = o_c;
+    __syncthreads();
+    {
+        // coalesced float4 write-back of the [.,3] conics
+        float* dst = conics + ((int64_t)cam * N + base) * 3;
+        const int nf = (int)n_here * 3;
+        const bool aligned = ((((int64_t)cam * N + base) * 3) & 3) == 0;
+        if (aligned) {
+            const int nf4 = nf >> 2;
+            if (tid < nf4) reinterpret_cast<float4*>(dst)[tid] = reinterpret_cast<float4*>(s_conics)[tid];
+            const int rem = nf - (nf4 << 2);
+            if (tid < rem) dst[(nf4 << 2) + tid] = s_conics[(nf4 << 2) + tid];
+        } else {
+            for (int i = tid; i < nf; i += PROJ_THREADS) dst[i] = s_conics[i];
+        }
+    }
+}
+
+// ------------------------------------------------------------------ tile bounds (A3 pass 1)
+struct TileBox { int x0, x1, y0, y1; };
+
+__device__ __forceinline__ TileBox tile_box(float mx, float my, int32_t radius, float ts, int tw, int th) {
+    const float r = (float)radius / ts;
+    const float tx = mx / ts;
+    const float ty = my / ts;
+    TileBox b;
+    b.x0 = (int)fminf(fmaxf(floorf(tx - r), 0.0f), (float)tw);
+    b.x1 = (int)fminf(fmaxf(ceilf(tx + r), 0.0f), (float)tw);
+    b.y0 = (int)fminf(fmaxf(floorf(ty - r), 0.0f), (float)th);
+    b.y1 = (int)fminf(fmaxf(ceilf(ty + r), 0.0f), (float)th);
+    return b;
+}
+
+__global__ void __launch_bounds__(256)
+isect_count_kernel(int64_t CN, const float2* __restrict__ means2d, const int32_t* __restrict__ radii,
+                   float ts, int tw, int th, int32_t* __restrict__ tiles_per_gauss) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= CN) return;
+    const int32_t r = __ldg(radii + i);
+    int32_t n = 0;
+    if (r > 0) {
+        const float2 m = __ldg(means2d + i);
+        const TileBox b = tile_box(m.x, m.y, r, ts, tw, th);
+        n = (b.x1 - b.x0) * (b.y1 - b.y0);
+    }
+    tiles_per_gauss[i] = n;
+}
+
+// ------------------------------------------------------------------ emit (A3 pass 2)
+// One warp owns 32 consecutive (camera, Gaussian) entries and writes their concatenated tile
+// lists with a load-balanced search, so every store instruction covers 32 CONSECUTIVE output
+// slots (coalesced 256 B of keys + 128 B of values) regardless of how skewed the per-Gaussian
+// tile counts are (a near-camera Gaussian can cover the whole screen).
+__global__ void __launch_bounds__(256)
+isect_emit_kernel(int64_t N, int64_t CN, const float2* __restrict__ means2d,
+                  const int32_t* __restrict__ radii, const float* __restrict__ depths,
+                  const int64_t* __restrict__ cum_tiles, float ts, int tw, int th, int tile_n_bits,
+                  int64_t n_isects, int64_t* __restrict__ isect_ids, int32_t* __restrict__ flatten_ids) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t i = warp * 32 + lane;
+    int x0 = 0, w = 1, y0 = 0, cnt = 0;
+    uint32_t dbits = 0;
+    int64_t start = 0;
+    if (i < CN) {
+        const int32_t r = __ldg(radii + i);
+        start = __ldg(cum_tiles + i);
+        if (r > 0) {
+            const float2 m = __ldg(means2d + i);
+            const TileBox b = tile_box(m.x, m.y, r, ts, tw, th);
+            x0 = b.x0; y0 = b.y0;
+            w = max(b.x1 - b.x0, 1);
+            cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
+            dbits = __float_as_uint(__ldg(depths + i));
+        }
+    }
+    // exclusive prefix of counts inside the warp
+    int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int v = __shfl_up_sync(full, incl, d);
+        if (lane >= d) incl += v;
+    }
+    const int excl = incl - cnt;
+    const int total = __shfl_sync(full, incl, 31);
+    const int64_t warp_start = __shfl_sync(full, start, 0);
+    const int64_t cam_of_i = (i < CN) ? i / N : 0;
+    for (int basej = 0; basej < total; basej += 32) {
+        const int j = basej + lane;
+        int lo = 0;
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1) {
+            const int cand = lo + step;
+            const int pv = __shfl_sync(full, excl, cand & 31);
+            if (cand < 32 && pv <= j) lo = cand;
+        }
+        // zero-count lanes share excl with their successor; the search lands on the LAST lane
+        // whose excl <= j, which is the one that actually owns slot j (its count > 0).
+        const int o_excl = __shfl_sync(full, excl, lo);
+        const int o_x0 = __shfl_sync(full, x0, lo);
+        const int o_y0 = __shfl_sync(full, y0, lo);
+        const int o_w = __shfl_sync(full, w, lo);
+        const uint32_t o_d = __shfl_sync(full, dbits, lo);
+        const int64_t o_cam = __shfl_sync(full, cam_of_i, lo);
+        if (j < total) {
+            const int k = j - o_excl;
+            const int ty = o_y0 + k / o_w;
+            const int tx = o_x0 + k % o_w;
+            const int64_t tile = (int64_t)ty * tw + tx;
+            const int64_t key = (o_cam << (32 + tile_n_bits)) | (tile << 32) | (int64_t)o_d;
+            const int64_t pos = warp_start + j;
+            if (pos < n_isects) {
+                isect_ids[pos] = key;
+                flatten_ids[pos] = (int32_t)(warp * 32 + lo);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ offsets (A4)
+__global__ void __launch_bounds__(256)
+isect_offset_encode_kernel(int64_t n_isects, const int64_t* __restrict__ isect_ids, int n_tiles_total,
+                           int n_tiles, int tile_n_bits, int32_t* __restrict__ offsets) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_isects) return;
+    const int64_t mask = ((int64_t)1 << tile_n_bits) - 1;
+    const int64_t k = __ldg(isect_ids + i);
+    const int64_t slot = (k >> (32 + tile_n_bits)) * n_tiles + ((k >> 32) & mask);
+    if (i == 0) {
+        for (int64_t s = 0; s <= slot; ++s) offsets[s] = 0;
+    } else {
+        const int64_t kp = __ldg(isect_ids + i - 1);
+        const int64_t slot_p = (kp >> (32 + tile_n_bits)) * n_tiles + ((kp >> 32) & mask);
+        for (int64_t s = slot_p + 1; s <= slot; ++s) offsets[s] = (int32_t)i;
+    }
+    if (i == n_isects - 1) {
+        for (int64_t s = slot + 1; s < n_tiles_total; ++s) offsets[s] = (int32_t)n_isects;
+    }
+}
+
+}  // namespace
+
+extern "C" int sc_projection_fwd(int64_t N, int C, const float* means, const float* quats,
+                                 const float* scales, const float* viewmats, const float* Ks, int width,
+                                 int height, float eps2d, float near_plane, float far_plane,
+                                 float radius_clip, int32_t* radii, float* means2d, float* depths,
+                                 float* conics, float* compensations, void* stream) {
+    SC_CHECK_ARG(N >= 0 && C >= 1, "N, C");
+    SC_CHECK_ARG(width > 0 && height > 0, "image size");
+    if (N == 0) return SC_OK;
+    SC_CHECK_ARG(means && quats && scales && viewmats && Ks && radii && means2d && depths && conics,
+                 "null pointer");
+    SC_CHECK_ARG(((uintptr_t)means & 15) == 0 && ((uintptr_t)scales & 15) == 0 &&
+                     ((uintptr_t)quats & 15) == 0 && ((uintptr_t)means2d & 7) == 0 &&
+                     ((uintptr_t)conics & 15) == 0,
+                 "16-byte alignment of means/quats/scales/conics");
+    dim3 grid((unsigned)sc_div_up(N, PROJ_THREADS), (unsigned)C);
+    projection_fwd_kernel<<<grid, PROJ_THREADS, 0, (cudaStream_t)stream>>>(
+        N, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip,
+        radii, means2d, depths, conics, compensations);
+    SC_CHECK_LAUNCH("projection_fwd_kernel");
+    return SC_OK;
+}
+
+extern "C" int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, int tile_size,
+                              int tile_width, int tile_height, int32_t* tiles_per_gauss, void* stream) {
+    SC_CHECK_ARG(CN >= 0 && tile_size > 0 && tile_width > 0 && tile_height > 0, "sizes");
+    if (CN == 0) return SC_OK;
+    SC_CHECK_ARG(means2d && radii && tiles_per_gauss, "null pointer");
+    isect_count_kernel<<<(unsigned)sc_div_up(CN, 256), 256, 0, (cudaStream_t)stream>>>(
+        CN, reinterpret_cast<const float2*>(means2d), radii, (float)tile_size, tile_width, tile_height,
+        tiles_per_gauss);
+    SC_CHECK_LAUNCH("isect_count_kernel");
+    return SC_OK;
+}
+
+extern "C" int sc_isect_emit(int64_t N, int C, const float* means2d, const int32_t* radii,
+                             const float* depths, const int64_t* cum_tiles, int tile_size, int tile_width,
+                             int tile_height, int tile_n_bits, int64_t n_isects, int64_t* isect_ids,
+                             int32_t* flatten_ids, void* stream) {
+    SC_CHECK_ARG(N >= 0 && C >= 1 && n_isects >= 0, "sizes");
+    SC_CHECK_ARG(tile_n_bits > 0 && tile_n_bits < 24, "tile_n_bits");
+    if (N == 0 || n_isects == 0) return SC_OK;
+    SC_CHECK_ARG(means2d && radii && depths && cum_tiles && isect_ids && flatten_ids, "null pointer");
+    const int64_t CN = N * C;
+    const int64_t warps = sc_div_up(CN, 32);
+    isect_emit_kernel<<<(unsigned)sc_div_up(warps, 8), 256, 0, (cudaStream_t)stream>>>(
+        N, CN, reinterpret_cast<const float2*>(means2d), radii, depths, cum_tiles, (float)tile_size,
+        tile_width, tile_height, tile_n_bits, n_isects, isect_ids, flatten_ids);
+    SC_CHECK_LAUNCH("isect_emit_kernel");
+    return SC_OK;
+}
+
+extern "C" int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, int tile_width,
+                                      int tile_height, int tile_n_bits, int32_t* offsets, void* stream) {
+    SC_CHECK_ARG(n_isects >= 0 && C >= 1 && tile_width > 0 && tile_height > 0, "sizes");
+    SC_CHECK_ARG(offsets, "null pointer");
+    const int n_tiles = tile_width * tile_height;
+    if (n_isects == 0) {
+        SC_CUDA(cudaMemsetAsync(offsets, 0, sizeof(int32_t) * (size_t)n_tiles * C, (cudaStream_t)stream));
+        return SC_OK;
+    }
+    SC_CHECK_ARG(isect_ids, "null pointer");
+    isect_offset_encode_kernel<<<(unsigned)sc_div_up(n_isects, 256), 256, 0, (cudaStream_t)stream>>>(
+        n_isects, isect_ids, n_tiles * C, n_tiles, tile_n_bits, offsets);
+    SC_CHECK_LAUNCH("isect_offset_encode_kernel");
+    return SC_OK;
+}

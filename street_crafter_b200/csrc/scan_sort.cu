@@ -1,0 +1,383 @@
+// Hand-written device scan and stable LSD radix sort (the cumsum and cub::DeviceRadixSort
+// inside gsplat.isect_tiles, /root/reference/street_gaussian/models/street_gaussian_renderer.py:243-252).
+//
+// Sort design (HBM-bound, integer work; no tensor cores):
+//   * one histogram kernel reads the keys once and builds the digit histograms of ALL passes;
+//   * each 8-bit pass is ONE kernel ("onesweep"): a tile of 4096 pairs is ranked stably in
+//     shared memory (warp match.any multi-split), tile prefixes are resolved with a chained
+//     decoupled look-back, and pairs leave through shared memory so that every digit run is
+//     written with consecutive, coalesced stores.  Traffic per pass = 12 B read + 12 B write
+//     per pair.  Tiles are handed out by an atomic ticket so a waiting tile's predecessors are
+//     always resident (forward progress).
+//   * only the significant key bits are sorted: 32 depth bits + tile bits (+ camera bits).
+#include "common.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------- scan
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+__device__ __forceinline__ int64_t block_exclusive_scan_i64(int64_t v, int64_t* s_warp, int64_t& block_total) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int64_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int64_t t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[w] = incl;
+    __syncthreads();
+    int64_t wsum = 0, tot = 0;
+    const int nw = blockDim.x >> 5;
+    for (int i = 0; i < nw; ++i) {
+        const int64_t t = s_warp[i];
+        if (i < w) wsum += t;
+        tot += t;
+    }
+    block_total = tot;
+    __syncthreads();
+    return wsum + incl - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_block_sums_kernel(int64_t n, const int32_t* __restrict__ in, int64_t* __restrict__ block_sums) {
+    __shared__ int64_t s_warp[SCAN_THREADS / 32];
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+    int64_t s = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        const int64_t idx = base + i * SCAN_THREADS + threadIdx.x;
+        if (idx < n) s += __ldg(in + idx);
+    }
+    int64_t tot;
+    block_exclusive_scan_i64(s, s_warp, tot);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = tot;
+}
+
+__global__ void __launch_bounds__(1024)
+scan_spine_kernel(int64_t nb, int64_t* __restrict__ block_sums, int64_t* __restrict__ total) {
+    __shared__ int64_t s_warp[32];
+    int64_t carry = 0;
+    for (int64_t base = 0; base < nb; base += 1024) {
+        const int64_t idx = base + threadIdx.x;
+        const int64_t v = idx < nb ? block_sums[idx] : 0;
+        int64_t tot;
+        const int64_t ex = block_exclusive_scan_i64(v, s_warp, tot);
+        if (idx < nb) block_sums[idx] = carry + ex;
+        carry += tot;
+    }
+    if (threadIdx.x == 0 && total) *total = carry;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply_kernel(int64_t n, const int32_t* __restrict__ in, const int64_t* __restrict__ block_sums,
+                  int64_t* __restrict__ out) {
+    __shared__ int64_t s_warp[SCAN_THREADS / 32];
+    // blocked arrangement per thread: thread t owns SCAN_ITEMS consecutive elements
+    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    int32_t v[SCAN_ITEMS];
+    int64_t s = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        v[i] = (base + i < n) ? __ldg(in + base + i) : 0;
+        s += v[i];
+    }
+    int64_t tot;
+    int64_t ex = block_exclusive_scan_i64(s, s_warp, tot) + block_sums[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; ++i) {
+        if (base + i < n) out[base + i] = ex;
+        ex += v[i];
+    }
+}
+
+// ------------------------------------------------------------------------------- radix sort
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+constexpr int SORT_KPT = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_KPT;  // 4096 pairs
+constexpr int MAX_PASSES = 8;
+constexpr uint32_t FLAG_AGG = 1u << 30;
+constexpr uint32_t FLAG_INC = 2u << 30;
+constexpr uint32_t FLAG_MASK = 3u << 30;
+constexpr uint32_t VAL_MASK = ~FLAG_MASK;
+
+struct SortSmem {
+    uint64_t keys[SORT_TILE];
+    uint32_t vals[SORT_TILE];
+    uint32_t warp_hist[SORT_WARPS][RADIX];
+    uint32_t digit_start[RADIX];   // exclusive start of each digit inside the tile
+    int64_t gbase[RADIX];          // global position of local slot 0 of each digit run
+    uint32_t scan_tmp[SORT_WARPS];
+    uint32_t tile_id;
+};
+
+__global__ void __launch_bounds__(256)
+sort_histogram_kernel(int64_t n, const uint64_t* __restrict__ keys, int passes, int end_bit,
+                      uint32_t* __restrict__ hist /*[passes][RADIX]*/) {
+    extern __shared__ uint32_t s_hist[];  // [passes][RADIX]
+    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) s_hist[i] = 0;
+    __syncthreads();
+    // warp-aggregated shared atomics: the keys of one warp share most high digits (same tile,
+    // similar depth), so un-aggregated atomics would serialise 32-deep on one bank.
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    const int64_t n_round = (n + 31) & ~(int64_t)31;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        const bool in = i < n;
+        const uint64_t k = in ? __ldg(keys + i) : 0ull;
+        const unsigned act = __ballot_sync(0xffffffffu, in);
+        for (int p = 0; p < passes; ++p) {
+            const int shift = p * RADIX_BITS;
+            const int nb = min(RADIX_BITS, end_bit - shift);
+            const uint32_t d = (uint32_t)(k >> shift) & ((1u << nb) - 1u);
+            const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu) & act;
+            if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p * RADIX + d], (uint32_t)__popc(peers));
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) {
+        const uint32_t v = s_hist[i];
+        if (v) atomicAdd(&hist[i], v);
+    }
+}
+
+__global__ void __launch_bounds__(RADIX)
+sort_hist_scan_kernel(uint32_t* __restrict__ hist) {
+    // exclusive scan of each pass's 256 bins, in place
+    __shared__ uint32_t s[RADIX];
+    uint32_t* h = hist + blockIdx.x * RADIX;
+    s[threadIdx.x] = h[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t acc = 0;
+        for (int i = 0; i < RADIX; ++i) {
+            const uint32_t v = s[i];
+            s[i] = acc;
+            acc += v;
+        }
+    }
+    __syncthreads();
+    h[threadIdx.x] = s[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(SORT_THREADS)
+onesweep_pass_kernel(int64_t n, const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                     uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int nbits,
+                     const uint32_t* __restrict__ digit_offset /*[RADIX] exclusive*/,
+                     volatile uint32_t* __restrict__ lookback /*[tiles][RADIX]*/,
+                     uint32_t* __restrict__ ticket) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    SortSmem& sm = *reinterpret_cast<SortSmem*>(smem_raw);
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t dmask = (1u << nbits) - 1u;
+
+    if (tid == 0) sm.tile_id = atomicAdd(ticket, 1u);
+    for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&sm.warp_hist[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t tile = sm.tile_id;
+    const int64_t tile_base = (int64_t)tile * SORT_TILE;
+    const int n_valid = (int)min((int64_t)SORT_TILE, n - tile_base);
+
+    // ---- load keys (warp-striped: item i of lane l = warp_base + i*32 + l)
+    uint64_t key[SORT_KPT];
+    uint16_t rank[SORT_KPT];
+    const int warp_base = w * (32 * SORT_KPT);
+#pragma unroll
+    for (int i = 0; i < SORT_KPT; ++i) {
+        const int local = warp_base + i * 32 + lane;
+        key[i] = (local < n_valid) ? __ldg(keys_in + tile_base + local) : ~0ull;
+    }
+    // ---- stable warp-level ranking
+    const uint32_t lt_mask = (1u << lane) - 1u;
+#pragma unroll
+    for (int i = 0; i < SORT_KPT; ++i) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t pre = sm.warp_hist[w][d];
+        rank[i] = (uint16_t)(pre + __popc(peers & lt_mask));
+        __syncwarp();
+        if ((peers & lt_mask) == 0) sm.warp_hist[w][d] = pre + __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- per digit (thread == digit): warp-exclusive offsets, tile count, look-back
+    {
+        const int d = tid;
+        uint32_t acc = 0;
+#pragma unroll
+        for (int ww = 0; ww < SORT_WARPS; ++ww) {
+            const uint32_t c = sm.warp_hist[ww][d];
+            sm.warp_hist[ww][d] = acc;
+            acc += c;
+        }
+        const uint32_t count = acc;
+        // publish aggregate, then resolve exclusive prefix over previous tiles
+        volatile uint32_t* my = lookback + (size_t)tile * RADIX + d;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            *my = count | FLAG_INC;
+        } else {
+            *my = count | FLAG_AGG;
+            int64_t t = (int64_t)tile - 1;
+            while (true) {
+                const uint32_t v = lookback[(size_t)t * RADIX + d];
+                const uint32_t f = v & FLAG_MASK;
+                if (f == 0) continue;  // not yet published: spin
+                excl += v & VAL_MASK;
+                if (f == FLAG_INC) break;
+                --t;
+            }
+            *my = (excl + count) | FLAG_INC;
+        }
+        // block exclusive scan of counts over digits
+        uint32_t incl = count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t2 = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t2;
+        }
+        if (lane == 31) sm.scan_tmp[w] = incl;
+        __syncthreads();
+        uint32_t wsum = 0;
+#pragma unroll
+        for (int ww = 0; ww < SORT_WARPS; ++ww)
+            if (ww < w) wsum += sm.scan_tmp[ww];
+        const uint32_t dstart = wsum + incl - count;
+        sm.digit_start[d] = dstart;
+        sm.gbase[d] = (int64_t)digit_offset[d] + (int64_t)excl - (int64_t)dstart;
+    }
+    __syncthreads();
+
+    // ---- scatter into shared memory in sorted order
+#pragma unroll
+    for (int i = 0; i < SORT_KPT; ++i) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+        const uint32_t pos = sm.digit_start[d] + sm.warp_hist[w][d] + rank[i];
+        rank[i] = (uint16_t)pos;
+        sm.keys[pos] = key[i];
+    }
+#pragma unroll
+    for (int i = 0; i < SORT_KPT; ++i) {
+        const int local = warp_base + i * 32 + lane;
+        if (local < n_valid) sm.vals[rank[i]] = __ldg(vals_in + tile_base + local);
+    }
+    __syncthreads();
+    // ---- coalesced write-out: consecutive threads -> consecutive slots of a digit run
+#pragma unroll
+    for (int i = 0; i < SORT_KPT; ++i) {
+        const int local = i * SORT_THREADS + tid;
+        if (local < n_valid) {
+            const uint64_t k = sm.keys[local];
+            const uint32_t d = (uint32_t)(k >> shift) & dmask;
+            const int64_t g = sm.gbase[d] + local;
+            keys_out[g] = k;
+            vals_out[g] = sm.vals[local];
+        }
+    }
+}
+
+struct SortPlan {
+    int passes;
+    int64_t tiles;
+    int64_t hist_off, lookback_off, ticket_off, total;
+};
+
+SortPlan make_plan(int64_t n, int end_bit) {
+    SortPlan p;
+    p.passes = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+    p.tiles = sc_div_up(n, SORT_TILE);
+    p.hist_off = 0;
+    p.ticket_off = sc_align_up((int64_t)MAX_PASSES * RADIX * 4, 256);
+    p.lookback_off = p.ticket_off + 256;
+    p.total = p.lookback_off + (int64_t)MAX_PASSES * p.tiles * RADIX * 4;
+    return p;
+}
+
+}  // namespace
+
+extern "C" int64_t sc_scan_workspace_bytes(int64_t n) { return (sc_div_up(n, SCAN_TILE) + 1) * 8; }
+
+extern "C" int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out, int64_t* total,
+                                     void* workspace, int64_t workspace_bytes, void* stream) {
+    SC_CHECK_ARG(n >= 0, "n");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        if (total) SC_CUDA(cudaMemsetAsync(total, 0, 8, st));
+        return SC_OK;
+    }
+    SC_CHECK_ARG(in && out && workspace, "null pointer");
+    if (workspace_bytes < sc_scan_workspace_bytes(n)) {
+        sc_set_error("scan workspace too small: %lld < %lld", (long long)workspace_bytes,
+                     (long long)sc_scan_workspace_bytes(n));
+        return SC_ERR_WORKSPACE;
+    }
+    const int64_t nb = sc_div_up(n, SCAN_TILE);
+    int64_t* block_sums = (int64_t*)workspace;
+    scan_block_sums_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(n, in, block_sums);
+    SC_CHECK_LAUNCH("scan_block_sums_kernel");
+    scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, total);
+    SC_CHECK_LAUNCH("scan_spine_kernel");
+    scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(n, in, block_sums, out);
+    SC_CHECK_LAUNCH("scan_apply_kernel");
+    return SC_OK;
+}
+
+extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return make_plan(n, 64).total; }
+
+// returns 0 if the sorted pairs are in keys_out/vals_out, 1 if they are in keys_in/vals_in
+// (even number of passes), negative on error.
+extern "C" int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
+                                   uint32_t* vals_out, int end_bit, void* workspace, int64_t workspace_bytes,
+                                   void* stream) {
+    SC_CHECK_ARG(n >= 0 && n < (1ll << 30), "n (must be < 2^30)");
+    SC_CHECK_ARG(end_bit > 0 && end_bit <= 64, "end_bit");
+    if (n == 0) return 0;
+    SC_CHECK_ARG(keys_in && vals_in && keys_out && vals_out && workspace, "null pointer");
+    const SortPlan plan = make_plan(n, end_bit);
+    if (workspace_bytes < plan.total) {
+        sc_set_error("sort workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)plan.total);
+        return SC_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* ws = (unsigned char*)workspace;
+    uint32_t* hist = (uint32_t*)(ws + plan.hist_off);
+    uint32_t* tickets = (uint32_t*)(ws + plan.ticket_off);
+    uint32_t* lookback = (uint32_t*)(ws + plan.lookback_off);
+    SC_CUDA(cudaMemsetAsync(ws, 0, (size_t)(plan.lookback_off + (int64_t)plan.passes * plan.tiles * RADIX * 4), st));
+    {
+        const int grid = (int)min(sc_div_up(n, 256 * 8), (int64_t)SC_NUM_SMS * 8);
+        sort_histogram_kernel<<<grid, 256, plan.passes * RADIX * 4, st>>>(n, keys_in, plan.passes, end_bit, hist);
+        SC_CHECK_LAUNCH("sort_histogram_kernel");
+        sort_hist_scan_kernel<<<plan.passes, RADIX, 0, st>>>(hist);
+        SC_CHECK_LAUNCH("sort_hist_scan_kernel");
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        SC_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(SortSmem)));
+        attr_set = true;
+    }
+    uint64_t* kin = keys_in;
+    uint32_t* vin = vals_in;
+    uint64_t* kout = keys_out;
+    uint32_t* vout = vals_out;
+    for (int p = 0; p < plan.passes; ++p) {
+        const int shift = p * RADIX_BITS;
+        const int nb = end_bit - shift < RADIX_BITS ? end_bit - shift : RADIX_BITS;
+        onesweep_pass_kernel<<<(unsigned)plan.tiles, SORT_THREADS, sizeof(SortSmem), st>>>(
+            n, kin, vin, kout, vout, shift, nb, hist + p * RADIX, lookback + (size_t)p * plan.tiles * RADIX,
+            tickets + p);
+        SC_CHECK_LAUNCH("onesweep_pass_kernel");
+        uint64_t* tk = kin; kin = kout; kout = tk;
+        uint32_t* tv = vin; vin = vout; vout = tv;
+    }
+    // after the swap `kin` holds the result
+    return kin == keys_out ? 0 : 1;
+}

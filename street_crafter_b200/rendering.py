@@ -1,0 +1,446 @@
+"""Drop-in for the `gsplat.rendering` names the reference renderer imports
+(/root/reference/street_gaussian/models/street_gaussian_renderer.py:204):
+
+    rasterization, fully_fused_projection, isect_tiles, isect_offset_encode,
+    rasterize_to_pixels, spherical_harmonics
+
+Same positional order, keyword names, shapes, dtypes and autograd conventions as the
+reference's call sites (street_gaussian_renderer.py:219-280): `radii[C,N]` int32,
+`packed=False` only, `means2d.absgrad` set as a side effect of the rasterizer's backward when
+`absgrad=True` (consumed at street_gaussian/models/street_gaussian_model.py:505-506).
+
+Host code is plumbing only: tensors are allocated with torch, every computation is a
+hand-written sm_100a kernel reached through the C ABI in include/scb200.h.  There is no CPU
+path: CPU tensors raise."""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from ._lib import check, lib
+
+
+# ------------------------------------------------------------------------------------------
+# helpers
+# ------------------------------------------------------------------------------------------
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _f32c(t: Tensor, name: str, align: int = 16) -> Tensor:
+    """contiguous fp32 CUDA tensor whose base pointer is `align`-byte aligned."""
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: street_crafter_b200 has no CPU path")
+    if t.dtype != torch.float32:
+        raise AssertionError(f"{name} must be float32, got {t.dtype}")
+    t = t.contiguous()
+    if t.data_ptr() % align:
+        t = t.clone(memory_format=torch.contiguous_format)
+    return t
+
+
+def _grad_or_zeros(g: Optional[Tensor], like_shape, device) -> Tensor:
+    if g is None:
+        return torch.zeros(like_shape, dtype=torch.float32, device=device)
+    return _f32c(g, "grad")
+
+
+# ------------------------------------------------------------------------------------------
+# A1  fully_fused_projection
+# ------------------------------------------------------------------------------------------
+class _FullyFusedProjection(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
+                radius_clip, calc_compensations):
+        means = _f32c(means, "means")
+        quats = _f32c(quats, "quats")
+        scales = _f32c(scales, "scales")
+        viewmats = _f32c(viewmats, "viewmats")
+        Ks = _f32c(Ks, "Ks")
+        N, C = means.shape[0], viewmats.shape[0]
+        dev = means.device
+        radii = torch.empty((C, N), dtype=torch.int32, device=dev)
+        means2d = torch.empty((C, N, 2), dtype=torch.float32, device=dev)
+        depths = torch.empty((C, N), dtype=torch.float32, device=dev)
+        conics = torch.empty((C, N, 3), dtype=torch.float32, device=dev)
+        comps = torch.empty((C, N), dtype=torch.float32, device=dev) if calc_compensations else None
+        with torch.cuda.device(dev):
+            check(lib.sc_projection_fwd(N, C, _p(means), _p(quats), _p(scales), _p(viewmats), _p(Ks),
+                                        int(width), int(height), float(eps2d), float(near_plane),
+                                        float(far_plane), float(radius_clip), _p(radii), _p(means2d),
+                                        _p(depths), _p(conics), _p(comps), _stream()),
+                  "sc_projection_fwd")
+        ctx.save_for_backward(means, quats, scales, viewmats, Ks, radii)
+        ctx.dims = (int(width), int(height), float(eps2d), bool(calc_compensations))
+        ctx.mark_non_differentiable(radii)
+        if comps is None:
+            return radii, means2d, depths, conics
+        return radii, means2d, depths, conics, comps
+
+    @staticmethod
+    def backward(ctx, v_radii, v_means2d, v_depths, v_conics, v_comps=None):
+        means, quats, scales, viewmats, Ks, radii = ctx.saved_tensors
+        width, height, eps2d, has_comp = ctx.dims
+        N, C = means.shape[0], viewmats.shape[0]
+        dev = means.device
+        v_means2d = _grad_or_zeros(v_means2d, (C, N, 2), dev)
+        v_depths = _grad_or_zeros(v_depths, (C, N), dev)
+        v_conics = _grad_or_zeros(v_conics, (C, N, 3), dev)
+        if has_comp and v_comps is not None:
+            v_comps = _f32c(v_comps, "v_compensations")
+        else:
+            v_comps = None
+        need = ctx.needs_input_grad
+        v_means = torch.empty_like(means) if need[0] else None
+        v_quats = torch.empty_like(quats) if need[1] else None
+        v_scales = torch.empty_like(scales) if need[2] else None
+        if need[3]:
+            raise NotImplementedError("viewmats gradients are not produced (cameras are not optimised "
+                                      "in the reference, street_gaussian/config/config.py:126)")
+        with torch.cuda.device(dev):
+            check(lib.sc_projection_bwd(N, C, _p(means), _p(quats), _p(scales), _p(viewmats), _p(Ks), width,
+                                        height, eps2d, _p(radii), _p(v_means2d), _p(v_depths), _p(v_conics),
+                                        _p(v_comps), _p(v_means), _p(v_quats), _p(v_scales), _stream()),
+                  "sc_projection_bwd")
+        return (v_means, v_quats, v_scales, None, None, None, None, None, None, None, None, None)
+
+
+def fully_fused_projection(means: Tensor, covars: Optional[Tensor], quats: Optional[Tensor],
+                           scales: Optional[Tensor], viewmats: Tensor, Ks: Tensor, width: int, height: int,
+                           eps2d: float = 0.3, near_plane: float = 0.01, far_plane: float = 1e10,
+                           radius_clip: float = 0.0, packed: bool = False, sparse_grad: bool = False,
+                           calc_compensations: bool = False, camera_model: str = "pinhole",
+                           ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Optional[Tensor]]:
+    """-> (radii[C,N] i32, means2d[C,N,2], depths[C,N], conics[C,N,3], compensations[C,N]|None)."""
+    N = means.shape[0]
+    C = viewmats.shape[0]
+    assert means.shape == (N, 3), means.shape
+    assert viewmats.shape == (C, 4, 4), viewmats.shape
+    assert Ks.shape == (C, 3, 3), Ks.shape
+    if covars is not None:
+        raise NotImplementedError("covars input is not used by the reference (it passes quats/scales)")
+    if packed:
+        raise NotImplementedError("packed=True is not used by the reference (packed=False at "
+                                  "street_gaussian_renderer.py:228)")
+    assert camera_model == "pinhole"
+    assert quats is not None and scales is not None, "quats and scales are required"
+    assert quats.shape == (N, 4), quats.shape
+    assert scales.shape == (N, 3), scales.shape
+    out = _FullyFusedProjection.apply(means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
+                                      far_plane, radius_clip, calc_compensations)
+    if calc_compensations:
+        return out
+    return out + (None,)
+
+
+# ------------------------------------------------------------------------------------------
+# A5  spherical_harmonics
+# ------------------------------------------------------------------------------------------
+class _SphericalHarmonics(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, degree, dirs, coeffs, masks):
+        dirs = _f32c(dirs, "dirs", 4)
+        coeffs = _f32c(coeffs, "coeffs")
+        K = coeffs.shape[-2]
+        M = dirs.numel() // 3
+        m8 = None
+        if masks is not None:
+            m8 = masks.contiguous().view(torch.uint8) if masks.dtype == torch.bool else \
+                masks.to(torch.uint8).contiguous()
+        colors = torch.empty(dirs.shape, dtype=torch.float32, device=dirs.device)
+        with torch.cuda.device(dirs.device):
+            check(lib.sc_sh_fwd(M, K, int(degree), _p(dirs), _p(coeffs), _p(m8), _p(colors), _stream()),
+                  "sc_sh_fwd")
+        ctx.save_for_backward(dirs, coeffs, m8 if m8 is not None else torch.empty(0, device=dirs.device))
+        ctx.degree = int(degree)
+        ctx.has_mask = m8 is not None
+        return colors
+
+    @staticmethod
+    def backward(ctx, v_colors):
+        dirs, coeffs, m8 = ctx.saved_tensors
+        if not ctx.has_mask:
+            m8 = None
+        K = coeffs.shape[-2]
+        M = dirs.numel() // 3
+        v_colors = _f32c(v_colors, "v_colors", 4)
+        v_coeffs = torch.empty_like(coeffs)
+        v_dirs = torch.empty_like(dirs) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(dirs.device):
+            check(lib.sc_sh_bwd(M, K, ctx.degree, _p(dirs), _p(coeffs), _p(m8), _p(v_colors), _p(v_coeffs),
+                                _p(v_dirs), _stream()), "sc_sh_bwd")
+        return None, v_dirs, (v_coeffs if ctx.needs_input_grad[2] else None), None
+
+
+def spherical_harmonics(degrees_to_use: int, dirs: Tensor, coeffs: Tensor,
+                        masks: Optional[Tensor] = None) -> Tensor:
+    """dirs [...,3] (normalised inside the kernel), coeffs [...,K,3], masks [...] -> [...,3]."""
+    assert (degrees_to_use + 1) ** 2 <= coeffs.shape[-2], coeffs.shape
+    assert dirs.shape[:-1] == coeffs.shape[:-2], (dirs.shape, coeffs.shape)
+    assert dirs.shape[-1] == 3 and coeffs.shape[-1] == 3
+    if masks is not None:
+        assert masks.shape == dirs.shape[:-1], masks.shape
+    return _SphericalHarmonics.apply(degrees_to_use, dirs, coeffs, masks)
+
+
+# ------------------------------------------------------------------------------------------
+# A3/A4  isect_tiles / isect_offset_encode
+# ------------------------------------------------------------------------------------------
+def _tile_n_bits(tile_width: int, tile_height: int) -> int:
+    return int(math.floor(math.log2(tile_width * tile_height))) + 1
+
+
+@torch.no_grad()
+def isect_tiles(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int, tile_width: int,
+                tile_height: int, sort: bool = True, packed: bool = False, n_cameras: Optional[int] = None,
+                camera_ids: Optional[Tensor] = None, gaussian_ids: Optional[Tensor] = None,
+                ) -> Tuple[Tensor, Tensor, Tensor]:
+    """-> (tiles_per_gauss[C,N] i32, isect_ids[I] i64 (sorted), flatten_ids[I] i32).
+
+    One host read-back (the total number of intersections sizes the outputs), exactly as the
+    reference's op does."""
+    if packed:
+        raise NotImplementedError("packed=True is not used by the reference")
+    C, N = radii.shape
+    assert means2d.shape == (C, N, 2) and depths.shape == (C, N), (means2d.shape, depths.shape)
+    if n_cameras is not None:
+        assert n_cameras == C
+    dev = means2d.device
+    means2d = _f32c(means2d.detach(), "means2d", 8)
+    depths = _f32c(depths.detach(), "depths", 4)
+    radii = radii.contiguous()
+    assert radii.dtype == torch.int32
+    CN = C * N
+    bits = _tile_n_bits(tile_width, tile_height)
+    cam_bits = 0 if C == 1 else int(math.floor(math.log2(C))) + 1
+    assert 32 + bits + cam_bits <= 64
+    st = _stream()
+    with torch.cuda.device(dev):
+        tpg = torch.empty((C, N), dtype=torch.int32, device=dev)
+        check(lib.sc_isect_count(CN, _p(means2d), _p(radii), tile_size, tile_width, tile_height, _p(tpg), st),
+              "sc_isect_count")
+        cum = torch.empty(CN + 1, dtype=torch.int64, device=dev)
+        ws_bytes = int(lib.sc_scan_workspace_bytes(CN))
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        check(lib.sc_exclusive_scan_i32(CN, _p(tpg), _p(cum), cum.data_ptr() + 8 * CN, _p(ws), ws_bytes, st),
+              "sc_exclusive_scan_i32")
+        n_isects = int(cum[CN].item())  # the one D->H sync of the pipeline
+        ids_a = torch.empty(n_isects, dtype=torch.int64, device=dev)
+        flat_a = torch.empty(n_isects, dtype=torch.int32, device=dev)
+        if n_isects == 0:
+            return tpg, ids_a, flat_a
+        check(lib.sc_isect_emit(N, C, _p(means2d), _p(radii), _p(depths), _p(cum), tile_size, tile_width,
+                                tile_height, bits, n_isects, _p(ids_a), _p(flat_a), st), "sc_isect_emit")
+        if not sort:
+            return tpg, ids_a, flat_a
+        ids_b = torch.empty_like(ids_a)
+        flat_b = torch.empty_like(flat_a)
+        sws_bytes = int(lib.sc_sort_workspace_bytes(n_isects))
+        sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
+        where = check(lib.sc_radix_sort_pairs(n_isects, _p(ids_a), _p(flat_a), _p(ids_b), _p(flat_b),
+                                              32 + bits + cam_bits, _p(sws), sws_bytes, st),
+                      "sc_radix_sort_pairs")
+    if where == 0:
+        return tpg, ids_b, flat_b
+    return tpg, ids_a, flat_a
+
+
+@torch.no_grad()
+def isect_offset_encode(isect_ids: Tensor, n_cameras: int, tile_width: int, tile_height: int) -> Tensor:
+    """-> offsets[C, tile_height, tile_width] i32 (first sorted index of every tile)."""
+    assert isect_ids.dtype == torch.int64
+    if not isect_ids.is_cuda:
+        raise RuntimeError("isect_ids must be a CUDA tensor: street_crafter_b200 has no CPU path")
+    isect_ids = isect_ids.contiguous()
+    dev = isect_ids.device
+    offsets = torch.empty((n_cameras, tile_height, tile_width), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.sc_isect_offset_encode(isect_ids.numel(), _p(isect_ids), n_cameras, tile_width, tile_height,
+                                         _tile_n_bits(tile_width, tile_height), _p(offsets), _stream()),
+              "sc_isect_offset_encode")
+    return offsets
+
+
+# ------------------------------------------------------------------------------------------
+# A7/A8  rasterize_to_pixels
+# ------------------------------------------------------------------------------------------
+class _RasterizeToPixels(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means2d, conics, colors, opacities, backgrounds, width, height, tile_size,
+                isect_offsets, flatten_ids, absgrad, max_hit):
+        means2d_in = means2d
+        means2d = _f32c(means2d, "means2d", 8)
+        conics = _f32c(conics, "conics", 4)
+        colors = _f32c(colors, "colors", 4)
+        opacities = _f32c(opacities, "opacities", 4)
+        if backgrounds is not None:
+            backgrounds = _f32c(backgrounds, "backgrounds", 4)
+        C, N = opacities.shape
+        CH = colors.shape[-1]
+        dev = means2d.device
+        isect_offsets = isect_offsets.contiguous()
+        flatten_ids = flatten_ids.contiguous()
+        assert isect_offsets.dtype == torch.int32 and flatten_ids.dtype == torch.int32
+        n_isects = flatten_ids.numel()
+        render_colors = torch.empty((C, height, width, CH), dtype=torch.float32, device=dev)
+        render_alphas = torch.empty((C, height, width, 1), dtype=torch.float32, device=dev)
+        last_ids = torch.empty((C, height, width), dtype=torch.int32, device=dev)
+        final_T = torch.empty((C, height, width), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.sc_rasterize_fwd(C, N, n_isects, CH, width, height, tile_size, _p(means2d), _p(conics),
+                                       _p(colors), _p(opacities), _p(backgrounds), _p(isect_offsets),
+                                       _p(flatten_ids), int(max_hit), _p(render_colors), _p(render_alphas),
+                                       _p(last_ids), _p(final_T), _stream()), "sc_rasterize_fwd")
+        ctx.save_for_backward(means2d, conics, colors, opacities,
+                              backgrounds if backgrounds is not None else torch.empty(0, device=dev),
+                              isect_offsets, flatten_ids, last_ids, final_T)
+        ctx.cfg = (width, height, tile_size, bool(absgrad), backgrounds is not None)
+        # the caller's tensor object: `.absgrad` is attached to it in backward
+        # (street_gaussian/models/street_gaussian_model.py:505-506 reads it)
+        ctx.means2d_ref = means2d_in
+        return render_colors, render_alphas
+
+    @staticmethod
+    def backward(ctx, v_render_colors, v_render_alphas):
+        (means2d, conics, colors, opacities, backgrounds, isect_offsets, flatten_ids, last_ids,
+         final_T) = ctx.saved_tensors
+        width, height, tile_size, absgrad, has_bg = ctx.cfg
+        if not has_bg:
+            backgrounds = None
+        C, N = opacities.shape
+        CH = colors.shape[-1]
+        dev = means2d.device
+        v_render_colors = _grad_or_zeros(v_render_colors, (C, height, width, CH), dev)
+        v_render_alphas = _grad_or_zeros(v_render_alphas, (C, height, width, 1), dev)
+        # one zero-filled arena for all five gradient outputs (a single memset launch)
+        n2, n3, nc, n1 = C * N * 2, C * N * 3, C * N * CH, C * N
+        sizes = [n2, n2 if absgrad else 0, n3, nc, n1]
+        arena = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)
+        parts = torch.split(arena, sizes)
+        v_means2d = parts[0].view(C, N, 2)
+        v_abs = parts[1].view(C, N, 2) if absgrad else None
+        v_conics = parts[2].view(C, N, 3)
+        v_colors = parts[3].view(C, N, CH)
+        v_opacities = parts[4].view(C, N)
+        with torch.cuda.device(dev):
+            check(lib.sc_rasterize_bwd(C, N, flatten_ids.numel(), CH, width, height, tile_size, _p(means2d),
+                                       _p(conics), _p(colors), _p(opacities), _p(backgrounds),
+                                       _p(isect_offsets), _p(flatten_ids), _p(final_T), _p(last_ids),
+                                       _p(v_render_colors), _p(v_render_alphas), _p(v_means2d), _p(v_abs),
+                                       _p(v_conics), _p(v_colors), _p(v_opacities), _stream()),
+                  "sc_rasterize_bwd")
+        if absgrad:
+            ctx.means2d_ref.absgrad = v_abs
+        v_bg = None
+        if has_bg and ctx.needs_input_grad[4]:
+            v_bg = (v_render_colors * final_T[..., None]).sum(dim=(1, 2))
+        return (v_means2d, v_conics, v_colors, v_opacities, v_bg, None, None, None, None, None, None, None)
+
+
+def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opacities: Tensor, image_width: int,
+                        image_height: int, tile_size: int, isect_offsets: Tensor, flatten_ids: Tensor,
+                        backgrounds: Optional[Tensor] = None, masks: Optional[Tensor] = None,
+                        packed: bool = False, absgrad: bool = False, max_hit: int = 0,
+                        ) -> Tuple[Tensor, Tensor]:
+    """-> (render_colors[C,H,W,CH], render_alphas[C,H,W,1]).  `max_hit` (extension, default off)
+    caps the number of contributing splats per pixel for the LiDAR point-splat mode."""
+    if packed:
+        raise NotImplementedError("packed=True is not used by the reference")
+    if masks is not None:
+        raise NotImplementedError("tile masks are not used by the reference")
+    C, N = opacities.shape
+    assert means2d.shape == (C, N, 2), means2d.shape
+    assert conics.shape == (C, N, 3), conics.shape
+    assert colors.shape[:2] == (C, N), colors.shape
+    if backgrounds is not None:
+        assert backgrounds.shape == (C, colors.shape[-1]), backgrounds.shape
+    tile_h, tile_w = isect_offsets.shape[1:]
+    assert tile_h * tile_size >= image_height and tile_w * tile_size >= image_width, \
+        "tile grid does not cover the image"
+    CH = colors.shape[-1]
+    if CH > 5:
+        # wide feature maps are composited 4 channels at a time (not on the reference's path)
+        outs, alphas = [], None
+        for s in range(0, CH, 4):
+            bg = None if backgrounds is None else backgrounds[:, s:s + 4]
+            rc, ra = _RasterizeToPixels.apply(means2d, conics, colors[..., s:s + 4], opacities, bg, image_width,
+                                              image_height, tile_size, isect_offsets, flatten_ids,
+                                              absgrad, max_hit)
+            outs.append(rc)
+            alphas = ra if alphas is None else alphas
+        return torch.cat(outs, -1), alphas
+    return _RasterizeToPixels.apply(means2d, conics, colors, opacities, backgrounds, image_width, image_height,
+                                    tile_size, isect_offsets, flatten_ids, absgrad, max_hit)
+
+
+# ------------------------------------------------------------------------------------------
+# rasterization(): the fused high-level entry (imported by the reference, see header)
+# ------------------------------------------------------------------------------------------
+def rasterization(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, colors: Tensor,
+                  viewmats: Tensor, Ks: Tensor, width: int, height: int, near_plane: float = 0.01,
+                  far_plane: float = 1e10, radius_clip: float = 0.0, eps2d: float = 0.3,
+                  sh_degree: Optional[int] = None, packed: bool = False, tile_size: int = 16,
+                  backgrounds: Optional[Tensor] = None, render_mode: str = "RGB", sparse_grad: bool = False,
+                  absgrad: bool = False, rasterize_mode: str = "classic", channel_chunk: int = 32,
+                  distributed: bool = False, camera_model: str = "pinhole", covars: Optional[Tensor] = None,
+                  max_hit: int = 0) -> Tuple[Tensor, Tensor, Dict]:
+    """means[N,3] quats[N,4] scales[N,3] opacities[N] colors[N,D]|[N,K,3] (SH when sh_degree is
+    given) viewmats[C,4,4] Ks[C,3,3] -> (render_colors[C,H,W,X], render_alphas[C,H,W,1], meta).
+
+    Equivalent to the reference renderer's inlined sequence
+    (street_gaussian_renderer.py:219-280) with packed=False; `render_mode` in
+    {RGB, D, ED, RGB+D, RGB+ED}; `rasterize_mode` in {classic, antialiased}."""
+    assert render_mode in ("RGB", "D", "ED", "RGB+D", "RGB+ED"), render_mode
+    assert rasterize_mode in ("classic", "antialiased"), rasterize_mode
+    if packed or sparse_grad or distributed or covars is not None:
+        raise NotImplementedError("packed / sparse_grad / distributed / covars are not used by the reference")
+    N = means.shape[0]
+    C = viewmats.shape[0]
+    assert opacities.shape == (N,), opacities.shape
+    radii, means2d, depths, conics, comps = fully_fused_projection(
+        means, None, quats, scales, viewmats, Ks, width, height, eps2d=eps2d, near_plane=near_plane,
+        far_plane=far_plane, radius_clip=radius_clip, calc_compensations=(rasterize_mode == "antialiased"),
+        camera_model=camera_model)
+    op = opacities[None].expand(C, N)
+    if comps is not None:
+        op = op * comps
+    tile_width = math.ceil(width / float(tile_size))
+    tile_height = math.ceil(height / float(tile_size))
+    tiles_per_gauss, isect_ids, flatten_ids = isect_tiles(means2d, radii, depths, tile_size, tile_width,
+                                                          tile_height, n_cameras=C)
+    isect_offsets = isect_offset_encode(isect_ids, C, tile_width, tile_height)
+    if sh_degree is None:
+        cols = colors[None].expand(C, -1, -1) if colors.dim() == 2 else colors
+    else:
+        campos = torch.inverse(viewmats)[:, :3, 3]
+        dirs = means[None, :, :] - campos[:, None, :]
+        shs = colors[None].expand(C, -1, -1, -1) if colors.dim() == 3 else colors
+        cols = spherical_harmonics(sh_degree, dirs, shs, masks=radii > 0)
+        cols = torch.clamp_min(cols + 0.5, 0.0)
+    if render_mode in ("RGB+D", "RGB+ED"):
+        cols = torch.cat((cols, depths[..., None]), dim=-1)
+        if backgrounds is not None:
+            backgrounds = torch.cat([backgrounds, torch.zeros(C, 1, device=backgrounds.device)], dim=-1)
+    elif render_mode in ("D", "ED"):
+        cols = depths[..., None]
+        if backgrounds is not None:
+            backgrounds = torch.zeros(C, 1, device=backgrounds.device)
+    render_colors, render_alphas = rasterize_to_pixels(
+        means2d, conics, cols, op, width, height, tile_size, isect_offsets, flatten_ids,
+        backgrounds=backgrounds, absgrad=absgrad, max_hit=max_hit)
+    if render_mode in ("ED", "RGB+ED"):
+        render_colors = torch.cat([render_colors[..., :-1],
+                                   render_colors[..., -1:] / render_alphas.clamp(min=1e-10)], dim=-1)
+    meta = {"camera_ids": None, "gaussian_ids": None, "radii": radii, "means2d": means2d, "depths": depths,
+            "conics": conics, "opacities": op, "tile_width": tile_width, "tile_height": tile_height,
+            "tiles_per_gauss": tiles_per_gauss, "isect_ids": isect_ids, "flatten_ids": flatten_ids,
+            "isect_offsets": isect_offsets, "width": width, "height": height, "tile_size": tile_size,
+            "n_cameras": C}
+    return render_colors, render_alphas, meta

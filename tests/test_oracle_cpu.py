@@ -1,0 +1,267 @@
+"""CPU tests (-m "not gpu"): the oracle against the reference-derived golden vectors and its
+own invariants, and the C-ABI library's export table.  No GPU compute here."""
+import ctypes
+import math
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gsplat_torch as G
+from oracle import knn as KO
+from tools.scene import make_camera, make_gaussians
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ---------------------------------------------------------------- SH pinned on the reference
+@pytest.mark.parametrize("deg", [0, 1, 2, 3, 4])
+def test_sh_matches_reference_golden(deg):
+    """tests/golden/sh_eval.npz was produced by /root/reference/street_gaussian/utils/sh_utils.py
+    eval_sh (tools/make_golden.py); the oracle must reproduce it."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "sh_eval.npz"))
+    dirs = torch.from_numpy(z["dirs"])
+    coeffs = torch.from_numpy(z["coeffs"])
+    K = (deg + 1) ** 2
+    got = G.spherical_harmonics(deg, dirs, coeffs[:, :K])
+    want = torch.from_numpy(z[f"colors_deg{deg}"])
+    assert torch.allclose(got, want, atol=2e-5, rtol=1e-5), (got - want).abs().max()
+
+
+def test_sh_mask_zeroes():
+    g = torch.Generator().manual_seed(1)
+    dirs = torch.randn(10, 3, generator=g)
+    coeffs = torch.randn(10, 16, 3, generator=g)
+    m = torch.arange(10) % 2 == 0
+    out = G.spherical_harmonics(3, dirs, coeffs, m)
+    assert (out[~m] == 0).all() and (out[m] != 0).any()
+
+
+# ---------------------------------------------------------------- projection invariants
+def _small_scene(n=4000, W=320, H=192, seed=3):
+    s = make_gaussians(n, seed=seed)
+    V, K = make_camera(W, H)
+    return s, V, K, W, H
+
+
+def test_projection_matches_matrix_form_fp64():
+    """the scalar-op restatement equals the textbook matrix form  J W Σ Wᵀ Jᵀ  in fp64."""
+    s, V, K, W, H = _small_scene()
+    d = {k: v.double() for k, v in s.items()}
+    Vd, Kd = V.double(), K.double()
+    radii, m2, dep, con, comp = G.fully_fused_projection(d["means"], None, d["quats"], d["scales"], Vd[None],
+                                                         Kd[None], W, H, near_plane=0.001, far_plane=1000.0,
+                                                         calc_compensations=True)
+    q = torch.nn.functional.normalize(d["quats"], dim=-1)
+    w, x, y, z = q.unbind(-1)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                     2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                     2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)], -1).reshape(-1, 3, 3)
+    M = R * d["scales"][:, None, :]
+    S = M @ M.transpose(1, 2)
+    Rw, t = Vd[:3, :3], Vd[:3, 3]
+    pc = d["means"] @ Rw.T + t
+    Sc = Rw @ S @ Rw.T
+    vis = radii[0] > 0
+    fx, fy, cx, cy = Kd[0, 0], Kd[1, 1], Kd[0, 2], Kd[1, 2]
+    zc = pc[:, 2]
+    assert torch.allclose(dep[0][vis], zc[vis])
+    assert torch.allclose(m2[0][vis, 0], fx * pc[vis, 0] / zc[vis] + cx)
+    # unclamped Gaussians only (well inside the frustum)
+    inside = vis & (m2[0, :, 0] > 0) & (m2[0, :, 0] < W) & (m2[0, :, 1] > 0) & (m2[0, :, 1] < H)
+    J = torch.zeros(len(zc), 2, 3, dtype=torch.float64)
+    J[:, 0, 0] = fx / zc
+    J[:, 0, 2] = -fx * pc[:, 0] / zc ** 2
+    J[:, 1, 1] = fy / zc
+    J[:, 1, 2] = -fy * pc[:, 1] / zc ** 2
+    c2 = J @ Sc @ J.transpose(1, 2)
+    c2[:, 0, 0] += 0.3
+    c2[:, 1, 1] += 0.3
+    inv = torch.linalg.inv(c2[inside])
+    assert torch.allclose(con[0][inside, 0], inv[:, 0, 0], rtol=1e-9)
+    assert torch.allclose(con[0][inside, 1], inv[:, 0, 1], rtol=1e-9, atol=1e-12)
+    assert torch.allclose(con[0][inside, 2], inv[:, 1, 1], rtol=1e-9)
+    assert inside.sum() > 100
+    assert (comp[0][vis] <= 1.0 + 1e-12).all() and (comp[0][vis] > 0).all()
+
+
+def test_projection_culls_and_zeroes():
+    s, V, K, W, H = _small_scene()
+    radii, m2, dep, con, comp = G.fully_fused_projection(s["means"], None, s["quats"], s["scales"], V[None],
+                                                         K[None], W, H, near_plane=0.001, far_plane=1000.0,
+                                                         calc_compensations=True)
+    culled = radii[0] == 0
+    assert culled.any() and (~culled).any()
+    for t in (m2[0], con[0]):
+        assert (t[culled] == 0).all()
+    assert (dep[0][culled] == 0).all() and (comp[0][culled] == 0).all()
+    assert radii.dtype == torch.int32
+    behind = (s["means"] @ V[:3, :3].T + V[:3, 3])[:, 2] < 0.001
+    assert (radii[0][behind] == 0).all()
+
+
+# ---------------------------------------------------------------- binning invariants
+def test_isect_keys_sorted_and_offsets_consistent():
+    s, V, K, W, H = _small_scene()
+    rc, ra, aux = G.render_reference_sequence(s["means"], s["quats"], s["scales"], s["opacities"], s["shs"], V,
+                                              K, W, H, 3, return_aux=True)
+    ids, flat, off, tpg = aux["isect_ids"], aux["flatten_ids"], aux["isect_offsets"], aux["tiles_per_gauss"]
+    assert ids.dtype == torch.int64 and flat.dtype == torch.int32 and off.dtype == torch.int32
+    assert int(tpg.sum()) == ids.numel() > 0
+    assert (ids[1:] >= ids[:-1]).all()
+    tw, th = math.ceil(W / 16), math.ceil(H / 16)
+    tile = (ids >> 32).int()
+    offs = off.reshape(-1).tolist() + [ids.numel()]
+    for t in range(tw * th):
+        seg = tile[offs[t]:offs[t + 1]]
+        assert (seg == t).all()
+    # depth bits round-trip
+    dbits = (ids & 0xFFFFFFFF).to(torch.int32).view(torch.float32)
+    assert torch.equal(dbits, aux["depths"][0][flat.long()])
+    # brute-force recount of tile coverage for a few Gaussians
+    vis = torch.nonzero(aux["radii"][0] > 0).flatten()[:50]
+    for g in vis.tolist():
+        x, y = aux["means2d"][0, g].tolist()
+        r = int(aux["radii"][0, g])
+        x0 = min(max(0, math.floor((x - r) / 16)), tw); x1 = min(max(0, math.ceil((x + r) / 16)), tw)
+        y0 = min(max(0, math.floor((y - r) / 16)), th); y1 = min(max(0, math.ceil((y + r) / 16)), th)
+        assert int(tpg[0, g]) == (x1 - x0) * (y1 - y0)
+
+
+def test_isect_empty_and_multicamera():
+    tpg, ids, flat = G.isect_tiles(torch.zeros(2, 5, 2), torch.zeros(2, 5, dtype=torch.int32),
+                                   torch.zeros(2, 5), 16, 4, 4, n_cameras=2)
+    assert ids.numel() == 0 and flat.numel() == 0 and int(tpg.sum()) == 0
+    off = G.isect_offset_encode(ids, 2, 4, 4)
+    assert off.shape == (2, 4, 4) and (off == 0).all()
+    m2 = torch.tensor([[[8.0, 8.0]], [[40.0, 40.0]]])
+    rad = torch.tensor([[3], [3]], dtype=torch.int32)
+    dep = torch.tensor([[2.0], [1.0]])
+    tpg, ids, flat = G.isect_tiles(m2, rad, dep, 16, 4, 4, n_cameras=2)
+    assert tpg.tolist() == [[1], [1]]
+    bits = 5  # floor(log2(16)) + 1
+    assert (ids >> (32 + bits)).tolist() == [0, 1]
+    assert ((ids >> 32) & 31).tolist() == [0, 2 * 4 + 2]
+    assert flat.tolist() == [0, 1]
+
+
+# ---------------------------------------------------------------- compositing
+def test_rasterize_matches_naive_loop():
+    """vectorised oracle == literal per-pixel front-to-back loop on a tiny scene."""
+    s = make_gaussians(300, seed=5, scale_mean=0.6)
+    W, H = 48, 32
+    V, K = make_camera(W, H)
+    rc, ra, aux = G.render_reference_sequence(s["means"], s["quats"], s["scales"], s["opacities"], s["shs"], V,
+                                              K, W, H, 3, return_aux=True)
+    off = aux["isect_offsets"].reshape(-1).tolist() + [aux["flatten_ids"].numel()]
+    tw = math.ceil(W / 16)
+    m2, con, col, op = aux["means2d"][0], aux["conics"][0], aux["colors"][0], aux["opacities"][0]
+    worst = 0.0
+    for (i, j) in [(0, 0), (5, 7), (17, 33), (31, 47), (16, 16), (20, 40)]:
+        t = (i // 16) * tw + j // 16
+        T, pix = 1.0, torch.zeros(4)
+        for g in aux["flatten_ids"][off[t]:off[t + 1]].tolist():
+            dx, dy = float(m2[g, 0]) - (j + 0.5), float(m2[g, 1]) - (i + 0.5)
+            sig = 0.5 * (float(con[g, 0]) * dx * dx + float(con[g, 2]) * dy * dy) + float(con[g, 1]) * dx * dy
+            a = min(0.999, float(op[g]) * math.exp(-sig))
+            if sig < 0 or a < 1 / 255:
+                continue
+            nT = T * (1 - a)
+            if nT <= 1e-4:
+                break
+            pix += col[g] * a * T
+            T = nT
+        worst = max(worst, float((pix - rc[0, i, j]).abs().max()), abs((1 - T) - float(ra[0, i, j, 0])))
+    assert worst < 1e-4, worst
+    assert ra.max() > 0.2
+
+
+def test_oracle_gradcheck_fp64():
+    """finite-difference check of the oracle's autograd backward on a tiny fp64 scene."""
+    s = make_gaussians(24, seed=7, scale_mean=1.5, sh_degree=1)
+    W, H = 32, 32
+    V, K = make_camera(W, H)
+    d = {k: v.double() for k, v in s.items()}
+    d["means"][:, 2] = d["means"][:, 2].abs() + 20.0
+    d["means"][:, 0] *= 0.05
+    d["means"][:, 1] *= 0.2
+    Vd, Kd = V.double(), K.double()
+    g = torch.Generator().manual_seed(0)
+    wc = torch.randn(1, H, W, 4, generator=g, dtype=torch.float64)
+    wa = torch.randn(1, H, W, 1, generator=g, dtype=torch.float64)
+
+    def loss(means, quats, scales, opac, shs):
+        rc, ra = G.render_reference_sequence(means, quats, scales, opac, shs, Vd, Kd, W, H, 1)
+        return (rc * wc).sum() + (ra * wa).sum()
+
+    leaves = [d[k].clone().requires_grad_(True) for k in ("means", "quats", "scales", "opacities", "shs")]
+    L = loss(*leaves)
+    grads = torch.autograd.grad(L, leaves)
+    eps = 1e-6
+    rng = np.random.RandomState(0)
+    for li, (leaf, gr) in enumerate(zip(leaves, grads)):
+        flat = leaf.detach().reshape(-1)
+        for idx in rng.choice(flat.numel(), size=4, replace=False):
+            args_p = [l.detach().clone() for l in leaves]
+            args_m = [l.detach().clone() for l in leaves]
+            args_p[li].reshape(-1)[idx] += eps
+            args_m[li].reshape(-1)[idx] -= eps
+            fd = (loss(*args_p) - loss(*args_m)) / (2 * eps)
+            an = gr.reshape(-1)[idx]
+            assert abs(fd - an) <= 1e-4 * max(1.0, abs(fd)), (li, idx, float(fd), float(an))
+
+
+# ---------------------------------------------------------------- KNN oracle
+def test_knn_bruteforce_vs_kdtree():
+    g = torch.Generator().manual_seed(0)
+    pts = torch.randn(3000, 3, generator=g) * torch.tensor([10.0, 2.0, 30.0])
+    pts[100] = pts[7]  # exact duplicate -> distance 0 counts
+    a = KO.dist_knn3_bruteforce(pts)
+    b = KO.dist_knn3_kdtree(pts)
+    assert torch.allclose(a, b, rtol=1e-4, atol=1e-7)
+    d = ((pts[7] - pts) ** 2).sum(-1)
+    d[7] = float("inf")
+    assert abs(float(a[7]) - float(d.topk(3, largest=False).values.mean())) < 1e-5
+    assert float(d.min()) == 0.0
+
+
+def test_knn_tiny():
+    pts = torch.tensor([[0.0, 0, 0], [1, 0, 0], [0, 2, 0], [0, 0, 3]])
+    out = KO.dist_knn3_bruteforce(pts)
+    assert torch.allclose(out[0], torch.tensor((1.0 + 4.0 + 9.0) / 3))
+    # P < 4: FLT_MAX placeholders survive into the mean (simple_knn.cu:149,183)
+    assert (KO.dist_knn3_bruteforce(pts[:3]) > 1e37).all()
+
+
+# ---------------------------------------------------------------- C ABI export table
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "scb200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)  # comments mention names loosely
+    names = sorted(set(re.findall(r"\b(sc_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) >= 18, names
+    from street_crafter_b200 import _lib
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for n in names:
+        assert hasattr(lib, n), f"libscb200.so does not export {n}"
+    assert set(_lib.SIGNATURES) == set(names), set(_lib.SIGNATURES) ^ set(names)
+    assert _lib.lib.sc_version() >= 100
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "street_crafter_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dp, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src, f
+
+
+def test_cpu_tensors_raise():
+    import street_crafter_b200 as S
+    with pytest.raises(RuntimeError):
+        S.distCUDA2(torch.zeros(8, 3))
+    with pytest.raises(RuntimeError):
+        S.fully_fused_projection(torch.zeros(4, 3), None, torch.ones(4, 4), torch.ones(4, 3),
+                                 torch.eye(4)[None], torch.eye(3)[None], 32, 32)
