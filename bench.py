@@ -1,0 +1,467 @@
+"""bench.py — 3DGS fwd+bwd throughput of the rasterizer hot path on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1]): Waymo-scale street scene, 2M Gaussians (SH degree 3),
+3 cameras at 1920x1280, one training step = for each camera a forward + backward pass through
+the reference renderer's call sequence (street_gaussian_renderer.py:219-280) — three C=1 passes,
+exactly as the reference issues them.  Metric: Mpix/s = rendered pixels / step time.
+
+N > 1 (torchrun, one rank per GPU): view-sharded weak scaling — every rank holds the full
+Gaussian set and renders its own 3 views, then ONE NCCL all-reduce sums the flat per-Gaussian
+gradient arena (59 floats/Gaussian).  value = all ranks' pixels / max-over-ranks time.
+
+--impl reference: the CPU oracle (oracle/gsplat_torch.py, the restatement of gsplat's
+pure-torch reference rasterizer; gsplat itself is absent from the reference tree) timed on the
+host cores on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+N_GAUSS = 2_000_000
+WIDTH, HEIGHT = 1920, 1280
+SH_DEGREE = 3
+CAM_YAWS = (0.0, 45.0, -45.0)  # Waymo FRONT / FRONT_LEFT / FRONT_RIGHT
+WORKLOAD = "cfg2: 2M Gaussians SH3, 3 cameras 1920x1280, fwd+bwd (3 C=1 passes)"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--gaussians", type=int, default=N_GAUSS)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------
+# CPU oracle timing (cpu_baseline leg and --impl reference)
+# ------------------------------------------------------------------------------------------
+def cpu_oracle_step(scene, V, K, W, H, deg, v_rc, v_ra):
+    from oracle import gsplat_torch as G
+    leaves = {k: v.clone().requires_grad_(True) for k, v in scene.items()}
+    rc, ra = G.render_reference_sequence(leaves["means"], leaves["quats"], leaves["scales"],
+                                         leaves["opacities"], leaves["shs"], V, K, W, H, deg)
+    ((rc * v_rc).sum() + (ra * v_ra).sum()).backward()
+    return rc
+
+
+def make_cpu_sample(n, W, H):
+    from tools.scene import make_camera, make_gaussians
+    scene = make_gaussians(n, sh_degree=SH_DEGREE, seed=0)
+    V, K = make_camera(W, H)
+    g = torch.Generator().manual_seed(0)
+    return scene, V, K, torch.randn(1, H, W, 4, generator=g), torch.randn(1, H, W, 1, generator=g)
+
+
+def time_cpu_oracle(n, W, H, reps):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    scene, V, K, v_rc, v_ra = make_cpu_sample(n, W, H)
+    best = float("inf")
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        cpu_oracle_step(scene, V, K, W, H, SH_DEGREE, v_rc, v_ra)
+        best = min(best, time.perf_counter() - t0)
+    return best, cores
+
+
+def run_reference(args):
+    """Reference arm: the CPU restatement of the reference path on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    # bounded sample: configs[0] (100k Gaussians, 960x640) when the whole run fits ~4 min,
+    # else the same scene density at quarter size
+    n, W, H = 100_000, 960, 640
+    scene, V, K, v_rc, v_ra = make_cpu_sample(n, W, H)
+    t0 = time.perf_counter()
+    cpu_oracle_step(scene, V, K, W, H, SH_DEGREE, v_rc, v_ra)
+    t_first = time.perf_counter() - t0
+    total = args.steps + args.warmup
+    done_warm = 1
+    if t_first * total > 240.0:
+        n, W, H = 25_000, 480, 320
+        scene, V, K, v_rc, v_ra = make_cpu_sample(n, W, H)
+        done_warm = 0
+    for _ in range(max(0, args.warmup - done_warm)):
+        cpu_oracle_step(scene, V, K, W, H, SH_DEGREE, v_rc, v_ra)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_oracle_step(scene, V, K, W, H, SH_DEGREE, v_rc, v_ra)
+    dt = (time.perf_counter() - t0) / args.steps
+    mpix = W * H / dt / 1e6
+    sample = f"{n} Gaussians SH3, one {W}x{H} camera, fwd+bwd (torch CPU oracle, same scene generator)"
+    print(json.dumps({
+        "impl": "reference", "metric": "3DGS fwd+bwd Mpix/s", "value": mpix, "unit": "Mpix/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": mpix, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": mpix, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for nme, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nme)
+            except Exception:
+                pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class StageTimer:
+    """CUDA-event timing of every C-ABI call made during the timed region (same stream)."""
+
+    def __init__(self):
+        self.events = []
+        self.enabled = False
+
+    def wrap(self, libmod, names):
+        self.orig = {}
+        for nme in names:
+            fn = getattr(libmod, nme)
+            self.orig[nme] = fn
+
+            def make(fn=fn, nme=nme):
+                def call(*a):
+                    if not self.enabled:
+                        return fn(*a)
+                    e0 = torch.cuda.Event(enable_timing=True)
+                    e1 = torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    r = fn(*a)
+                    e1.record()
+                    self.events.append((nme, e0, e1))
+                    return r
+                return call
+            setattr(libmod, nme, make())
+
+    def summary(self):
+        out = {}
+        for nme, e0, e1 in self.events:
+            ms = e0.elapsed_time(e1)
+            d = out.setdefault(nme, [0.0, 0])
+            d[0] += ms
+            d[1] += 1
+        return out
+
+
+class _LibProxy:
+    """attribute proxy so StageTimer can interpose on ctypes functions"""
+
+    def __init__(self, lib):
+        object.__setattr__(self, "_lib", lib)
+
+    def __getattr__(self, k):
+        return getattr(object.__getattribute__(self, "_lib"), k)
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    import street_crafter_b200 as S
+    from street_crafter_b200 import _lib, rendering
+    from street_crafter_b200.parallel import GaussianArena, allreduce_gradients
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    from tools.scene import make_camera, make_gaussians
+
+    timer = StageTimer()
+    proxy = _LibProxy(_lib.lib)
+    stage_fns = ["sc_projection_fwd", "sc_projection_bwd", "sc_sh_fwd", "sc_sh_bwd", "sc_isect_count",
+                 "sc_exclusive_scan_i32", "sc_isect_emit", "sc_radix_sort_pairs", "sc_isect_offset_encode",
+                 "sc_rasterize_fwd", "sc_rasterize_bwd"]
+    timer.wrap(proxy, stage_fns)
+    rendering.lib = proxy
+
+    n = args.gaussians
+    scene = make_gaussians(n, sh_degree=SH_DEGREE, seed=0)
+    arena = GaussianArena(scene, dev)  # flat parameter + gradient arenas (attribute-major)
+    n_views = len(CAM_YAWS)
+    cams = []
+    for v in range(n_views):
+        # rank r renders frame r of the multi-camera rig (ego advances 1.5 m per frame)
+        Vm, Km = make_camera(WIDTH, HEIGHT, yaw_deg=CAM_YAWS[v], z_shift=1.5 * rank)
+        cams.append((Vm, Km, -(Vm[:3, :3].T @ Vm[:3, 3])))
+    g = torch.Generator().manual_seed(1234 + rank)
+    # host-resident per-step inputs (pinned): camera matrices + the target image of every view
+    host_V = [c[0][None].contiguous().pin_memory() for c in cams]
+    host_K = [c[1][None].contiguous().pin_memory() for c in cams]
+    host_C = [c[2].contiguous().pin_memory() for c in cams]
+    host_gt = [torch.rand(3, HEIGHT, WIDTH, generator=g).pin_memory() for _ in cams]
+    dev_V = [t.to(dev) for t in host_V]
+    dev_K = [t.to(dev) for t in host_K]
+    dev_C = [t.to(dev) for t in host_C]
+    v_rc = [torch.randn(1, HEIGHT, WIDTH, 4, generator=g).to(dev) for _ in cams]
+    v_ra = [torch.randn(1, HEIGHT, WIDTH, 1, generator=g).to(dev) for _ in cams]
+    for t in v_rc:
+        t[..., 3] *= 0.02
+
+    def step_resident():
+        """inputs already in HBM; upstream gradients fixed (loss-independent)"""
+        arena.zero_grad()
+        for v in range(n_views):
+            out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
+                                       dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE)
+            torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc[v], v_ra[v]])
+        if world > 1:
+            allreduce_gradients(arena)
+
+    def step_e2e():
+        """host buffers in, loss out: camera + target image H2D, L1 loss, backward, loss D2H"""
+        arena.zero_grad()
+        losses = []
+        for v in range(n_views):
+            Vd = host_V[v].to(dev, non_blocking=True)
+            Kd = host_K[v].to(dev, non_blocking=True)
+            Cd = host_C[v].to(dev, non_blocking=True)
+            gt = host_gt[v].to(dev, non_blocking=True)
+            out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
+                                       Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE)
+            loss = (out["rgb"] - gt).abs().mean() + 0.01 * out["acc"].mean()
+            loss.backward()
+            losses.append(loss.detach())
+        if world > 1:
+            allreduce_gradients(arena)
+        return torch.stack(losses).cpu()  # D2H read of the step's result
+
+    h2d = sum(t.numel() * 4 for t in host_V + host_K + host_C + host_gt)
+    d2h = 4 * n_views
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps
+
+    # ---- warm-up, then the timed device-resident region
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = _lib.launch_count()
+    timer.enabled = True
+    ms_step = timed(step_resident, args.steps)
+    timer.enabled = False
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop()
+    stages = timer.summary()
+    # ---- end-to-end (host buffers) region
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+
+    pix_per_step_rank = n_views * WIDTH * HEIGHT
+    value = world * pix_per_step_rank / (ms_step * 1e-3) / 1e6
+    e2e_value = world * pix_per_step_rank / (ms_e2e * 1e-3) / 1e6
+
+    result = None
+    if rank == 0:
+        # ---- roofline of the dominant kernel (rasterize backward), measured in the timed region
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback 6650"
+        # algorithmic pair counts of ONE camera pass, from the STATS instance of the fwd kernel
+        stats = torch.zeros(2, dtype=torch.int64, device=dev)
+        rendering._STATS["buf"] = stats
+        I_total, V_total = 0, 0
+        with torch.no_grad():
+            for v in range(n_views):
+                out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
+                                           dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE, train=False)
+                I_total += out["aux"]["isect_ids"].numel()
+                V_total += int(out["visibility_filter"].sum())
+        rendering._STATS["buf"] = None
+        torch.cuda.synchronize()
+        visited, contributing = (int(x) for x in stats.tolist())
+        # FP32 / SFU issue peaks, measured here with the probe kernels
+        sink = torch.empty(148 * 8 * 256, device=dev)
+        def probe(kind, iters=4096):
+            _lib.check(_lib.lib.sc_probe_fp32(kind, 148 * 8, 256, 64, sink.data_ptr(), torch.cuda.current_stream().cuda_stream), "probe")
+            torch.cuda.synchronize()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.check(_lib.lib.sc_probe_fp32(kind, 148 * 8, 256, iters, sink.data_ptr(), torch.cuda.current_stream().cuda_stream), "probe")
+            e1.record(); torch.cuda.synchronize()
+            ops = 148 * 8 * 256 * iters * (16 if kind == 0 else 8)
+            return ops / (e0.elapsed_time(e1) * 1e-3)
+        fp32_peak = max(probe(0) for _ in range(3)) / 1e12      # TFLOP/s
+        sfu_peak = max(probe(1) for _ in range(3)) / 1e12       # T ex2/s
+        # SURVEY §8d per-pair figures: fwd 17 FLOP/visited + 11/contributing ; bwd 17/visited + 66/contributing
+        flop_fwd = 17.0 * visited + 11.0 * contributing
+        flop_bwd = 17.0 * visited + 66.0 * contributing
+        def per_launch(name):
+            ms, cnt = stages.get(name, (0.0, 0))
+            return (ms / cnt) if cnt else None
+        t_bwd = per_launch("sc_rasterize_bwd")
+        t_fwd = per_launch("sc_rasterize_fwd")
+        # one launch = one camera; flop_* are sums over the 3 cameras
+        ach_bwd = flop_bwd / n_views / (t_bwd * 1e-3) / 1e12 if t_bwd else None
+        ach_fwd = flop_fwd / n_views / (t_fwd * 1e-3) / 1e12 if t_fwd else None
+        roofline = {"kernel": "rasterize_bwd_kernel<4>", "bound": "fp32", "achieved": ach_bwd,
+                    "peak": fp32_peak, "unit": "TFLOP/s", "frac": (ach_bwd / fp32_peak) if ach_bwd else None,
+                    "traffic": None,
+                    "peak_source": "sc_probe_fp32 FMA probe run in this process (no tensor cores on this path)",
+                    "ms_per_launch": t_bwd, "alg_flop_per_launch": flop_bwd / n_views,
+                    "visited_pairs_per_launch": visited / n_views,
+                    "contributing_pairs_per_launch": contributing / n_views}
+        # HBM-bound stages: algorithmic bytes per camera pass
+        Ic, Vc, P = I_total / n_views, V_total / n_views, WIDTH * HEIGHT
+        alg_bytes = {
+            "sc_projection_fwd": 80.0 * n, "sc_sh_fwd": 204.0 * Vc + 12.0 * n,
+            "sc_isect_count": 16.0 * n, "sc_isect_emit": 24.0 * n + 12.0 * Ic,
+            "sc_radix_sort_pairs": 24.0 * Ic, "sc_isect_offset_encode": 8.0 * Ic,
+            "sc_sh_bwd": 216.0 * Vc + 192.0 * n, "sc_projection_bwd": 128.0 * n,
+        }
+        stage_table = {}
+        for nme in stage_fns:
+            ms, cnt = stages.get(nme, (0.0, 0))
+            row = {"ms_per_step": ms / args.steps, "calls_per_step": cnt / args.steps}
+            if nme in alg_bytes and cnt:
+                gbs = alg_bytes[nme] / (ms / cnt * 1e-3) / 1e9
+                row.update({"alg_GB_per_call": alg_bytes[nme] / 1e9, "achieved_GBs": gbs, "frac_hbm": gbs / hbm_peak})
+            stage_table[nme] = row
+        stage_table["sc_rasterize_fwd"].update({"achieved_TFLOPs": ach_fwd,
+                                                "frac_fp32": (ach_fwd / fp32_peak) if ach_fwd else None})
+        stage_table["sc_rasterize_bwd"].update({"achieved_TFLOPs": ach_bwd,
+                                                "frac_fp32": (ach_bwd / fp32_peak) if ach_bwd else None})
+        kernel_ms = sum(r["ms_per_step"] for r in stage_table.values())
+        # step roofline: sum over stages of max(bytes/BW, flop/R) for the 3 cameras
+        t_roof = 0.0
+        for nme, b in alg_bytes.items():
+            t_roof += n_views * b / (hbm_peak * 1e9)
+        t_roof += (flop_fwd + flop_bwd) / (fp32_peak * 1e12)
+        t_roof += (44.0 * Ic * 2 + 24.0 * P + 28.0 * P) * n_views / (hbm_peak * 1e9) * 0  # compositing bytes hide under FP32
+
+        cpu = None
+        if not args.no_cpu_baseline:
+            n_s, W_s, H_s = 100_000, 960, 640
+            t_cpu, cores = time_cpu_oracle(n_s, W_s, H_s, reps=1)
+            cpu = {"value": W_s * H_s / t_cpu / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "port",
+                   "sample": f"BASELINE configs[0]: {n_s} Gaussians SH3, one {W_s}x{H_s} camera, fwd+bwd, "
+                             f"torch CPU oracle, best of 1 ({t_cpu:.1f} s)"}
+        result = {
+            "metric": "3DGS fwd+bwd Mpix/s", "value": value, "unit": "Mpix/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_step,
+            "iters_per_s": 1e3 / ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "gaussians": n, "views_per_gpu": n_views,
+                       "isects_per_step": I_total, "visible_per_step": V_total,
+                       "l2_policy": "inputs larger than L2 (472 MB parameters + 0.9 GB/step intermediates)",
+                       "parallelism": f"view-sharded x{world}, flat-arena gradient all-reduce" if world > 1 else "single GPU"},
+            "e2e": {"value": e2e_value, "unit": "Mpix/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h,
+                    "what": "pinned host camera matrices + target images -> device, render, L1 loss, backward, loss -> host"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": roofline,
+            "roofline_step": {"t_roof_ms": t_roof * 1e3, "frac": t_roof * 1e3 / ms_step,
+                              "kernel_ms_per_step": kernel_ms,
+                              "hbm_peak_GBs": hbm_peak, "hbm_peak_source": hbm_src,
+                              "fp32_peak_TFLOPs": fp32_peak, "sfu_peak_Tops": sfu_peak},
+            "stages": stage_table,
+            "cpu_baseline": cpu,
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if result is not None:
+        print(json.dumps(result))
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -97,12 +97,15 @@ int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, in
 /* CH in 1..5; backgrounds[C,CH] nullable; max_hit 0 = unlimited.
  * render_colors[C,H,W,CH], render_alphas[C,H,W]; saved for backward (nullable):
  * last_ids[C,H,W] i32 (index into flatten_ids of the last contributing splat, -1 if none),
- * final_T[C,H,W] (exact final transmittance; 1-render_alpha loses bits near saturation). */
+ * final_T[C,H,W] (exact final transmittance; 1-render_alpha loses bits near saturation).
+ * stats (nullable, measurement only): two u64 counters ADDED to: [0] visited (pixel,splat)
+ * pairs, [1] contributing pairs — the algorithmic-FLOP basis of the roofline. */
 int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
                      int tile_size, const float* means2d, const float* conics, const float* colors,
                      const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
                      const int32_t* flatten_ids, int max_hit, float* render_colors,
-                     float* render_alphas, int32_t* last_ids, float* final_T, void* stream);
+                     float* render_alphas, int32_t* last_ids, float* final_T, uint64_t* stats,
+                     void* stream);
 /* gradient buffers must be ZEROED by the caller; v_means2d_abs nullable. */
 int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
                      int tile_size, const float* means2d, const float* conics, const float* colors,
@@ -119,6 +122,12 @@ int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int 
 int64_t sc_knn_workspace_bytes(int64_t P);
 int sc_knn3_mean_dist2(int64_t P, const float* points, float* mean_dist2, void* workspace,
                        int64_t workspace_bytes, void* stream);
+
+/* ---- measurement helper ----------------------------------------------------------------- */
+/* FP32 FMA / SFU(ex2) issue-rate probes used by bench.py as the roofline denominator of the
+ * compositing kernels: every thread runs `iters` rounds of 8 independent dependent chains.
+ * flops = grid*block*iters*16 (fma) ; ex2 ops = grid*block*iters*8.  sink[grid*block] out. */
+int sc_probe_fp32(int kind /*0 fma, 1 ex2*/, int grid, int block, int iters, float* sink, void* stream);
 
 #ifdef __cplusplus
 }

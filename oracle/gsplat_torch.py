@@ -23,6 +23,7 @@ from __future__ import annotations
 import math
 from typing import Optional, Tuple
 
+import numpy as np
 import torch
 from torch import Tensor
 
@@ -45,6 +46,28 @@ SH_C4 = [2.5033429417967046, -1.7701307697799304, 0.9461746957575601, -0.6690465
          0.6258357354491761]
 
 
+class _SqrtRN(torch.autograd.Function):
+    """Correctly rounded (IEEE round-to-nearest) square root.  torch.sqrt on CPU goes through a
+    vectorised SLEEF routine that is NOT correctly rounded (~0.6 % of fp32 results are 1 ulp off
+    numpy / the FPU / CUDA's sqrt.rn), which would make the integer-feeding chain
+    implementation-defined.  numpy's sqrt is the hardware instruction."""
+
+    @staticmethod
+    def forward(ctx, x):
+        y = torch.from_numpy(np.sqrt(x.detach().contiguous().numpy()))
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        (y,) = ctx.saved_tensors
+        return g * 0.5 / y
+
+
+def sqrt_rn(x: Tensor) -> Tensor:
+    return _SqrtRN.apply(x)
+
+
 # --------------------------------------------------------------------------------------
 # A1: fully_fused_projection   (street_gaussian_renderer.py:219-232)
 # --------------------------------------------------------------------------------------
@@ -54,7 +77,7 @@ def quat_scale_to_covar(quats: Tensor, scales: Tensor):
     Restates gsplat `_quat_scale_to_covar_preci` with explicit op order."""
     w, x, y, z = quats.unbind(-1)
     n2 = ((w * w + x * x) + y * y) + z * z
-    nrm = torch.sqrt(n2).clamp_min(1e-12)
+    nrm = sqrt_rn(n2).clamp_min(1e-12)
     w, x, y, z = w / nrm, x / nrm, y / nrm, z / nrm
     x2, y2, z2 = x * x, y * y, z * z
     xy, xz, yz = x * y, x * z, y * z
@@ -141,13 +164,13 @@ def fully_fused_projection(means: Tensor, covars, quats: Tensor, scales: Tensor,
         det = b00 * b11 - v01 * v01
         valid = (det > 0) & (zc > near_plane) & (zc < far_plane)
         dets = torch.where(det > 0, det, torch.ones_like(det))
-        comp = torch.sqrt((det_orig / dets).clamp_min(0.0))
+        comp = sqrt_rn((det_orig / dets).clamp_min(0.0))
         conic_a = b11 / dets
         conic_b = -v01 / dets
         conic_c = b00 / dets
         b = half * (b00 + b11)
-        v1 = b + torch.sqrt((b * b - det).clamp_min(EIGEN_FLOOR))
-        radius = torch.ceil(3.0 * torch.sqrt(v1))
+        v1 = b + sqrt_rn((b * b - det).clamp_min(EIGEN_FLOOR))
+        radius = torch.ceil(3.0 * sqrt_rn(v1))
         valid = valid & (radius > radius_clip)
         inside = (mx + radius > 0) & (mx - radius < Wf) & (my + radius > 0) & (my - radius < Hf)
         valid = valid & inside

@@ -33,31 +33,38 @@ SIGNATURES = {
     "sc_radix_sort_pairs": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _i64, _ptr]),
     "sc_isect_offset_encode": (_i32, [_i64, _ptr, _i32, _i32, _i32, _i32, _ptr, _ptr]),
     "sc_rasterize_fwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
-                                _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr]),
+                                _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_rasterize_bwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                 _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_knn_workspace_bytes": (_i64, [_i64]),
     "sc_knn3_mean_dist2": (_i32, [_i64, _ptr, _ptr, _ptr, _i64, _ptr]),
+    "sc_probe_fp32": (_i32, [_i32, _i32, _i32, _i32, _ptr, _ptr]),
 }
 
 
-def _load() -> C.CDLL:
-    if not os.path.exists(LIB_PATH):
-        # in-tree build (nvcc cross-compiles sm_100a without a GPU); never a CPU fallback
-        from .build import build
-        build()
-    if not os.path.exists(LIB_PATH):
-        raise ImportError(f"{LIB_PATH} is missing; run `python -m street_crafter_b200.build`")
-    lib = C.CDLL(LIB_PATH)
+def _bind(path: str):
+    lib = C.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
-        try:
-            fn = getattr(lib, name)
-        except AttributeError as e:  # stale build
-            raise ImportError(f"{LIB_PATH} does not export {name}; rebuild with "
-                              f"`python -m street_crafter_b200.build --force`") from e
+        fn = getattr(lib, name)  # AttributeError when the build is stale
         fn.restype = res
         fn.argtypes = args
     return lib
+
+
+def _load() -> C.CDLL:
+    """dlopen the in-tree library, (re)building it first with nvcc when it is missing or older
+    than its sources (nvcc cross-compiles sm_100a without a GPU).  Never a CPU fallback."""
+    from .build import build
+    try:
+        build()  # incremental: a no-op when libscb200.so is newer than every source
+    except Exception:
+        if not os.path.exists(LIB_PATH):
+            raise
+    try:
+        return _bind(LIB_PATH)
+    except AttributeError as e:
+        raise ImportError(f"{LIB_PATH} does not export every symbol of include/scb200.h; rebuild "
+                          f"with `python -m street_crafter_b200.build --force`") from e
 
 
 lib = _load()

@@ -151,8 +151,10 @@ knn_parent_box_kernel(int64_t n_child, int64_t n_parent, const Box* __restrict__
     }
 }
 
+// Same contraction nvcc picks for the reference's `d.x*d.x + d.y*d.y + d.z*d.z`
+// (simple_knn.cu:135-136; SASS: FMUL dy², FFMA dx², FFMA dz²) so results are bit-identical.
 __device__ __forceinline__ float sqdist3(float dx, float dy, float dz) {
-    return fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+    return fmaf(dz, dz, fmaf(dx, dx, dy * dy));
 }
 
 __device__ __forceinline__ float box_box_dist2(const float (&alo)[3], const float (&ahi)[3], const Box& b) {

@@ -1,0 +1,32 @@
+// FP32-FMA and SFU(ex2) issue-rate probes: the measured denominators of the compositing
+// kernels' roofline (MEASURED_PEAKS.json only carries HBM and bf16-tensor peaks).
+#include "common.cuh"
+
+namespace {
+template <int KIND>
+__global__ void probe_kernel(int iters, float* __restrict__ sink) {
+    float a[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = 1.0f + 1e-3f * (float)(threadIdx.x + k);
+    const float m = 0.999f + 1e-9f * (float)blockIdx.x, c = 1e-4f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            if (KIND == 0) a[k] = fmaf(a[k], m, c);
+            else a[k] = exp2f(a[k] * 0.5f - 1.0f);
+        }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += a[k];
+    sink[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+}  // namespace
+
+extern "C" int sc_probe_fp32(int kind, int grid, int block, int iters, float* sink, void* stream) {
+    SC_CHECK_ARG(grid > 0 && block > 0 && block <= 1024 && iters > 0 && sink, "probe args");
+    if (kind == 0) probe_kernel<0><<<grid, block, 0, (cudaStream_t)stream>>>(iters, sink);
+    else probe_kernel<1><<<grid, block, 0, (cudaStream_t)stream>>>(iters, sink);
+    SC_CHECK_LAUNCH("probe_kernel");
+    return SC_OK;
+}

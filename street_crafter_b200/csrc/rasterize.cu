@@ -28,7 +28,7 @@ constexpr float LOG2_ALPHA_FLOOR = -7.994353436858858f;  // log2(1/255)
 struct __align__(16) StagedA { float x, y, a2, b2; };       // a2 = .5*a*log2e, b2 = b*log2e
 struct __align__(16) StagedB { float c2, lo, inv_opac, pad; };  // c2 = .5*c*log2e, lo = log2(opacity)
 
-template <int CH>
+template <int CH, bool STATS>
 __global__ void __launch_bounds__(RT)
 rasterize_fwd_kernel(int64_t N, int64_t n_isects, int width, int height, int tile_w, int tile_h,
                      const float2* __restrict__ means2d, const float* __restrict__ conics,
@@ -36,7 +36,7 @@ rasterize_fwd_kernel(int64_t N, int64_t n_isects, int width, int height, int til
                      const float* __restrict__ backgrounds, const int32_t* __restrict__ isect_offsets,
                      const int32_t* __restrict__ flatten_ids, int max_hit, float* __restrict__ render_colors,
                      float* __restrict__ render_alphas, int32_t* __restrict__ last_ids,
-                     float* __restrict__ final_T) {
+                     float* __restrict__ final_T, unsigned long long* __restrict__ stats) {
     __shared__ StagedA sA[RT];
     __shared__ StagedB sB[RT];
     __shared__ __align__(16) float sC[RT * CH];
@@ -58,6 +58,7 @@ rasterize_fwd_kernel(int64_t N, int64_t n_isects, int width, int height, int til
     float T = 1.0f;
     int cur_idx = -1;
     int hits = 0;
+    unsigned visited = 0, contributing = 0;  // STATS only
     float pix[CH];
 #pragma unroll
     for (int c = 0; c < CH; ++c) pix[c] = 0.f;
@@ -83,6 +84,7 @@ rasterize_fwd_kernel(int64_t N, int64_t n_isects, int width, int height, int til
             for (int t = 0; t < bs && !done; ++t) {
                 const StagedA A = sA[t];
                 const StagedB B = sB[t];
+                if (STATS) ++visited;
                 const float dx = A.x - px, dy = A.y - py;
                 const float s2 = A.a2 * dx * dx + B.c2 * dy * dy + A.b2 * dx * dy;  // sigma*log2e
                 const float e = B.lo - s2;
@@ -99,6 +101,7 @@ rasterize_fwd_kernel(int64_t N, int64_t n_isects, int width, int height, int til
                 for (int c = 0; c < CH; ++c) pix[c] += sC[t * CH + c] * vis;
                 cur_idx = batch_start + t;
                 T = next_T;
+                if (STATS) ++contributing;
                 if (max_hit > 0 && ++hits >= max_hit) {
                     done = true;
                     break;
@@ -114,6 +117,18 @@ rasterize_fwd_kernel(int64_t N, int64_t n_isects, int width, int height, int til
             render_colors[pix_id * CH + c] = backgrounds ? pix[c] + T * __ldg(backgrounds + cam * CH + c) : pix[c];
         if (last_ids) last_ids[pix_id] = cur_idx;
         if (final_T) final_T[pix_id] = T;
+    }
+    if (STATS) {
+        unsigned long long v = visited, c = contributing;
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            v += __shfl_xor_sync(0xffffffffu, v, o);
+            c += __shfl_xor_sync(0xffffffffu, c, o);
+        }
+        if ((tid & 31) == 0) {
+            atomicAdd(stats + 0, v);
+            atomicAdd(stats + 1, c);
+        }
     }
 }
 
@@ -300,13 +315,20 @@ template <int CH>
 int launch_fwd(int C, int64_t N, int64_t n_isects, int width, int height, const float* means2d,
                const float* conics, const float* colors, const float* opacities, const float* backgrounds,
                const int32_t* isect_offsets, const int32_t* flatten_ids, int max_hit, float* render_colors,
-               float* render_alphas, int32_t* last_ids, float* final_T, cudaStream_t st) {
+               float* render_alphas, int32_t* last_ids, float* final_T, unsigned long long* stats,
+               cudaStream_t st) {
     const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
     dim3 grid(tile_w, tile_h, C), block(TILE, TILE);
-    rasterize_fwd_kernel<CH><<<grid, block, 0, st>>>(
-        N, n_isects, width, height, tile_w, tile_h, reinterpret_cast<const float2*>(means2d), conics, colors,
-        opacities, backgrounds, isect_offsets, flatten_ids, max_hit, render_colors, render_alphas, last_ids,
-        final_T);
+    if (stats)
+        rasterize_fwd_kernel<CH, true><<<grid, block, 0, st>>>(
+            N, n_isects, width, height, tile_w, tile_h, reinterpret_cast<const float2*>(means2d), conics,
+            colors, opacities, backgrounds, isect_offsets, flatten_ids, max_hit, render_colors, render_alphas,
+            last_ids, final_T, stats);
+    else
+        rasterize_fwd_kernel<CH, false><<<grid, block, 0, st>>>(
+            N, n_isects, width, height, tile_w, tile_h, reinterpret_cast<const float2*>(means2d), conics,
+            colors, opacities, backgrounds, isect_offsets, flatten_ids, max_hit, render_colors, render_alphas,
+            last_ids, final_T, nullptr);
     SC_CHECK_LAUNCH("rasterize_fwd_kernel");
     return SC_OK;
 }
@@ -334,7 +356,8 @@ extern "C" int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int 
                                 int tile_size, const float* means2d, const float* conics, const float* colors,
                                 const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
                                 const int32_t* flatten_ids, int max_hit, float* render_colors,
-                                float* render_alphas, int32_t* last_ids, float* final_T, void* stream) {
+                                float* render_alphas, int32_t* last_ids, float* final_T, uint64_t* stats,
+                                void* stream) {
     SC_CHECK_ARG(C >= 1 && N >= 0 && n_isects >= 0 && width > 0 && height > 0, "sizes");
     SC_CHECK_ARG(n_isects < (1ll << 31), "n_isects must fit int32");
     if (tile_size != TILE) {
@@ -345,7 +368,8 @@ extern "C" int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int 
     SC_CHECK_ARG(n_isects == 0 || (means2d && conics && colors && opacities && flatten_ids), "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
 #define ARGS C, N, n_isects, width, height, means2d, conics, colors, opacities, backgrounds, isect_offsets, \
-             flatten_ids, max_hit, render_colors, render_alphas, last_ids, final_T, st
+             flatten_ids, max_hit, render_colors, render_alphas, last_ids, final_T,                          \
+             reinterpret_cast<unsigned long long*>(stats), st
     switch (CH) {
         case 1: return launch_fwd<1>(ARGS);
         case 2: return launch_fwd<2>(ARGS);

@@ -271,6 +271,11 @@ def isect_offset_encode(isect_ids: Tensor, n_cameras: int, tile_width: int, tile
 # ------------------------------------------------------------------------------------------
 # A7/A8  rasterize_to_pixels
 # ------------------------------------------------------------------------------------------
+# measurement hook (bench.py): when "buf" holds a 2-element int64 CUDA tensor the forward
+# kernel adds its visited / contributing pair counts to it (a separate template instance).
+_STATS = {"buf": None}
+
+
 class _RasterizeToPixels(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means2d, conics, colors, opacities, backgrounds, width, height, tile_size,
@@ -297,7 +302,8 @@ class _RasterizeToPixels(torch.autograd.Function):
             check(lib.sc_rasterize_fwd(C, N, n_isects, CH, width, height, tile_size, _p(means2d), _p(conics),
                                        _p(colors), _p(opacities), _p(backgrounds), _p(isect_offsets),
                                        _p(flatten_ids), int(max_hit), _p(render_colors), _p(render_alphas),
-                                       _p(last_ids), _p(final_T), _stream()), "sc_rasterize_fwd")
+                                       _p(last_ids), _p(final_T), _p(_STATS["buf"]), _stream()),
+                  "sc_rasterize_fwd")
         ctx.save_for_backward(means2d, conics, colors, opacities,
                               backgrounds if backgrounds is not None else torch.empty(0, device=dev),
                               isect_offsets, flatten_ids, last_ids, final_T)

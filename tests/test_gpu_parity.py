@@ -1,0 +1,499 @@
+"""GPU parity tests (-m gpu): the sm_100a kernels, called through the C ABI, against the CPU
+oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star):
+  * radii, tiles_per_gauss, sorted isect_ids, flatten_ids, isect_offsets  -> BIT-EXACT
+  * rendered RGB / depth / alpha                                           -> 1e-4 max-abs (fp32)
+  * gradients                                                              -> 1e-3 relative
+The alpha >= 1/255 accept test is a hard discontinuity of the algorithm itself: two fp32
+implementations whose exp() differ in the last bits can disagree on a (pixel, Gaussian) pair
+that sits exactly on the threshold, which moves that pixel by up to alpha*T*colour ~ 4e-3.
+IMAGE_OUTLIER_FRAC bounds how many pixels may do that (and by how much); everything else must
+meet 1e-4."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import gsplat_torch as G
+from oracle import knn as KO
+from tools.scene import make_camera, make_gaussians, make_lidar_points
+
+pytestmark = pytest.mark.gpu
+
+IMG_TOL = 1e-4
+GRAD_RTOL = 1e-3
+IMAGE_OUTLIER_FRAC = 2e-5
+IMAGE_OUTLIER_MAX = 8e-3  # ~ 2/255 of a unit colour
+
+
+@pytest.fixture(scope="module")
+def S():
+    import street_crafter_b200 as S
+    return S
+
+
+@pytest.fixture(scope="module")
+def dev():
+    return torch.device("cuda:0")
+
+
+def cuda(d, dev):
+    return {k: v.to(dev) for k, v in d.items()}
+
+
+def assert_image_close(got, want, what, scale=1.0):
+    diff = (got.cpu() - want).abs() / scale
+    bad = diff > IMG_TOL
+    frac = bad.float().mean().item()
+    assert frac <= IMAGE_OUTLIER_FRAC, f"{what}: {bad.sum().item()} of {bad.numel()} values off by > {IMG_TOL}"
+    assert diff.max().item() <= IMAGE_OUTLIER_MAX, f"{what}: max diff {diff.max().item()}"
+    return int(bad.sum())
+
+
+def assert_grad_close(got, want, what, rtol=GRAD_RTOL):
+    got = got.detach().cpu().double()
+    want = want.detach().double()
+    assert torch.isfinite(got).all(), what
+    denom = want.abs().max().item() + 1e-30
+    err = (got - want).abs().max().item() / denom
+    l2 = ((got - want).norm() / (want.norm() + 1e-30)).item()
+    assert err <= rtol and l2 <= rtol, f"{what}: max-rel {err:.3e}, l2-rel {l2:.3e}"
+
+
+# ------------------------------------------------------------------------------ projection
+@pytest.mark.parametrize("n,W,H,yaw", [(20000, 960, 640, 0.0), (5003, 1920, 886, 45.0), (1, 64, 48, 0.0),
+                                       (257, 100, 70, -45.0)])
+def test_projection_bit_exact(S, dev, n, W, H, yaw):
+    s = make_gaussians(n, seed=n)
+    V, K = make_camera(W, H, yaw_deg=yaw)
+    want = G.fully_fused_projection(s["means"], None, s["quats"], s["scales"], V[None], K[None], W, H,
+                                    near_plane=0.001, far_plane=1000.0, calc_compensations=True)
+    c = cuda(s, dev)
+    got = S.fully_fused_projection(c["means"], None, c["quats"], c["scales"], V[None].to(dev), K[None].to(dev), W,
+                                   H, near_plane=0.001, far_plane=1000.0, calc_compensations=True, packed=False)
+    names = ["radii", "means2d", "depths", "conics", "compensations"]
+    for nm, g, w in zip(names, got, want):
+        assert g.shape == w.shape and g.dtype == w.dtype, nm
+        assert torch.equal(g.cpu(), w), f"{nm} not bit-exact: {(g.cpu() != w).sum().item()} mismatches"
+    assert got[0].dtype == torch.int32
+
+
+def test_projection_multi_camera_and_no_comp(S, dev):
+    s = make_gaussians(3000, seed=11)
+    cams = [make_camera(640, 384, yaw_deg=y, z_shift=z) for y, z in [(0, 0), (45, 1.5), (-45, 3.0)]]
+    V = torch.stack([c[0] for c in cams])
+    K = torch.stack([c[1] for c in cams])
+    want = G.fully_fused_projection(s["means"], None, s["quats"], s["scales"], V, K, 640, 384,
+                                    near_plane=0.001, far_plane=1000.0, calc_compensations=False)
+    c = cuda(s, dev)
+    got = S.fully_fused_projection(c["means"], None, c["quats"], c["scales"], V.to(dev), K.to(dev), 640, 384,
+                                   near_plane=0.001, far_plane=1000.0)
+    assert got[4] is None and want[4] is None
+    for g, w in zip(got[:4], want[:4]):
+        assert torch.equal(g.cpu(), w)
+
+
+def test_projection_backward(S, dev):
+    s = make_gaussians(6000, seed=21)
+    W, H = 640, 384
+    V, K = make_camera(W, H)
+    leaves = [s[k].clone().requires_grad_(True) for k in ("means", "quats", "scales")]
+    r, m2, dp, cn, cp = G.fully_fused_projection(leaves[0], None, leaves[1], leaves[2], V[None], K[None], W, H,
+                                                 near_plane=0.001, far_plane=1000.0, calc_compensations=True)
+    g = torch.Generator().manual_seed(0)
+    ws = [torch.randn(t.shape, generator=g) for t in (m2, dp, cn, cp)]
+    # conic entries span many orders of magnitude: weight them so every path matters
+    (m2 * ws[0]).sum().add((dp * ws[1]).sum()).add((cn * ws[2]).sum()).add((cp * ws[3]).sum()).backward()
+    cl = [s[k].to(dev).requires_grad_(True) for k in ("means", "quats", "scales")]
+    r2, m2g, dpg, cng, cpg = S.fully_fused_projection(cl[0], None, cl[1], cl[2], V[None].to(dev), K[None].to(dev),
+                                                      W, H, near_plane=0.001, far_plane=1000.0,
+                                                      calc_compensations=True)
+    ((m2g * ws[0].to(dev)).sum() + (dpg * ws[1].to(dev)).sum() + (cng * ws[2].to(dev)).sum()
+     + (cpg * ws[3].to(dev)).sum()).backward()
+    vis = (r[0] > 0)
+    for nm, a, b in zip(("means", "quats", "scales"), cl, leaves):
+        ref = torch.nan_to_num(b.grad)
+        assert_grad_close(a.grad, ref, f"v_{nm}")
+        assert (a.grad.cpu()[~vis] == 0).all(), f"culled Gaussians must get zero v_{nm}"
+
+
+# ------------------------------------------------------------------------------ binning
+def _binning_case(n, W, H, seed, C=1):
+    s = make_gaussians(n, seed=seed)
+    cams = [make_camera(W, H, yaw_deg=20.0 * c, z_shift=1.5 * c) for c in range(C)]
+    V = torch.stack([c[0] for c in cams])
+    K = torch.stack([c[1] for c in cams])
+    proj = G.fully_fused_projection(s["means"], None, s["quats"], s["scales"], V, K, W, H, near_plane=0.001,
+                                    far_plane=1000.0, calc_compensations=True)
+    return s, V, K, proj
+
+
+@pytest.mark.parametrize("n,W,H,C", [(30000, 960, 640, 1), (4000, 1920, 886, 1), (2000, 320, 192, 3),
+                                     (50, 33, 17, 1)])
+def test_isect_bit_exact(S, dev, n, W, H, C):
+    s, V, K, (radii, m2, dep, con, comp) = _binning_case(n, W, H, seed=n + C, C=C)
+    tw, th = math.ceil(W / 16), math.ceil(H / 16)
+    tpg_w, ids_w, flat_w = G.isect_tiles(m2, radii, dep, 16, tw, th, n_cameras=C)
+    off_w = G.isect_offset_encode(ids_w, C, tw, th)
+    tpg, ids, flat = S.isect_tiles(m2.to(dev), radii.to(dev), dep.to(dev), 16, tw, th, packed=False, n_cameras=C)
+    off = S.isect_offset_encode(ids, C, tw, th)
+    assert ids.dtype == torch.int64 and flat.dtype == torch.int32 and tpg.dtype == torch.int32
+    assert off.dtype == torch.int32 and off.shape == (C, th, tw)
+    assert torch.equal(tpg.cpu(), tpg_w), "tiles_per_gauss"
+    assert ids.numel() == ids_w.numel() > 0
+    assert torch.equal(ids.cpu(), ids_w), "sorted isect_ids"
+    assert torch.equal(flat.cpu(), flat_w), "flatten_ids (stable tie-break)"
+    assert torch.equal(off.cpu(), off_w), "isect_offsets"
+    # unsorted emission order too
+    _, ids_u_w, flat_u_w = G.isect_tiles(m2, radii, dep, 16, tw, th, sort=False, n_cameras=C)
+    _, ids_u, flat_u = S.isect_tiles(m2.to(dev), radii.to(dev), dep.to(dev), 16, tw, th, sort=False, n_cameras=C)
+    assert torch.equal(ids_u.cpu(), ids_u_w) and torch.equal(flat_u.cpu(), flat_u_w)
+
+
+def test_isect_empty(S, dev):
+    m2 = torch.zeros(1, 10, 2, device=dev)
+    radii = torch.zeros(1, 10, dtype=torch.int32, device=dev)
+    dep = torch.zeros(1, 10, device=dev)
+    tpg, ids, flat = S.isect_tiles(m2, radii, dep, 16, 4, 3, n_cameras=1)
+    assert ids.numel() == 0 and flat.numel() == 0 and int(tpg.sum()) == 0
+    off = S.isect_offset_encode(ids, 1, 4, 3)
+    assert off.shape == (1, 3, 4) and (off == 0).all()
+
+
+def test_isect_ties_are_stable(S, dev):
+    """many Gaussians with IDENTICAL depth in one tile: order must be emission order."""
+    n = 5000
+    m2 = torch.full((1, n, 2), 24.0)
+    radii = torch.full((1, n), 2, dtype=torch.int32)
+    dep = torch.full((1, n), 5.0)
+    dep[0, ::7] = 3.0
+    _, ids_w, flat_w = G.isect_tiles(m2, radii, dep, 16, 8, 8, n_cameras=1)
+    _, ids, flat = S.isect_tiles(m2.to(dev), radii.to(dev), dep.to(dev), 16, 8, 8, n_cameras=1)
+    assert torch.equal(ids.cpu(), ids_w) and torch.equal(flat.cpu(), flat_w)
+
+
+@pytest.mark.parametrize("n", [1, 31, 4095, 4096, 4097, 100003, 1 << 20])
+@pytest.mark.parametrize("end_bit", [8, 30, 44, 46, 64])
+def test_radix_sort_matches_stable_sort(S, dev, n, end_bit):
+    from street_crafter_b200._lib import check, lib
+    g = torch.Generator().manual_seed(n * 131 + end_bit)
+    hi = min(end_bit, 62)
+    keys = torch.randint(0, 2 ** hi, (n,), generator=g, dtype=torch.int64)
+    if n > 100:
+        keys[n // 3: n // 3 + n // 4] = keys[0]          # long run of duplicates
+        keys[::5] &= 0xFFFF                              # and clustered small keys
+    if end_bit == 64:
+        keys[::3] |= (1 << 62)
+    vals = torch.arange(n, dtype=torch.int32)
+    ka, va = keys.to(dev), vals.to(dev)
+    kb, vb = torch.empty_like(ka), torch.empty_like(va)
+    ws_bytes = int(lib.sc_sort_workspace_bytes(n))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    where = check(lib.sc_radix_sort_pairs(n, ka.data_ptr(), va.data_ptr(), kb.data_ptr(), vb.data_ptr(), end_bit,
+                                          ws.data_ptr(), ws_bytes, torch.cuda.current_stream().cuda_stream),
+                  "sort")
+    ko, vo = (kb, vb) if where == 0 else (ka, va)
+    mask = (1 << end_bit) - 1 if end_bit < 64 else -1
+    sk, order = torch.sort(keys & mask if end_bit < 63 else keys, stable=True)
+    assert torch.equal((ko.cpu() & mask) if end_bit < 63 else ko.cpu(), sk)
+    assert torch.equal(vo.cpu(), vals[order])
+
+
+# ------------------------------------------------------------------------------ SH
+@pytest.mark.parametrize("K,deg", [(1, 0), (4, 1), (4, 0), (9, 2), (16, 3), (16, 1), (25, 4), (25, 3)])
+@pytest.mark.parametrize("M", [1, 33, 5000])
+def test_sh_forward_backward(S, dev, K, deg, M):
+    g = torch.Generator().manual_seed(K * 100 + deg + M)
+    dirs = (torch.randn(1, M, 3, generator=g) * 5).requires_grad_(True)
+    coeffs = torch.randn(1, M, K, 3, generator=g).requires_grad_(True)
+    masks = torch.rand(1, M, generator=g) > 0.3
+    w = torch.randn(1, M, 3, generator=g)
+    out_w = G.spherical_harmonics(deg, dirs, coeffs, masks)
+    (out_w * w).sum().backward()
+    d2 = dirs.detach().to(dev).requires_grad_(True)
+    c2 = coeffs.detach().to(dev).requires_grad_(True)
+    out = S.spherical_harmonics(deg, d2, c2, masks=masks.to(dev))
+    (out * w.to(dev)).sum().backward()
+    assert torch.allclose(out.cpu(), out_w, atol=2e-5, rtol=1e-5), (out.cpu() - out_w).abs().max()
+    assert (out.cpu()[~masks] == 0).all()
+    assert_grad_close(c2.grad, coeffs.grad, "v_coeffs", 1e-4)
+    if deg > 0:
+        assert_grad_close(d2.grad, dirs.grad, "v_dirs")
+    else:
+        assert d2.grad.abs().max().item() < 1e-6
+    # no mask at all
+    out_nm = S.spherical_harmonics(deg, d2.detach(), c2.detach())
+    assert torch.allclose(out_nm.cpu(), G.spherical_harmonics(deg, dirs.detach(), coeffs.detach()), atol=2e-5)
+
+
+def test_sh_golden_from_reference(S, dev):
+    """same fixture the CPU suite uses: values produced by the reference's own sh_utils.eval_sh"""
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "sh_eval.npz"))
+    dirs = torch.from_numpy(z["dirs"]).to(dev)
+    coeffs = torch.from_numpy(z["coeffs"]).to(dev)
+    for deg in range(5):
+        got = S.spherical_harmonics(deg, dirs, coeffs, None)
+        want = torch.from_numpy(z[f"colors_deg{deg}"])
+        assert torch.allclose(got.cpu(), want, atol=3e-5, rtol=1e-5), deg
+
+
+# ------------------------------------------------------------------------------ compositing
+def _raster_inputs(n, W, H, seed, scale_mean=0.08, sh_degree=3):
+    s = make_gaussians(n, seed=seed, scale_mean=scale_mean, sh_degree=sh_degree)
+    V, K = make_camera(W, H)
+    rc, ra, aux = G.render_reference_sequence(s["means"], s["quats"], s["scales"], s["opacities"], s["shs"], V, K,
+                                              W, H, sh_degree, return_aux=True)
+    return s, V, K, rc, ra, aux
+
+
+@pytest.mark.parametrize("n,W,H,scale", [(20000, 640, 400, 0.08), (3000, 333, 211, 0.5), (200, 48, 32, 1.0)])
+def test_rasterize_forward(S, dev, n, W, H, scale):
+    s, V, K, rc_w, ra_w, aux = _raster_inputs(n, W, H, seed=n, scale_mean=scale)
+    a = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in aux.items()}
+    rc, ra = S.rasterize_to_pixels(a["means2d"], a["conics"], a["colors"], a["opacities"], W, H, 16,
+                                   a["isect_offsets"], a["flatten_ids"], backgrounds=None, packed=False, absgrad=True)
+    assert rc.shape == (1, H, W, 4) and ra.shape == (1, H, W, 1)
+    assert_image_close(rc[..., :3], rc_w[..., :3], "rgb")
+    assert_image_close(ra, ra_w, "alpha")
+    dscale = float(aux["depths"].max())
+    assert_image_close(rc[..., 3], rc_w[..., 3], "depth-weighted", scale=max(1.0, dscale))
+    assert float(ra.max()) > 0.3
+    # backgrounds
+    bg = torch.tensor([[0.2, 0.4, 0.6, 0.0]])
+    rcb, _ = S.rasterize_to_pixels(a["means2d"], a["conics"], a["colors"], a["opacities"], W, H, 16,
+                                   a["isect_offsets"], a["flatten_ids"], backgrounds=bg.to(dev))
+    want = rc_w + bg[:, None, None, :] * (1 - ra_w)
+    assert_image_close(rcb[..., :3], want[..., :3], "rgb+bg")
+
+
+@pytest.mark.parametrize("CH", [1, 3, 5])
+def test_rasterize_channel_counts(S, dev, CH):
+    s, V, K, rc_w, ra_w, aux = _raster_inputs(2500, 200, 120, seed=9, scale_mean=0.4)
+    g = torch.Generator().manual_seed(CH)
+    cols = torch.rand(1, 2500, CH, generator=g)
+    want, wa = G.rasterize_to_pixels(aux["means2d"], aux["conics"], cols, aux["opacities"], 200, 120, 16,
+                                     aux["isect_offsets"], aux["flatten_ids"])
+    got, ga = S.rasterize_to_pixels(aux["means2d"].to(dev), aux["conics"].to(dev), cols.to(dev),
+                                    aux["opacities"].to(dev), 200, 120, 16, aux["isect_offsets"].to(dev),
+                                    aux["flatten_ids"].to(dev))
+    assert_image_close(got, want, f"CH={CH}")
+    assert_image_close(ga, wa, "alpha")
+
+
+@pytest.mark.parametrize("n,W,H,scale,bg", [(6000, 320, 200, 0.25, False), (800, 100, 75, 0.8, True)])
+def test_rasterize_backward(S, dev, n, W, H, scale, bg):
+    s, V, K, _, _, aux = _raster_inputs(n, W, H, seed=n + 1, scale_mean=scale)
+    g = torch.Generator().manual_seed(0)
+    v_rc = torch.randn(1, H, W, 4, generator=g)
+    v_ra = torch.randn(1, H, W, 1, generator=g)
+    bgt = torch.tensor([[0.3, 0.1, 0.7, 0.5]]) if bg else None
+    names = ("means2d", "conics", "colors", "opacities")
+    leaves = [aux[k].detach().clone().requires_grad_(True) for k in names]
+    rc, ra = G.rasterize_to_pixels(*leaves, W, H, 16, aux["isect_offsets"], aux["flatten_ids"], backgrounds=bgt)
+    ((rc * v_rc).sum() + (ra * v_ra).sum()).backward()
+    cl = [aux[k].detach().to(dev).requires_grad_(True) for k in names]
+    rc2, ra2 = S.rasterize_to_pixels(*cl, W, H, 16, aux["isect_offsets"].to(dev), aux["flatten_ids"].to(dev),
+                                     backgrounds=None if bgt is None else bgt.to(dev), absgrad=True)
+    ((rc2 * v_rc.to(dev)).sum() + (ra2 * v_ra.to(dev)).sum()).backward()
+    for nm, a, b in zip(names, cl, leaves):
+        assert_grad_close(a.grad, b.grad, f"v_{nm}")
+    ag = cl[0].absgrad
+    assert ag.shape == (1, n, 2) and (ag >= 0).all()
+    assert (ag.cpu() + 1e-6 >= cl[0].grad.abs().cpu() * (1 - 1e-4)).all(), "absgrad >= |grad|"
+
+
+def test_absgrad_matches_per_pixel_sum(S, dev):
+    """absgrad := sum over pixels of |d L_pixel / d means2d|, checked by per-pixel autograd."""
+    n, W, H = 40, 16, 16
+    s, V, K, _, _, aux = _raster_inputs(n, W, H, seed=77, scale_mean=2.0, sh_degree=1)
+    g = torch.Generator().manual_seed(1)
+    v_rc = torch.randn(1, H, W, 4, generator=g)
+    v_ra = torch.randn(1, H, W, 1, generator=g)
+    m2 = aux["means2d"].detach().clone().requires_grad_(True)
+    rc, ra = G.rasterize_to_pixels(m2, aux["conics"], aux["colors"], aux["opacities"], W, H, 16,
+                                   aux["isect_offsets"], aux["flatten_ids"])
+    per_pix = (rc * v_rc).sum(-1) + (ra * v_ra).sum(-1)  # [1,H,W]
+    want = torch.zeros(1, n, 2)
+    for i in range(H):
+        for j in range(W):
+            (gr,) = torch.autograd.grad(per_pix[0, i, j], m2, retain_graph=True)
+            want += gr.abs()
+    cl = aux["means2d"].detach().to(dev).requires_grad_(True)
+    rc2, ra2 = S.rasterize_to_pixels(cl, aux["conics"].to(dev), aux["colors"].to(dev), aux["opacities"].to(dev), W,
+                                     H, 16, aux["isect_offsets"].to(dev), aux["flatten_ids"].to(dev), absgrad=True)
+    ((rc2 * v_rc.to(dev)).sum() + (ra2 * v_ra.to(dev)).sum()).backward()
+    assert want.abs().max() > 0
+    assert_grad_close(cl.absgrad, want, "absgrad")
+
+
+# ------------------------------------------------------------------------------ whole pipeline
+def _pipeline_gpu(S, dev, s, V, K, W, H, deg, train=True):
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    c = {k: v.to(dev) for k, v in s.items()}
+    for k in c:
+        c[k].requires_grad_(train)
+    cam_center = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
+    out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None],
+                               V[None].to(dev), K[None].to(dev), cam_center, W, H, deg, train=train)
+    return c, out
+
+
+def test_full_sequence_cfg1_forward_and_backward(S, dev):
+    """BASELINE.json configs[0]: 100k Gaussians, SH deg 3, one 960x640 camera, fwd+bwd."""
+    n, W, H, deg = 100000, 960, 640, 3
+    s = make_gaussians(n, sh_degree=deg, seed=0)
+    V, K = make_camera(W, H)
+    leaves = {k: v.clone().requires_grad_(True) for k, v in s.items()}
+    rc_w, ra_w, aux_w = G.render_reference_sequence(leaves["means"], leaves["quats"], leaves["scales"],
+                                                    leaves["opacities"], leaves["shs"], V, K, W, H, deg,
+                                                    return_aux=True)
+    g = torch.Generator().manual_seed(0)
+    v_rc = torch.randn(1, H, W, 4, generator=g)
+    v_ra = torch.randn(1, H, W, 1, generator=g)
+    v_rc[..., 3] *= 0.02  # depth channel is O(50): keep its share of the loss comparable
+    ((rc_w * v_rc).sum() + (ra_w * v_ra).sum()).backward()
+
+    c, out = _pipeline_gpu(S, dev, s, V, K, W, H, deg)
+    aux = out["aux"]
+    for k in ("radii", "tiles_per_gauss", "isect_ids", "flatten_ids", "isect_offsets"):
+        assert torch.equal(aux[k].cpu(), aux_w[k]), f"{k} not bit-exact"
+    assert_image_close(out["render_colors"][..., :3], rc_w[..., :3].detach(), "rgb")
+    assert_image_close(out["render_alphas"], ra_w.detach(), "alpha")
+    assert_image_close(out["render_colors"][..., 3], rc_w[..., 3].detach(), "depth", scale=100.0)
+    ((out["render_colors"] * v_rc.to(dev)).sum() + (out["render_alphas"] * v_ra.to(dev)).sum()).backward()
+    for k in ("means", "quats", "scales", "opacities", "shs"):
+        assert_grad_close(c[k].grad, torch.nan_to_num(leaves[k].grad), f"v_{k}")
+    vp = out["viewspace_points"]
+    assert vp.grad is not None and vp.absgrad.shape == vp.shape      # retain_grad + absgrad side effect
+    assert out["rgb"].shape == (3, H, W) and out["acc"].shape == (1, H, W) and out["depth"].shape == (1, H, W)
+    assert out["visibility_filter"].dtype == torch.bool and out["radii"].dtype == torch.float32
+
+
+def test_rasterization_entry_matches_sequence(S, dev):
+    n, W, H = 20000, 640, 384
+    s = make_gaussians(n, seed=4)
+    V, K = make_camera(W, H)
+    c, out = _pipeline_gpu(S, dev, s, V, K, W, H, 3, train=False)
+    rc, ra, meta = S.rasterization(c["means"], c["quats"], c["scales"], c["opacities"], c["shs"], V[None].to(dev),
+                                   K[None].to(dev), W, H, near_plane=0.001, far_plane=1000.0, sh_degree=3,
+                                   render_mode="RGB+ED", rasterize_mode="antialiased", absgrad=True, packed=False)
+    assert torch.equal(meta["isect_ids"], out["aux"]["isect_ids"])
+    assert torch.allclose(rc[..., :3], out["render_colors"][..., :3], atol=1e-5)
+    assert torch.allclose(ra, out["render_alphas"], atol=1e-6)
+    assert torch.allclose(rc[0, ..., 3], out["depth"][0], atol=1e-4)
+
+
+# ------------------------------------------------------------------------------ size-independent properties
+def test_cfg2_scale_properties(S, dev):
+    """BASELINE.json configs[1] shape (2M Gaussians, 1920x1280): structural invariants +
+    linearity in colour + determinism of the forward pass."""
+    n, W, H = 2_000_000, 1920, 1280
+    s = make_gaussians(n, seed=0)
+    V, K = make_camera(W, H)
+    c, out = _pipeline_gpu(S, dev, s, V, K, W, H, 3, train=False)
+    aux = out["aux"]
+    ids, flat, off, tpg = aux["isect_ids"], aux["flatten_ids"], aux["isect_offsets"], aux["tiles_per_gauss"]
+    I = ids.numel()
+    assert I == int(tpg.sum()) and I > 1_000_000
+    assert bool((ids[1:] >= ids[:-1]).all()), "keys sorted"
+    tile = (ids >> 32)
+    offs = torch.cat([off.reshape(-1).long(), torch.tensor([I], device=dev)])
+    assert bool((offs[1:] >= offs[:-1]).all())
+    counts = torch.bincount(tile, minlength=off.numel())
+    assert torch.equal(counts, offs[1:] - offs[:-1]), "offsets == per-tile histogram"
+    # stable tie-break: equal keys keep ascending flatten id
+    same = ids[1:] == ids[:-1]
+    assert bool((flat[1:][same] > flat[:-1][same]).all())
+    # depth bits of every key equal the depth of its Gaussian
+    assert torch.equal((ids & 0xFFFFFFFF).to(torch.int32).view(torch.float32), aux["depths"][0][flat.long()])
+    # checksum of the multiset of values survives the sort
+    assert int(flat.long().sum()) == int((tpg[0].long() * torch.arange(n, device=dev)).sum())
+    ra = out["render_alphas"]
+    assert float(ra.min()) >= 0 and float(ra.max()) <= 1.0
+    a = aux
+    rc1, ra1 = S.rasterize_to_pixels(a["means2d"], a["conics"], a["colors"], a["opacities"], W, H, 16,
+                                     a["isect_offsets"], a["flatten_ids"])
+    rc2, ra2 = S.rasterize_to_pixels(a["means2d"], a["conics"], a["colors"] * 2.0, a["opacities"], W, H, 16,
+                                     a["isect_offsets"], a["flatten_ids"])
+    assert torch.equal(rc1, out["render_colors"]) and torch.equal(ra1, ra), "forward is deterministic"
+    assert torch.equal(rc2, rc1 * 2.0) and torch.equal(ra2, ra1), "compositing is linear in colour"
+
+
+# ------------------------------------------------------------------------------ KNN
+@pytest.mark.parametrize("P", [1, 2, 3, 4, 5, 31, 32, 33, 1000, 20000])
+def test_knn_vs_bruteforce(S, dev, P):
+    g = torch.Generator().manual_seed(P)
+    pts = torch.randn(P, 3, generator=g) * torch.tensor([20.0, 3.0, 40.0])
+    if P > 100:
+        pts[50] = pts[3]
+        pts[51] = pts[3]
+    got = S.distCUDA2(pts.to(dev)).cpu()
+    want = KO.dist_knn3_bruteforce(pts)
+    assert got.shape == (P,) and got.dtype == torch.float32
+    if P < 4:
+        assert (got > 1e37).all() and (want > 1e37).all()
+    else:
+        assert torch.allclose(got, want, rtol=2e-6, atol=1e-12), (got - want).abs().max()
+
+
+def test_knn_large_vs_kdtree(S, dev):
+    xyz, _ = make_lidar_points(300000, seed=2)
+    xyz[:1000] = xyz[1000:2000] * 1.0  # block of exact duplicates
+    got = S.distCUDA2(xyz.to(dev)).cpu()
+    want = KO.dist_knn3_kdtree(xyz)
+    assert torch.allclose(got, want, rtol=1e-4, atol=1e-9), (got - want).abs().max()
+
+
+def test_knn_vs_compiled_reference(S, dev):
+    """oracle/_ref/libsimpleknn_ref.so = the reference's own simple_knn.cu compiled for sm_100a
+    (oracle/build_ref.sh).  Skipped when it was not built."""
+    import ctypes
+    path = os.path.join(os.path.dirname(os.path.dirname(__file__)), "oracle", "_ref", "libsimpleknn_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref not built")
+    ref = ctypes.CDLL(path)
+    ref.ref_knn.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    xyz, _ = make_lidar_points(200000, seed=5)
+    p = xyz.to(dev).contiguous()
+    want = torch.zeros(p.shape[0], device=dev)
+    torch.cuda.synchronize()
+    ref.ref_knn(p.shape[0], p.data_ptr(), want.data_ptr())
+    torch.cuda.synchronize()
+    got = S.distCUDA2(p)
+    assert torch.allclose(got, want, rtol=1e-6, atol=0), (got - want).abs().max()
+    exact = (got == want).float().mean().item()
+    assert exact > 0.99, f"only {exact:.4f} bit-identical to the reference kernel"
+
+
+# ------------------------------------------------------------------------------ LiDAR point splat
+def test_point_rasterizer_max_hit(S, dev):
+    N, W, H = 20000, 256, 144
+    xyz, rgb = make_lidar_points(N, seed=3)
+    V, K = make_camera(W, H)
+    fx = float(K[0, 0])
+    z = (xyz @ V[:3, :3].T + V[:3, 3])[:, 2:3]
+    radius = 0.01 * z / fx * 0.5 * min(H, W) * 4.0  # a few px so that splats overlap
+    st = S.PointRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=W / (2 * fx), tanfovy=H / (2 * fx), bg=torch.zeros(3),
+        scale_modifier=1.0, viewmatrix=V.T.contiguous(), projmatrix=torch.eye(4), sh_degree=0, max_hit=10,
+        campos=torch.zeros(3), prefiltered=False, debug=False)
+    img, depth, alpha, radii = S.PointRasterizer(st)(xyz.to(dev), torch.zeros_like(xyz).to(dev), rgb.to(dev),
+                                                     torch.ones(N, 1, device=dev), radius.to(dev))
+    assert img.shape == (3, H, W) and depth.shape == (1, H, W) and alpha.shape == (1, H, W) and radii.shape == (N,)
+    # oracle with the same restated semantics
+    quats = torch.zeros(N, 4); quats[:, 0] = 1
+    r, m2, dp, cn, _ = G.fully_fused_projection(xyz, None, quats, radius.expand(N, 3).contiguous(), V[None], K[None],
+                                                W, H, near_plane=1.0, far_plane=100.0)
+    assert torch.equal(radii.cpu(), r[0])
+    tw, th = math.ceil(W / 16), math.ceil(H / 16)
+    _, ids, flat = G.isect_tiles(m2, r, dp, 16, tw, th)
+    off = G.isect_offset_encode(ids, 1, tw, th)
+    cols = torch.cat([rgb[None], dp[..., None]], -1)
+    want, wa = G.rasterize_to_pixels(m2, cn, cols, torch.ones(1, N), W, H, 16, off, flat, max_hit=10)
+    assert_image_close(img.permute(1, 2, 0), want[0, ..., :3], "lidar rgb")
+    assert_image_close(alpha[0], wa[0, ..., 0], "lidar alpha")
+    nolimit, _ = G.rasterize_to_pixels(m2, cn, cols, torch.ones(1, N), W, H, 16, off, flat)
+    assert (nolimit - want).abs().max() > 1e-3, "max_hit must matter in this scene"
