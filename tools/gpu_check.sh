@@ -1,0 +1,21 @@
+#!/bin/bash
+# One gpurun call: GPU parity tests, a short bench, the ncu launch list and one --set full
+# capture of the compositing + sort kernels.  Usage (from the repo root):
+#   gpurun --timeout 1500 -- 'bash tools/gpu_check.sh [tag]'
+TAG=${1:-r01}
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1
+echo "pytest exit $?" | tee -a gpurun_out/${TAG}_pytest.log
+tail -3 gpurun_out/${TAG}_pytest.log
+python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
+echo "bench exit $?"; tail -c 600 gpurun_out/${TAG}_bench.json
+python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_plain.log 2>&1 &&
+ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
+    --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline \
+    > gpurun_out/${TAG}_ncu_launches.log 2>&1
+echo "ncu launches exit $?"
+ncu --set full --clock-control none --import-source on \
+    -k regex:'rasterize_|onesweep' -s 40 -c 8 -o gpurun_out/${TAG}_prof -f \
+    python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
+echo "ncu full exit $?"
+ls -la gpurun_out | tail -20
