@@ -70,26 +70,42 @@ int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const float* coef
               void* stream);
 
 /* ---- A3/A4: tile intersection ---------------------------------------------------------- */
-int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, int tile_size,
-                   int tile_width, int tile_height, int32_t* tiles_per_gauss, void* stream);
+/* tiles_per_gauss[i] = size of the tile AABB of entry i (0 when radii[i] == 0).  Optional
+ * (both or neither; need depths): depth_keys[i] = raw depth bits (0xffffffff when the entry
+ * emits nothing), order_init[i] = i — the input of the depth pre-sort below. */
+int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, const float* depths,
+                   int tile_size, int tile_width, int tile_height, int32_t* tiles_per_gauss,
+                   uint32_t* depth_keys, uint32_t* order_init, void* stream);
+/* counts_in_order[j] = tiles_per_gauss[order[j]] */
+int sc_isect_gather_counts(int64_t CN, const uint32_t* order, const int32_t* tiles_per_gauss,
+                           int32_t* counts_in_order, void* stream);
 /* out[i] = sum_{j<i} in[j] (int64 accumulate); total (nullable) receives the grand total.
  * workspace >= sc_scan_workspace_bytes(n). */
 int64_t sc_scan_workspace_bytes(int64_t n);
 int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out, int64_t* total,
                           void* workspace, int64_t workspace_bytes, void* stream);
-/* emits, for camera-major then Gaussian order, the row-major tile list of each Gaussian:
- * isect_ids = cam << (32+tile_n_bits) | tile << 32 | bits(depth); flatten_ids = cam*N + g. */
+/* emits the row-major tile list of entry order[j] at cum_tiles[j] for j = 0..C*N-1
+ * (order == NULL: identity, i.e. camera-major then Gaussian order, gsplat's unsorted output):
+ * isect_ids = cam << (32+tile_n_bits) | tile << 32 | bits(depth); flatten_ids = cam*N + g.
+ * With `order` = the stable depth order of the entries, a stable sort of the emitted pairs on
+ * the (camera,tile) bits [32, 32+tile_n_bits+cam_bits) ALONE yields exactly the list a stable
+ * sort on the full key yields (ties fall back to entry index in both) — 2 sort passes over
+ * the intersection list instead of 6. */
 int sc_isect_emit(int64_t N, int C, const float* means2d, const int32_t* radii, const float* depths,
-                  const int64_t* cum_tiles, int tile_size, int tile_width, int tile_height,
-                  int tile_n_bits, int64_t n_isects, int64_t* isect_ids, int32_t* flatten_ids,
-                  void* stream);
-/* stable LSD radix sort of (u64 key, u32 value) pairs on key bits [0, end_bit), n < 2^30.
- * Both buffer pairs are ping-pong storage; RETURNS 0 if the sorted pairs ended in
- * keys_out/vals_out, 1 if they ended in keys_in/vals_in (even pass count), <0 on error. */
+                  const int64_t* cum_tiles, const uint32_t* order, int tile_size, int tile_width,
+                  int tile_height, int tile_n_bits, int64_t n_isects, int64_t* isect_ids,
+                  int32_t* flatten_ids, void* stream);
+/* stable LSD radix sort of (key, u32 value) pairs on key bits [begin_bit, end_bit), n < 2^30;
+ * u64-key and u32-key variants.  Both buffer pairs are ping-pong storage; RETURNS 0 if the
+ * sorted pairs ended in keys_out/vals_out, 1 if they ended in keys_in/vals_in (even pass
+ * count), <0 on error.  workspace >= sc_sort_workspace_bytes(n). */
 int64_t sc_sort_workspace_bytes(int64_t n);
 int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
-                        uint32_t* vals_out, int end_bit, void* workspace, int64_t workspace_bytes,
-                        void* stream);
+                        uint32_t* vals_out, int begin_bit, int end_bit, void* workspace,
+                        int64_t workspace_bytes, void* stream);
+int sc_radix_sort_pairs_u32(int64_t n, uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_out,
+                            uint32_t* vals_out, int begin_bit, int end_bit, void* workspace,
+                            int64_t workspace_bytes, void* stream);
 int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, int tile_width,
                            int tile_height, int tile_n_bits, int32_t* offsets, void* stream);
 

@@ -24,13 +24,15 @@ SIGNATURES = {
                                  _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_sh_fwd": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_sh_bwd": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
-    "sc_isect_count": (_i32, [_i64, _ptr, _ptr, _i32, _i32, _i32, _ptr, _ptr]),
+    "sc_isect_count": (_i32, [_i64, _ptr, _ptr, _ptr, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr]),
+    "sc_isect_gather_counts": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr]),
     "sc_scan_workspace_bytes": (_i64, [_i64]),
     "sc_exclusive_scan_i32": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
-    "sc_isect_emit": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i64, _ptr, _ptr,
-                             _ptr]),
+    "sc_isect_emit": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i64, _ptr,
+                             _ptr, _ptr]),
     "sc_sort_workspace_bytes": (_i64, [_i64]),
-    "sc_radix_sort_pairs": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _i64, _ptr]),
+    "sc_radix_sort_pairs": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _i64, _ptr]),
+    "sc_radix_sort_pairs_u32": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _i64, _ptr]),
     "sc_isect_offset_encode": (_i32, [_i64, _ptr, _i32, _i32, _i32, _i32, _ptr, _ptr]),
     "sc_rasterize_fwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                 _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),

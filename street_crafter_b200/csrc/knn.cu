@@ -307,7 +307,7 @@ extern "C" int sc_knn3_mean_dist2(int64_t P, const float* points, float* mean_di
     SC_CHECK_LAUNCH("knn_bounds_kernel");
     knn_morton_kernel<<<(unsigned)sc_div_up(P, 256), 256, 0, st>>>(P, points, bounds, keys_a, vals_a);
     SC_CHECK_LAUNCH("knn_morton_kernel");
-    const int where = sc_radix_sort_pairs(P, keys_a, vals_a, keys_b, vals_b, 30, ws + pl.off_sort_ws,
+    const int where = sc_radix_sort_pairs(P, keys_a, vals_a, keys_b, vals_b, 0, 30, ws + pl.off_sort_ws,
                                           pl.sort_ws_bytes, stream);
     if (where < 0) return where;
     const uint32_t* order = where == 0 ? vals_b : vals_a;

@@ -209,7 +209,9 @@ __device__ __forceinline__ TileBox tile_box(float mx, float my, int32_t radius, 
 
 __global__ void __launch_bounds__(256)
 isect_count_kernel(int64_t CN, const float2* __restrict__ means2d, const int32_t* __restrict__ radii,
-                   float ts, int tw, int th, int32_t* __restrict__ tiles_per_gauss) {
+                   const float* __restrict__ depths, float ts, int tw, int th,
+                   int32_t* __restrict__ tiles_per_gauss, uint32_t* __restrict__ depth_keys,
+                   uint32_t* __restrict__ order_init) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= CN) return;
     const int32_t r = __ldg(radii + i);
@@ -220,76 +222,99 @@ isect_count_kernel(int64_t CN, const float2* __restrict__ means2d, const int32_t
         n = (b.x1 - b.x0) * (b.y1 - b.y0);
     }
     tiles_per_gauss[i] = n;
+    if (depth_keys) {
+        // entries that emit nothing sort last; the others by the raw depth bits (the low 32 key bits)
+        depth_keys[i] = n > 0 ? __float_as_uint(__ldg(depths + i)) : 0xffffffffu;
+        order_init[i] = (uint32_t)i;
+    }
+}
+
+// counts in depth order: out[j] = tiles_per_gauss[order[j]]
+__global__ void __launch_bounds__(256)
+isect_gather_counts_kernel(int64_t CN, const uint32_t* __restrict__ order,
+                           const int32_t* __restrict__ tiles_per_gauss, int32_t* __restrict__ out) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= CN) return;
+    out[j] = __ldg(tiles_per_gauss + __ldg(order + j));
 }
 
 // ------------------------------------------------------------------ emit (A3 pass 2)
-// One warp owns 32 consecutive (camera, Gaussian) entries and writes their concatenated tile
-// lists with a load-balanced search, so every store instruction covers 32 CONSECUTIVE output
-// slots (coalesced 256 B of keys + 128 B of values) regardless of how skewed the per-Gaussian
-// tile counts are (a near-camera Gaussian can cover the whole screen).
-__global__ void __launch_bounds__(256)
+// Output-centric and load-balanced: a CTA owns EMIT_OUT CONSECUTIVE output slots, whatever the
+// per-entry tile counts are (in depth order the near, screen-filling Gaussians are neighbours:
+// an entry-centric split would leave a few warps with all the work).  The CTA finds the first
+// entry that owns one of its slots by binary search in the exclusive scan, stages entries 256
+// at a time in shared memory (tile box, depth bits, id), and every thread resolves its slots'
+// owners with a shared-memory binary search.  All stores are consecutive 8 B + 4 B per lane.
+constexpr int EMIT_THREADS = 256;
+constexpr int EMIT_OUT = 2048;
+
+__global__ void __launch_bounds__(EMIT_THREADS)
 isect_emit_kernel(int64_t N, int64_t CN, const float2* __restrict__ means2d,
                   const int32_t* __restrict__ radii, const float* __restrict__ depths,
-                  const int64_t* __restrict__ cum_tiles, float ts, int tw, int th, int tile_n_bits,
-                  int64_t n_isects, int64_t* __restrict__ isect_ids, int32_t* __restrict__ flatten_ids) {
-    const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t i = warp * 32 + lane;
-    int x0 = 0, w = 1, y0 = 0, cnt = 0;
-    uint32_t dbits = 0;
-    int64_t start = 0;
-    if (i < CN) {
-        const int32_t r = __ldg(radii + i);
-        start = __ldg(cum_tiles + i);
-        if (r > 0) {
-            const float2 m = __ldg(means2d + i);
-            const TileBox b = tile_box(m.x, m.y, r, ts, tw, th);
-            x0 = b.x0; y0 = b.y0;
-            w = max(b.x1 - b.x0, 1);
-            cnt = (b.x1 - b.x0) * (b.y1 - b.y0);
-            dbits = __float_as_uint(__ldg(depths + i));
+                  const int64_t* __restrict__ cum_tiles /*[CN+1]*/, const uint32_t* __restrict__ order,
+                  float ts, int tw, int th, int tile_n_bits, int64_t n_isects,
+                  int64_t* __restrict__ isect_ids, int32_t* __restrict__ flatten_ids) {
+    __shared__ int s_start[EMIT_THREADS];   // first output slot of the entry, relative to p0
+    __shared__ int s_x0[EMIT_THREADS], s_y0[EMIT_THREADS], s_w[EMIT_THREADS];
+    __shared__ uint32_t s_dbits[EMIT_THREADS];
+    __shared__ int s_id[EMIT_THREADS], s_camhi[EMIT_THREADS];
+    __shared__ int64_t s_j0;
+    const int tid = threadIdx.x;
+    const int64_t p0 = (int64_t)blockIdx.x * EMIT_OUT;
+    const int64_t p1 = min(p0 + EMIT_OUT, n_isects);
+    if (tid == 0) {
+        // largest j in [0, CN) with cum[j] <= p0 (the last of equal starts owns the slot)
+        int64_t lo = 0, hi = CN;  // invariant: cum[lo] <= p0, cum[hi] > p0 (cum[CN] = n_isects > p0)
+        while (hi - lo > 1) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (__ldg(cum_tiles + mid) <= p0) lo = mid; else hi = mid;
         }
+        s_j0 = lo;
     }
-    // exclusive prefix of counts inside the warp
-    int incl = cnt;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        const int v = __shfl_up_sync(full, incl, d);
-        if (lane >= d) incl += v;
-    }
-    const int excl = incl - cnt;
-    const int total = __shfl_sync(full, incl, 31);
-    const int64_t warp_start = __shfl_sync(full, start, 0);
-    const int64_t cam_of_i = (i < CN) ? i / N : 0;
-    for (int basej = 0; basej < total; basej += 32) {
-        const int j = basej + lane;
-        int lo = 0;
-#pragma unroll
-        for (int step = 16; step >= 1; step >>= 1) {
-            const int cand = lo + step;
-            const int pv = __shfl_sync(full, excl, cand & 31);
-            if (cand < 32 && pv <= j) lo = cand;
-        }
-        // zero-count lanes share excl with their successor; the search lands on the LAST lane
-        // whose excl <= j, which is the one that actually owns slot j (its count > 0).
-        const int o_excl = __shfl_sync(full, excl, lo);
-        const int o_x0 = __shfl_sync(full, x0, lo);
-        const int o_y0 = __shfl_sync(full, y0, lo);
-        const int o_w = __shfl_sync(full, w, lo);
-        const uint32_t o_d = __shfl_sync(full, dbits, lo);
-        const int64_t o_cam = __shfl_sync(full, cam_of_i, lo);
-        if (j < total) {
-            const int k = j - o_excl;
-            const int ty = o_y0 + k / o_w;
-            const int tx = o_x0 + k % o_w;
-            const int64_t tile = (int64_t)ty * tw + tx;
-            const int64_t key = (o_cam << (32 + tile_n_bits)) | (tile << 32) | (int64_t)o_d;
-            const int64_t pos = warp_start + j;
-            if (pos < n_isects) {
-                isect_ids[pos] = key;
-                flatten_ids[pos] = (int32_t)(warp * 32 + lo);
+    __syncthreads();
+    for (int64_t je = s_j0; je < CN; je += EMIT_THREADS) {
+        const int64_t chunk_first = __ldg(cum_tiles + je);
+        if (chunk_first >= p1) break;
+        const int64_t jn = min(je + EMIT_THREADS, CN);
+        const int64_t chunk_end = __ldg(cum_tiles + jn);  // first slot owned by a later chunk
+        __syncthreads();                                   // previous chunk's readers are done
+        {
+            const int64_t j = je + tid;
+            int start = 0x7fffffff, x0 = 0, y0 = 0, w = 1, id = 0, camhi = 0;
+            uint32_t dbits = 0;
+            if (j < jn) {
+                const int64_t st = __ldg(cum_tiles + j);
+                start = (int)max(min(st - p0, (int64_t)EMIT_OUT), (int64_t)-0x40000000);
+                if (st < p1 && __ldg(cum_tiles + j + 1) > st) {
+                    const int64_t i = order ? (int64_t)__ldg(order + j) : j;
+                    const float2 m = __ldg(means2d + i);
+                    const TileBox b = tile_box(m.x, m.y, __ldg(radii + i), ts, tw, th);
+                    x0 = b.x0; y0 = b.y0;
+                    w = max(b.x1 - b.x0, 1);
+                    dbits = __float_as_uint(__ldg(depths + i));
+                    id = (int)i;
+                    camhi = (int)(i / N) << tile_n_bits;
+                }
             }
+            s_start[tid] = start; s_x0[tid] = x0; s_y0[tid] = y0; s_w[tid] = w;
+            s_dbits[tid] = dbits; s_id[tid] = id; s_camhi[tid] = camhi;
+        }
+        __syncthreads();
+        const int qlo = (int)(max(p0, chunk_first) - p0);
+        const int qhi = (int)(min(p1, chunk_end) - p0);
+        for (int q = qlo + tid; q < qhi; q += EMIT_THREADS) {
+            // last t with s_start[t] <= q (padding entries hold INT_MAX)
+            int t = 0;
+#pragma unroll
+            for (int step = EMIT_THREADS / 2; step >= 1; step >>= 1)
+                if (s_start[t + step] <= q) t += step;
+            const int k = q - s_start[t];
+            const int w = s_w[t];
+            const int ty = s_y0[t] + k / w;
+            const int tx = s_x0[t] + k % w;
+            const int64_t hi32 = (int64_t)(s_camhi[t] | (ty * tw + tx));
+            isect_ids[p0 + q] = (hi32 << 32) | (int64_t)s_dbits[t];
+            flatten_ids[p0 + q] = s_id[t];
         }
     }
 }
@@ -339,30 +364,44 @@ extern "C" int sc_projection_fwd(int64_t N, int C, const float* means, const flo
     return SC_OK;
 }
 
-extern "C" int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, int tile_size,
-                              int tile_width, int tile_height, int32_t* tiles_per_gauss, void* stream) {
-    SC_CHECK_ARG(CN >= 0 && tile_size > 0 && tile_width > 0 && tile_height > 0, "sizes");
+extern "C" int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, const float* depths,
+                              int tile_size, int tile_width, int tile_height, int32_t* tiles_per_gauss,
+                              uint32_t* depth_keys, uint32_t* order_init, void* stream) {
+    SC_CHECK_ARG(CN >= 0 && CN < (1ll << 31) && tile_size > 0 && tile_width > 0 && tile_height > 0, "sizes");
     if (CN == 0) return SC_OK;
     SC_CHECK_ARG(means2d && radii && tiles_per_gauss, "null pointer");
+    SC_CHECK_ARG((depth_keys == nullptr) == (order_init == nullptr), "depth_keys and order_init go together");
+    SC_CHECK_ARG(depth_keys == nullptr || depths != nullptr, "depths needed for depth_keys");
     isect_count_kernel<<<(unsigned)sc_div_up(CN, 256), 256, 0, (cudaStream_t)stream>>>(
-        CN, reinterpret_cast<const float2*>(means2d), radii, (float)tile_size, tile_width, tile_height,
-        tiles_per_gauss);
+        CN, reinterpret_cast<const float2*>(means2d), radii, depths, (float)tile_size, tile_width, tile_height,
+        tiles_per_gauss, depth_keys, order_init);
     SC_CHECK_LAUNCH("isect_count_kernel");
     return SC_OK;
 }
 
+extern "C" int sc_isect_gather_counts(int64_t CN, const uint32_t* order, const int32_t* tiles_per_gauss,
+                                      int32_t* counts_in_order, void* stream) {
+    SC_CHECK_ARG(CN >= 0, "CN");
+    if (CN == 0) return SC_OK;
+    SC_CHECK_ARG(order && tiles_per_gauss && counts_in_order, "null pointer");
+    isect_gather_counts_kernel<<<(unsigned)sc_div_up(CN, 256), 256, 0, (cudaStream_t)stream>>>(
+        CN, order, tiles_per_gauss, counts_in_order);
+    SC_CHECK_LAUNCH("isect_gather_counts_kernel");
+    return SC_OK;
+}
+
 extern "C" int sc_isect_emit(int64_t N, int C, const float* means2d, const int32_t* radii,
-                             const float* depths, const int64_t* cum_tiles, int tile_size, int tile_width,
-                             int tile_height, int tile_n_bits, int64_t n_isects, int64_t* isect_ids,
-                             int32_t* flatten_ids, void* stream) {
+                             const float* depths, const int64_t* cum_tiles, const uint32_t* order,
+                             int tile_size, int tile_width, int tile_height, int tile_n_bits,
+                             int64_t n_isects, int64_t* isect_ids, int32_t* flatten_ids, void* stream) {
     SC_CHECK_ARG(N >= 0 && C >= 1 && n_isects >= 0, "sizes");
     SC_CHECK_ARG(tile_n_bits > 0 && tile_n_bits < 24, "tile_n_bits");
     if (N == 0 || n_isects == 0) return SC_OK;
     SC_CHECK_ARG(means2d && radii && depths && cum_tiles && isect_ids && flatten_ids, "null pointer");
     const int64_t CN = N * C;
-    const int64_t warps = sc_div_up(CN, 32);
-    isect_emit_kernel<<<(unsigned)sc_div_up(warps, 8), 256, 0, (cudaStream_t)stream>>>(
-        N, CN, reinterpret_cast<const float2*>(means2d), radii, depths, cum_tiles, (float)tile_size,
+    SC_CHECK_ARG(CN < (1ll << 31), "C*N must fit int32 (flatten_ids)");
+    isect_emit_kernel<<<(unsigned)sc_div_up(n_isects, EMIT_OUT), EMIT_THREADS, 0, (cudaStream_t)stream>>>(
+        N, CN, reinterpret_cast<const float2*>(means2d), radii, depths, cum_tiles, order, (float)tile_size,
         tile_width, tile_height, tile_n_bits, n_isects, isect_ids, flatten_ids);
     SC_CHECK_LAUNCH("isect_emit_kernel");
     return SC_OK;

@@ -101,13 +101,15 @@ constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_KPT = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_KPT;  // 4096 pairs
 constexpr int MAX_PASSES = 8;
+constexpr int SORT_MIN_BLOCKS = 3;  // caps registers at 85/thread: 3 CTAs (24 warps) per SM
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_INC = 2u << 30;
 constexpr uint32_t FLAG_MASK = 3u << 30;
 constexpr uint32_t VAL_MASK = ~FLAG_MASK;
 
+template <typename KeyT>
 struct SortSmem {
-    uint64_t keys[SORT_TILE];
+    KeyT keys[SORT_TILE];
     uint32_t vals[SORT_TILE];
     uint32_t warp_hist[SORT_WARPS][RADIX];
     uint32_t digit_start[RADIX];   // exclusive start of each digit inside the tile
@@ -116,11 +118,19 @@ struct SortSmem {
     uint32_t tile_id;
 };
 
+// per-pass digit layout: pass p sorts bits [shift[p], shift[p]+nbits[p])
+struct PassPlan {
+    int passes;
+    int shift[MAX_PASSES];
+    int nbits[MAX_PASSES];
+};
+
+template <typename KeyT>
 __global__ void __launch_bounds__(256)
-sort_histogram_kernel(int64_t n, const uint64_t* __restrict__ keys, int passes, int end_bit,
+sort_histogram_kernel(int64_t n, const KeyT* __restrict__ keys, PassPlan pp,
                       uint32_t* __restrict__ hist /*[passes][RADIX]*/) {
     extern __shared__ uint32_t s_hist[];  // [passes][RADIX]
-    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) s_hist[i] = 0;
+    for (int i = threadIdx.x; i < pp.passes * RADIX; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
     // warp-aggregated shared atomics: the keys of one warp share most high digits (same tile,
     // similar depth), so un-aggregated atomics would serialise 32-deep on one bank.
@@ -130,18 +140,16 @@ sort_histogram_kernel(int64_t n, const uint64_t* __restrict__ keys, int passes, 
     const int64_t n_round = (n + 31) & ~(int64_t)31;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         const bool in = i < n;
-        const uint64_t k = in ? __ldg(keys + i) : 0ull;
+        const KeyT k = in ? __ldg(keys + i) : (KeyT)0;
         const unsigned act = __ballot_sync(0xffffffffu, in);
-        for (int p = 0; p < passes; ++p) {
-            const int shift = p * RADIX_BITS;
-            const int nb = min(RADIX_BITS, end_bit - shift);
-            const uint32_t d = (uint32_t)(k >> shift) & ((1u << nb) - 1u);
+        for (int p = 0; p < pp.passes; ++p) {
+            const uint32_t d = (uint32_t)(k >> pp.shift[p]) & ((1u << pp.nbits[p]) - 1u);
             const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu) & act;
             if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p * RADIX + d], (uint32_t)__popc(peers));
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) {
+    for (int i = threadIdx.x; i < pp.passes * RADIX; i += blockDim.x) {
         const uint32_t v = s_hist[i];
         if (v) atomicAdd(&hist[i], v);
     }
@@ -166,14 +174,15 @@ sort_hist_scan_kernel(uint32_t* __restrict__ hist) {
     h[threadIdx.x] = s[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(SORT_THREADS)
-onesweep_pass_kernel(int64_t n, const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
-                     uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int nbits,
+template <typename KeyT>
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MIN_BLOCKS)
+onesweep_pass_kernel(int64_t n, const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                     KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int nbits,
                      const uint32_t* __restrict__ digit_offset /*[RADIX] exclusive*/,
                      volatile uint32_t* __restrict__ lookback /*[tiles][RADIX]*/,
                      uint32_t* __restrict__ ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    SortSmem& sm = *reinterpret_cast<SortSmem*>(smem_raw);
+    SortSmem<KeyT>& sm = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t dmask = (1u << nbits) - 1u;
 
@@ -185,13 +194,13 @@ onesweep_pass_kernel(int64_t n, const uint64_t* __restrict__ keys_in, const uint
     const int n_valid = (int)min((int64_t)SORT_TILE, n - tile_base);
 
     // ---- load keys (warp-striped: item i of lane l = warp_base + i*32 + l)
-    uint64_t key[SORT_KPT];
+    KeyT key[SORT_KPT];
     uint16_t rank[SORT_KPT];
     const int warp_base = w * (32 * SORT_KPT);
 #pragma unroll
     for (int i = 0; i < SORT_KPT; ++i) {
         const int local = warp_base + i * 32 + lane;
-        key[i] = (local < n_valid) ? __ldg(keys_in + tile_base + local) : ~0ull;
+        key[i] = (local < n_valid) ? __ldg(keys_in + tile_base + local) : (KeyT)~(KeyT)0;
     }
     // ---- stable warp-level ranking
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -274,7 +283,7 @@ onesweep_pass_kernel(int64_t n, const uint64_t* __restrict__ keys_in, const uint
     for (int i = 0; i < SORT_KPT; ++i) {
         const int local = i * SORT_THREADS + tid;
         if (local < n_valid) {
-            const uint64_t k = sm.keys[local];
+            const KeyT k = sm.keys[local];
             const uint32_t d = (uint32_t)(k >> shift) & dmask;
             const int64_t g = sm.gbase[d] + local;
             keys_out[g] = k;
@@ -284,20 +293,81 @@ onesweep_pass_kernel(int64_t n, const uint64_t* __restrict__ keys_in, const uint
 }
 
 struct SortPlan {
-    int passes;
+    PassPlan pp;
     int64_t tiles;
     int64_t hist_off, lookback_off, ticket_off, total;
 };
 
-SortPlan make_plan(int64_t n, int end_bit) {
+// passes of <= 8 bits over [begin_bit, end_bit), widths balanced (14 bits -> 7+7, not 8+6)
+SortPlan make_plan(int64_t n, int begin_bit, int end_bit) {
     SortPlan p;
-    p.passes = (end_bit + RADIX_BITS - 1) / RADIX_BITS;
+    const int bits = end_bit - begin_bit;
+    p.pp.passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
+    int shift = begin_bit, left = bits;
+    for (int i = 0; i < MAX_PASSES; ++i) {
+        const int remaining = p.pp.passes - i;
+        const int nb = remaining > 0 ? (left + remaining - 1) / remaining : 0;
+        p.pp.shift[i] = shift;
+        p.pp.nbits[i] = nb;
+        shift += nb;
+        left -= nb;
+    }
     p.tiles = sc_div_up(n, SORT_TILE);
     p.hist_off = 0;
     p.ticket_off = sc_align_up((int64_t)MAX_PASSES * RADIX * 4, 256);
     p.lookback_off = p.ticket_off + 256;
     p.total = p.lookback_off + (int64_t)MAX_PASSES * p.tiles * RADIX * 4;
     return p;
+}
+
+// returns 0 if the sorted pairs are in keys_out/vals_out, 1 if they are in keys_in/vals_in
+// (even number of passes), negative on error.
+template <typename KeyT>
+int radix_sort_pairs(int64_t n, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out, uint32_t* vals_out,
+                     int begin_bit, int end_bit, void* workspace, int64_t workspace_bytes, void* stream) {
+    SC_CHECK_ARG(n >= 0 && n < (1ll << 30), "n (must be < 2^30)");
+    SC_CHECK_ARG(begin_bit >= 0 && end_bit > begin_bit && end_bit <= (int)sizeof(KeyT) * 8, "bit range");
+    if (n == 0) return 0;
+    SC_CHECK_ARG(keys_in && vals_in && keys_out && vals_out && workspace, "null pointer");
+    const SortPlan plan = make_plan(n, begin_bit, end_bit);
+    if (workspace_bytes < plan.total) {
+        sc_set_error("sort workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)plan.total);
+        return SC_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* ws = (unsigned char*)workspace;
+    uint32_t* hist = (uint32_t*)(ws + plan.hist_off);
+    uint32_t* tickets = (uint32_t*)(ws + plan.ticket_off);
+    uint32_t* lookback = (uint32_t*)(ws + plan.lookback_off);
+    const int passes = plan.pp.passes;
+    SC_CUDA(cudaMemsetAsync(ws, 0, (size_t)(plan.lookback_off + (int64_t)passes * plan.tiles * RADIX * 4), st));
+    {
+        const int grid = (int)min(sc_div_up(n, 256 * 8), (int64_t)SC_NUM_SMS * 8);
+        sort_histogram_kernel<KeyT><<<grid, 256, passes * RADIX * 4, st>>>(n, keys_in, plan.pp, hist);
+        SC_CHECK_LAUNCH("sort_histogram_kernel");
+        sort_hist_scan_kernel<<<passes, RADIX, 0, st>>>(hist);
+        SC_CHECK_LAUNCH("sort_hist_scan_kernel");
+    }
+    static bool attr_set = false;  // one flag per KeyT instantiation
+    if (!attr_set) {
+        SC_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(SortSmem<KeyT>)));
+        attr_set = true;
+    }
+    KeyT* kin = keys_in;
+    uint32_t* vin = vals_in;
+    KeyT* kout = keys_out;
+    uint32_t* vout = vals_out;
+    for (int p = 0; p < passes; ++p) {
+        onesweep_pass_kernel<KeyT><<<(unsigned)plan.tiles, SORT_THREADS, sizeof(SortSmem<KeyT>), st>>>(
+            n, kin, vin, kout, vout, plan.pp.shift[p], plan.pp.nbits[p], hist + p * RADIX,
+            lookback + (size_t)p * plan.tiles * RADIX, tickets + p);
+        SC_CHECK_LAUNCH("onesweep_pass_kernel");
+        KeyT* tk = kin; kin = kout; kout = tk;
+        uint32_t* tv = vin; vin = vout; vout = tv;
+    }
+    // after the swap `kin` holds the result
+    return kin == keys_out ? 0 : 1;
 }
 
 }  // namespace
@@ -329,55 +399,18 @@ extern "C" int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out,
     return SC_OK;
 }
 
-extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return make_plan(n, 64).total; }
+extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return make_plan(n, 0, 64).total; }
 
-// returns 0 if the sorted pairs are in keys_out/vals_out, 1 if they are in keys_in/vals_in
-// (even number of passes), negative on error.
 extern "C" int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
-                                   uint32_t* vals_out, int end_bit, void* workspace, int64_t workspace_bytes,
-                                   void* stream) {
-    SC_CHECK_ARG(n >= 0 && n < (1ll << 30), "n (must be < 2^30)");
-    SC_CHECK_ARG(end_bit > 0 && end_bit <= 64, "end_bit");
-    if (n == 0) return 0;
-    SC_CHECK_ARG(keys_in && vals_in && keys_out && vals_out && workspace, "null pointer");
-    const SortPlan plan = make_plan(n, end_bit);
-    if (workspace_bytes < plan.total) {
-        sc_set_error("sort workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)plan.total);
-        return SC_ERR_WORKSPACE;
-    }
-    cudaStream_t st = (cudaStream_t)stream;
-    unsigned char* ws = (unsigned char*)workspace;
-    uint32_t* hist = (uint32_t*)(ws + plan.hist_off);
-    uint32_t* tickets = (uint32_t*)(ws + plan.ticket_off);
-    uint32_t* lookback = (uint32_t*)(ws + plan.lookback_off);
-    SC_CUDA(cudaMemsetAsync(ws, 0, (size_t)(plan.lookback_off + (int64_t)plan.passes * plan.tiles * RADIX * 4), st));
-    {
-        const int grid = (int)min(sc_div_up(n, 256 * 8), (int64_t)SC_NUM_SMS * 8);
-        sort_histogram_kernel<<<grid, 256, plan.passes * RADIX * 4, st>>>(n, keys_in, plan.passes, end_bit, hist);
-        SC_CHECK_LAUNCH("sort_histogram_kernel");
-        sort_hist_scan_kernel<<<plan.passes, RADIX, 0, st>>>(hist);
-        SC_CHECK_LAUNCH("sort_hist_scan_kernel");
-    }
-    static bool attr_set = false;
-    if (!attr_set) {
-        SC_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sizeof(SortSmem)));
-        attr_set = true;
-    }
-    uint64_t* kin = keys_in;
-    uint32_t* vin = vals_in;
-    uint64_t* kout = keys_out;
-    uint32_t* vout = vals_out;
-    for (int p = 0; p < plan.passes; ++p) {
-        const int shift = p * RADIX_BITS;
-        const int nb = end_bit - shift < RADIX_BITS ? end_bit - shift : RADIX_BITS;
-        onesweep_pass_kernel<<<(unsigned)plan.tiles, SORT_THREADS, sizeof(SortSmem), st>>>(
-            n, kin, vin, kout, vout, shift, nb, hist + p * RADIX, lookback + (size_t)p * plan.tiles * RADIX,
-            tickets + p);
-        SC_CHECK_LAUNCH("onesweep_pass_kernel");
-        uint64_t* tk = kin; kin = kout; kout = tk;
-        uint32_t* tv = vin; vin = vout; vout = tv;
-    }
-    // after the swap `kin` holds the result
-    return kin == keys_out ? 0 : 1;
+                                   uint32_t* vals_out, int begin_bit, int end_bit, void* workspace,
+                                   int64_t workspace_bytes, void* stream) {
+    return radix_sort_pairs<uint64_t>(n, keys_in, vals_in, keys_out, vals_out, begin_bit, end_bit, workspace,
+                                      workspace_bytes, stream);
+}
+
+extern "C" int sc_radix_sort_pairs_u32(int64_t n, uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_out,
+                                       uint32_t* vals_out, int begin_bit, int end_bit, void* workspace,
+                                       int64_t workspace_bytes, void* stream) {
+    return radix_sort_pairs<uint32_t>(n, keys_in, vals_in, keys_out, vals_out, begin_bit, end_bit, workspace,
+                                      workspace_bytes, stream);
 }

@@ -40,7 +40,9 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
     # Spherical harmonics                                       (reference :256-260)
     dirs = xyz3[None, :, :] - camera_center
     masks = radii > 0
-    shs = rgb3.expand(1, -1, -1, -1)
+    # the reference writes rgb3.expand(1, -1, -1, -1) (:258); unsqueeze is the same view but its
+    # backward is a view too, where ExpandBackward launches a 384 MB sum over the size-1 dim
+    shs = rgb3[None]
     colors = spherical_harmonics(max_sh_degree, dirs, shs, masks=masks)
     colors = torch.clamp_min(colors + 0.5, 0.0)
     if train and means2d.requires_grad:

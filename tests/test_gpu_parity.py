@@ -176,8 +176,9 @@ def test_isect_ties_are_stable(S, dev):
 
 
 @pytest.mark.parametrize("n", [1, 31, 4095, 4096, 4097, 100003, 1 << 20])
-@pytest.mark.parametrize("end_bit", [8, 30, 44, 46, 64])
-def test_radix_sort_matches_stable_sort(S, dev, n, end_bit):
+@pytest.mark.parametrize("begin_bit,end_bit", [(0, 8), (0, 30), (0, 44), (0, 46), (0, 64), (32, 46), (32, 44),
+                                               (7, 21)])
+def test_radix_sort_matches_stable_sort(S, dev, n, begin_bit, end_bit):
     from street_crafter_b200._lib import check, lib
     g = torch.Generator().manual_seed(n * 131 + end_bit)
     hi = min(end_bit, 62)
@@ -192,13 +193,39 @@ def test_radix_sort_matches_stable_sort(S, dev, n, end_bit):
     kb, vb = torch.empty_like(ka), torch.empty_like(va)
     ws_bytes = int(lib.sc_sort_workspace_bytes(n))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    where = check(lib.sc_radix_sort_pairs(n, ka.data_ptr(), va.data_ptr(), kb.data_ptr(), vb.data_ptr(), end_bit,
-                                          ws.data_ptr(), ws_bytes, torch.cuda.current_stream().cuda_stream),
-                  "sort")
+    where = check(lib.sc_radix_sort_pairs(n, ka.data_ptr(), va.data_ptr(), kb.data_ptr(), vb.data_ptr(),
+                                          begin_bit, end_bit, ws.data_ptr(), ws_bytes,
+                                          torch.cuda.current_stream().cuda_stream), "sort")
     ko, vo = (kb, vb) if where == 0 else (ka, va)
-    mask = (1 << end_bit) - 1 if end_bit < 64 else -1
-    sk, order = torch.sort(keys & mask if end_bit < 63 else keys, stable=True)
-    assert torch.equal((ko.cpu() & mask) if end_bit < 63 else ko.cpu(), sk)
+    # the digit actually sorted on: bits [begin_bit, end_bit) as an unsigned number
+    digit = (keys >> begin_bit) & ((1 << (end_bit - begin_bit)) - 1) if end_bit - begin_bit < 63 else keys
+    _, order = torch.sort(digit, stable=True)
+    assert torch.equal(ko.cpu(), keys[order])            # whole keys travel, order is by the digit
+    assert torch.equal(vo.cpu(), vals[order])
+
+
+@pytest.mark.parametrize("n", [1, 33, 4097, 300001])
+@pytest.mark.parametrize("begin_bit,end_bit", [(0, 32), (0, 30), (5, 17)])
+def test_radix_sort_u32_matches_stable_sort(S, dev, n, begin_bit, end_bit):
+    from street_crafter_b200._lib import check, lib
+    g = torch.Generator().manual_seed(n + end_bit)
+    keys = torch.randint(0, 2 ** 32, (n,), generator=g, dtype=torch.int64)
+    if n > 100:
+        keys[n // 2: n // 2 + n // 4] = 0xFFFFFFFF       # the "emits nothing" sentinel run
+        keys[::7] = keys[0]
+    vals = torch.arange(n, dtype=torch.int32)
+    ka = keys.to(torch.uint32).view(torch.int32).to(dev) if hasattr(torch, "uint32") else None
+    va = vals.to(dev)
+    kb, vb = torch.empty_like(ka), torch.empty_like(va)
+    ws_bytes = int(lib.sc_sort_workspace_bytes(n))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    where = check(lib.sc_radix_sort_pairs_u32(n, ka.data_ptr(), va.data_ptr(), kb.data_ptr(), vb.data_ptr(),
+                                              begin_bit, end_bit, ws.data_ptr(), ws_bytes,
+                                              torch.cuda.current_stream().cuda_stream), "sort32")
+    ko, vo = (kb, vb) if where == 0 else (ka, va)
+    digit = (keys >> begin_bit) & ((1 << (end_bit - begin_bit)) - 1)
+    _, order = torch.sort(digit, stable=True)
+    assert torch.equal(ko.cpu().view(torch.uint32).to(torch.int64), keys[order])
     assert torch.equal(vo.cpu(), vals[order])
 
 
