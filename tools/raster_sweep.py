@@ -24,7 +24,7 @@ for yaw in (0.0, 45.0):
     v_ra = torch.randn(1, H, W, 1, generator=g).to(dev)
     print(f"yaw {yaw}: I={a['isect_ids'].numel()}")
     ref = None
-    for ppt in (1, 2, 4, 8):
+    for ppt in (8,):
         os.environ["SCB200_FWD_PPT"] = str(ppt)
         os.environ["SCB200_BWD_PPT"] = str(ppt)
         tf, tb = [], []
