@@ -15,7 +15,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
     > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
 ncu --set full --clock-control none --import-source on \
-    -k regex:'rasterize_|onesweep' -s 40 -c 8 -o gpurun_out/${TAG}_prof -f \
+    -k regex:'rasterize_|onesweep' -s 24 -c 6 -o gpurun_out/${TAG}_prof -f \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la gpurun_out | tail -20
