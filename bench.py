@@ -265,12 +265,14 @@ def run_ours(args):
     for t in v_rc:
         t[..., 3] *= 0.02
 
+    sinks = arena.sinks()  # projection / SH backward add straight into the flat gradient arena
+
     def step_resident():
         """inputs already in HBM; upstream gradients fixed (loss-independent)"""
         arena.zero_grad()
         for v in range(n_views):
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
-                                       dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE)
+                                       dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks)
             torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc[v], v_ra[v]])
         if world > 1:
             allreduce_gradients(arena)
@@ -285,7 +287,7 @@ def run_ours(args):
             Cd = host_C[v].to(dev, non_blocking=True)
             gt = host_gt[v].to(dev, non_blocking=True)
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
-                                       Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE)
+                                       Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks)
             loss = (out["rgb"] - gt).abs().mean() + 0.01 * out["acc"].mean()
             loss.backward()
             losses.append(loss.detach())

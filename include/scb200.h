@@ -53,21 +53,24 @@ int sc_projection_fwd(int64_t N, int C, const float* means, const float* quats, 
                       float* means2d, float* depths, float* conics, float* compensations,
                       void* stream);
 /* v_* inputs [C,N,...] (v_compensations nullable) -> v_means[N,3] v_quats[N,4] v_scales[N,3]
- * (each nullable; summed over cameras, written not accumulated). */
+ * (each nullable; summed over cameras).  accumulate == 0: outputs are WRITTEN (zeros for
+ * Gaussians no camera sees); accumulate != 0 (gradient-arena mode of the multi-view step):
+ * outputs are += and Gaussians no camera sees are not touched. */
 int sc_projection_bwd(int64_t N, int C, const float* means, const float* quats, const float* scales,
                       const float* viewmats, const float* Ks, int width, int height, float eps2d,
                       const int32_t* radii, const float* v_means2d, const float* v_depths,
                       const float* v_conics, const float* v_compensations, float* v_means,
-                      float* v_quats, float* v_scales, void* stream);
+                      float* v_quats, float* v_scales, int accumulate, void* stream);
 
 /* ---- A5: spherical harmonics ----------------------------------------------------------- */
 /* dirs[M,3] (un-normalised), coeffs[M,K,3], masks[M] u8 (nullable) -> colors[M,3]. */
 int sc_sh_fwd(int64_t M, int K, int degree, const float* dirs, const float* coeffs,
               const uint8_t* masks, float* colors, void* stream);
-/* v_colors[M,3] -> v_coeffs[M,K,3] (fully written, zeros where masked), v_dirs[M,3] (nullable). */
+/* v_colors[M,3] -> v_coeffs[M,K,3], v_dirs[M,3] (nullable).  accumulate == 0: fully written,
+ * zeros where masked; accumulate != 0: += on unmasked entries only (gradient-arena mode). */
 int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const float* coeffs,
               const uint8_t* masks, const float* v_colors, float* v_coeffs, float* v_dirs,
-              void* stream);
+              int accumulate, void* stream);
 
 /* ---- A3/A4: tile intersection ---------------------------------------------------------- */
 /* tiles_per_gauss[i] = size of the tile AABB of entry i (0 when radii[i] == 0).  Optional

@@ -19,9 +19,28 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
                       const int32_t* __restrict__ radii, const float* __restrict__ v_means2d,
                       const float* __restrict__ v_depths, const float* __restrict__ v_conics,
                       const float* __restrict__ v_comps, float* __restrict__ v_means,
-                      float* __restrict__ v_quats, float* __restrict__ v_scales) {
+                      float* __restrict__ v_quats, float* __restrict__ v_scales, int accumulate) {
     const int64_t g = (int64_t)blockIdx.x * PB_THREADS + threadIdx.x;
     if (g >= N) return;
+    // Gaussians no camera sees: nothing to compute (zeros, or untouched in accumulate mode)
+    bool seen = false;
+    for (int cam = 0; cam < C; ++cam) seen |= __ldg(radii + (int64_t)cam * N + g) > 0;
+    if (!seen) {
+        if (!accumulate) {
+            if (v_means) { v_means[g * 3 + 0] = 0.f; v_means[g * 3 + 1] = 0.f; v_means[g * 3 + 2] = 0.f; }
+            if (v_scales) { v_scales[g * 3 + 0] = 0.f; v_scales[g * 3 + 1] = 0.f; v_scales[g * 3 + 2] = 0.f; }
+            if (v_quats) reinterpret_cast<float4*>(v_quats)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        return;
+    }
+    // accumulate mode: fetch the running sums now, so their latency hides under the math
+    float old_p[3] = {0.f, 0.f, 0.f}, old_s[3] = {0.f, 0.f, 0.f};
+    float4 old_q = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (accumulate) {
+        if (v_means) { old_p[0] = v_means[g * 3 + 0]; old_p[1] = v_means[g * 3 + 1]; old_p[2] = v_means[g * 3 + 2]; }
+        if (v_scales) { old_s[0] = v_scales[g * 3 + 0]; old_s[1] = v_scales[g * 3 + 1]; old_s[2] = v_scales[g * 3 + 2]; }
+        if (v_quats) old_q = reinterpret_cast<const float4*>(v_quats)[g];
+    }
     // ---- forward recompute: rotation, M = R diag(s), Sigma
     const float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
     const float n2 = q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
@@ -211,13 +230,18 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
         vq[2] = (vy - y * dotq) * inv_n;
         vq[3] = (vzq - z * dotq) * inv_n;
     }
+    // (old_* are zero unless accumulate)
     if (v_means) {
-        v_means[g * 3 + 0] = vp[0]; v_means[g * 3 + 1] = vp[1]; v_means[g * 3 + 2] = vp[2];
+        v_means[g * 3 + 0] = old_p[0] + vp[0]; v_means[g * 3 + 1] = old_p[1] + vp[1];
+        v_means[g * 3 + 2] = old_p[2] + vp[2];
     }
     if (v_scales) {
-        v_scales[g * 3 + 0] = vs[0]; v_scales[g * 3 + 1] = vs[1]; v_scales[g * 3 + 2] = vs[2];
+        v_scales[g * 3 + 0] = old_s[0] + vs[0]; v_scales[g * 3 + 1] = old_s[1] + vs[1];
+        v_scales[g * 3 + 2] = old_s[2] + vs[2];
     }
-    if (v_quats) reinterpret_cast<float4*>(v_quats)[g] = make_float4(vq[0], vq[1], vq[2], vq[3]);
+    if (v_quats)
+        reinterpret_cast<float4*>(v_quats)[g] =
+            make_float4(old_q.x + vq[0], old_q.y + vq[1], old_q.z + vq[2], old_q.w + vq[3]);
 }
 
 }  // namespace
@@ -226,7 +250,8 @@ extern "C" int sc_projection_bwd(int64_t N, int C, const float* means, const flo
                                  const float* scales, const float* viewmats, const float* Ks, int width,
                                  int height, float eps2d, const int32_t* radii, const float* v_means2d,
                                  const float* v_depths, const float* v_conics, const float* v_compensations,
-                                 float* v_means, float* v_quats, float* v_scales, void* stream) {
+                                 float* v_means, float* v_quats, float* v_scales, int accumulate,
+                                 void* stream) {
     SC_CHECK_ARG(N >= 0 && C >= 1, "N, C");
     if (N == 0) return SC_OK;
     SC_CHECK_ARG(means && quats && scales && viewmats && Ks && radii && v_means2d && v_depths && v_conics,
@@ -235,7 +260,7 @@ extern "C" int sc_projection_bwd(int64_t N, int C, const float* means, const flo
                  "16-byte alignment of quats");
     projection_bwd_kernel<<<(unsigned)sc_div_up(N, PB_THREADS), PB_THREADS, 0, (cudaStream_t)stream>>>(
         N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, radii, v_means2d, v_depths,
-        v_conics, v_compensations, v_means, v_quats, v_scales);
+        v_conics, v_compensations, v_means, v_quats, v_scales, accumulate);
     SC_CHECK_LAUNCH("projection_bwd_kernel");
     return SC_OK;
 }

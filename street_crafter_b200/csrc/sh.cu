@@ -1,10 +1,9 @@
 // Spherical-harmonics colour evaluation (A5) and its backward (A8b).
 //
-// HBM-bound: the [M,K,3] coefficient block is 192 B per Gaussian at K=16.  A warp owns 32
-// consecutive Gaussians whose coefficients form ONE contiguous 32*K*3-float span: it is
-// loaded with fully coalesced float4 accesses (skipping spans of masked-out Gaussians),
-// transposed through odd-stride shared memory (conflict-free), and each lane then evaluates
-// its own Gaussian.  The backward writes v_coeffs the same way in reverse.
+// HBM-bound: the [M,K,3] coefficient block is 192 B per Gaussian at K=16.  Lane-per-coefficient
+// layout (see ShLayout below): a group of lanes owns one Gaussian, lane k its k-th coefficient,
+// so the group's accesses cover the Gaussian's contiguous span with fully used sectors, without
+// shared memory; masked-out Gaussians cost a predicate and no traffic.
 //
 // Replaces gsplat.spherical_harmonics as called at
 // /root/reference/street_gaussian/models/street_gaussian_renderer.py:256-260; basis signs and
@@ -101,79 +100,233 @@ __device__ __forceinline__ void sh_basis_vjp(float x, float y, float z, const fl
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Lane-per-coefficient layout.  A group of LPG = pow2 >= K lanes owns ONE Gaussian, lane k of
+// the group owns coefficient k (its 3 channels, 12 contiguous bytes): the group's accesses to
+// coeffs / v_coeffs cover the Gaussian's contiguous K*12-byte span (K = 16: 192 B per half
+// warp, fully used sectors), no shared memory, no transposes, ~40 registers of state, and a
+// masked-out Gaussian costs one predicate.  Every lane evaluates the whole basis (a few dozen
+// FMULs, redundant but free next to the HBM traffic) and keeps Y_k; colours are a 3-value
+// shuffle reduction over the group.  Two Gaussians per group are in flight per iteration.
 template <int K>
-struct ShCfg {
-    static constexpr int K3 = K * 3;
-    static constexpr int STRIDE = K3 | 1;  // odd -> conflict-free column access
-    static constexpr int SMEM_FLOATS = 32 * STRIDE;
+struct ShLayout {
+    static constexpr int LPG = K <= 1 ? 1 : K <= 4 ? 4 : K <= 16 ? 16 : 32;  // lanes per Gaussian
+    static constexpr int GPW = 32 / LPG;                                      // Gaussians per warp
 };
+constexpr int SH_UNROLL = 2;
 
-// coalesced span load: the warp's 32 Gaussians occupy floats [g0*K3, g0*K3 + n*K3)
-template <int K>
-__device__ __forceinline__ void warp_load_coeffs(const float* __restrict__ coeffs, int64_t g0, int n,
-                                                 unsigned vis, float* sm, int lane) {
-    constexpr int K3 = ShCfg<K>::K3;
-    constexpr int STRIDE = ShCfg<K>::STRIDE;
-    const float* src = coeffs + g0 * K3;  // 128*K3 bytes from an aligned base: 16B aligned
-    const int nf = n * K3;
-    const int nf4 = nf >> 2;
-    for (int i = lane; i < nf4; i += 32) {
-        const int e = i << 2;
-        const int ga = e / K3, gb = (e + 3) / K3;
-        if (((vis >> ga) | (vis >> gb)) & 1u) {
-            const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
-            const float vv[4] = {v.x, v.y, v.z, v.w};
+template <int NB>
+__device__ __forceinline__ float select_k(const float* Y, int k) {
+    float y = 0.f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int ee = e + j;
-                const int gl = ee / K3;
-                sm[gl * STRIDE + (ee - gl * K3)] = vv[j];
-            }
-        }
-    }
-    for (int ee = (nf4 << 2) + lane; ee < nf; ee += 32) {
-        const int gl = ee / K3;
-        sm[gl * STRIDE + (ee - gl * K3)] = __ldg(src + ee);
-    }
-}
-
-template <int K>
-__device__ __forceinline__ void warp_store_coeffs(float* __restrict__ dst_base, int64_t g0, int n,
-                                                  const float* sm, int lane) {
-    constexpr int K3 = ShCfg<K>::K3;
-    constexpr int STRIDE = ShCfg<K>::STRIDE;
-    float* dst = dst_base + g0 * K3;
-    const int nf = n * K3;
-    const int nf4 = nf >> 2;
-    for (int i = lane; i < nf4; i += 32) {
-        const int e = i << 2;
-        float vv[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int ee = e + j;
-            const int gl = ee / K3;
-            vv[j] = sm[gl * STRIDE + (ee - gl * K3)];
-        }
-        reinterpret_cast<float4*>(dst)[i] = make_float4(vv[0], vv[1], vv[2], vv[3]);
-    }
-    for (int ee = (nf4 << 2) + lane; ee < nf; ee += 32) {
-        const int gl = ee / K3;
-        dst[ee] = sm[gl * STRIDE + (ee - gl * K3)];
-    }
+    for (int i = 0; i < NB; ++i) y = (i == k) ? Y[i] : y;
+    return y;
 }
 
 template <int K, int DEG>
 __global__ void __launch_bounds__(SH_THREADS)
 sh_fwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict__ coeffs,
               const uint8_t* __restrict__ masks, float* __restrict__ colors) {
-    extern __shared__ float smem[];
     constexpr int NB = (DEG + 1) * (DEG + 1);
-    constexpr int STRIDE = ShCfg<K>::STRIDE;
+    constexpr int LPG = ShLayout<K>::LPG, GPW = ShLayout<K>::GPW;
+    const int lane = threadIdx.x & 31;
+    const int k = lane % LPG, grp = lane / LPG;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t n_iter = (M + GPW * SH_UNROLL - 1) / (GPW * SH_UNROLL);
+    for (int64_t it = warp; it < n_iter; it += n_warps) {
+        int64_t g[SH_UNROLL];
+        bool live[SH_UNROLL];
+        float dx[SH_UNROLL], dy[SH_UNROLL], dz[SH_UNROLL], c0[SH_UNROLL], c1[SH_UNROLL], c2[SH_UNROLL];
+#pragma unroll
+        for (int u = 0; u < SH_UNROLL; ++u) {
+            g[u] = (it * SH_UNROLL + u) * GPW + grp;
+            live[u] = (g[u] < M) && (masks == nullptr || __ldg(masks + g[u]) != 0);
+        }
+#pragma unroll
+        for (int u = 0; u < SH_UNROLL; ++u) {
+            dx[u] = dy[u] = dz[u] = c0[u] = c1[u] = c2[u] = 0.f;
+            if (live[u]) {
+                dx[u] = __ldg(dirs + g[u] * 3 + 0); dy[u] = __ldg(dirs + g[u] * 3 + 1); dz[u] = __ldg(dirs + g[u] * 3 + 2);
+                if (k < NB) {
+                    const float* c = coeffs + (g[u] * K + k) * 3;
+                    c0[u] = __ldg(c + 0); c1[u] = __ldg(c + 1); c2[u] = __ldg(c + 2);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < SH_UNROLL; ++u) {
+            float r = 0.f, gg = 0.f, b = 0.f;
+            if (__any_sync(0xffffffffu, live[u])) {
+                const float inv = 1.0f / fmaxf(sqrtf(dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u]), 1e-12f);
+                float Y[25];
+                sh_basis<DEG>(dx[u] * inv, dy[u] * inv, dz[u] * inv, Y);
+                const float yk = select_k<NB>(Y, k);
+                r = yk * c0[u]; gg = yk * c1[u]; b = yk * c2[u];
+#pragma unroll
+                for (int o = LPG / 2; o >= 1; o >>= 1) {
+                    r += __shfl_xor_sync(0xffffffffu, r, o);
+                    gg += __shfl_xor_sync(0xffffffffu, gg, o);
+                    b += __shfl_xor_sync(0xffffffffu, b, o);
+                }
+            }
+            if (g[u] < M) {
+                if (LPG >= 4) {
+                    if (k < 3) colors[g[u] * 3 + k] = live[u] ? (k == 0 ? r : k == 1 ? gg : b) : 0.f;
+                } else {
+                    colors[g[u] * 3 + 0] = live[u] ? r : 0.f;
+                    colors[g[u] * 3 + 1] = live[u] ? gg : 0.f;
+                    colors[g[u] * 3 + 2] = live[u] ? b : 0.f;
+                }
+            }
+        }
+    }
+}
+
+template <int K, int DEG>
+__global__ void __launch_bounds__(SH_THREADS)
+sh_bwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict__ coeffs,
+              const uint8_t* __restrict__ masks, const float* __restrict__ v_colors,
+              float* __restrict__ v_coeffs, float* __restrict__ v_dirs, int accumulate) {
+    constexpr int NB = (DEG + 1) * (DEG + 1);
+    constexpr int LPG = ShLayout<K>::LPG, GPW = ShLayout<K>::GPW;
+    const int lane = threadIdx.x & 31;
+    const int k = lane % LPG, grp = lane / LPG;
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t n_iter = (M + GPW * SH_UNROLL - 1) / (GPW * SH_UNROLL);
+    const bool want_dirs = v_dirs != nullptr;
+    for (int64_t it = warp; it < n_iter; it += n_warps) {
+        int64_t g[SH_UNROLL];
+        bool live[SH_UNROLL];
+        float dx[SH_UNROLL], dy[SH_UNROLL], dz[SH_UNROLL], vr[SH_UNROLL], vg[SH_UNROLL], vb[SH_UNROLL];
+        float c0[SH_UNROLL], c1[SH_UNROLL], c2[SH_UNROLL], o0[SH_UNROLL], o1[SH_UNROLL], o2[SH_UNROLL];
+#pragma unroll
+        for (int u = 0; u < SH_UNROLL; ++u) {
+            g[u] = (it * SH_UNROLL + u) * GPW + grp;
+            live[u] = (g[u] < M) && (masks == nullptr || __ldg(masks + g[u]) != 0);
+        }
+#pragma unroll
+        for (int u = 0; u < SH_UNROLL; ++u) {
+            dx[u] = dy[u] = dz[u] = vr[u] = vg[u] = vb[u] = 0.f;
+            c0[u] = c1[u] = c2[u] = o0[u] = o1[u] = o2[u] = 0.f;
+            if (live[u]) {
+                dx[u] = __ldg(dirs + g[u] * 3 + 0); dy[u] = __ldg(dirs + g[u] * 3 + 1); dz[u] = __ldg(dirs + g[u] * 3 + 2);
+                vr[u] = __ldg(v_colors + g[u] * 3 + 0); vg[u] = __ldg(v_colors + g[u] * 3 + 1);
+                vb[u] = __ldg(v_colors + g[u] * 3 + 2);
+                if (k < K) {
+                    const int64_t e = (g[u] * K + k) * 3;
+                    if (want_dirs && k < NB) { c0[u] = __ldg(coeffs + e); c1[u] = __ldg(coeffs + e + 1); c2[u] = __ldg(coeffs + e + 2); }
+                    if (accumulate) { o0[u] = v_coeffs[e]; o1[u] = v_coeffs[e + 1]; o2[u] = v_coeffs[e + 2]; }
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < SH_UNROLL; ++u) {
+            if (!__any_sync(0xffffffffu, live[u])) {
+                // nothing visible in this warp slice: zeros (or untouched in accumulate mode)
+                if (!accumulate && g[u] < M) {
+                    if (k < K) { const int64_t e = (g[u] * K + k) * 3; v_coeffs[e] = 0.f; v_coeffs[e + 1] = 0.f; v_coeffs[e + 2] = 0.f; }
+                    if (want_dirs && k < 3 && (LPG >= 4 || k == 0)) {
+                        if (LPG >= 4) v_dirs[g[u] * 3 + k] = 0.f;
+                        else { v_dirs[g[u] * 3] = 0.f; v_dirs[g[u] * 3 + 1] = 0.f; v_dirs[g[u] * 3 + 2] = 0.f; }
+                    }
+                }
+                continue;
+            }
+            const float inv = 1.0f / fmaxf(sqrtf(dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u]), 1e-12f);
+            const float x = dx[u] * inv, y = dy[u] * inv, z = dz[u] * inv;
+            float Y[25];
+            sh_basis<DEG>(x, y, z, Y);
+            const float yk = select_k<NB>(Y, k);  // 0 for k >= NB
+            if (g[u] < M && k < K && (live[u] || !accumulate)) {
+                const int64_t e = (g[u] * K + k) * 3;
+                const float m = live[u] ? yk : 0.f;
+                v_coeffs[e] = o0[u] + m * vr[u]; v_coeffs[e + 1] = o1[u] + m * vg[u]; v_coeffs[e + 2] = o2[u] + m * vb[u];
+            }
+            if (want_dirs) {
+                // s_k = <coeff[k,:], v_colour>, gathered to every lane of the group
+                const float sk = c0[u] * vr[u] + c1[u] * vg[u] + c2[u] * vb[u];
+                float s[25];
+#pragma unroll
+                for (int i = 0; i < NB; ++i) s[i] = __shfl_sync(0xffffffffu, sk, grp * LPG + (i % LPG));
+                float ax, ay, az;
+                sh_basis_vjp<DEG>(x, y, z, s, ax, ay, az);
+                const float dp = ax * x + ay * y + az * z;
+                const float gx = (ax - x * dp) * inv, gy = (ay - y * dp) * inv, gz = (az - z * dp) * inv;
+                if (g[u] < M && (live[u] || !accumulate)) {
+                    const float m = live[u] ? 1.f : 0.f;
+                    if (LPG >= 4) {
+                        if (k < 3) {
+                            const float val = m * (k == 0 ? gx : k == 1 ? gy : gz);
+                            if (accumulate) v_dirs[g[u] * 3 + k] += val; else v_dirs[g[u] * 3 + k] = val;
+                        }
+                    } else {
+                        if (accumulate) { v_dirs[g[u] * 3] += gx; v_dirs[g[u] * 3 + 1] += gy; v_dirs[g[u] * 3 + 2] += gz; }
+                        else { v_dirs[g[u] * 3] = m * gx; v_dirs[g[u] * 3 + 1] = m * gy; v_dirs[g[u] * 3 + 2] = m * gz; }
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Transposing kernels for K*3 % 4 == 0 (K = 4, 16 — the reference's sh_degree 1 and 3).
+// Compute is lane-per-Gaussian (one warp instruction serves 32 Gaussians); global traffic is
+// float4 over the warp's contiguous 32*K*12-byte span; the transpose goes through a padded
+// shared-memory tile (row stride K3+4 floats: float4 accesses are conflict-free per quarter
+// warp both row-wise and lane-per-row).  Everything is streamed float4 by float4 with
+// compile-time indices, so the kernels stay near 64 registers and 32 warps fit on an SM —
+// these kernels are latency-bound otherwise (each chunk is a mask -> coefficients -> result
+// chain of dependent DRAM round trips).
+template <int K>
+struct ShT {
+    static constexpr int K3 = K * 3;
+    static constexpr int Q = K3 / 4;        // float4 per Gaussian
+    static constexpr int STRIDE = K3 + 4;   // floats per padded row
+    static constexpr int TILE_FLOATS = 32 * STRIDE;
+};
+constexpr int SHT_WARPS = 8;
+
+// coalesced: the chunk's n*Q float4 <-> padded rows; only Gaussians in `vis`
+template <int K>
+__device__ __forceinline__ void sht_load(const float4* __restrict__ src4, int n, unsigned vis, float* tile,
+                                         int lane) {
+    constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
+    constexpr int UB = Q < 6 ? Q : 6;  // loads in flight per lane
+#pragma unroll
+    for (int u0 = 0; u0 < Q; u0 += UB) {
+        float4 v[UB];
+        bool on[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int i = lane + 32 * (u0 + u);
+            const int gl = i / Q;
+            on[u] = (u0 + u < Q) && (gl < n) && ((vis >> gl) & 1u);
+            if (on[u]) v[u] = __ldg(src4 + i);
+        }
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+            const int i = lane + 32 * (u0 + u);
+            const int gl = i / Q;
+            if (on[u]) *reinterpret_cast<float4*>(tile + gl * STRIDE + 4 * (i - gl * Q)) = v[u];
+        }
+    }
+}
+
+template <int K, int DEG>
+__global__ void __launch_bounds__(SHT_WARPS * 32, 3)
+sh_fwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restrict__ coeffs4,
+                const uint8_t* __restrict__ masks, float* __restrict__ colors) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int NB = (DEG + 1) * (DEG + 1);
+    constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    float* sm = smem + wib * ShCfg<K>::SMEM_FLOATS;
+    float* tile = smem + wib * ShT<K>::TILE_FLOATS;
     const int64_t n_chunks = (M + 31) >> 5;
-    for (int64_t chunk = (int64_t)blockIdx.x * SH_WARPS + wib; chunk < n_chunks;
-         chunk += (int64_t)gridDim.x * SH_WARPS) {
+    for (int64_t chunk = (int64_t)blockIdx.x * SHT_WARPS + wib; chunk < n_chunks;
+         chunk += (int64_t)gridDim.x * SHT_WARPS) {
         const int64_t g0 = chunk << 5;
         const int n = (int)min((int64_t)32, M - g0);
         const int64_t g = g0 + lane;
@@ -181,21 +334,29 @@ sh_fwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict
         const unsigned vis = __ballot_sync(0xffffffffu, live);
         float r = 0.f, gg = 0.f, b = 0.f;
         if (vis) {
-            warp_load_coeffs<K>(coeffs, g0, n, vis, sm, lane);
+            float x = 0.f, y = 0.f, z = 0.f;
+            if (live) { x = __ldg(dirs + g * 3 + 0); y = __ldg(dirs + g * 3 + 1); z = __ldg(dirs + g * 3 + 2); }
+            sht_load<K>(coeffs4 + g0 * Q, n, vis, tile, lane);
             __syncwarp();
             if (live) {
-                float x = __ldg(dirs + g * 3 + 0), y = __ldg(dirs + g * 3 + 1), z = __ldg(dirs + g * 3 + 2);
                 const float inv = 1.0f / fmaxf(sqrtf(x * x + y * y + z * z), 1e-12f);
-                x *= inv; y *= inv; z *= inv;
                 float Y[25];
-                sh_basis<DEG>(x, y, z, Y);
-                const float* c = sm + lane * STRIDE;
+                sh_basis<DEG>(x * inv, y * inv, z * inv, Y);
+                const float4* row = reinterpret_cast<const float4*>(tile + lane * STRIDE);
+                float acc[3] = {0.f, 0.f, 0.f};
 #pragma unroll
-                for (int k = 0; k < NB; ++k) {
-                    r += Y[k] * c[k * 3 + 0];
-                    gg += Y[k] * c[k * 3 + 1];
-                    b += Y[k] * c[k * 3 + 2];
+                for (int q = 0; q < Q; ++q) {
+                    if (4 * q < NB * 3) {  // float4s wholly beyond the used degree are skipped
+                        const float4 c = row[q];
+                        const float cv[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int e = 4 * q + j;
+                            if (e < NB * 3) acc[e % 3] = fmaf(Y[e / 3], cv[j], acc[e % 3]);
+                        }
+                    }
                 }
+                r = acc[0]; gg = acc[1]; b = acc[2];
             }
             __syncwarp();
         }
@@ -206,43 +367,83 @@ sh_fwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict
 }
 
 template <int K, int DEG>
-__global__ void __launch_bounds__(SH_THREADS)
-sh_bwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict__ coeffs,
-              const uint8_t* __restrict__ masks, const float* __restrict__ v_colors,
-              float* __restrict__ v_coeffs, float* __restrict__ v_dirs) {
-    extern __shared__ float smem[];
+__global__ void __launch_bounds__(SHT_WARPS * 32, 3)
+sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restrict__ coeffs4,
+                const uint8_t* __restrict__ masks, const float* __restrict__ v_colors,
+                float4* __restrict__ v_coeffs4, float* __restrict__ v_dirs, int accumulate) {
+    extern __shared__ __align__(16) float smem[];
     constexpr int NB = (DEG + 1) * (DEG + 1);
-    constexpr int K3 = ShCfg<K>::K3;
-    constexpr int STRIDE = ShCfg<K>::STRIDE;
+    constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    float* sm = smem + wib * ShCfg<K>::SMEM_FLOATS;
+    float* tile = smem + wib * ShT<K>::TILE_FLOATS;
     const int64_t n_chunks = (M + 31) >> 5;
-    for (int64_t chunk = (int64_t)blockIdx.x * SH_WARPS + wib; chunk < n_chunks;
-         chunk += (int64_t)gridDim.x * SH_WARPS) {
+    const bool want_dirs = v_dirs != nullptr;
+    // per-lane inputs of a chunk (mask, direction, upstream colour gradient) are fetched one
+    // chunk AHEAD, unconditionally, so that the only DRAM latency a chunk exposes is its
+    // coefficient span
+    struct LaneIn { bool m; float x, y, z, r, g, b; };
+    auto fetch = [&](int64_t chunk) {
+        LaneIn in{false, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        const int64_t g = (chunk << 5) + lane;
+        if (chunk < n_chunks && g < M) {
+            in.m = masks == nullptr || __ldg(masks + g) != 0;
+            in.x = __ldg(dirs + g * 3 + 0); in.y = __ldg(dirs + g * 3 + 1); in.z = __ldg(dirs + g * 3 + 2);
+            in.r = __ldg(v_colors + g * 3 + 0); in.g = __ldg(v_colors + g * 3 + 1); in.b = __ldg(v_colors + g * 3 + 2);
+        }
+        return in;
+    };
+    const int64_t chunk_step = (int64_t)gridDim.x * SHT_WARPS;
+    LaneIn nxt = fetch((int64_t)blockIdx.x * SHT_WARPS + wib);
+    for (int64_t chunk = (int64_t)blockIdx.x * SHT_WARPS + wib; chunk < n_chunks; chunk += chunk_step) {
         const int64_t g0 = chunk << 5;
         const int n = (int)min((int64_t)32, M - g0);
         const int64_t g = g0 + lane;
-        const bool live = (lane < n) && (masks == nullptr || __ldg(masks + g) != 0);
+        const LaneIn cur = nxt;
+        nxt = fetch(chunk + chunk_step);
+        const bool live = (lane < n) && cur.m;
         const unsigned vis = __ballot_sync(0xffffffffu, live);
-        float x = 0.f, y = 0.f, z = 0.f, inv = 0.f, vr = 0.f, vg = 0.f, vb = 0.f;
+        float4* dst4 = v_coeffs4 + g0 * Q;
+        if (!vis) {
+            // nothing visible in the chunk: zeros, or untouched in accumulate mode
+            if (!accumulate) {
+#pragma unroll
+                for (int u = 0; u < Q; ++u) {
+                    const int i = lane + 32 * u;
+                    if (i < n * Q) dst4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                if (want_dirs && lane < n) { v_dirs[g * 3] = 0.f; v_dirs[g * 3 + 1] = 0.f; v_dirs[g * 3 + 2] = 0.f; }
+            }
+            continue;
+        }
+        float x = cur.x, y = cur.y, z = cur.z, inv = 0.f;
+        const float vc[3] = {live ? cur.r : 0.f, live ? cur.g : 0.f, live ? cur.b : 0.f};
+        if (want_dirs) sht_load<K>(coeffs4 + g0 * Q, n, vis, tile, lane);
         float Y[25];
         if (live) {
-            x = __ldg(dirs + g * 3 + 0); y = __ldg(dirs + g * 3 + 1); z = __ldg(dirs + g * 3 + 2);
             inv = 1.0f / fmaxf(sqrtf(x * x + y * y + z * z), 1e-12f);
             x *= inv; y *= inv; z *= inv;
-            vr = __ldg(v_colors + g * 3 + 0); vg = __ldg(v_colors + g * 3 + 1); vb = __ldg(v_colors + g * 3 + 2);
             sh_basis<DEG>(x, y, z, Y);
         }
         float gx = 0.f, gy = 0.f, gz = 0.f;
-        if (v_dirs != nullptr && vis) {
-            // s[k] = <coeff[k,:], v_color> needs the coefficients
-            warp_load_coeffs<K>(coeffs, g0, n, vis, sm, lane);
+        float4* row = reinterpret_cast<float4*>(tile + lane * STRIDE);
+        if (want_dirs) {
             __syncwarp();
             if (live) {
-                const float* c = sm + lane * STRIDE;
                 float s[25];
 #pragma unroll
-                for (int k = 0; k < NB; ++k) s[k] = c[k * 3 + 0] * vr + c[k * 3 + 1] * vg + c[k * 3 + 2] * vb;
+                for (int k = 0; k < NB; ++k) s[k] = 0.f;
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    if (4 * q < NB * 3) {
+                        const float4 c = row[q];
+                        const float cv[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int e = 4 * q + j;
+                            if (e < NB * 3) s[e / 3] = fmaf(cv[j], vc[e % 3], s[e / 3]);
+                        }
+                    }
+                }
                 float ax, ay, az;
                 sh_basis_vjp<DEG>(x, y, z, s, ax, ay, az);
                 const float dp = ax * x + ay * y + az * z;
@@ -250,24 +451,44 @@ sh_bwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict
             }
             __syncwarp();
         }
-        // v_coeffs: Y_k * v_color, zeros for k >= NB and for masked Gaussians
+        // v_coeffs rows: Y_k * v_colour, zeros beyond the used degree and for masked Gaussians
         if (lane < n) {
-            float* c = sm + lane * STRIDE;
-            if (live) {
 #pragma unroll
-                for (int k = 0; k < NB; ++k) {
-                    c[k * 3 + 0] = Y[k] * vr; c[k * 3 + 1] = Y[k] * vg; c[k * 3 + 2] = Y[k] * vb;
+            for (int q = 0; q < Q; ++q) {
+                float o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int e = 4 * q + j;
+                    o[j] = (live && e < NB * 3) ? Y[e / 3 < NB ? e / 3 : 0] * vc[e % 3] : 0.f;
                 }
-                for (int e = NB * 3; e < K3; ++e) c[e] = 0.f;
-            } else {
-                for (int e = 0; e < K3; ++e) c[e] = 0.f;
+                row[q] = make_float4(o[0], o[1], o[2], o[3]);
             }
         }
         __syncwarp();
-        warp_store_coeffs<K>(v_coeffs, g0, n, sm, lane);
+        if (accumulate) {
+            // red.global.add.v4.f32: fire-and-forget, no read of the running sums
+#pragma unroll
+            for (int u = 0; u < Q; ++u) {
+                const int i = lane + 32 * u;
+                const int gl = i / Q;
+                if ((gl < n) && ((vis >> gl) & 1u))
+                    atomicAdd(dst4 + i, *reinterpret_cast<const float4*>(tile + gl * STRIDE + 4 * (i - gl * Q)));
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < Q; ++u) {
+                const int i = lane + 32 * u;
+                const int gl = i / Q;
+                if (gl < n) dst4[i] = *reinterpret_cast<const float4*>(tile + gl * STRIDE + 4 * (i - gl * Q));
+            }
+        }
         __syncwarp();
-        if (v_dirs != nullptr && lane < n) {
-            v_dirs[g * 3 + 0] = gx; v_dirs[g * 3 + 1] = gy; v_dirs[g * 3 + 2] = gz;
+        if (want_dirs && lane < n) {
+            if (accumulate) {
+                if (live) { atomicAdd(v_dirs + g * 3 + 0, gx); atomicAdd(v_dirs + g * 3 + 1, gy); atomicAdd(v_dirs + g * 3 + 2, gz); }
+            } else {
+                v_dirs[g * 3 + 0] = gx; v_dirs[g * 3 + 1] = gy; v_dirs[g * 3 + 2] = gz;
+            }
         }
     }
 }
@@ -275,25 +496,39 @@ sh_bwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict
 template <int K, int DEG>
 int launch_fwd(int64_t M, const float* dirs, const float* coeffs, const uint8_t* masks, float* colors,
                cudaStream_t st) {
-    const int smem = SH_WARPS * ShCfg<K>::SMEM_FLOATS * (int)sizeof(float);
-    auto kern = sh_fwd_kernel<K, DEG>;
-    if (smem > 48 * 1024) SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    const int64_t chunks = (M + 31) >> 5;
-    const int grid = (int)min(sc_div_up(chunks, SH_WARPS), (int64_t)SC_NUM_SMS * 16);
-    kern<<<grid, SH_THREADS, smem, st>>>(M, dirs, coeffs, masks, colors);
+    if constexpr ((K * 3) % 4 == 0) {
+        const int smem = SHT_WARPS * ShT<K>::TILE_FLOATS * (int)sizeof(float);
+        auto kern = sh_fwd_t_kernel<K, DEG>;
+        if (smem > 48 * 1024) SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        const int grid = (int)min(sc_div_up((M + 31) >> 5, SHT_WARPS), (int64_t)SC_NUM_SMS * 16);
+        kern<<<grid, SHT_WARPS * 32, smem, st>>>(M, dirs, reinterpret_cast<const float4*>(coeffs), masks, colors);
+        SC_CHECK_LAUNCH("sh_fwd_t_kernel");
+        return SC_OK;
+    }
+    const int64_t iters = sc_div_up(M, ShLayout<K>::GPW * SH_UNROLL);
+    const int grid = (int)min(sc_div_up(iters, SH_WARPS), (int64_t)SC_NUM_SMS * 64);
+    sh_fwd_kernel<K, DEG><<<grid, SH_THREADS, 0, st>>>(M, dirs, coeffs, masks, colors);
     SC_CHECK_LAUNCH("sh_fwd_kernel");
     return SC_OK;
 }
 
 template <int K, int DEG>
 int launch_bwd(int64_t M, const float* dirs, const float* coeffs, const uint8_t* masks, const float* v_colors,
-               float* v_coeffs, float* v_dirs, cudaStream_t st) {
-    const int smem = SH_WARPS * ShCfg<K>::SMEM_FLOATS * (int)sizeof(float);
-    auto kern = sh_bwd_kernel<K, DEG>;
-    if (smem > 48 * 1024) SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    const int64_t chunks = (M + 31) >> 5;
-    const int grid = (int)min(sc_div_up(chunks, SH_WARPS), (int64_t)SC_NUM_SMS * 16);
-    kern<<<grid, SH_THREADS, smem, st>>>(M, dirs, coeffs, masks, v_colors, v_coeffs, v_dirs);
+               float* v_coeffs, float* v_dirs, int accumulate, cudaStream_t st) {
+    if constexpr ((K * 3) % 4 == 0) {
+        const int smem = SHT_WARPS * ShT<K>::TILE_FLOATS * (int)sizeof(float);
+        auto kern = sh_bwd_t_kernel<K, DEG>;
+        if (smem > 48 * 1024) SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        const int grid = (int)min(sc_div_up((M + 31) >> 5, SHT_WARPS), (int64_t)SC_NUM_SMS * 16);
+        kern<<<grid, SHT_WARPS * 32, smem, st>>>(M, dirs, reinterpret_cast<const float4*>(coeffs), masks, v_colors,
+                                                 reinterpret_cast<float4*>(v_coeffs), v_dirs, accumulate);
+        SC_CHECK_LAUNCH("sh_bwd_t_kernel");
+        return SC_OK;
+    }
+    const int64_t iters = sc_div_up(M, ShLayout<K>::GPW * SH_UNROLL);
+    const int grid = (int)min(sc_div_up(iters, SH_WARPS), (int64_t)SC_NUM_SMS * 64);
+    sh_bwd_kernel<K, DEG><<<grid, SH_THREADS, 0, st>>>(M, dirs, coeffs, masks, v_colors, v_coeffs, v_dirs,
+                                                       accumulate);
     SC_CHECK_LAUNCH("sh_bwd_kernel");
     return SC_OK;
 }
@@ -334,7 +569,7 @@ extern "C" int sc_sh_fwd(int64_t M, int K, int degree, const float* dirs, const 
 
 extern "C" int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const float* coeffs,
                          const uint8_t* masks, const float* v_colors, float* v_coeffs, float* v_dirs,
-                         void* stream) {
+                         int accumulate, void* stream) {
     SC_CHECK_ARG(M >= 0, "M");
     SC_CHECK_ARG(degree >= 0 && degree <= 4 && (degree + 1) * (degree + 1) <= K, "degree vs K");
     if (M == 0) return SC_OK;
@@ -342,7 +577,7 @@ extern "C" int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const 
     SC_CHECK_ARG(((uintptr_t)coeffs & 15) == 0 && ((uintptr_t)v_coeffs & 15) == 0,
                  "16-byte alignment of coeffs");
     cudaStream_t st = (cudaStream_t)stream;
-    SH_DISPATCH(launch_bwd, M, dirs, coeffs, masks, v_colors, v_coeffs, v_dirs, st)
+    SH_DISPATCH(launch_bwd, M, dirs, coeffs, masks, v_colors, v_coeffs, v_dirs, accumulate, st)
     sc_set_error("unsupported SH coefficient count K=%d (supported 1,4,9,16,25)", K);
     return SC_ERR_UNSUPPORTED;
 }

@@ -20,14 +20,15 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
                          w2c: Tensor, K: Tensor, camera_center: Tensor, width: int, height: int,
                          max_sh_degree: int, znear: float = 0.001, zfar: float = 1000.0,
                          tile_size: int = 16, use_depth: bool = True, absgrad: bool = True,
-                         antialiasing: bool = True, train: bool = True) -> Dict[str, Tensor]:
+                         antialiasing: bool = True, train: bool = True,
+                         grad_sinks: Optional[Dict[str, Tensor]] = None) -> Dict[str, Tensor]:
     """xyz3[N,3] rgb3[N,K,3] (SH) scale[N,3] quats[N,4] occ1[N,1] w2c[1,4,4] K[1,3,3]
     camera_center[3] -> the reference's result dict (rgb[3,H,W], acc, depth, viewspace_points,
     visibility_filter, radii) plus the raw render tensors."""
     # Project Gaussians to 2D                                   (reference :219-232)
     radii, means2d, depths, conics, compensations = fully_fused_projection(
         xyz3, None, quats, scale, w2c, K, width, height, packed=False, near_plane=znear, far_plane=zfar,
-        calc_compensations=antialiasing)
+        calc_compensations=antialiasing, grad_sinks=grad_sinks)
     opacities = occ1[None, :, 0]
     if compensations is not None:
         opacities = opacities * compensations
@@ -43,7 +44,7 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
     # the reference writes rgb3.expand(1, -1, -1, -1) (:258); unsqueeze is the same view but its
     # backward is a view too, where ExpandBackward launches a 384 MB sum over the size-1 dim
     shs = rgb3[None]
-    colors = spherical_harmonics(max_sh_degree, dirs, shs, masks=masks)
+    colors = spherical_harmonics(max_sh_degree, dirs, shs, masks=masks, grad_sinks=grad_sinks)
     colors = torch.clamp_min(colors + 0.5, 0.0)
     if train and means2d.requires_grad:
         means2d.retain_grad()

@@ -58,7 +58,7 @@ def _grad_or_zeros(g: Optional[Tensor], like_shape, device) -> Tensor:
 class _FullyFusedProjection(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
-                radius_clip, calc_compensations):
+                radius_clip, calc_compensations, sinks=None):
         means = _f32c(means, "means")
         quats = _f32c(quats, "quats")
         scales = _f32c(scales, "scales")
@@ -79,6 +79,7 @@ class _FullyFusedProjection(torch.autograd.Function):
                   "sc_projection_fwd")
         ctx.save_for_backward(means, quats, scales, viewmats, Ks, radii)
         ctx.dims = (int(width), int(height), float(eps2d), bool(calc_compensations))
+        ctx.sinks = sinks
         ctx.mark_non_differentiable(radii)
         if comps is None:
             return radii, means2d, depths, conics
@@ -98,18 +99,27 @@ class _FullyFusedProjection(torch.autograd.Function):
         else:
             v_comps = None
         need = ctx.needs_input_grad
-        v_means = torch.empty_like(means) if need[0] else None
-        v_quats = torch.empty_like(quats) if need[1] else None
-        v_scales = torch.empty_like(scales) if need[2] else None
+        sinks = ctx.sinks
+        if sinks is not None:
+            # gradient-arena mode: += straight into the caller's buffers, nothing flows to autograd
+            assert C == 1, "gradient sinks need C == 1"
+            v_means, v_quats, v_scales = (sinks.get(k) for k in ("means", "quats", "scales"))
+        else:
+            v_means = torch.empty_like(means) if need[0] else None
+            v_quats = torch.empty_like(quats) if need[1] else None
+            v_scales = torch.empty_like(scales) if need[2] else None
         if need[3]:
             raise NotImplementedError("viewmats gradients are not produced (cameras are not optimised "
                                       "in the reference, street_gaussian/config/config.py:126)")
         with torch.cuda.device(dev):
             check(lib.sc_projection_bwd(N, C, _p(means), _p(quats), _p(scales), _p(viewmats), _p(Ks), width,
                                         height, eps2d, _p(radii), _p(v_means2d), _p(v_depths), _p(v_conics),
-                                        _p(v_comps), _p(v_means), _p(v_quats), _p(v_scales), _stream()),
+                                        _p(v_comps), _p(v_means), _p(v_quats), _p(v_scales),
+                                        0 if sinks is None else 1, _stream()),
                   "sc_projection_bwd")
-        return (v_means, v_quats, v_scales, None, None, None, None, None, None, None, None, None)
+        if sinks is not None:
+            return (None,) * 13
+        return (v_means, v_quats, v_scales, None, None, None, None, None, None, None, None, None, None)
 
 
 def fully_fused_projection(means: Tensor, covars: Optional[Tensor], quats: Optional[Tensor],
@@ -117,8 +127,13 @@ def fully_fused_projection(means: Tensor, covars: Optional[Tensor], quats: Optio
                            eps2d: float = 0.3, near_plane: float = 0.01, far_plane: float = 1e10,
                            radius_clip: float = 0.0, packed: bool = False, sparse_grad: bool = False,
                            calc_compensations: bool = False, camera_model: str = "pinhole",
+                           grad_sinks: Optional[Dict[str, Tensor]] = None,
                            ) -> Tuple[Tensor, Tensor, Tensor, Tensor, Optional[Tensor]]:
-    """-> (radii[C,N] i32, means2d[C,N,2], depths[C,N], conics[C,N,3], compensations[C,N]|None)."""
+    """-> (radii[C,N] i32, means2d[C,N,2], depths[C,N], conics[C,N,3], compensations[C,N]|None).
+
+    `grad_sinks` (extension, C == 1): {"means","quats","scales"} -> contiguous fp32 buffers the
+    backward ADDS its gradients into (the flat gradient arena of parallel.py) instead of
+    returning them to autograd — no AccumulateGrad add kernels, culled Gaussians untouched."""
     N = means.shape[0]
     C = viewmats.shape[0]
     assert means.shape == (N, 3), means.shape
@@ -134,7 +149,7 @@ def fully_fused_projection(means: Tensor, covars: Optional[Tensor], quats: Optio
     assert quats.shape == (N, 4), quats.shape
     assert scales.shape == (N, 3), scales.shape
     out = _FullyFusedProjection.apply(means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
-                                      far_plane, radius_clip, calc_compensations)
+                                      far_plane, radius_clip, calc_compensations, grad_sinks)
     if calc_compensations:
         return out
     return out + (None,)
@@ -145,7 +160,7 @@ def fully_fused_projection(means: Tensor, covars: Optional[Tensor], quats: Optio
 # ------------------------------------------------------------------------------------------
 class _SphericalHarmonics(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, degree, dirs, coeffs, masks):
+    def forward(ctx, degree, dirs, coeffs, masks, sinks=None):
         dirs = _f32c(dirs, "dirs", 4)
         coeffs = _f32c(coeffs, "coeffs")
         K = coeffs.shape[-2]
@@ -161,6 +176,7 @@ class _SphericalHarmonics(torch.autograd.Function):
         ctx.save_for_backward(dirs, coeffs, m8 if m8 is not None else torch.empty(0, device=dirs.device))
         ctx.degree = int(degree)
         ctx.has_mask = m8 is not None
+        ctx.sinks = sinks
         return colors
 
     @staticmethod
@@ -171,23 +187,37 @@ class _SphericalHarmonics(torch.autograd.Function):
         K = coeffs.shape[-2]
         M = dirs.numel() // 3
         v_colors = _f32c(v_colors, "v_colors", 4)
+        sinks = ctx.sinks
+        if sinks is not None:
+            # gradient-arena mode: v_coeffs += into the sh slice, v_dirs += into the means slice
+            # (dirs = means - camera centre), masked Gaussians untouched
+            with torch.cuda.device(dirs.device):
+                check(lib.sc_sh_bwd(M, K, ctx.degree, _p(dirs), _p(coeffs), _p(m8), _p(v_colors),
+                                    _p(sinks["shs"]), _p(sinks.get("means")), 1, _stream()), "sc_sh_bwd")
+            return None, None, None, None, None
         v_coeffs = torch.empty_like(coeffs)
         v_dirs = torch.empty_like(dirs) if ctx.needs_input_grad[1] else None
         with torch.cuda.device(dirs.device):
             check(lib.sc_sh_bwd(M, K, ctx.degree, _p(dirs), _p(coeffs), _p(m8), _p(v_colors), _p(v_coeffs),
-                                _p(v_dirs), _stream()), "sc_sh_bwd")
-        return None, v_dirs, (v_coeffs if ctx.needs_input_grad[2] else None), None
+                                _p(v_dirs), 0, _stream()), "sc_sh_bwd")
+        return None, v_dirs, (v_coeffs if ctx.needs_input_grad[2] else None), None, None
 
 
 def spherical_harmonics(degrees_to_use: int, dirs: Tensor, coeffs: Tensor,
-                        masks: Optional[Tensor] = None) -> Tensor:
-    """dirs [...,3] (normalised inside the kernel), coeffs [...,K,3], masks [...] -> [...,3]."""
+                        masks: Optional[Tensor] = None,
+                        grad_sinks: Optional[Dict[str, Tensor]] = None) -> Tensor:
+    """dirs [...,3] (normalised inside the kernel), coeffs [...,K,3], masks [...] -> [...,3].
+
+    `grad_sinks` (extension): {"shs": buffer of coeffs' shape, "means": buffer of dirs' shape}
+    the backward ADDS into (see fully_fused_projection)."""
     assert (degrees_to_use + 1) ** 2 <= coeffs.shape[-2], coeffs.shape
     assert dirs.shape[:-1] == coeffs.shape[:-2], (dirs.shape, coeffs.shape)
     assert dirs.shape[-1] == 3 and coeffs.shape[-1] == 3
     if masks is not None:
         assert masks.shape == dirs.shape[:-1], masks.shape
-    return _SphericalHarmonics.apply(degrees_to_use, dirs, coeffs, masks)
+    if grad_sinks is not None:
+        assert grad_sinks["shs"].numel() == coeffs.numel() and grad_sinks["shs"].is_contiguous()
+    return _SphericalHarmonics.apply(degrees_to_use, dirs, coeffs, masks, grad_sinks)
 
 
 # ------------------------------------------------------------------------------------------
