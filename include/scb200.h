@@ -109,6 +109,25 @@ int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_
 int sc_radix_sort_pairs_u32(int64_t n, uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_out,
                             uint32_t* vals_out, int begin_bit, int end_bit, void* workspace,
                             int64_t workspace_bytes, void* stream);
+/* Fused binning pipeline (what isect_tiles(sort=True) runs): two calls around the one host
+ * read-back of the counts.
+ *   sc_isect_prepare: tiles_per_gauss[CN]; order-preserving compaction of the emitting entries,
+ *     their stable depth order, the exclusive scan of their tile counts — all left in
+ *     `workspace` (>= sc_isect_workspace_bytes, 256-byte aligned), whose first 16 bytes hold
+ *     int64 {n_visible, n_isects} once the stream has drained.
+ *   sc_isect_emit_sorted: emits the (key, id) pairs in depth order (building the sort
+ *     histograms on the fly) and stably sorts them on the (camera, tile) bits; the sorted list
+ *     ends in isect_ids / flatten_ids; tmp_* are ping-pong buffers of the same sizes;
+ *     sort_workspace >= sc_sort_workspace_bytes(n_isects). */
+int64_t sc_isect_workspace_bytes(int64_t CN, int tile_width, int tile_height);
+int sc_isect_prepare(int64_t CN, const float* means2d, const int32_t* radii, const float* depths,
+                     int tile_size, int tile_width, int tile_height, int32_t* tiles_per_gauss,
+                     void* workspace, int64_t workspace_bytes, void* stream);
+int sc_isect_emit_sorted(int64_t N, int C, const float* means2d, const int32_t* radii, const float* depths,
+                         int tile_size, int tile_width, int tile_height, int tile_n_bits, int cam_bits,
+                         int64_t n_visible, int64_t n_isects, const void* prepare_workspace,
+                         int64_t* isect_ids, int32_t* flatten_ids, int64_t* tmp_ids, int32_t* tmp_flatten,
+                         void* sort_workspace, int64_t sort_workspace_bytes, void* stream);
 int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, int tile_width,
                            int tile_height, int tile_n_bits, int32_t* offsets, void* stream);
 

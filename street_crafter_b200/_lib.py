@@ -33,6 +33,10 @@ SIGNATURES = {
     "sc_sort_workspace_bytes": (_i64, [_i64]),
     "sc_radix_sort_pairs": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _i64, _ptr]),
     "sc_radix_sort_pairs_u32": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _i64, _ptr]),
+    "sc_isect_workspace_bytes": (_i64, [_i64, _i32, _i32]),
+    "sc_isect_prepare": (_i32, [_i64, _ptr, _ptr, _ptr, _i32, _i32, _i32, _ptr, _ptr, _i64, _ptr]),
+    "sc_isect_emit_sorted": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32, _i64, _i64,
+                                    _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
     "sc_isect_offset_encode": (_i32, [_i64, _ptr, _i32, _i32, _i32, _i32, _ptr, _ptr]),
     "sc_rasterize_fwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                 _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),

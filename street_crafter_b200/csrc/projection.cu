@@ -8,6 +8,7 @@
 // Replaces gsplat.fully_fused_projection / isect_tiles / isect_offset_encode as called at
 // /root/reference/street_gaussian/models/street_gaussian_renderer.py:219-253.
 #include "common.cuh"
+#include "sort_internal.cuh"
 
 namespace {
 
@@ -319,6 +320,287 @@ isect_emit_kernel(int64_t N, int64_t CN, const float2* __restrict__ means2d,
     }
 }
 
+// ------------------------------------------------------------------ fused binning pipeline
+// sc_isect_prepare / sc_isect_emit_sorted: the same result as count -> depth pre-sort ->
+// gather -> scan -> emit -> tile sort, in fewer launches and over fewer bytes:
+//   * isect_count_compact_kernel writes tiles_per_gauss AND the ORDER-PRESERVING compaction of
+//     the entries that emit something (depth bits, entry index): the depth pre-sort then moves
+//     V (visible) pairs instead of C*N; the visible count stays on the device (every consumer
+//     reads it from memory, grids are sized for C*N and surplus CTAs exit);
+//   * isect_scan_kernel gathers the tile counts in depth order and scans them in ONE pass
+//     (decoupled look-back), and records for every 2048-slot output block the entry that owns
+//     its first slot, so the emit CTAs start without a 21-step binary search;
+//   * the emit kernel accumulates the digit histograms of the tile sort while it writes the
+//     keys (the keys are not re-read for a histogram pass).
+// Look-back words pack {flag (2 bits), value (62 bits)} in one 64-bit word: a single store
+// publishes both, no fences.
+#define LB_AGG (1ull << 62)
+#define LB_INC (2ull << 62)
+#define LB_VAL ((1ull << 62) - 1ull)
+
+// exclusive prefix of tile `tile` over the published states of tiles [0, tile): called by ONE
+// full warp, every lane returns the result
+__device__ __forceinline__ unsigned long long lookback_exclusive(volatile unsigned long long* state,
+                                                                 int64_t tile, int lane) {
+    unsigned long long excl = 0;
+    int64_t idx = tile - 1;
+    while (idx >= 0) {
+        const int64_t i = idx - lane;
+        unsigned long long s;
+        do {
+            s = (i >= 0) ? state[i] : LB_INC;
+        } while (__any_sync(0xffffffffu, (s >> 62) == 0));
+        const unsigned inc = __ballot_sync(0xffffffffu, (s >> 62) == 2);
+        const int first = inc ? __ffs(inc) - 1 : 31;  // nearest tile with an inclusive prefix
+        unsigned long long v = (lane <= first) ? (s & LB_VAL) : 0ull;
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        excl += v;
+        if (inc) break;
+        idx -= 32;
+    }
+    return excl;
+}
+
+constexpr int CC_THREADS = 256;
+constexpr int CC_ITEMS = 4;
+constexpr int CC_TILE = CC_THREADS * CC_ITEMS;
+
+__global__ void __launch_bounds__(CC_THREADS)
+isect_count_compact_kernel(int64_t CN, const float2* __restrict__ means2d, const int32_t* __restrict__ radii,
+                           const float* __restrict__ depths, float ts, int tw, int th,
+                           int32_t* __restrict__ tiles_per_gauss, uint32_t* __restrict__ depth_keys,
+                           uint32_t* __restrict__ entry_ids, volatile unsigned long long* __restrict__ state,
+                           uint32_t* __restrict__ ticket, int64_t* __restrict__ totals) {
+    __shared__ uint32_t s_cnt[CC_ITEMS][CC_THREADS / 32];
+    __shared__ uint32_t s_tile;
+    __shared__ unsigned long long s_excl;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const int64_t tile = s_tile;
+    const int64_t base = tile * CC_TILE;
+    // striped: item k of thread t is entry base + k*256 + t (coalesced); the compaction order is
+    // entry order = (k, t) lexicographic
+    uint32_t key[CC_ITEMS];
+    bool vis[CC_ITEMS];
+    uint32_t pre[CC_ITEMS];  // visible entries of the same item in lower lanes of this warp
+#pragma unroll
+    for (int k = 0; k < CC_ITEMS; ++k) {
+        const int64_t i = base + k * CC_THREADS + tid;
+        int32_t n = 0;
+        key[k] = 0;
+        if (i < CN) {
+            const int32_t r = __ldg(radii + i);
+            if (r > 0) {
+                const float2 m = __ldg(means2d + i);
+                const TileBox b = tile_box(m.x, m.y, r, ts, tw, th);
+                n = (b.x1 - b.x0) * (b.y1 - b.y0);
+                key[k] = __float_as_uint(__ldg(depths + i));
+            }
+            tiles_per_gauss[i] = n;
+        }
+        vis[k] = n > 0;
+        const unsigned bal = __ballot_sync(0xffffffffu, vis[k]);
+        pre[k] = __popc(bal & ((1u << lane) - 1u));
+        if (lane == 0) s_cnt[k][w] = __popc(bal);
+    }
+    __syncthreads();
+    // block-level exclusive offsets of (item, warp) groups, in (k, w) order
+    uint32_t my_off[CC_ITEMS];
+    uint32_t run = 0;
+#pragma unroll
+    for (int k = 0; k < CC_ITEMS; ++k) {
+#pragma unroll
+        for (int ww = 0; ww < CC_THREADS / 32; ++ww) {
+            if (ww == w) my_off[k] = run;
+            run += s_cnt[k][ww];
+        }
+    }
+    const uint32_t block_total = run;
+    if (w == 0) {
+        if (lane == 0) state[tile] = (tile == 0 ? LB_INC : LB_AGG) | (unsigned long long)block_total;
+        unsigned long long excl = 0;
+        if (tile > 0) {
+            excl = lookback_exclusive(state, tile, lane);
+            if (lane == 0) state[tile] = LB_INC | (excl + block_total);
+        }
+        if (lane == 0) {
+            s_excl = excl;
+            if (base + CC_TILE >= CN) totals[0] = (int64_t)(excl + block_total);  // the last tile
+        }
+    }
+    __syncthreads();
+    const int64_t out0 = (int64_t)s_excl;
+#pragma unroll
+    for (int k = 0; k < CC_ITEMS; ++k) {
+        if (vis[k]) {
+            const int64_t o = out0 + my_off[k] + pre[k];
+            depth_keys[o] = key[k];
+            entry_ids[o] = (uint32_t)(base + k * CC_THREADS + tid);
+        }
+    }
+}
+
+// cum[j] = sum_{j' < j} tiles_per_gauss[order[j']] for j in [0, V], V read from the device;
+// first_entry[b] = the entry that owns output slot b * EMIT_OUT.
+constexpr int SG_THREADS = 256;
+constexpr int SG_ITEMS = 8;
+constexpr int SG_TILE = SG_THREADS * SG_ITEMS;
+constexpr int EMIT_OUT_LOG2 = 11;
+
+__global__ void __launch_bounds__(SG_THREADS)
+isect_scan_kernel(const int64_t* __restrict__ totals, const uint32_t* __restrict__ order,
+                  const int32_t* __restrict__ tiles_per_gauss, int64_t* __restrict__ cum,
+                  uint32_t* __restrict__ first_entry, int64_t first_cap,
+                  volatile unsigned long long* __restrict__ state, uint32_t* __restrict__ ticket,
+                  int64_t* __restrict__ total_out) {
+    __shared__ unsigned long long s_warp[SG_THREADS / 32];
+    __shared__ uint32_t s_tile;
+    __shared__ unsigned long long s_excl;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int64_t V = totals[0];
+    if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const int64_t tile = s_tile;
+    const int64_t base = tile * SG_TILE;
+    if (base >= V) {
+        if (tile == 0 && tid == 0) { cum[0] = 0; *total_out = 0; }
+        return;
+    }
+    // blocked: thread t owns entries base + t*8 .. +7
+    const int64_t j0 = base + (int64_t)tid * SG_ITEMS;
+    int32_t v[SG_ITEMS];
+    unsigned long long sum = 0;
+#pragma unroll
+    for (int k = 0; k < SG_ITEMS; ++k) {
+        v[k] = (j0 + k < V) ? __ldg(tiles_per_gauss + __ldg(order + j0 + k)) : 0;
+        sum += (unsigned long long)v[k];
+    }
+    unsigned long long incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[w] = incl;
+    __syncthreads();
+    unsigned long long wpre = 0, block_total = 0;
+#pragma unroll
+    for (int ww = 0; ww < SG_THREADS / 32; ++ww) {
+        const unsigned long long t = s_warp[ww];
+        if (ww < w) wpre += t;
+        block_total += t;
+    }
+    if (w == 0) {
+        if (lane == 0) state[tile] = (tile == 0 ? LB_INC : LB_AGG) | block_total;
+        unsigned long long excl = 0;
+        if (tile > 0) {
+            excl = lookback_exclusive(state, tile, lane);
+            if (lane == 0) state[tile] = LB_INC | (excl + block_total);
+        }
+        if (lane == 0) s_excl = excl;
+    }
+    __syncthreads();
+    int64_t ex = (int64_t)(s_excl + wpre + incl - sum);
+#pragma unroll
+    for (int k = 0; k < SG_ITEMS; ++k) {
+        if (j0 + k < V) {
+            cum[j0 + k] = ex;
+            const int64_t end = ex + v[k];
+            // output blocks whose first slot b*EMIT_OUT lies in [ex, end)
+            for (int64_t b = (ex + (1 << EMIT_OUT_LOG2) - 1) >> EMIT_OUT_LOG2; (b << EMIT_OUT_LOG2) < end; ++b)
+                if (b < first_cap) first_entry[b] = (uint32_t)(j0 + k);
+            ex = end;
+            if (j0 + k == V - 1) { cum[V] = end; *total_out = end; }
+        }
+    }
+}
+
+// emit with the entry table and the fused sort histogram (see the pipeline header above)
+__global__ void __launch_bounds__(EMIT_THREADS)
+isect_emit_hist_kernel(int64_t N, int64_t V, const float2* __restrict__ means2d,
+                       const int32_t* __restrict__ radii, const float* __restrict__ depths,
+                       const int64_t* __restrict__ cum_tiles /*[V+1]*/, const uint32_t* __restrict__ order,
+                       const uint32_t* __restrict__ first_entry, float ts, int tw, int th, int tile_n_bits,
+                       int64_t n_isects, int64_t* __restrict__ isect_ids, int32_t* __restrict__ flatten_ids,
+                       ScPassPlan pp, uint32_t* __restrict__ hist /*[passes][256]*/) {
+    static_assert(EMIT_OUT == (1 << EMIT_OUT_LOG2), "first_entry granularity");
+    __shared__ int s_start[EMIT_THREADS];
+    __shared__ int s_x0[EMIT_THREADS], s_y0[EMIT_THREADS], s_w[EMIT_THREADS];
+    __shared__ uint32_t s_dbits[EMIT_THREADS];
+    __shared__ int s_id[EMIT_THREADS], s_camhi[EMIT_THREADS];
+    __shared__ uint32_t s_hist[4][SC_SORT_RADIX];
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int64_t p0 = (int64_t)blockIdx.x * EMIT_OUT;
+    const int64_t p1 = min(p0 + EMIT_OUT, n_isects);
+    for (int i = tid; i < pp.passes * SC_SORT_RADIX; i += EMIT_THREADS) (&s_hist[0][0])[i] = 0;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    for (int64_t je = __ldg(first_entry + blockIdx.x); je < V; je += EMIT_THREADS) {
+        const int64_t chunk_first = __ldg(cum_tiles + je);
+        if (chunk_first >= p1) break;
+        const int64_t jn = min(je + EMIT_THREADS, V);
+        const int64_t chunk_end = __ldg(cum_tiles + jn);
+        __syncthreads();
+        {
+            const int64_t j = je + tid;
+            int start = 0x7fffffff, x0 = 0, y0 = 0, w = 1, id = 0, camhi = 0;
+            uint32_t dbits = 0;
+            if (j < jn) {
+                const int64_t st = __ldg(cum_tiles + j);
+                start = (int)max(min(st - p0, (int64_t)EMIT_OUT), (int64_t)-0x40000000);
+                if (st < p1) {
+                    const int64_t i = (int64_t)__ldg(order + j);
+                    const float2 m = __ldg(means2d + i);
+                    const TileBox b = tile_box(m.x, m.y, __ldg(radii + i), ts, tw, th);
+                    x0 = b.x0; y0 = b.y0;
+                    w = max(b.x1 - b.x0, 1);
+                    dbits = __float_as_uint(__ldg(depths + i));
+                    id = (int)i;
+                    camhi = (int)(i / N) << tile_n_bits;
+                }
+            }
+            s_start[tid] = start; s_x0[tid] = x0; s_y0[tid] = y0; s_w[tid] = w;
+            s_dbits[tid] = dbits; s_id[tid] = id; s_camhi[tid] = camhi;
+        }
+        __syncthreads();
+        const int qlo = (int)(max(p0, chunk_first) - p0);
+        const int qhi = (int)(min(p1, chunk_end) - p0);
+        // all lanes of a warp iterate together (the histogram uses warp votes)
+        for (int qb = qlo + (tid & ~31); qb < qhi; qb += EMIT_THREADS) {
+            const int q = qb + lane;
+            const bool in = q < qhi;
+            uint32_t hi32 = 0;
+            if (in) {
+                int t = 0;
+#pragma unroll
+                for (int step = EMIT_THREADS / 2; step >= 1; step >>= 1)
+                    if (s_start[t + step] <= q) t += step;
+                const int k = q - s_start[t];
+                const int w = s_w[t];
+                const int ty = s_y0[t] + k / w;
+                const int tx = s_x0[t] + k % w;
+                hi32 = (uint32_t)(s_camhi[t] | (ty * tw + tx));
+                isect_ids[p0 + q] = (int64_t)(((uint64_t)hi32 << 32) | (uint64_t)s_dbits[t]);
+                flatten_ids[p0 + q] = s_id[t];
+            }
+            // pass 0 digits of neighbouring slots are consecutive tiles (distinct): plain atomics;
+            // higher digits are shared by most of the warp: one atomic per distinct digit
+            if (in) atomicAdd(&s_hist[0][(hi32 >> (pp.shift[0] - 32)) & ((1u << pp.nbits[0]) - 1u)], 1u);
+            for (int p = 1; p < pp.passes; ++p) {
+                const uint32_t d = (hi32 >> (pp.shift[p] - 32)) & ((1u << pp.nbits[p]) - 1u);
+                const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu);
+                if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < pp.passes * SC_SORT_RADIX; i += EMIT_THREADS) {
+        const uint32_t v = (&s_hist[0][0])[i];
+        if (v) atomicAdd(&hist[i], v);
+    }
+}
+
 // ------------------------------------------------------------------ offsets (A4)
 __global__ void __launch_bounds__(256)
 isect_offset_encode_kernel(int64_t n_isects, const int64_t* __restrict__ isect_ids, int n_tiles_total,
@@ -404,6 +686,129 @@ extern "C" int sc_isect_emit(int64_t N, int C, const float* means2d, const int32
         N, CN, reinterpret_cast<const float2*>(means2d), radii, depths, cum_tiles, order, (float)tile_size,
         tile_width, tile_height, tile_n_bits, n_isects, isect_ids, flatten_ids);
     SC_CHECK_LAUNCH("isect_emit_kernel");
+    return SC_OK;
+}
+
+// ---- fused binning pipeline (see the kernels' header comment) ----------------------------
+namespace {
+struct IsectWs {
+    ScSortPlan plan32;
+    int64_t cc_tiles, sg_tiles, first_cap;
+    int64_t totals_off, ticket_off, cc_state_off, sg_state_off, sort32_off, ctrl_bytes;
+    int64_t dk_off, od_off, cum_off, first_off, total;
+};
+IsectWs isect_ws_layout(int64_t CN, int64_t n_tiles_total) {
+    IsectWs L;
+    L.plan32 = sc_sort_make_plan(CN, 0, 32);
+    L.cc_tiles = sc_div_up(CN, CC_TILE);
+    L.sg_tiles = sc_div_up(CN, SG_TILE);
+    // n_isects < 2^31 (int32 flatten positions) bounds the number of emit blocks
+    const int64_t max_isects = (CN > 0 && n_tiles_total > (1ll << 31) / CN) ? (1ll << 31) : CN * n_tiles_total;
+    L.first_cap = sc_div_up(max_isects, EMIT_OUT) + 1;
+    int64_t o = 0;
+    L.totals_off = o; o += 256;
+    L.ticket_off = o; o += 256;
+    L.cc_state_off = o; o = sc_align_up(o + L.cc_tiles * 8, 256);
+    L.sg_state_off = o; o = sc_align_up(o + L.sg_tiles * 8, 256);
+    L.sort32_off = o;
+    L.ctrl_bytes = o + L.plan32.ctrl_bytes;
+    o += L.plan32.total;
+    L.dk_off = o; o = sc_align_up(o + 2 * CN * 4, 256);
+    L.od_off = o; o = sc_align_up(o + 2 * CN * 4, 256);
+    L.cum_off = o; o = sc_align_up(o + (CN + 1) * 8, 256);
+    L.first_off = o; o = sc_align_up(o + L.first_cap * 4, 256);
+    L.total = o;
+    return L;
+}
+}  // namespace
+
+extern "C" int64_t sc_isect_workspace_bytes(int64_t CN, int tile_width, int tile_height) {
+    return isect_ws_layout(CN, (int64_t)tile_width * tile_height).total;
+}
+
+extern "C" int sc_isect_prepare(int64_t CN, const float* means2d, const int32_t* radii, const float* depths,
+                                int tile_size, int tile_width, int tile_height, int32_t* tiles_per_gauss,
+                                void* workspace, int64_t workspace_bytes, void* stream) {
+    SC_CHECK_ARG(CN >= 0 && CN < (1ll << 30) && tile_size > 0 && tile_width > 0 && tile_height > 0, "sizes");
+    SC_CHECK_ARG(workspace && ((uintptr_t)workspace & 255) == 0, "workspace (256-byte aligned)");
+    const IsectWs L = isect_ws_layout(CN, (int64_t)tile_width * tile_height);
+    if (workspace_bytes < L.total) {
+        sc_set_error("isect workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)L.total);
+        return SC_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    unsigned char* ws = (unsigned char*)workspace;
+    SC_CUDA(cudaMemsetAsync(ws, 0, (size_t)L.ctrl_bytes, st));
+    if (CN == 0) return SC_OK;
+    SC_CHECK_ARG(means2d && radii && depths && tiles_per_gauss, "null pointer");
+    int64_t* totals = (int64_t*)(ws + L.totals_off);
+    uint32_t* tickets = (uint32_t*)(ws + L.ticket_off);
+    uint32_t* dk0 = (uint32_t*)(ws + L.dk_off);
+    uint32_t* dk1 = dk0 + CN;
+    uint32_t* od0 = (uint32_t*)(ws + L.od_off);
+    uint32_t* od1 = od0 + CN;
+    isect_count_compact_kernel<<<(unsigned)L.cc_tiles, CC_THREADS, 0, st>>>(
+        CN, reinterpret_cast<const float2*>(means2d), radii, depths, (float)tile_size, tile_width, tile_height,
+        tiles_per_gauss, dk0, od0, (volatile unsigned long long*)(ws + L.cc_state_off), tickets + 0, totals);
+    SC_CHECK_LAUNCH("isect_count_compact_kernel");
+    void* sws = ws + L.sort32_off;
+    int rc = sc_sort_histogram_u32(CN, totals, dk0, L.plan32, sws, st);
+    if (rc < 0) return rc;
+    rc = sc_sort_run_u32(CN, totals, dk0, od0, dk1, od1, L.plan32, sws, st);
+    if (rc < 0) return rc;
+    const uint32_t* order = rc == 0 ? od1 : od0;
+    isect_scan_kernel<<<(unsigned)L.sg_tiles, SG_THREADS, 0, st>>>(
+        totals, order, tiles_per_gauss, (int64_t*)(ws + L.cum_off), (uint32_t*)(ws + L.first_off), L.first_cap,
+        (volatile unsigned long long*)(ws + L.sg_state_off), tickets + 1, totals + 1);
+    SC_CHECK_LAUNCH("isect_scan_kernel");
+    return SC_OK;
+}
+
+extern "C" int sc_isect_emit_sorted(int64_t N, int C, const float* means2d, const int32_t* radii,
+                                    const float* depths, int tile_size, int tile_width, int tile_height,
+                                    int tile_n_bits, int cam_bits, int64_t n_visible, int64_t n_isects,
+                                    const void* prepare_workspace, int64_t* isect_ids, int32_t* flatten_ids,
+                                    int64_t* tmp_ids, int32_t* tmp_flatten, void* sort_workspace,
+                                    int64_t sort_workspace_bytes, void* stream) {
+    SC_CHECK_ARG(N >= 0 && C >= 1 && n_isects >= 0 && n_visible >= 0 && n_visible <= N * C, "sizes");
+    SC_CHECK_ARG(tile_n_bits > 0 && cam_bits >= 0 && tile_n_bits + cam_bits <= 32, "key bits");
+    SC_CHECK_ARG(n_isects < (1ll << 30), "n_isects (must be < 2^30)");
+    if (n_isects == 0) return SC_OK;
+    SC_CHECK_ARG(means2d && radii && depths && prepare_workspace && isect_ids && flatten_ids && tmp_ids &&
+                     tmp_flatten && sort_workspace, "null pointer");
+    const int64_t CN = N * C;
+    const IsectWs L = isect_ws_layout(CN, (int64_t)tile_width * tile_height);
+    SC_CHECK_ARG(sc_div_up(n_isects, EMIT_OUT) <= L.first_cap, "n_isects exceeds the entry table");
+    const ScSortPlan plan = sc_sort_make_plan(n_isects, 32, 32 + tile_n_bits + cam_bits);
+    if (sort_workspace_bytes < plan.total) {
+        sc_set_error("sort workspace too small: %lld < %lld", (long long)sort_workspace_bytes,
+                     (long long)plan.total);
+        return SC_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const unsigned char* pws = (const unsigned char*)prepare_workspace;
+    const uint32_t* od0 = (const uint32_t*)(pws + L.od_off);
+    const uint32_t* order = (L.plan32.pp.passes % 2 == 0) ? od0 : od0 + CN;
+    SC_CUDA(cudaMemsetAsync(sort_workspace, 0, (size_t)plan.ctrl_bytes, st));
+    // emit into the buffer from which `passes` ping-pong steps end in (isect_ids, flatten_ids)
+    const bool into_tmp = (plan.pp.passes % 2) != 0;
+    uint64_t* k_a = (uint64_t*)(into_tmp ? tmp_ids : isect_ids);
+    uint32_t* v_a = (uint32_t*)(into_tmp ? tmp_flatten : flatten_ids);
+    uint64_t* k_b = (uint64_t*)(into_tmp ? isect_ids : tmp_ids);
+    uint32_t* v_b = (uint32_t*)(into_tmp ? flatten_ids : tmp_flatten);
+    isect_emit_hist_kernel<<<(unsigned)sc_div_up(n_isects, EMIT_OUT), EMIT_THREADS, 0, st>>>(
+        N, n_visible, reinterpret_cast<const float2*>(means2d), radii, depths,
+        (const int64_t*)(pws + L.cum_off), order, (const uint32_t*)(pws + L.first_off), (float)tile_size,
+        tile_width, tile_height, tile_n_bits, n_isects, (int64_t*)k_a, (int32_t*)v_a, plan.pp,
+        (uint32_t*)((unsigned char*)sort_workspace + plan.hist_off));
+    SC_CHECK_LAUNCH("isect_emit_hist_kernel");
+    const int rc = sc_sort_run_u64(n_isects, nullptr, k_a, v_a, k_b, v_b, plan, sort_workspace, st);
+    if (rc < 0) return rc;
+    const uint64_t* res = rc == 0 ? k_b : k_a;
+    if (res != (const uint64_t*)isect_ids) {
+        sc_set_error("internal: sorted list ended in the wrong buffer");
+        return SC_ERR_CUDA;
+    }
     return SC_OK;
 }
 

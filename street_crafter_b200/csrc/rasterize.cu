@@ -53,14 +53,18 @@ __device__ __forceinline__ PairX pair_x(const StagedA& A, float px) {
     p.v = A.b2 * p.dx;
     return p;
 }
-// un-capped alpha and the accept decision; IDENTICAL instruction sequence in both kernels
-__device__ __forceinline__ bool pair_test(const PairX& X, float c2, float lo, float dy, float& au,
-                                          float& alpha) {
-    const float s2 = fmaf(fmaf(c2, dy, X.v), dy, X.u);  // sigma * log2e
-    au = exp2f(lo - s2);                                // opacity * exp(-sigma)
-    alpha = fminf(SC_ALPHA_CAP, au);
-    return (s2 >= 0.f) && (alpha >= SC_ALPHA_FLOOR);
+// The accept decision, IDENTICAL in both kernels, taken in the log domain so that it needs no
+// SFU result:  sigma >= 0  and  alpha = opacity * exp(-sigma) >= 1/255
+//          <=> 0 <= s2 <= thr,  s2 = sigma * log2(e),  thr = log2(opacity) - log2(1/255)
+//          <=> |s2 - h| <= h,   h = thr / 2            (one add + one compare).
+// A DEAD pixel (saturated in the forward, not yet reached in the backward, or outside the
+// image) holds y = +inf: s2 becomes +inf or NaN and fails the window, so liveness costs no
+// instruction in the per-pair chain.
+__device__ __forceinline__ bool pair_test(const PairX& X, float c2, float h, float dy, float& s2) {
+    s2 = fmaf(fmaf(c2, dy, X.v), dy, X.u);  // sigma * log2e
+    return fabsf(s2 - h) <= h;
 }
+#define SC_DEAD_Y __int_as_float(0x7f800000)
 
 // minimum of f(t) = p t^2 + q t + r over [lo, hi], p > 0
 __device__ __forceinline__ float parabola_min(float p, float q, float r, float lo, float hi) {
@@ -178,9 +182,16 @@ struct WarpSmem {
     StagedB B[BATCH];
     float C[BATCH * CH];
     int G[WITH_GID ? BATCH : 1];
+    int P[PPT][32];  // per-pixel list positions touched only on rare events (kept out of registers)
 };
 
 // ------------------------------------------------------------------------------- forward
+// Per (pixel, Gaussian) pair the chain is: window test (3 FMA-pipe + 2 compares); then, inside
+// one warp-uniform branch per 4 row pairs: ex2, cap, next T, two chained compares (stop / used),
+// one select, and the colour FMAs.  Saturation is a RARE event handled in its own warp-uniform
+// branch (kill the pixel's y, clear its live bit, record where its backward pass starts).
+// last_ids[pixel] = the last list position the backward pass must visit: range_end-1 for a
+// pixel that never saturated, else the position just before the entry that saturated it.
 template <int CH, bool STATS, bool MAXHIT>
 __global__ void __launch_bounds__(WARPS_PER_CTA * 32, FWD_MIN_CTAS)
 rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int tile_w, int tile_h,
@@ -201,30 +212,32 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
     const int tyi = tile_id / tile_w, txi = tile_id - tyi * tile_w;
     const int j = txi * TILE + (lane & 15);
     const int i0 = tyi * TILE + (lane >> 4);
-    const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
+    const float px = (float)j + 0.5f;
     const float X0 = (float)(txi * TILE) + 0.5f, Y0 = (float)(tyi * TILE) + 0.5f;
 
     const int range_start = isect_offsets[tslot];
     const int range_end = (tslot == n_slots - 1) ? (int)n_isects : isect_offsets[tslot + 1];
 
-    float T[PPT], pix[PPT][CH];
-    int last[PPT], hits[PPT], stop[PPT];
-    unsigned live = 0;  // bit r: pixel r still accumulating
+    float T[PPT], pix[PPT][CH], pyv[PPT];
+    int hits[PPT];
+    unsigned live = 0;          // bit r: pixel r still accumulating
     unsigned contributing = 0;  // STATS only
 #pragma unroll
     for (int r = 0; r < PPT; ++r) {
         T[r] = 1.0f;
-        last[r] = -1;
         hits[r] = 0;
-        stop[r] = range_end - 1;
-        if (j < width && i0 + r * ROW_STEP < height) live |= 1u << r;
+        const bool in = j < width && i0 + r * ROW_STEP < height;
+        if (in) live |= 1u << r;
+        pyv[r] = in ? (float)(i0 + r * ROW_STEP) + 0.5f : SC_DEAD_Y;
+        sm.P[r][lane] = range_end - 1;
 #pragma unroll
         for (int c = 0; c < CH; ++c) pix[r][c] = 0.f;
     }
     const unsigned inside = live;
 
     int next = range_start;
-    while (next < range_end && __any_sync(FULL, live != 0)) {
+    bool done = !__any_sync(FULL, live != 0);
+    while (next < range_end && !done) {
         int count = 0;
         while (count <= BATCH - ROUND && next < range_end) {
             count = stage_round<CH, false>(next, 1, min(ROUND, range_end - next), count, lane, X0, Y0, means2d,
@@ -232,58 +245,76 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             next += ROUND;
         }
         __syncwarp();
-        for (int t = 0; t < count; ++t) {
+        for (int t = 0; t < count && !done; ++t) {
             const StagedA A = sm.A[t];
             const StagedB B = sm.B[t];
             const PairX X = pair_x(A, px);
-            const float dy0 = A.y - py0;
+            const float hwin = 0.5f * (B.lo - LOG2_ALPHA_FLOOR);
             float col[CH];
             load_colors<CH>(sm.C, t, col);
-            bool ended = false;
             // two halves of 4 row pairs: one warp-uniform branch each, the 4 pixel chains inside
-            // are branch-free (selects) so that they interleave
+            // are branch-free so that they interleave
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if ((B.rmask >> (4 * h)) & 0xfu) {
-                    float alpha[4];
-                    bool okr[4];
+                    float s2[4];
+                    bool ok[4];
                     bool any_ok = false;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const int r = 4 * h + q;
-                        float au;
-                        okr[q] = pair_test(X, B.c2, B.lo, dy0 - (float)(r * ROW_STEP), au, alpha[q]) &&
-                                 ((live >> r) & 1u);
-                        any_ok |= okr[q];
+                        ok[q] = pair_test(X, B.c2, hwin, A.y - pyv[4 * h + q], s2[q]);
+                        any_ok |= ok[q];
                     }
                     if (__any_sync(FULL, any_ok)) {
+                        float a[4], next_T[4];
+                        bool any_stop = false;
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const int r = 4 * h + q;
-                            const float a = okr[q] ? alpha[q] : 0.f;
-                            const float next_T = fmaf(-a, T[r], T[r]);
-                            bool stop_now = okr[q] && (next_T <= SC_T_STOP);
-                            const float vis = stop_now ? 0.f : a * T[r];
+                            a[q] = ok[q] ? fminf(SC_ALPHA_CAP, exp2f(B.lo - s2[q])) : 0.f;
+                            next_T[q] = fmaf(-a[q], T[r], T[r]);
+                            // a == 0 leaves T (> 1e-4 for every pixel, live or not) unchanged
+                            any_stop |= next_T[q] <= SC_T_STOP;
+                            if (MAXHIT) any_stop |= ok[q] && (hits[r] + 1 >= max_hit);
+                        }
+                        if (!__any_sync(FULL, any_stop)) {
 #pragma unroll
-                            for (int c = 0; c < CH; ++c) pix[r][c] = fmaf(col[c], vis, pix[r][c]);
-                            T[r] = stop_now ? T[r] : next_T;
-                            const bool used = okr[q] && !stop_now;
-                            last[r] = used ? B.idx : last[r];
-                            if (STATS) contributing += used ? 1u : 0u;
-                            if (MAXHIT) {
-                                hits[r] += used ? 1 : 0;
-                                stop_now = stop_now || (used && hits[r] >= max_hit);
+                            for (int q = 0; q < 4; ++q) {
+                                const int r = 4 * h + q;
+                                const float vis = a[q] * T[r];
+#pragma unroll
+                                for (int c = 0; c < CH; ++c) pix[r][c] = fmaf(col[c], vis, pix[r][c]);
+                                T[r] = next_T[q];
+                                if (STATS) contributing += ok[q] ? 1u : 0u;
+                                if (MAXHIT) hits[r] += ok[q] ? 1 : 0;
                             }
-                            if (stop_now) {
-                                live &= ~(1u << r);
-                                ended = true;
-                                if (STATS) stop[r] = B.idx;
+                        } else {  // rare: some pixel saturates (or reaches max_hit) on this entry
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const int r = 4 * h + q;
+                                const bool sat = next_T[q] <= SC_T_STOP;  // stops BEFORE using the entry
+                                const bool used = ok[q] && !sat;
+                                const float vis = used ? a[q] * T[r] : 0.f;
+#pragma unroll
+                                for (int c = 0; c < CH; ++c) pix[r][c] = fmaf(col[c], vis, pix[r][c]);
+                                T[r] = used ? next_T[q] : T[r];
+                                if (STATS) contributing += used ? 1u : 0u;
+                                bool full = false;  // max_hit stops AFTER using the entry
+                                if (MAXHIT) {
+                                    hits[r] += used ? 1 : 0;
+                                    full = used && hits[r] >= max_hit;
+                                }
+                                if (sat || full) {
+                                    pyv[r] = SC_DEAD_Y;
+                                    live &= ~(1u << r);
+                                    sm.P[r][lane] = full ? B.idx : B.idx - 1;
+                                }
                             }
+                            done = !__any_sync(FULL, live != 0);
                         }
                     }
                 }
             }
-            if (__any_sync(FULL, ended) && !__any_sync(FULL, live != 0)) break;
         }
         __syncwarp();
     }
@@ -305,17 +336,22 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                     render_colors[pix_id * CH + c] =
                         backgrounds ? pix[r][c] + T[r] * __ldg(backgrounds + cam * CH + c) : pix[r][c];
             }
-            if (last_ids) last_ids[pix_id] = last[r];
+            if (last_ids) last_ids[pix_id] = sm.P[r][lane];
             if (final_T) final_T[pix_id] = T[r];
         }
     }
     if (STATS) {
-        // visited = list entries up to and including the one that saturated the pixel (the
-        // algorithmic count: independent of the culling above)
+        // visited = list entries up to and including the one that ended the pixel (the
+        // algorithmic count: independent of the culling above); a pixel that never ended
+        // visited its whole list
         unsigned long long v = 0, c = contributing;
 #pragma unroll
         for (int r = 0; r < PPT; ++r)
-            if (inside & (1u << r)) v += (unsigned long long)(stop[r] - range_start + 1);
+            if (inside & (1u << r)) {
+                const int lastp = sm.P[r][lane];
+                const int visited_to = (live & (1u << r)) ? range_end - 1 : min(lastp + 1, range_end - 1);
+                v += (unsigned long long)max(visited_to - range_start + 1, 0);
+            }
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) {
             v += __shfl_xor_sync(FULL, v, o);
@@ -361,6 +397,8 @@ __device__ __forceinline__ float warp_reduce_scatter16(float (&v)[16], int lane)
 
 // Slots of the reduced vector: 0..4 v_colors, 5..7 second moments (w dx dx, w dx dy, w dy dy),
 // 8..9 sum w*h (h = d s2 / d mean), 10..11 the same with |.|, 12 sum w;  w = -au * v_alpha.
+// A pixel joins the walk when the list position reaches its last_ids entry (a rare event,
+// handled in its own warp-uniform branch: until then its y is +inf and every test fails).
 template <int CH>
 __global__ void __launch_bounds__(WARPS_PER_CTA * 32, BWD_MIN_CTAS)
 rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int tile_w, int tile_h,
@@ -384,14 +422,13 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
     const int tyi = tile_id / tile_w, txi = tile_id - tyi * tile_w;
     const int j = txi * TILE + (lane & 15);
     const int i0 = tyi * TILE + (lane >> 4);
-    const float px = (float)j + 0.5f, py0 = (float)i0 + 0.5f;
+    const float px = (float)j + 0.5f;
     const float X0 = (float)(txi * TILE) + 0.5f, Y0 = (float)(tyi * TILE) + 0.5f;
     const int range_start = isect_offsets[tslot];
 
     // per-pixel state: T (running transmittance, walking back), R = <v_rc, colour behind> -
     // T_final * v_ra (+ T_final * <bg, v_rc>), so that v_alpha = <v_rc,col> * T - R / (1-alpha)
-    float T[PPT], R[PPT], v_rc[PPT][CH];
-    int binf[PPT];
+    float T[PPT], R[PPT], v_rc[PPT][CH], pyv[PPT];
     int tile_last = -1;
 #pragma unroll
     for (int r = 0; r < PPT; ++r) {
@@ -399,9 +436,11 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
         const bool inside = (i < height) && (j < width);
         const int64_t pix_id = ((int64_t)cam * height + min(i, height - 1)) * width + min(j, width - 1);
         const float Tf = inside ? final_T[pix_id] : 1.0f;
-        binf[r] = inside ? last_ids[pix_id] : -1;
-        tile_last = max(tile_last, binf[r]);
+        const int binf = inside ? last_ids[pix_id] : -1;
+        sm.P[r][lane] = binf;
+        tile_last = max(tile_last, binf);
         T[r] = Tf;
+        pyv[r] = SC_DEAD_Y;
         float bg_dot = 0.f;
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
@@ -415,6 +454,27 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) tile_last = max(tile_last, __shfl_xor_sync(FULL, tile_last, o));
     if (tile_last < range_start) return;
+    int next_wake = tile_last;  // largest last id among this lane's sleeping pixels (-1: none)
+    {
+        int m = -1;
+#pragma unroll
+        for (int r = 0; r < PPT; ++r) m = max(m, sm.P[r][lane]);
+        next_wake = m;
+    }
+
+    // where this lane's reduced value goes (lane pair k = lane >> 1 ends with slot k)
+    const int k_slot = lane >> 1;
+    float* my_base = nullptr;
+    int my_stride = 0;
+    float my_scale = 1.0f;
+    if ((lane & 1) == 0) {
+        if (k_slot < CH) { my_base = v_colors + k_slot; my_stride = CH; }
+        else if (k_slot >= 5 && k_slot < 8) { my_base = v_conics + (k_slot - 5); my_stride = 3; my_scale = (k_slot == 6) ? 1.0f : 0.5f; }
+        else if (k_slot == 8 || k_slot == 9) { my_base = v_means2d + (k_slot - 8); my_stride = 2; my_scale = LN2; }
+        else if ((k_slot == 10 || k_slot == 11) && v_means2d_abs) { my_base = v_means2d_abs + (k_slot - 10); my_stride = 2; my_scale = LN2; }
+        else if (k_slot == 12) { my_base = v_opacities; my_stride = 1; }
+    }
+    const bool my_is_opacity = k_slot == 12;
 
     int next = tile_last;  // candidates are taken from here downwards
     while (next >= range_start) {
@@ -429,8 +489,22 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
         for (int t = 0; t < count; ++t) {
             const StagedA A = sm.A[t];
             const StagedB B = sm.B[t];
+            if (__any_sync(FULL, B.idx <= next_wake)) {  // rare: a pixel's walk starts at this entry
+                int m = -1;
+#pragma unroll
+                for (int r = 0; r < PPT; ++r) {
+                    const int b = sm.P[r][lane];
+                    if (b >= B.idx) {
+                        pyv[r] = (float)(i0 + r * ROW_STEP) + 0.5f;
+                        sm.P[r][lane] = -1;
+                    } else {
+                        m = max(m, b);
+                    }
+                }
+                next_wake = m;
+            }
             const PairX X = pair_x(A, px);
-            const float dy0 = A.y - py0;
+            const float hwin = 0.5f * (B.lo - LOG2_ALPHA_FLOOR);
             float col[CH];
             load_colors<CH>(sm.C, t, col);
             const float hx0 = 2.0f * A.a2 * X.dx;  // d s2 / d mean.x = 2 a2 dx + b2 dy
@@ -440,27 +514,28 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             for (int k = 0; k < 16; ++k) v[k] = 0.f;
             bool any_entry = false;
             // two halves of 4 row pairs: one warp-uniform branch each; the 4 pixel chains inside
-            // are branch-free (selects) so that they interleave
+            // are branch-free so that they interleave
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if ((B.rmask >> (4 * h)) & 0xfu) {
-                    float alpha[4], au[4];
-                    bool okr[4];
+                    float s2[4], dyq[4];
+                    bool ok[4];
                     bool any_ok = false;
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const int r = 4 * h + q;
-                        okr[q] = pair_test(X, B.c2, B.lo, dy0 - (float)(r * ROW_STEP), au[q], alpha[q]) &&
-                                 (B.idx <= binf[r]);
-                        any_ok |= okr[q];
+                        dyq[q] = A.y - pyv[4 * h + q];
+                        ok[q] = pair_test(X, B.c2, hwin, dyq[q], s2[q]);
+                        any_ok |= ok[q];
                     }
                     if (__any_sync(FULL, any_ok)) {
                         any_entry = true;
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const int r = 4 * h + q;
-                            const float dy = dy0 - (float)(r * ROW_STEP);
-                            const float a = okr[q] ? alpha[q] : 0.f;
+                            // a dead pixel has dy = -inf: keep it out of the moment sums
+                            const float dy = ok[q] ? dyq[q] : 0.f;
+                            const float au = exp2f(B.lo - s2[q]);
+                            const float a = ok[q] ? fminf(SC_ALPHA_CAP, au) : 0.f;
                             const float ra = __fdividef(1.0f, 1.0f - a);  // MUFU.RCP; exactly 1 when the pair is not used
                             T[r] *= ra;
                             const float fac = a * T[r];
@@ -472,17 +547,17 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                             }
                             const float v_alpha = d * T[r] - R[r] * ra;
                             R[r] = fmaf(d, fac, R[r]);
-                            const float w = (okr[q] && au[q] <= SC_ALPHA_CAP) ? -au[q] * v_alpha : 0.f;
+                            const float w = (ok[q] && au <= SC_ALPHA_CAP) ? -au * v_alpha : 0.f;
                             const float wdx = w * X.dx, wdy = w * dy;
                             v[5] = fmaf(wdx, X.dx, v[5]);
                             v[6] = fmaf(wdx, dy, v[6]);
                             v[7] = fmaf(wdy, dy, v[7]);
-                            const float gx = w * fmaf(A.b2, dy, hx0);
-                            const float gy = w * fmaf(c2x2, dy, X.v);
-                            v[8] += gx;
-                            v[9] += gy;
-                            v[10] += fabsf(gx);
-                            v[11] += fabsf(gy);
+                            const float hx = fmaf(A.b2, dy, hx0);
+                            const float hy = fmaf(c2x2, dy, X.v);
+                            v[8] = fmaf(w, hx, v[8]);
+                            v[9] = fmaf(w, hy, v[9]);
+                            v[10] = fmaf(fabsf(w), fabsf(hx), v[10]);
+                            v[11] = fmaf(fabsf(w), fabsf(hy), v[11]);
                             v[12] += w;
                         }
                     }
@@ -490,18 +565,8 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             }
             if (!any_entry) continue;  // warp-uniform
             const float red = warp_reduce_scatter16(v, lane);
-            if ((lane & 1) == 0) {
-                const int k = lane >> 1;
-                const int64_t g = sm.G[t];
-                float* dst = nullptr;
-                float val = red;
-                if (k < CH) dst = v_colors + g * CH + k;
-                else if (k >= 5 && k < 8) { dst = v_conics + g * 3 + (k - 5); val *= (k == 6) ? 1.0f : 0.5f; }
-                else if (k == 8 || k == 9) { dst = v_means2d + g * 2 + (k - 8); val *= LN2; }
-                else if ((k == 10 || k == 11) && v_means2d_abs) { dst = v_means2d_abs + g * 2 + (k - 10); val *= LN2; }
-                else if (k == 12) { dst = v_opacities + g; val *= -exp2f(-B.lo); }
-                if (dst && val != 0.f) atomicAdd(dst, val);
-            }
+            const float val = red * (my_is_opacity ? -exp2f(-B.lo) : my_scale);
+            if (my_base && val != 0.f) atomicAdd(my_base + (int64_t)sm.G[t] * my_stride, val);
         }
         __syncwarp();
     }

@@ -11,6 +11,7 @@
 //     always resident (forward progress).
 //   * only the significant key bits are sorted: 32 depth bits + tile bits (+ camera bits).
 #include "common.cuh"
+#include "sort_internal.cuh"
 
 namespace {
 
@@ -95,12 +96,13 @@ scan_apply_kernel(int64_t n, const int32_t* __restrict__ in, const int64_t* __re
 
 // ------------------------------------------------------------------------------- radix sort
 constexpr int RADIX_BITS = 8;
-constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int RADIX = SC_SORT_RADIX;
+static_assert(RADIX == (1 << RADIX_BITS), "radix");
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_KPT = 16;
 constexpr int SORT_TILE = SORT_THREADS * SORT_KPT;  // 4096 pairs
-constexpr int MAX_PASSES = 8;
+constexpr int MAX_PASSES = SC_SORT_MAX_PASSES;
 constexpr int SORT_MIN_BLOCKS = 3;  // caps registers at 85/thread: 3 CTAs (24 warps) per SM
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_INC = 2u << 30;
@@ -118,18 +120,14 @@ struct SortSmem {
     uint32_t tile_id;
 };
 
-// per-pass digit layout: pass p sorts bits [shift[p], shift[p]+nbits[p])
-struct PassPlan {
-    int passes;
-    int shift[MAX_PASSES];
-    int nbits[MAX_PASSES];
-};
+using PassPlan = ScPassPlan;
 
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
-sort_histogram_kernel(int64_t n, const KeyT* __restrict__ keys, PassPlan pp,
+sort_histogram_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* __restrict__ keys, PassPlan pp,
                       uint32_t* __restrict__ hist /*[passes][RADIX]*/) {
     extern __shared__ uint32_t s_hist[];  // [passes][RADIX]
+    if (n_dev) n = min(n, *n_dev);
     for (int i = threadIdx.x; i < pp.passes * RADIX; i += blockDim.x) s_hist[i] = 0;
     __syncthreads();
     // warp-aggregated shared atomics: the keys of one warp share most high digits (same tile,
@@ -176,7 +174,8 @@ sort_hist_scan_kernel(uint32_t* __restrict__ hist) {
 
 template <typename KeyT>
 __global__ void __launch_bounds__(SORT_THREADS, SORT_MIN_BLOCKS)
-onesweep_pass_kernel(int64_t n, const KeyT* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* __restrict__ keys_in,
+                     const uint32_t* __restrict__ vals_in,
                      KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int nbits,
                      const uint32_t* __restrict__ digit_offset /*[RADIX] exclusive*/,
                      volatile uint32_t* __restrict__ lookback /*[tiles][RADIX]*/,
@@ -186,11 +185,13 @@ onesweep_pass_kernel(int64_t n, const KeyT* __restrict__ keys_in, const uint32_t
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t dmask = (1u << nbits) - 1u;
 
+    if (n_dev) n = min(n, *n_dev);
     if (tid == 0) sm.tile_id = atomicAdd(ticket, 1u);
     for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&sm.warp_hist[0][0])[i] = 0;
     __syncthreads();
     const uint32_t tile = sm.tile_id;
     const int64_t tile_base = (int64_t)tile * SORT_TILE;
+    if (tile_base >= n) return;  // grid is sized for the maximum count (device-resident n)
     const int n_valid = (int)min((int64_t)SORT_TILE, n - tile_base);
 
     // ---- load keys (warp-striped: item i of lane l = warp_base + i*32 + l)
@@ -292,62 +293,30 @@ onesweep_pass_kernel(int64_t n, const KeyT* __restrict__ keys_in, const uint32_t
     }
 }
 
-struct SortPlan {
-    PassPlan pp;
-    int64_t tiles;
-    int64_t hist_off, lookback_off, ticket_off, total;
-};
-
-// passes of <= 8 bits over [begin_bit, end_bit), widths balanced (14 bits -> 7+7, not 8+6)
-SortPlan make_plan(int64_t n, int begin_bit, int end_bit) {
-    SortPlan p;
-    const int bits = end_bit - begin_bit;
-    p.pp.passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
-    int shift = begin_bit, left = bits;
-    for (int i = 0; i < MAX_PASSES; ++i) {
-        const int remaining = p.pp.passes - i;
-        const int nb = remaining > 0 ? (left + remaining - 1) / remaining : 0;
-        p.pp.shift[i] = shift;
-        p.pp.nbits[i] = nb;
-        shift += nb;
-        left -= nb;
-    }
-    p.tiles = sc_div_up(n, SORT_TILE);
-    p.hist_off = 0;
-    p.ticket_off = sc_align_up((int64_t)MAX_PASSES * RADIX * 4, 256);
-    p.lookback_off = p.ticket_off + 256;
-    p.total = p.lookback_off + (int64_t)MAX_PASSES * p.tiles * RADIX * 4;
-    return p;
+template <typename KeyT>
+int sort_histogram(int64_t n_max, const int64_t* n_dev, const KeyT* keys, const ScSortPlan& plan, void* ws,
+                   cudaStream_t st) {
+    if (n_max == 0) return SC_OK;
+    uint32_t* hist = (uint32_t*)((unsigned char*)ws + plan.hist_off);
+    const int grid = (int)min(sc_div_up(n_max, 256 * 8), (int64_t)SC_NUM_SMS * 8);
+    sort_histogram_kernel<KeyT><<<grid, 256, plan.pp.passes * RADIX * 4, st>>>(n_max, n_dev, keys, plan.pp, hist);
+    SC_CHECK_LAUNCH("sort_histogram_kernel");
+    return SC_OK;
 }
 
 // returns 0 if the sorted pairs are in keys_out/vals_out, 1 if they are in keys_in/vals_in
 // (even number of passes), negative on error.
 template <typename KeyT>
-int radix_sort_pairs(int64_t n, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out, uint32_t* vals_out,
-                     int begin_bit, int end_bit, void* workspace, int64_t workspace_bytes, void* stream) {
-    SC_CHECK_ARG(n >= 0 && n < (1ll << 30), "n (must be < 2^30)");
-    SC_CHECK_ARG(begin_bit >= 0 && end_bit > begin_bit && end_bit <= (int)sizeof(KeyT) * 8, "bit range");
-    if (n == 0) return 0;
-    SC_CHECK_ARG(keys_in && vals_in && keys_out && vals_out && workspace, "null pointer");
-    const SortPlan plan = make_plan(n, begin_bit, end_bit);
-    if (workspace_bytes < plan.total) {
-        sc_set_error("sort workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)plan.total);
-        return SC_ERR_WORKSPACE;
-    }
-    cudaStream_t st = (cudaStream_t)stream;
+int sort_run(int64_t n_max, const int64_t* n_dev, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out,
+             uint32_t* vals_out, const ScSortPlan& plan, void* workspace, cudaStream_t st) {
+    if (n_max == 0) return 0;
     unsigned char* ws = (unsigned char*)workspace;
     uint32_t* hist = (uint32_t*)(ws + plan.hist_off);
     uint32_t* tickets = (uint32_t*)(ws + plan.ticket_off);
     uint32_t* lookback = (uint32_t*)(ws + plan.lookback_off);
     const int passes = plan.pp.passes;
-    SC_CUDA(cudaMemsetAsync(ws, 0, (size_t)(plan.lookback_off + (int64_t)passes * plan.tiles * RADIX * 4), st));
-    {
-        const int grid = (int)min(sc_div_up(n, 256 * 8), (int64_t)SC_NUM_SMS * 8);
-        sort_histogram_kernel<KeyT><<<grid, 256, passes * RADIX * 4, st>>>(n, keys_in, plan.pp, hist);
-        SC_CHECK_LAUNCH("sort_histogram_kernel");
-        sort_hist_scan_kernel<<<passes, RADIX, 0, st>>>(hist);
-        SC_CHECK_LAUNCH("sort_hist_scan_kernel");
-    }
+    sort_hist_scan_kernel<<<passes, RADIX, 0, st>>>(hist);
+    SC_CHECK_LAUNCH("sort_hist_scan_kernel");
     static bool attr_set = false;  // one flag per KeyT instantiation
     if (!attr_set) {
         SC_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -360,7 +329,7 @@ int radix_sort_pairs(int64_t n, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out
     uint32_t* vout = vals_out;
     for (int p = 0; p < passes; ++p) {
         onesweep_pass_kernel<KeyT><<<(unsigned)plan.tiles, SORT_THREADS, sizeof(SortSmem<KeyT>), st>>>(
-            n, kin, vin, kout, vout, plan.pp.shift[p], plan.pp.nbits[p], hist + p * RADIX,
+            n_max, n_dev, kin, vin, kout, vout, plan.pp.shift[p], plan.pp.nbits[p], hist + p * RADIX,
             lookback + (size_t)p * plan.tiles * RADIX, tickets + p);
         SC_CHECK_LAUNCH("onesweep_pass_kernel");
         KeyT* tk = kin; kin = kout; kout = tk;
@@ -370,7 +339,66 @@ int radix_sort_pairs(int64_t n, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out
     return kin == keys_out ? 0 : 1;
 }
 
+template <typename KeyT>
+int radix_sort_pairs(int64_t n, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out, uint32_t* vals_out,
+                     int begin_bit, int end_bit, void* workspace, int64_t workspace_bytes, void* stream) {
+    SC_CHECK_ARG(n >= 0 && n < (1ll << 30), "n (must be < 2^30)");
+    SC_CHECK_ARG(begin_bit >= 0 && end_bit > begin_bit && end_bit <= (int)sizeof(KeyT) * 8, "bit range");
+    if (n == 0) return 0;
+    SC_CHECK_ARG(keys_in && vals_in && keys_out && vals_out && workspace, "null pointer");
+    const ScSortPlan plan = sc_sort_make_plan(n, begin_bit, end_bit);
+    if (workspace_bytes < plan.total) {
+        sc_set_error("sort workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)plan.total);
+        return SC_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    SC_CUDA(cudaMemsetAsync(workspace, 0, (size_t)plan.ctrl_bytes, st));
+    const int rc = sort_histogram<KeyT>(n, nullptr, keys_in, plan, workspace, st);
+    if (rc < 0) return rc;
+    return sort_run<KeyT>(n, nullptr, keys_in, vals_in, keys_out, vals_out, plan, workspace, st);
+}
+
 }  // namespace
+
+// passes of <= 8 bits over [begin_bit, end_bit), widths balanced (14 bits -> 7+7, not 8+6)
+ScSortPlan sc_sort_make_plan(int64_t n_max, int begin_bit, int end_bit) {
+    ScSortPlan p;
+    const int bits = end_bit - begin_bit;
+    p.pp.passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
+    int shift = begin_bit, left = bits;
+    for (int i = 0; i < MAX_PASSES; ++i) {
+        const int remaining = p.pp.passes - i;
+        const int nb = remaining > 0 ? (left + remaining - 1) / remaining : 0;
+        p.pp.shift[i] = shift;
+        p.pp.nbits[i] = nb;
+        shift += nb;
+        left -= nb;
+    }
+    p.tiles = sc_div_up(n_max, SORT_TILE);
+    p.hist_off = 0;
+    p.ticket_off = sc_align_up((int64_t)MAX_PASSES * RADIX * 4, 256);
+    p.lookback_off = p.ticket_off + 256;
+    p.ctrl_bytes = p.lookback_off + (int64_t)p.pp.passes * p.tiles * RADIX * 4;
+    p.total = sc_align_up(p.lookback_off + (int64_t)MAX_PASSES * p.tiles * RADIX * 4, 256);
+    return p;
+}
+
+int sc_sort_histogram_u32(int64_t n_max, const int64_t* n_dev, const uint32_t* keys, const ScSortPlan& plan,
+                          void* ws, cudaStream_t st) {
+    return sort_histogram<uint32_t>(n_max, n_dev, keys, plan, ws, st);
+}
+int sc_sort_histogram_u64(int64_t n_max, const int64_t* n_dev, const uint64_t* keys, const ScSortPlan& plan,
+                          void* ws, cudaStream_t st) {
+    return sort_histogram<uint64_t>(n_max, n_dev, keys, plan, ws, st);
+}
+int sc_sort_run_u32(int64_t n_max, const int64_t* n_dev, uint32_t* keys_in, uint32_t* vals_in,
+                    uint32_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st) {
+    return sort_run<uint32_t>(n_max, n_dev, keys_in, vals_in, keys_out, vals_out, plan, ws, st);
+}
+int sc_sort_run_u64(int64_t n_max, const int64_t* n_dev, uint64_t* keys_in, uint32_t* vals_in,
+                    uint64_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st) {
+    return sort_run<uint64_t>(n_max, n_dev, keys_in, vals_in, keys_out, vals_out, plan, ws, st);
+}
 
 extern "C" int64_t sc_scan_workspace_bytes(int64_t n) { return (sc_div_up(n, SCAN_TILE) + 1) * 8; }
 
@@ -399,7 +427,7 @@ extern "C" int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out,
     return SC_OK;
 }
 
-extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return make_plan(n, 0, 64).total; }
+extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return sc_sort_make_plan(n, 0, 64).total; }
 
 extern "C" int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
                                    uint32_t* vals_out, int begin_bit, int end_bit, void* workspace,

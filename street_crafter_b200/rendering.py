@@ -255,48 +255,41 @@ def isect_tiles(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int, 
     end_bit = 32 + bits + cam_bits
     with torch.cuda.device(dev):
         tpg = torch.empty((C, N), dtype=torch.int32, device=dev)
+        if sort:
+            # fused pipeline: compaction of the emitting entries + their stable depth order +
+            # scan (one C call), the host read-back of {n_visible, n_isects}, then emit + tile
+            # sort on the (camera, tile) bits only (one C call)
+            ws_bytes = int(lib.sc_isect_workspace_bytes(CN, tile_width, tile_height))
+            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+            check(lib.sc_isect_prepare(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width,
+                                       tile_height, _p(tpg), _p(ws), ws_bytes, st), "sc_isect_prepare")
+            n_visible, n_isects = ws[:16].view(torch.int64).tolist()  # the one D->H sync of the pipeline
+            ids = torch.empty((2, n_isects), dtype=torch.int64, device=dev)
+            flat = torch.empty((2, n_isects), dtype=torch.int32, device=dev)
+            if n_isects == 0:
+                return tpg, ids[0], flat[0]
+            sws_bytes = int(lib.sc_sort_workspace_bytes(n_isects))
+            sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
+            check(lib.sc_isect_emit_sorted(N, C, _p(means2d), _p(radii), _p(depths), tile_size, tile_width,
+                                           tile_height, bits, cam_bits, n_visible, n_isects, _p(ws),
+                                           _p(ids[0]), _p(flat[0]), _p(ids[1]), _p(flat[1]), _p(sws),
+                                           sws_bytes, st), "sc_isect_emit_sorted")
+            return tpg, ids[0], flat[0]
+        # unsorted (gsplat's sort=False): entry order, through the stand-alone entry points
         cum = torch.empty(CN + 1, dtype=torch.int64, device=dev)
         ws_bytes = int(lib.sc_scan_workspace_bytes(CN))
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        order = None
-        if sort:
-            # depth pre-sort of the C*N entries (u32 keys, 4 passes over N-sized arrays), so that
-            # the I-sized intersection list only needs sorting on its (camera, tile) bits
-            dk = torch.empty((2, CN), dtype=torch.int32, device=dev)
-            od = torch.empty((2, CN), dtype=torch.int32, device=dev)
-            check(lib.sc_isect_count(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width, tile_height,
-                                     _p(tpg), _p(dk[0]), _p(od[0]), st), "sc_isect_count")
-            sws_bytes = int(lib.sc_sort_workspace_bytes(CN))
-            sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
-            where = check(lib.sc_radix_sort_pairs_u32(CN, _p(dk[0]), _p(od[0]), _p(dk[1]), _p(od[1]), 0, 32,
-                                                      _p(sws), sws_bytes, st), "sc_radix_sort_pairs_u32")
-            order = od[1] if where == 0 else od[0]
-            counts = dk[0] if where == 0 else dk[1]  # the free key buffer is reused for the counts
-            check(lib.sc_isect_gather_counts(CN, _p(order), _p(tpg), _p(counts), st), "sc_isect_gather_counts")
-        else:
-            check(lib.sc_isect_count(CN, _p(means2d), _p(radii), None, tile_size, tile_width, tile_height,
-                                     _p(tpg), None, None, st), "sc_isect_count")
-            counts = tpg
-        check(lib.sc_exclusive_scan_i32(CN, _p(counts), _p(cum), cum.data_ptr() + 8 * CN, _p(ws), ws_bytes, st),
+        check(lib.sc_isect_count(CN, _p(means2d), _p(radii), None, tile_size, tile_width, tile_height,
+                                 _p(tpg), None, None, st), "sc_isect_count")
+        check(lib.sc_exclusive_scan_i32(CN, _p(tpg), _p(cum), cum.data_ptr() + 8 * CN, _p(ws), ws_bytes, st),
               "sc_exclusive_scan_i32")
-        n_isects = int(cum[CN].item())  # the one D->H sync of the pipeline
+        n_isects = int(cum[CN].item())
         ids_a = torch.empty(n_isects, dtype=torch.int64, device=dev)
         flat_a = torch.empty(n_isects, dtype=torch.int32, device=dev)
-        if n_isects == 0:
-            return tpg, ids_a, flat_a
-        check(lib.sc_isect_emit(N, C, _p(means2d), _p(radii), _p(depths), _p(cum), _p(order), tile_size,
-                                tile_width, tile_height, bits, n_isects, _p(ids_a), _p(flat_a), st),
-              "sc_isect_emit")
-        if not sort:
-            return tpg, ids_a, flat_a
-        ids_b = torch.empty_like(ids_a)
-        flat_b = torch.empty_like(flat_a)
-        sws_bytes = int(lib.sc_sort_workspace_bytes(n_isects))
-        sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
-        where = check(lib.sc_radix_sort_pairs(n_isects, _p(ids_a), _p(flat_a), _p(ids_b), _p(flat_b),
-                                              32, end_bit, _p(sws), sws_bytes, st), "sc_radix_sort_pairs")
-    if where == 0:
-        return tpg, ids_b, flat_b
+        if n_isects:
+            check(lib.sc_isect_emit(N, C, _p(means2d), _p(radii), _p(depths), _p(cum), None, tile_size,
+                                    tile_width, tile_height, bits, n_isects, _p(ids_a), _p(flat_a), st),
+                  "sc_isect_emit")
     return tpg, ids_a, flat_a
 
 

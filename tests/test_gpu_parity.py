@@ -132,7 +132,7 @@ def _binning_case(n, W, H, seed, C=1):
 
 
 @pytest.mark.parametrize("n,W,H,C", [(30000, 960, 640, 1), (4000, 1920, 886, 1), (2000, 320, 192, 3),
-                                     (50, 33, 17, 1)])
+                                     (50, 33, 17, 1), (150000, 960, 640, 1), (40000, 640, 384, 2)])
 def test_isect_bit_exact(S, dev, n, W, H, C):
     s, V, K, (radii, m2, dep, con, comp) = _binning_case(n, W, H, seed=n + C, C=C)
     tw, th = math.ceil(W / 16), math.ceil(H / 16)
