@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libscb200.so")
+# SCB200_LIB (tuning sweeps only): load a pre-built variant of the library instead
+LIB_PATH = os.environ.get("SCB200_LIB") or os.path.join(_HERE, "libscb200.so")
 
 _i64, _i32, _f32, _ptr = C.c_int64, C.c_int, C.c_float, C.c_void_p
 
@@ -61,11 +62,12 @@ def _load() -> C.CDLL:
     """dlopen the in-tree library, (re)building it first with nvcc when it is missing or older
     than its sources (nvcc cross-compiles sm_100a without a GPU).  Never a CPU fallback."""
     from .build import build
-    try:
-        build()  # incremental: a no-op when libscb200.so is newer than every source
-    except Exception:
-        if not os.path.exists(LIB_PATH):
-            raise
+    if not os.environ.get("SCB200_LIB"):
+        try:
+            build()  # incremental: a no-op when libscb200.so is newer than every source
+        except Exception:
+            if not os.path.exists(LIB_PATH):
+                raise
     try:
         return _bind(LIB_PATH)
     except AttributeError as e:

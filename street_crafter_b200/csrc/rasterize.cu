@@ -13,9 +13,9 @@
 //     memory with one ballot, together with an 8-bit row-pair mask.  A rejected entry costs
 //     ~1 issue slot instead of a full per-pixel evaluation by all 32 lanes, and the
 //     compositing loop only evaluates the row pairs the ellipse can reach;
-//   * backward: a lane first accumulates the 12 per-Gaussian partials over its own 8 pixels
-//     in registers (the adds fold into FMAs), then ONE halving butterfly per (tile, Gaussian)
-//     (16 shuffles) leaves one finished sum per lane pair and 12 lanes issue one
+//   * backward: a lane first accumulates the 13 per-Gaussian partials over its own 8 pixels
+//     in registers (the adds fold into FMAs), then ONE transposed reduction through shared
+//     memory per (tile, Gaussian) leaves one finished sum per lane pair and 13 lanes issue one
 //     red.global.add each — per-Gaussian accumulation, no per-pixel atomics.  means2d
 //     gradients are reduced as raw moments and scaled once per Gaussian after the reduction.
 // Forward and backward share the cull and the pair test verbatim, so they take identical
@@ -40,6 +40,8 @@ constexpr float LN2 = 0.6931471805599453f;
 constexpr float LOG2_ALPHA_FLOOR = -7.994353436858858f;  // log2(1/255)
 constexpr float CULL_MARGIN = 1e-3f;  // slack of the conservative cull (log2 units of alpha)
 
+constexpr int NRED = 13;         // reduced values per (tile, Gaussian) in the backward pass
+constexpr int RED_STRIDE = 36;   // floats per row: 16-byte aligned, conflict-free LDS.128 (see warp_reduce_rows)
 struct __align__(16) StagedA { float x, y, a2, b2; };  // a2 = .5*a*log2e, b2 = b*log2e
 // c2 = .5*c*log2e, lo = log2(opacity), idx = position in flatten_ids, rmask = row pairs to test
 struct __align__(16) StagedB { float c2, lo; int idx; unsigned rmask; };
@@ -172,9 +174,16 @@ __device__ __forceinline__ int stage_round(int first, int step, int n_cand, int 
     return count;
 }
 
+// tuning knobs (overridable with -D for the sweeps of tools/raster_variants.sh)
+#ifndef SC_FWD_MIN_CTAS
+#define SC_FWD_MIN_CTAS 4  // register cap 128 -> 16 warps per SM: no spills beats more warps (tools/raster_variants.sh)
+#endif
+#ifndef SC_BWD_MIN_CTAS
+#define SC_BWD_MIN_CTAS 4  // register cap 128 -> 16 warps per SM
+#endif
 constexpr int WARPS_PER_CTA = 4;  // independent tiles per CTA (no inter-warp communication)
-constexpr int FWD_MIN_CTAS = 6;   // register cap 80 -> 24 warps per SM
-constexpr int BWD_MIN_CTAS = 4;   // register cap 128 -> 16 warps per SM
+constexpr int FWD_MIN_CTAS = SC_FWD_MIN_CTAS;
+constexpr int BWD_MIN_CTAS = SC_BWD_MIN_CTAS;
 
 template <int CH, bool WITH_GID>
 struct WarpSmem {
@@ -183,6 +192,7 @@ struct WarpSmem {
     float C[BATCH * CH];
     int G[WITH_GID ? BATCH : 1];
     int P[PPT][32];  // per-pixel list positions touched only on rare events (kept out of registers)
+    float Rd[WITH_GID ? NRED : 1][RED_STRIDE];  // backward: transposed per-lane partials
 };
 
 // ------------------------------------------------------------------------------- forward
@@ -365,34 +375,27 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 }
 
 // ------------------------------------------------------------------------------- backward
-// Halving butterfly: 16 per-lane values -> lane l (and its xor-1 partner) ends with the full
-// warp sum of value index (l >> 1).
-__device__ __forceinline__ float warp_reduce_scatter16(float (&v)[16], int lane) {
-    float w8[8], w4[4], w2[2];
-    const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
+// Sum of NRED per-lane values over the warp, through shared memory: every lane stores its
+// values as a column of Rd[NRED][RED_STRIDE]; lane l then sums half (l & 1) of row (l >> 1)
+// with four LDS.128 (rows are 36 floats apart, so the 8 lanes of a quarter-warp hit 32
+// distinct banks) and one shuffle joins the halves: 13 STS + 4 LDS.128 + 17 FADD + 1 SHFL per
+// (tile, Gaussian) instead of 16 SHFL + 31 FADD + 30 selects for the register butterfly.
+// Lanes 2k and 2k+1 both return the total of value k (k < NRED; other lanes return 0).
+__device__ __forceinline__ float warp_reduce_rows(const float (&v)[NRED], float (*Rd)[RED_STRIDE], int lane) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const float send = b4 ? v[k] : v[k + 8];
-        const float keep = b4 ? v[k + 8] : v[k];
-        w8[k] = keep + __shfl_xor_sync(FULL, send, 16);
+    for (int k = 0; k < NRED; ++k) Rd[k][lane] = v[k];
+    __syncwarp();
+    const int k = lane >> 1;
+    float r = 0.f;
+    if (k < NRED) {
+        const float4* row = reinterpret_cast<const float4*>(&Rd[k][(lane & 1) * 16]);
+        const float4 a = row[0], b = row[1], c = row[2], d = row[3];
+        r = ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w)) +
+            (((c.x + c.y) + (c.z + c.w)) + ((d.x + d.y) + (d.z + d.w)));
     }
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const float send = b3 ? w8[k] : w8[k + 4];
-        const float keep = b3 ? w8[k + 4] : w8[k];
-        w4[k] = keep + __shfl_xor_sync(FULL, send, 8);
-    }
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const float send = b2 ? w4[k] : w4[k + 2];
-        const float keep = b2 ? w4[k + 2] : w4[k];
-        w2[k] = keep + __shfl_xor_sync(FULL, send, 4);
-    }
-    const float send = b1 ? w2[0] : w2[1];
-    const float keep = b1 ? w2[1] : w2[0];
-    float r = keep + __shfl_xor_sync(FULL, send, 2);
     r += __shfl_xor_sync(FULL, r, 1);
-    return r;  // value index = (b4<<3)|(b3<<2)|(b2<<1)|b1 = lane >> 1
+    __syncwarp();  // the rows are rewritten by the next Gaussian
+    return r;
 }
 
 // Slots of the reduced vector: 0..4 v_colors, 5..7 second moments (w dx dx, w dx dy, w dy dy),
@@ -410,7 +413,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                      const float* __restrict__ v_render_alphas, float* __restrict__ v_means2d,
                      float* __restrict__ v_means2d_abs, float* __restrict__ v_conics,
                      float* __restrict__ v_colors, float* __restrict__ v_opacities) {
-    static_assert(CH <= 5, "reduce-scatter layout holds 16 values");
+    static_assert(CH <= 5, "slots 0..4 hold v_colors");
     __shared__ __align__(16) WarpSmem<CH, true> smem[WARPS_PER_CTA];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t n_slots = (int64_t)n_cams * tile_w * tile_h;
@@ -509,9 +512,9 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             load_colors<CH>(sm.C, t, col);
             const float hx0 = 2.0f * A.a2 * X.dx;  // d s2 / d mean.x = 2 a2 dx + b2 dy
             const float c2x2 = 2.0f * B.c2;        // d s2 / d mean.y = 2 c2 dy + b2 dx
-            float v[16];
+            float v[NRED];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) v[k] = 0.f;
+            for (int k = 0; k < NRED; ++k) v[k] = 0.f;
             bool any_entry = false;
             // two halves of 4 row pairs: one warp-uniform branch each; the 4 pixel chains inside
             // are branch-free so that they interleave
@@ -564,7 +567,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                 }
             }
             if (!any_entry) continue;  // warp-uniform
-            const float red = warp_reduce_scatter16(v, lane);
+            const float red = warp_reduce_rows(v, sm.Rd, lane);
             const float val = red * (my_is_opacity ? -exp2f(-B.lo) : my_scale);
             if (my_base && val != 0.f) atomicAdd(my_base + (int64_t)sm.G[t] * my_stride, val);
         }
