@@ -512,9 +512,12 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             load_colors<CH>(sm.C, t, col);
             const float hx0 = 2.0f * A.a2 * X.dx;  // d s2 / d mean.x = 2 a2 dx + b2 dy
             const float c2x2 = 2.0f * B.c2;        // d s2 / d mean.y = 2 c2 dy + b2 dx
-            float v[NRED];
+            // dx is constant over a lane's 8 pixels, so of the moments of w = -au * v_alpha only
+            // sum w, sum w dy, sum w dy^2 (and the two |.| sums, which are not linear) are
+            // accumulated per pixel; the dx factors are applied once per (lane, Gaussian)
+            float vc[CH], sw = 0.f, swy = 0.f, swyy = 0.f, abx = 0.f, aby = 0.f;
 #pragma unroll
-            for (int k = 0; k < NRED; ++k) v[k] = 0.f;
+            for (int c = 0; c < CH; ++c) vc[c] = 0.f;
             bool any_entry = false;
             // two halves of 4 row pairs: one warp-uniform branch each; the 4 pixel chains inside
             // are branch-free so that they interleave
@@ -546,27 +549,36 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 #pragma unroll
                             for (int c = 0; c < CH; ++c) {
                                 d = fmaf(col[c], v_rc[r][c], d);
-                                v[c] = fmaf(fac, v_rc[r][c], v[c]);
+                                vc[c] = fmaf(fac, v_rc[r][c], vc[c]);
                             }
                             const float v_alpha = d * T[r] - R[r] * ra;
                             R[r] = fmaf(d, fac, R[r]);
                             const float w = (ok[q] && au <= SC_ALPHA_CAP) ? -au * v_alpha : 0.f;
-                            const float wdx = w * X.dx, wdy = w * dy;
-                            v[5] = fmaf(wdx, X.dx, v[5]);
-                            v[6] = fmaf(wdx, dy, v[6]);
-                            v[7] = fmaf(wdy, dy, v[7]);
-                            const float hx = fmaf(A.b2, dy, hx0);
-                            const float hy = fmaf(c2x2, dy, X.v);
-                            v[8] = fmaf(w, hx, v[8]);
-                            v[9] = fmaf(w, hy, v[9]);
-                            v[10] = fmaf(fabsf(w), fabsf(hx), v[10]);
-                            v[11] = fmaf(fabsf(w), fabsf(hy), v[11]);
-                            v[12] += w;
+                            const float wdy = w * dy;
+                            sw += w;
+                            swy += wdy;
+                            swyy = fmaf(wdy, dy, swyy);
+                            abx = fmaf(fabsf(w), fabsf(fmaf(A.b2, dy, hx0)), abx);
+                            aby = fmaf(fabsf(w), fabsf(fmaf(c2x2, dy, X.v)), aby);
                         }
                     }
                 }
             }
             if (!any_entry) continue;  // warp-uniform
+            float v[NRED];
+#pragma unroll
+            for (int c = 0; c < CH; ++c) v[c] = vc[c];
+#pragma unroll
+            for (int c = CH; c < 5; ++c) v[c] = 0.f;
+            const float swx = sw * X.dx;       // sum w dx
+            v[5] = swx * X.dx;                 // sum w dx dx
+            v[6] = swy * X.dx;                 // sum w dx dy
+            v[7] = swyy;                       // sum w dy dy
+            v[8] = fmaf(2.0f * A.a2, swx, A.b2 * swy);  // sum w (2 a2 dx + b2 dy)
+            v[9] = fmaf(c2x2, swy, A.b2 * swx);         // sum w (2 c2 dy + b2 dx)
+            v[10] = abx;
+            v[11] = aby;
+            v[12] = sw;
             const float red = warp_reduce_rows(v, sm.Rd, lane);
             const float val = red * (my_is_opacity ? -exp2f(-B.lo) : my_scale);
             if (my_base && val != 0.f) atomicAdd(my_base + (int64_t)sm.G[t] * my_stride, val);
