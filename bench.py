@@ -235,7 +235,8 @@ def run_ours(args):
 
     timer = StageTimer()
     proxy = _LibProxy(_lib.lib)
-    stage_fns = ["sc_projection_fwd", "sc_projection_bwd", "sc_sh_fwd", "sc_sh_bwd", "sc_isect_prepare",
+    stage_fns = ["sc_projection_fwd_opacity", "sc_projection_bwd_opacity", "sc_sh_fwd_view", "sc_sh_bwd_view",
+                 "sc_isect_prepare",
                  "sc_isect_emit_sorted", "sc_isect_offset_encode", "sc_rasterize_fwd", "sc_rasterize_bwd"]
     timer.wrap(proxy, stage_fns)
     rendering.lib = proxy
@@ -395,12 +396,12 @@ def run_ours(args):
         # HBM-bound stages: algorithmic bytes per camera pass
         Ic, Vc, P = I_total / n_views, V_total / n_views, WIDTH * HEIGHT
         alg_bytes = {
-            "sc_projection_fwd": 80.0 * n, "sc_sh_fwd": 204.0 * Vc + 12.0 * n,
+            "sc_projection_fwd_opacity": 80.0 * n, "sc_sh_fwd_view": 204.0 * Vc + 12.0 * n,
             # prepare = count (28 N) + depth sort of the visible pairs (16 V, one logical pass) + scan (12 V);
             # emit_sorted = emit (28 V + 12 I) + tile sort (24 I, one logical pass)
             "sc_isect_prepare": 28.0 * n + 28.0 * Vc, "sc_isect_emit_sorted": 28.0 * Vc + 36.0 * Ic,
             "sc_isect_offset_encode": 8.0 * Ic,
-            "sc_sh_bwd": 216.0 * Vc + 192.0 * n, "sc_projection_bwd": 128.0 * n,
+            "sc_sh_bwd_view": 216.0 * Vc + 192.0 * n, "sc_projection_bwd_opacity": 128.0 * n,
         }
         stage_table = {}
         for nme in stage_fns:

@@ -72,6 +72,35 @@ int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const float* coef
               const uint8_t* masks, const float* v_colors, float* v_coeffs, float* v_dirs,
               int accumulate, void* stream);
 
+/* "View mode" of the same kernels, used by the fused renderer path (rows A2, A5, A6 of
+ * SURVEY.md section 8 folded into their producers; K = 4 or 16):
+ *   sc_projection_fwd_opacity: additionally opacities_out[C,N] = opacities[N] * compensation
+ *     (plain opacity when compensations == NULL);
+ *   sc_sh_fwd_view: dirs = means - campos (campos: DEVICE float[3]), mask = radii > 0,
+ *     colors4[M,4] = (clamp_min(colour + 0.5, 0), depths[M]);
+ *   sc_sh_bwd_view: upstream v_colors4[M,4], clamp mask from the saved colors4_fwd; v_means
+ *     receives the direction gradient;
+ *   sc_projection_bwd_opacity: v_depths read with a stride (4: the depth channel of v_colors4),
+ *     v_opacities_in = gradient w.r.t. opacities_out, v_opacities[N] receives its share. */
+int sc_projection_fwd_opacity(int64_t N, int C, const float* means, const float* quats, const float* scales,
+                              const float* opacities, const float* viewmats, const float* Ks, int width,
+                              int height, float eps2d, float near_plane, float far_plane, float radius_clip,
+                              int32_t* radii, float* means2d, float* depths, float* conics,
+                              float* compensations, float* opacities_out, void* stream);
+int sc_projection_bwd_opacity(int64_t N, int C, const float* means, const float* quats, const float* scales,
+                              const float* opacities, const float* viewmats, const float* Ks, int width,
+                              int height, float eps2d, const int32_t* radii, const float* v_means2d,
+                              const float* v_depths, int v_depths_stride, const float* v_conics,
+                              const float* v_opacities_in, int use_compensations, float* v_means,
+                              float* v_quats, float* v_scales, float* v_opacities, int accumulate,
+                              void* stream);
+int sc_sh_fwd_view(int64_t M, int K, int degree, const float* means, const float* campos,
+                   const float* coeffs, const int32_t* radii, const float* depths, float* colors4,
+                   void* stream);
+int sc_sh_bwd_view(int64_t M, int K, int degree, const float* means, const float* campos,
+                   const float* coeffs, const int32_t* radii, const float* colors4_fwd,
+                   const float* v_colors4, float* v_coeffs, float* v_means, int accumulate, void* stream);
+
 /* ---- A3/A4: tile intersection ---------------------------------------------------------- */
 /* tiles_per_gauss[i] = size of the tile AABB of entry i (0 when radii[i] == 0).  Optional
  * (both or neither; need depths): depth_keys[i] = raw depth bits (0xffffffff when the entry

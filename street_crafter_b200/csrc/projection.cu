@@ -69,7 +69,8 @@ projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* _
                       const float* __restrict__ Ks, int width, int height, float eps2d, float near_plane,
                       float far_plane, float radius_clip, int32_t* __restrict__ radii,
                       float* __restrict__ means2d, float* __restrict__ depths,
-                      float* __restrict__ conics, float* __restrict__ comps) {
+                      float* __restrict__ conics, float* __restrict__ comps,
+                      const float* __restrict__ opacities, float* __restrict__ op_out) {
     // stage the two 12-byte-stride arrays through shared memory so that global loads are
     // full-line float4 accesses (AoS [N,3] would otherwise be 3 strided scalar loads)
     __shared__ float s_means[PROJ_THREADS * 3];
@@ -172,6 +173,8 @@ projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* _
         reinterpret_cast<float2*>(means2d)[o] = make_float2(o_mx, o_my);
         depths[o] = o_z;
         if (comps) comps[o] = o_comp;
+        // A2 fused: opacity * compensation (plain opacity in classic mode)
+        if (op_out) op_out[o] = comps ? __ldg(opacities + g) * o_comp : __ldg(opacities + g);
     }
     s_conics[tid * 3 + 0] = o_a;
     s_conics[tid * 3 + 1] = o_b;
@@ -624,16 +627,17 @@ isect_offset_encode_kernel(int64_t n_isects, const int64_t* __restrict__ isect_i
 
 }  // namespace
 
-extern "C" int sc_projection_fwd(int64_t N, int C, const float* means, const float* quats,
-                                 const float* scales, const float* viewmats, const float* Ks, int width,
-                                 int height, float eps2d, float near_plane, float far_plane,
-                                 float radius_clip, int32_t* radii, float* means2d, float* depths,
-                                 float* conics, float* compensations, void* stream) {
+static int projection_fwd_launch(int64_t N, int C, const float* means, const float* quats, const float* scales,
+                                 const float* viewmats, const float* Ks, int width, int height, float eps2d,
+                                 float near_plane, float far_plane, float radius_clip, int32_t* radii,
+                                 float* means2d, float* depths, float* conics, float* compensations,
+                                 const float* opacities, float* op_out, void* stream) {
     SC_CHECK_ARG(N >= 0 && C >= 1, "N, C");
     SC_CHECK_ARG(width > 0 && height > 0, "image size");
     if (N == 0) return SC_OK;
     SC_CHECK_ARG(means && quats && scales && viewmats && Ks && radii && means2d && depths && conics,
                  "null pointer");
+    SC_CHECK_ARG((opacities == nullptr) == (op_out == nullptr), "opacities and op_out go together");
     SC_CHECK_ARG(((uintptr_t)means & 15) == 0 && ((uintptr_t)scales & 15) == 0 &&
                      ((uintptr_t)quats & 15) == 0 && ((uintptr_t)means2d & 7) == 0 &&
                      ((uintptr_t)conics & 15) == 0,
@@ -641,9 +645,31 @@ extern "C" int sc_projection_fwd(int64_t N, int C, const float* means, const flo
     dim3 grid((unsigned)sc_div_up(N, PROJ_THREADS), (unsigned)C);
     projection_fwd_kernel<<<grid, PROJ_THREADS, 0, (cudaStream_t)stream>>>(
         N, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip,
-        radii, means2d, depths, conics, compensations);
+        radii, means2d, depths, conics, compensations, opacities, op_out);
     SC_CHECK_LAUNCH("projection_fwd_kernel");
     return SC_OK;
+}
+
+extern "C" int sc_projection_fwd(int64_t N, int C, const float* means, const float* quats,
+                                 const float* scales, const float* viewmats, const float* Ks, int width,
+                                 int height, float eps2d, float near_plane, float far_plane,
+                                 float radius_clip, int32_t* radii, float* means2d, float* depths,
+                                 float* conics, float* compensations, void* stream) {
+    return projection_fwd_launch(N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
+                                 far_plane, radius_clip, radii, means2d, depths, conics, compensations, nullptr,
+                                 nullptr, stream);
+}
+
+extern "C" int sc_projection_fwd_opacity(int64_t N, int C, const float* means, const float* quats,
+                                         const float* scales, const float* opacities, const float* viewmats,
+                                         const float* Ks, int width, int height, float eps2d, float near_plane,
+                                         float far_plane, float radius_clip, int32_t* radii, float* means2d,
+                                         float* depths, float* conics, float* compensations,
+                                         float* opacities_out, void* stream) {
+    SC_CHECK_ARG(opacities && opacities_out, "null pointer");
+    return projection_fwd_launch(N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
+                                 far_plane, radius_clip, radii, means2d, depths, conics, compensations,
+                                 opacities, opacities_out, stream);
 }
 
 extern "C" int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, const float* depths,

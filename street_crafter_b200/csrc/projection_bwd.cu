@@ -19,7 +19,11 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
                       const int32_t* __restrict__ radii, const float* __restrict__ v_means2d,
                       const float* __restrict__ v_depths, const float* __restrict__ v_conics,
                       const float* __restrict__ v_comps, float* __restrict__ v_means,
-                      float* __restrict__ v_quats, float* __restrict__ v_scales, int accumulate) {
+                      float* __restrict__ v_quats, float* __restrict__ v_scales, int accumulate,
+                      int vd_stride, const float* __restrict__ opacities, float* __restrict__ v_opacities, int use_comp) {
+    // fused-opacity mode (opacities != nullptr): the rasterizer consumed opacity * compensation
+    // (plain opacity without compensations), `v_comps` holds the gradient w.r.t. THAT product:
+    //   v_compensation = v_prod * opacity,  v_opacity (+)= sum_cam v_prod * compensation
     const int64_t g = (int64_t)blockIdx.x * PB_THREADS + threadIdx.x;
     if (g >= N) return;
     // Gaussians no camera sees: nothing to compute (zeros, or untouched in accumulate mode)
@@ -30,9 +34,12 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
             if (v_means) { v_means[g * 3 + 0] = 0.f; v_means[g * 3 + 1] = 0.f; v_means[g * 3 + 2] = 0.f; }
             if (v_scales) { v_scales[g * 3 + 0] = 0.f; v_scales[g * 3 + 1] = 0.f; v_scales[g * 3 + 2] = 0.f; }
             if (v_quats) reinterpret_cast<float4*>(v_quats)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (v_opacities) v_opacities[g] = 0.f;
         }
         return;
     }
+    const float occ = opacities ? __ldg(opacities + g) : 1.0f;
+    float v_occ = 0.f;
     // accumulate mode: fetch the running sums now, so their latency hides under the math
     float old_p[3] = {0.f, 0.f, 0.f}, old_s[3] = {0.f, 0.f, 0.f};
     float4 old_q = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -125,15 +132,20 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
         const float va = __ldg(v_conics + o * 3 + 0), vb = __ldg(v_conics + o * 3 + 1),
                     vc = __ldg(v_conics + o * 3 + 2);
         const float vmx = __ldg(v_means2d + o * 2 + 0), vmy = __ldg(v_means2d + o * 2 + 1);
-        const float vz_up = __ldg(v_depths + o);
+        const float vz_up = __ldg(v_depths + o * vd_stride);
         // conic = (b11, -v01, b00) / det
         float g_b00 = va * (-b11 * b11 * rdet2) + vb * (v01 * b11 * rdet2) + vc * (rdet - b00 * b11 * rdet2);
         float g_b11 = va * (rdet - b11 * b00 * rdet2) + vb * (v01 * b00 * rdet2) + vc * (-b00 * b00 * rdet2);
         float g_v01 = va * (2.f * b11 * v01 * rdet2) + vb * (-rdet - 2.f * v01 * v01 * rdet2) +
                       vc * (2.f * b00 * v01 * rdet2);
         if (v_comps) {
-            const float vcomp = __ldg(v_comps + o);
+            float vcomp = __ldg(v_comps + o);
             const float ratio = det_orig * rdet;
+            if (opacities) {
+                const float v_prod = vcomp;
+                vcomp = use_comp ? v_prod * occ : 0.f;
+                v_occ += use_comp ? (ratio > 0.f ? v_prod * sqrtf(ratio) : 0.f) : v_prod;
+            }
             if (ratio > 0.f) {
                 const float comp = sqrtf(ratio);
                 const float v_r = vcomp * 0.5f / comp;
@@ -242,16 +254,17 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
     if (v_quats)
         reinterpret_cast<float4*>(v_quats)[g] =
             make_float4(old_q.x + vq[0], old_q.y + vq[1], old_q.z + vq[2], old_q.w + vq[3]);
+    if (v_opacities) v_opacities[g] = (accumulate ? v_opacities[g] : 0.f) + v_occ;
 }
 
 }  // namespace
 
-extern "C" int sc_projection_bwd(int64_t N, int C, const float* means, const float* quats,
-                                 const float* scales, const float* viewmats, const float* Ks, int width,
-                                 int height, float eps2d, const int32_t* radii, const float* v_means2d,
-                                 const float* v_depths, const float* v_conics, const float* v_compensations,
-                                 float* v_means, float* v_quats, float* v_scales, int accumulate,
-                                 void* stream) {
+static int projection_bwd_launch(int64_t N, int C, const float* means, const float* quats, const float* scales,
+                                 const float* viewmats, const float* Ks, int width, int height, float eps2d,
+                                 const int32_t* radii, const float* v_means2d, const float* v_depths,
+                                 int vd_stride, const float* v_conics, const float* v_compensations,
+                                 const float* opacities, int use_comp, float* v_means, float* v_quats,
+                                 float* v_scales, float* v_opacities, int accumulate, void* stream) {
     SC_CHECK_ARG(N >= 0 && C >= 1, "N, C");
     if (N == 0) return SC_OK;
     SC_CHECK_ARG(means && quats && scales && viewmats && Ks && radii && v_means2d && v_depths && v_conics,
@@ -260,7 +273,33 @@ extern "C" int sc_projection_bwd(int64_t N, int C, const float* means, const flo
                  "16-byte alignment of quats");
     projection_bwd_kernel<<<(unsigned)sc_div_up(N, PB_THREADS), PB_THREADS, 0, (cudaStream_t)stream>>>(
         N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, radii, v_means2d, v_depths,
-        v_conics, v_compensations, v_means, v_quats, v_scales, accumulate);
+        v_conics, v_compensations, v_means, v_quats, v_scales, accumulate, vd_stride, opacities, v_opacities,
+        use_comp);
     SC_CHECK_LAUNCH("projection_bwd_kernel");
     return SC_OK;
+}
+
+extern "C" int sc_projection_bwd(int64_t N, int C, const float* means, const float* quats,
+                                 const float* scales, const float* viewmats, const float* Ks, int width,
+                                 int height, float eps2d, const int32_t* radii, const float* v_means2d,
+                                 const float* v_depths, const float* v_conics, const float* v_compensations,
+                                 float* v_means, float* v_quats, float* v_scales, int accumulate,
+                                 void* stream) {
+    return projection_bwd_launch(N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, radii,
+                                 v_means2d, v_depths, 1, v_conics, v_compensations, nullptr, 1, v_means,
+                                 v_quats, v_scales, nullptr, accumulate, stream);
+}
+
+extern "C" int sc_projection_bwd_opacity(int64_t N, int C, const float* means, const float* quats,
+                                         const float* scales, const float* opacities, const float* viewmats,
+                                         const float* Ks, int width, int height, float eps2d,
+                                         const int32_t* radii, const float* v_means2d, const float* v_depths,
+                                         int v_depths_stride, const float* v_conics,
+                                         const float* v_opacities_in, int use_compensations, float* v_means,
+                                         float* v_quats, float* v_scales, float* v_opacities,
+                                         int accumulate, void* stream) {
+    SC_CHECK_ARG(opacities && v_opacities_in && v_opacities && v_depths_stride >= 1, "fused-opacity arguments");
+    return projection_bwd_launch(N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, radii,
+                                 v_means2d, v_depths, v_depths_stride, v_conics, v_opacities_in, opacities,
+                                 use_compensations, v_means, v_quats, v_scales, v_opacities, accumulate, stream);
 }

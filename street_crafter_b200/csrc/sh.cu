@@ -280,6 +280,18 @@ sh_bwd_kernel(int64_t M, const float* __restrict__ dirs, const float* __restrict
 // compile-time indices, so the kernels stay near 64 registers and 32 warps fit on an SM —
 // these kernels are latency-bound otherwise (each chunk is a mask -> coefficients -> result
 // chain of dependent DRAM round trips).
+// "View mode" of the transposing kernels (the fused renderer path): directions are
+// means - camera centre, the mask is radii > 0, colours carry +0.5 / clamp_min 0 and the depth
+// as a 4th channel (rows A5 + A6 of SURVEY.md section 8 in one pass); the backward reads the
+// 4-channel upstream gradient and applies the clamp mask from the saved forward colours.
+struct ShView {
+    const float* campos;        // DEVICE pointer to the camera centre (nullptr: dirs are given)
+    const int32_t* radii;       // mask source (nullptr: use `masks`)
+    const float* depths;        // forward: 4th output channel (nullptr: 3-channel output)
+    const float* colors_fwd;    // backward: saved [M,4] forward colours (clamp mask), nullable
+    int vc_stride;              // backward: floats per row of v_colors (3, or 4 in view mode)
+};
+
 template <int K>
 struct ShT {
     static constexpr int K3 = K * 3;
@@ -318,24 +330,29 @@ __device__ __forceinline__ void sht_load(const float4* __restrict__ src4, int n,
 template <int K, int DEG>
 __global__ void __launch_bounds__(SHT_WARPS * 32, 3)
 sh_fwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restrict__ coeffs4,
-                const uint8_t* __restrict__ masks, float* __restrict__ colors) {
+                const uint8_t* __restrict__ masks, float* __restrict__ colors, ShView vw) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NB = (DEG + 1) * (DEG + 1);
     constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     float* tile = smem + wib * ShT<K>::TILE_FLOATS;
     const int64_t n_chunks = (M + 31) >> 5;
+    const float cx = vw.campos ? __ldg(vw.campos + 0) : 0.f, cy = vw.campos ? __ldg(vw.campos + 1) : 0.f,
+                cz = vw.campos ? __ldg(vw.campos + 2) : 0.f;
     for (int64_t chunk = (int64_t)blockIdx.x * SHT_WARPS + wib; chunk < n_chunks;
          chunk += (int64_t)gridDim.x * SHT_WARPS) {
         const int64_t g0 = chunk << 5;
         const int n = (int)min((int64_t)32, M - g0);
         const int64_t g = g0 + lane;
-        const bool live = (lane < n) && (masks == nullptr || __ldg(masks + g) != 0);
+        const bool live = (lane < n) && (vw.radii ? __ldg(vw.radii + g) > 0 : (masks == nullptr || __ldg(masks + g) != 0));
         const unsigned vis = __ballot_sync(0xffffffffu, live);
         float r = 0.f, gg = 0.f, b = 0.f;
         if (vis) {
             float x = 0.f, y = 0.f, z = 0.f;
-            if (live) { x = __ldg(dirs + g * 3 + 0); y = __ldg(dirs + g * 3 + 1); z = __ldg(dirs + g * 3 + 2); }
+            if (live) {
+                x = __ldg(dirs + g * 3 + 0) - cx; y = __ldg(dirs + g * 3 + 1) - cy;
+                z = __ldg(dirs + g * 3 + 2) - cz;
+            }
             sht_load<K>(coeffs4 + g0 * Q, n, vis, tile, lane);
             __syncwarp();
             if (live) {
@@ -361,7 +378,13 @@ sh_fwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restr
             __syncwarp();
         }
         if (lane < n) {
-            colors[g * 3 + 0] = r; colors[g * 3 + 1] = gg; colors[g * 3 + 2] = b;
+            if (vw.depths) {
+                // view mode (A5 + A6 fused): clamp_min(colour + 0.5, 0) and the depth channel
+                reinterpret_cast<float4*>(colors)[g] = make_float4(fmaxf(r + 0.5f, 0.f), fmaxf(gg + 0.5f, 0.f),
+                                                                   fmaxf(b + 0.5f, 0.f), __ldg(vw.depths + g));
+            } else {
+                colors[g * 3 + 0] = r; colors[g * 3 + 1] = gg; colors[g * 3 + 2] = b;
+            }
         }
     }
 }
@@ -370,7 +393,7 @@ template <int K, int DEG>
 __global__ void __launch_bounds__(SHT_WARPS * 32, 3)
 sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restrict__ coeffs4,
                 const uint8_t* __restrict__ masks, const float* __restrict__ v_colors,
-                float4* __restrict__ v_coeffs4, float* __restrict__ v_dirs, int accumulate) {
+                float4* __restrict__ v_coeffs4, float* __restrict__ v_dirs, int accumulate, ShView vw) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NB = (DEG + 1) * (DEG + 1);
     constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
@@ -378,6 +401,9 @@ sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restr
     float* tile = smem + wib * ShT<K>::TILE_FLOATS;
     const int64_t n_chunks = (M + 31) >> 5;
     const bool want_dirs = v_dirs != nullptr;
+    const int vs = vw.vc_stride;
+    const float cx = vw.campos ? __ldg(vw.campos + 0) : 0.f, cy = vw.campos ? __ldg(vw.campos + 1) : 0.f,
+                cz = vw.campos ? __ldg(vw.campos + 2) : 0.f;
     // per-lane inputs of a chunk (mask, direction, upstream colour gradient) are fetched one
     // chunk AHEAD, unconditionally, so that the only DRAM latency a chunk exposes is its
     // coefficient span
@@ -386,9 +412,21 @@ sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restr
         LaneIn in{false, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         const int64_t g = (chunk << 5) + lane;
         if (chunk < n_chunks && g < M) {
-            in.m = masks == nullptr || __ldg(masks + g) != 0;
-            in.x = __ldg(dirs + g * 3 + 0); in.y = __ldg(dirs + g * 3 + 1); in.z = __ldg(dirs + g * 3 + 2);
-            in.r = __ldg(v_colors + g * 3 + 0); in.g = __ldg(v_colors + g * 3 + 1); in.b = __ldg(v_colors + g * 3 + 2);
+            in.m = vw.radii ? __ldg(vw.radii + g) > 0 : (masks == nullptr || __ldg(masks + g) != 0);
+            in.x = __ldg(dirs + g * 3 + 0) - cx; in.y = __ldg(dirs + g * 3 + 1) - cy;
+            in.z = __ldg(dirs + g * 3 + 2) - cz;
+            if (vs == 4) {
+                // view mode: one 16-byte load per row; unconditional (a load gated on the mask
+                // would make this prefetch wait for the mask's DRAM round trip)
+                const float4 v = __ldg(reinterpret_cast<const float4*>(v_colors) + g);
+                in.r = v.x; in.g = v.y; in.b = v.z;
+                if (vw.colors_fwd) {  // backward of clamp_min(colour + 0.5, 0)
+                    const float4 c = __ldg(reinterpret_cast<const float4*>(vw.colors_fwd) + g);
+                    in.r = c.x > 0.f ? in.r : 0.f; in.g = c.y > 0.f ? in.g : 0.f; in.b = c.z > 0.f ? in.b : 0.f;
+                }
+            } else {
+                in.r = __ldg(v_colors + g * 3 + 0); in.g = __ldg(v_colors + g * 3 + 1); in.b = __ldg(v_colors + g * 3 + 2);
+            }
         }
         return in;
     };
@@ -495,15 +533,19 @@ sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restr
 
 template <int K, int DEG>
 int launch_fwd(int64_t M, const float* dirs, const float* coeffs, const uint8_t* masks, float* colors,
-               cudaStream_t st) {
+               ShView vw, cudaStream_t st) {
     if constexpr ((K * 3) % 4 == 0) {
         const int smem = SHT_WARPS * ShT<K>::TILE_FLOATS * (int)sizeof(float);
         auto kern = sh_fwd_t_kernel<K, DEG>;
         if (smem > 48 * 1024) SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         const int grid = (int)min(sc_div_up((M + 31) >> 5, SHT_WARPS), (int64_t)SC_NUM_SMS * 16);
-        kern<<<grid, SHT_WARPS * 32, smem, st>>>(M, dirs, reinterpret_cast<const float4*>(coeffs), masks, colors);
+        kern<<<grid, SHT_WARPS * 32, smem, st>>>(M, dirs, reinterpret_cast<const float4*>(coeffs), masks, colors, vw);
         SC_CHECK_LAUNCH("sh_fwd_t_kernel");
         return SC_OK;
+    }
+    if (vw.radii || vw.depths) {
+        sc_set_error("SH view mode needs K*3 %% 4 == 0 (K = 4, 16), got K=%d", K);
+        return SC_ERR_UNSUPPORTED;
     }
     const int64_t iters = sc_div_up(M, ShLayout<K>::GPW * SH_UNROLL);
     const int grid = (int)min(sc_div_up(iters, SH_WARPS), (int64_t)SC_NUM_SMS * 64);
@@ -514,16 +556,20 @@ int launch_fwd(int64_t M, const float* dirs, const float* coeffs, const uint8_t*
 
 template <int K, int DEG>
 int launch_bwd(int64_t M, const float* dirs, const float* coeffs, const uint8_t* masks, const float* v_colors,
-               float* v_coeffs, float* v_dirs, int accumulate, cudaStream_t st) {
+               float* v_coeffs, float* v_dirs, int accumulate, ShView vw, cudaStream_t st) {
     if constexpr ((K * 3) % 4 == 0) {
         const int smem = SHT_WARPS * ShT<K>::TILE_FLOATS * (int)sizeof(float);
         auto kern = sh_bwd_t_kernel<K, DEG>;
         if (smem > 48 * 1024) SC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         const int grid = (int)min(sc_div_up((M + 31) >> 5, SHT_WARPS), (int64_t)SC_NUM_SMS * 16);
         kern<<<grid, SHT_WARPS * 32, smem, st>>>(M, dirs, reinterpret_cast<const float4*>(coeffs), masks, v_colors,
-                                                 reinterpret_cast<float4*>(v_coeffs), v_dirs, accumulate);
+                                                 reinterpret_cast<float4*>(v_coeffs), v_dirs, accumulate, vw);
         SC_CHECK_LAUNCH("sh_bwd_t_kernel");
         return SC_OK;
+    }
+    if (vw.radii || vw.colors_fwd || vw.vc_stride != 3) {
+        sc_set_error("SH view mode needs K*3 %% 4 == 0 (K = 4, 16), got K=%d", K);
+        return SC_ERR_UNSUPPORTED;
     }
     const int64_t iters = sc_div_up(M, ShLayout<K>::GPW * SH_UNROLL);
     const int grid = (int)min(sc_div_up(iters, SH_WARPS), (int64_t)SC_NUM_SMS * 64);
@@ -562,8 +608,27 @@ extern "C" int sc_sh_fwd(int64_t M, int K, int degree, const float* dirs, const 
     SC_CHECK_ARG(dirs && coeffs && colors, "null pointer");
     SC_CHECK_ARG(((uintptr_t)coeffs & 15) == 0, "16-byte alignment of coeffs");
     cudaStream_t st = (cudaStream_t)stream;
-    SH_DISPATCH(launch_fwd, M, dirs, coeffs, masks, colors, st)
+    const ShView vw{nullptr, nullptr, nullptr, nullptr, 3};
+    SH_DISPATCH(launch_fwd, M, dirs, coeffs, masks, colors, vw, st)
     sc_set_error("unsupported SH coefficient count K=%d (supported 1,4,9,16,25)", K);
+    return SC_ERR_UNSUPPORTED;
+}
+
+extern "C" int sc_sh_fwd_view(int64_t M, int K, int degree, const float* means, const float* campos,
+                              const float* coeffs, const int32_t* radii, const float* depths,
+                              float* colors4, void* stream) {
+    SC_CHECK_ARG(M >= 0, "M");
+    SC_CHECK_ARG(degree >= 0 && degree <= 4 && (degree + 1) * (degree + 1) <= K, "degree vs K");
+    if (M == 0) return SC_OK;
+    SC_CHECK_ARG(means && campos && coeffs && radii && depths && colors4, "null pointer");
+    SC_CHECK_ARG(((uintptr_t)coeffs & 15) == 0 && ((uintptr_t)colors4 & 15) == 0, "16-byte alignment");
+    cudaStream_t st = (cudaStream_t)stream;
+    const ShView vw{campos, radii, depths, nullptr, 3};
+    const float* dirs = means;
+    const uint8_t* masks = nullptr;
+    float* colors = colors4;
+    SH_DISPATCH(launch_fwd, M, dirs, coeffs, masks, colors, vw, st)
+    sc_set_error("unsupported SH coefficient count K=%d (view mode: 4, 16)", K);
     return SC_ERR_UNSUPPORTED;
 }
 
@@ -577,7 +642,30 @@ extern "C" int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const 
     SC_CHECK_ARG(((uintptr_t)coeffs & 15) == 0 && ((uintptr_t)v_coeffs & 15) == 0,
                  "16-byte alignment of coeffs");
     cudaStream_t st = (cudaStream_t)stream;
-    SH_DISPATCH(launch_bwd, M, dirs, coeffs, masks, v_colors, v_coeffs, v_dirs, accumulate, st)
+    const ShView vw{nullptr, nullptr, nullptr, nullptr, 3};
+    SH_DISPATCH(launch_bwd, M, dirs, coeffs, masks, v_colors, v_coeffs, v_dirs, accumulate, vw, st)
     sc_set_error("unsupported SH coefficient count K=%d (supported 1,4,9,16,25)", K);
+    return SC_ERR_UNSUPPORTED;
+}
+
+extern "C" int sc_sh_bwd_view(int64_t M, int K, int degree, const float* means, const float* campos,
+                              const float* coeffs, const int32_t* radii, const float* colors4_fwd,
+                              const float* v_colors4, float* v_coeffs, float* v_means, int accumulate,
+                              void* stream) {
+    SC_CHECK_ARG(M >= 0, "M");
+    SC_CHECK_ARG(degree >= 0 && degree <= 4 && (degree + 1) * (degree + 1) <= K, "degree vs K");
+    if (M == 0) return SC_OK;
+    SC_CHECK_ARG(means && campos && coeffs && radii && colors4_fwd && v_colors4 && v_coeffs, "null pointer");
+    SC_CHECK_ARG(((uintptr_t)coeffs & 15) == 0 && ((uintptr_t)v_coeffs & 15) == 0, "16-byte alignment of coeffs");
+    SC_CHECK_ARG(((uintptr_t)colors4_fwd & 15) == 0 && ((uintptr_t)v_colors4 & 15) == 0,
+                 "16-byte alignment of the 4-channel colour rows");
+    cudaStream_t st = (cudaStream_t)stream;
+    const ShView vw{campos, radii, nullptr, colors4_fwd, 4};
+    const float* dirs = means;
+    const uint8_t* masks = nullptr;
+    const float* v_colors = v_colors4;
+    float* v_dirs = v_means;
+    SH_DISPATCH(launch_bwd, M, dirs, coeffs, masks, v_colors, v_coeffs, v_dirs, accumulate, vw, st)
+    sc_set_error("unsupported SH coefficient count K=%d (view mode: 4, 16)", K);
     return SC_ERR_UNSUPPORTED;
 }

@@ -51,8 +51,8 @@ class GaussianArena:
         """views of the gradient arena, keyed by parameter: pass as `grad_sinks=` so that the
         projection / SH backward kernels add straight into the arena (no per-view gradient
         tensors, no AccumulateGrad adds, untouched entries for culled Gaussians)"""
-        return {name: self.grads[off:off + numel].view(shape) for name, off, numel, shape in self.layout
-                if name != "opacities"}
+        return {name: self.grads[off:off + numel].view(shape if name != "opacities" else (-1,))
+                for name, off, numel, shape in self.layout}
 
     def tensors(self) -> List[Tensor]:
         return [getattr(self, name) for name, *_ in self.layout]

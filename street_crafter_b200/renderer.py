@@ -12,8 +12,8 @@ from typing import Dict, Optional
 import torch
 from torch import Tensor
 
-from .rendering import (fully_fused_projection, isect_offset_encode, isect_tiles, rasterize_to_pixels,
-                        spherical_harmonics)
+from .rendering import (fully_fused_projection, fused_view, isect_offset_encode, isect_tiles,
+                        rasterize_to_pixels, spherical_harmonics)
 
 
 def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tensor, occ1: Tensor,
@@ -21,10 +21,39 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
                          max_sh_degree: int, znear: float = 0.001, zfar: float = 1000.0,
                          tile_size: int = 16, use_depth: bool = True, absgrad: bool = True,
                          antialiasing: bool = True, train: bool = True,
-                         grad_sinks: Optional[Dict[str, Tensor]] = None) -> Dict[str, Tensor]:
+                         grad_sinks: Optional[Dict[str, Tensor]] = None, fused: bool = True) -> Dict[str, Tensor]:
     """xyz3[N,3] rgb3[N,K,3] (SH) scale[N,3] quats[N,4] occ1[N,1] w2c[1,4,4] K[1,3,3]
     camera_center[3] -> the reference's result dict (rgb[3,H,W], acc, depth, viewspace_points,
-    visibility_filter, radii) plus the raw render tensors."""
+    visibility_filter, radii) plus the raw render tensors.
+
+    fused=True (default) runs the same computation as ONE autograd node per camera
+    (rendering.fused_view): the elementwise glue between the five ops (opacity * compensation,
+    dirs, mask, +0.5 / clamp, cat with depth and their backward nodes) is folded into the
+    kernels.  fused=False issues the five ops exactly as the reference does (:219-280)."""
+    if fused and use_depth and rgb3.dim() == 3 and rgb3.shape[1] in (4, 16) and tile_size == 16:
+        render_colors, render_alphas, meta = fused_view(
+            xyz3, quats, scale, occ1[:, 0], rgb3, w2c, K, camera_center, width, height, max_sh_degree,
+            near_plane=znear, far_plane=zfar, antialiased=antialiasing, tile_size=tile_size, absgrad=absgrad,
+            grad_sinks=grad_sinks)
+        radii, means2d = meta["radii"], meta["means2d"]
+        rendered_color = render_colors[..., :-1]
+        rendered_depth = render_colors[..., -1:] / render_alphas.clamp(min=1e-10)
+        if not train:
+            rendered_color = torch.clamp(rendered_color, 0.0, 1.0)
+        return {
+            "rgb": rendered_color[0].permute(2, 0, 1),
+            "acc": render_alphas[..., 0],
+            "depth": rendered_depth[..., 0],
+            "viewspace_points": means2d,
+            "visibility_filter": radii[0] > 0,
+            "radii": radii[0] / float(max(height, width)),
+            "render_colors": render_colors,
+            "render_alphas": render_alphas,
+            "aux": dict(radii=radii, means2d=means2d, depths=meta["depths"], conics=meta["conics"],
+                        compensations=meta["compensations"], tiles_per_gauss=meta["tiles_per_gauss"],
+                        isect_ids=meta["isect_ids"], flatten_ids=meta["flatten_ids"],
+                        isect_offsets=meta["isect_offsets"], colors=meta["colors"], opacities=meta["opacities"]),
+        }
     # Project Gaussians to 2D                                   (reference :219-232)
     radii, means2d, depths, conics, compensations = fully_fused_projection(
         xyz3, None, quats, scale, w2c, K, width, height, packed=False, near_plane=znear, far_plane=zfar,

@@ -78,6 +78,7 @@ class _FullyFusedProjection(torch.autograd.Function):
                                         _p(depths), _p(conics), _p(comps), _stream()),
                   "sc_projection_fwd")
         ctx.save_for_backward(means, quats, scales, viewmats, Ks, radii)
+        ctx.set_materialize_grads(False)
         ctx.dims = (int(width), int(height), float(eps2d), bool(calc_compensations))
         ctx.sinks = sinks
         ctx.mark_non_differentiable(radii)
@@ -227,6 +228,56 @@ def _tile_n_bits(tile_width: int, tile_height: int) -> int:
     return int(math.floor(math.log2(tile_width * tile_height))) + 1
 
 
+# pinned landing buffers for the {n_visible, n_isects} read-back, one per (device, stream)
+_PINNED_TOTALS: Dict[Tuple[int, int], Tensor] = {}
+
+
+def _isect_begin(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int, tile_width: int,
+                 tile_height: int, tpg: Tensor, st: int):
+    """phase 1 of the fused binning pipeline: compaction of the emitting entries + their stable
+    depth order + scan (one C call), then an ASYNC copy of {n_visible, n_isects} to pinned host
+    memory and an event.  The caller may enqueue independent GPU work before _isect_finish()
+    waits on the event, so the GPU stays busy across the host read-back."""
+    C, N = radii.shape
+    CN = C * N
+    dev = means2d.device
+    ws_bytes = int(lib.sc_isect_workspace_bytes(CN, tile_width, tile_height))
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    check(lib.sc_isect_prepare(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width, tile_height,
+                               _p(tpg), _p(ws), ws_bytes, st), "sc_isect_prepare")
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), st)
+    host = _PINNED_TOTALS.get(key)
+    if host is None:
+        host = _PINNED_TOTALS[key] = torch.empty(2, dtype=torch.int64).pin_memory()
+    host.copy_(ws[:16].view(torch.int64), non_blocking=True)
+    ev = torch.cuda.Event()
+    ev.record()
+    return (means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, host, ev)
+
+
+def _isect_finish(state):
+    """phase 2: wait for the counts (the one host sync of the pipeline), then emit + tile sort on
+    the (camera, tile) bits (one C call)."""
+    means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, host, ev = state
+    C, N = radii.shape
+    dev = means2d.device
+    bits = _tile_n_bits(tile_width, tile_height)
+    cam_bits = 0 if C == 1 else int(math.floor(math.log2(C))) + 1
+    ev.synchronize()
+    n_visible, n_isects = host.tolist()
+    ids = torch.empty((2, n_isects), dtype=torch.int64, device=dev)
+    flat = torch.empty((2, n_isects), dtype=torch.int32, device=dev)
+    if n_isects == 0:
+        return tpg, ids[0], flat[0]
+    sws_bytes = int(lib.sc_sort_workspace_bytes(n_isects))
+    sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
+    check(lib.sc_isect_emit_sorted(N, C, _p(means2d), _p(radii), _p(depths), tile_size, tile_width,
+                                   tile_height, bits, cam_bits, n_visible, n_isects, _p(ws),
+                                   _p(ids[0]), _p(flat[0]), _p(ids[1]), _p(flat[1]), _p(sws),
+                                   sws_bytes, st), "sc_isect_emit_sorted")
+    return tpg, ids[0], flat[0]
+
+
 @torch.no_grad()
 def isect_tiles(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int, tile_width: int,
                 tile_height: int, sort: bool = True, packed: bool = False, n_cameras: Optional[int] = None,
@@ -256,25 +307,8 @@ def isect_tiles(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int, 
     with torch.cuda.device(dev):
         tpg = torch.empty((C, N), dtype=torch.int32, device=dev)
         if sort:
-            # fused pipeline: compaction of the emitting entries + their stable depth order +
-            # scan (one C call), the host read-back of {n_visible, n_isects}, then emit + tile
-            # sort on the (camera, tile) bits only (one C call)
-            ws_bytes = int(lib.sc_isect_workspace_bytes(CN, tile_width, tile_height))
-            ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-            check(lib.sc_isect_prepare(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width,
-                                       tile_height, _p(tpg), _p(ws), ws_bytes, st), "sc_isect_prepare")
-            n_visible, n_isects = ws[:16].view(torch.int64).tolist()  # the one D->H sync of the pipeline
-            ids = torch.empty((2, n_isects), dtype=torch.int64, device=dev)
-            flat = torch.empty((2, n_isects), dtype=torch.int32, device=dev)
-            if n_isects == 0:
-                return tpg, ids[0], flat[0]
-            sws_bytes = int(lib.sc_sort_workspace_bytes(n_isects))
-            sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
-            check(lib.sc_isect_emit_sorted(N, C, _p(means2d), _p(radii), _p(depths), tile_size, tile_width,
-                                           tile_height, bits, cam_bits, n_visible, n_isects, _p(ws),
-                                           _p(ids[0]), _p(flat[0]), _p(ids[1]), _p(flat[1]), _p(sws),
-                                           sws_bytes, st), "sc_isect_emit_sorted")
-            return tpg, ids[0], flat[0]
+            state = _isect_begin(means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st)
+            return _isect_finish(state)
         # unsorted (gsplat's sort=False): entry order, through the stand-alone entry points
         cum = torch.empty(CN + 1, dtype=torch.int64, device=dev)
         ws_bytes = int(lib.sc_scan_workspace_bytes(CN))
@@ -348,6 +382,7 @@ class _RasterizeToPixels(torch.autograd.Function):
         ctx.save_for_backward(means2d, conics, colors, opacities,
                               backgrounds if backgrounds is not None else torch.empty(0, device=dev),
                               isect_offsets, flatten_ids, last_ids, final_T)
+        ctx.set_materialize_grads(False)
         ctx.cfg = (width, height, tile_size, bool(absgrad), backgrounds is not None)
         # the caller's tensor object: `.absgrad` is attached to it in backward
         # (street_gaussian/models/street_gaussian_model.py:505-506 reads it)
@@ -428,6 +463,150 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
 
 
 # ------------------------------------------------------------------------------------------
+# one camera pass as ONE autograd node (rows A1..A8b with A2/A5-prologue/A6 folded into kernels)
+# ------------------------------------------------------------------------------------------
+class _FusedView(torch.autograd.Function):
+    """projection (+ opacity * compensation) -> binning -> SH (dirs, mask, +0.5, clamp, depth
+    channel in-kernel) -> compositing for ONE camera, with a single backward that runs the
+    three backward kernels back to back.  Removes the ~20 elementwise / cat / fill launches and
+    autograd nodes the op-by-op sequence of the reference renderer needs per camera
+    (street_gaussian_renderer.py:233-266); results are the same tensors."""
+
+    @staticmethod
+    def forward(ctx, means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
+                eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, sinks):
+        means = _f32c(means, "means")
+        quats = _f32c(quats, "quats")
+        scales = _f32c(scales, "scales")
+        opacities = _f32c(opacities, "opacities", 4)
+        shs = _f32c(shs, "shs")
+        viewmats = _f32c(viewmats, "viewmats")
+        Ks = _f32c(Ks, "Ks")
+        campos = _f32c(campos, "camera centre", 4)
+        N, Kc = shs.shape[0], shs.shape[1]
+        dev = means.device
+        st = _stream()
+        radii = torch.empty((1, N), dtype=torch.int32, device=dev)
+        means2d = torch.empty((1, N, 2), dtype=torch.float32, device=dev)
+        depths = torch.empty((1, N), dtype=torch.float32, device=dev)
+        conics = torch.empty((1, N, 3), dtype=torch.float32, device=dev)
+        comps = torch.empty((1, N), dtype=torch.float32, device=dev) if antialiased else None
+        op_c = torch.empty((1, N), dtype=torch.float32, device=dev)
+        colors4 = torch.empty((1, N, 4), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib.sc_projection_fwd_opacity(N, 1, _p(means), _p(quats), _p(scales), _p(opacities),
+                                                _p(viewmats), _p(Ks), int(width), int(height), float(eps2d),
+                                                float(near_plane), float(far_plane), float(radius_clip),
+                                                _p(radii), _p(means2d), _p(depths), _p(conics), _p(comps),
+                                                _p(op_c), st), "sc_projection_fwd_opacity")
+        tile_width = math.ceil(width / float(tile_size))
+        tile_height = math.ceil(height / float(tile_size))
+        with torch.cuda.device(dev):
+            tpg = torch.empty((1, N), dtype=torch.int32, device=dev)
+            state = _isect_begin(means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st)
+            # independent of the binning: runs on the GPU while the host waits for the counts
+            check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(radii),
+                                     _p(depths), _p(colors4), st), "sc_sh_fwd_view")
+            tpg, isect_ids, flatten_ids = _isect_finish(state)
+        isect_offsets = isect_offset_encode(isect_ids, 1, tile_width, tile_height)
+        with torch.cuda.device(dev):
+            render_colors = torch.empty((1, height, width, 4), dtype=torch.float32, device=dev)
+            render_alphas = torch.empty((1, height, width, 1), dtype=torch.float32, device=dev)
+            last_ids = torch.empty((1, height, width), dtype=torch.int32, device=dev)
+            final_T = torch.empty((1, height, width), dtype=torch.float32, device=dev)
+            check(lib.sc_rasterize_fwd(1, N, flatten_ids.numel(), 4, width, height, tile_size, _p(means2d),
+                                       _p(conics), _p(colors4), _p(op_c), None, _p(isect_offsets),
+                                       _p(flatten_ids), 0, _p(render_colors), _p(render_alphas), _p(last_ids),
+                                       _p(final_T), _p(_STATS["buf"]), st), "sc_rasterize_fwd")
+        ctx.save_for_backward(means, quats, scales, opacities, shs, viewmats, Ks, campos, radii, means2d, conics,
+                              colors4, op_c, isect_offsets, flatten_ids, last_ids, final_T)
+        ctx.cfg = (int(width), int(height), int(tile_size), float(eps2d), bool(antialiased), bool(absgrad),
+                   int(sh_degree))
+        ctx.sinks = sinks
+        ctx.means2d_ref = None  # weakref to the returned means2d: receives .grad / .absgrad in backward
+        ctx.set_materialize_grads(False)  # no zero-filled "gradients" for the auxiliary outputs
+        aux = (radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets)
+        ctx.mark_non_differentiable(*aux)
+        if comps is not None:
+            ctx.mark_non_differentiable(comps)
+        return (render_colors, render_alphas) + aux + ((comps,) if comps is not None else ())
+
+    @staticmethod
+    def backward(ctx, v_render_colors, v_render_alphas, *_unused):
+        (means, quats, scales, opacities, shs, viewmats, Ks, campos, radii, means2d, conics, colors4, op_c,
+         isect_offsets, flatten_ids, last_ids, final_T) = ctx.saved_tensors
+        width, height, tile_size, eps2d, antialiased, absgrad, sh_degree = ctx.cfg
+        N, Kc = shs.shape[0], shs.shape[1]
+        dev = means.device
+        st = _stream()
+        v_render_colors = _grad_or_zeros(v_render_colors, (1, height, width, 4), dev)
+        v_render_alphas = _grad_or_zeros(v_render_alphas, (1, height, width, 1), dev)
+        sizes = [4 * N, 2 * N, 2 * N if absgrad else 0, 3 * N, N]  # colours first: 16-byte aligned rows
+        arena = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)  # one memset for all five
+        v_colors4, v_means2d, v_abs, v_conics, v_opc = torch.split(arena, sizes)
+        sinks = ctx.sinks
+        if sinks is not None:
+            g_means, g_quats, g_scales, g_op, g_shs = (sinks[k] for k in ("means", "quats", "scales",
+                                                                           "opacities", "shs"))
+        else:
+            g_means, g_quats, g_scales = torch.zeros_like(means), torch.zeros_like(quats), torch.zeros_like(scales)
+            g_op, g_shs = torch.zeros_like(opacities), torch.zeros_like(shs)
+        with torch.cuda.device(dev):
+            check(lib.sc_rasterize_bwd(1, N, flatten_ids.numel(), 4, width, height, tile_size, _p(means2d),
+                                       _p(conics), _p(colors4), _p(op_c), None, _p(isect_offsets),
+                                       _p(flatten_ids), _p(final_T), _p(last_ids), _p(v_render_colors),
+                                       _p(v_render_alphas), _p(v_means2d), _p(v_abs) if absgrad else None,
+                                       _p(v_conics), _p(v_colors4), _p(v_opc), st), "sc_rasterize_bwd")
+            check(lib.sc_sh_bwd_view(N, Kc, sh_degree, _p(means), _p(campos), _p(shs), _p(radii), _p(colors4),
+                                     _p(v_colors4), _p(g_shs), _p(g_means), 1, st), "sc_sh_bwd_view")
+            check(lib.sc_projection_bwd_opacity(N, 1, _p(means), _p(quats), _p(scales), _p(opacities),
+                                                _p(viewmats), _p(Ks), width, height, eps2d, _p(radii),
+                                                _p(v_means2d), v_colors4.data_ptr() + 12, 4, _p(v_conics),
+                                                _p(v_opc), 1 if antialiased else 0, _p(g_means), _p(g_quats),
+                                                _p(g_scales), _p(g_op), 1, st), "sc_projection_bwd_opacity")
+        m2 = ctx.means2d_ref() if ctx.means2d_ref is not None else None
+        if m2 is not None:
+            # what the reference reads after backward (street_gaussian_model.py:504-508)
+            m2.grad = v_means2d.view(1, N, 2)
+            if absgrad:
+                m2.absgrad = v_abs.view(1, N, 2)
+        if sinks is not None:
+            return (None,) * 19
+        need = ctx.needs_input_grad
+        return (g_means if need[0] else None, g_quats if need[1] else None, g_scales if need[2] else None,
+                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 14
+
+
+def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, shs: Tensor, viewmats: Tensor,
+               Ks: Tensor, campos: Tensor, width: int, height: int, sh_degree: int, eps2d: float = 0.3,
+               near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
+               antialiased: bool = True, tile_size: int = 16, absgrad: bool = False,
+               grad_sinks: Optional[Dict[str, Tensor]] = None) -> Tuple[Tensor, Tensor, Dict]:
+    """One camera (viewmats[1,4,4], Ks[1,3,3], campos[3] on the device), SH colours with K = 4 or
+    16 coefficients, RGB + depth channel: -> (render_colors[1,H,W,4], render_alphas[1,H,W,1], meta).
+    `meta["means2d"].grad` / `.absgrad` are filled by the backward pass."""
+    import weakref
+    assert viewmats.shape == (1, 4, 4) and Ks.shape == (1, 3, 3) and campos.shape == (3,)
+    assert shs.dim() == 3 and shs.shape[1] in (4, 16) and (sh_degree + 1) ** 2 <= shs.shape[1]
+    assert opacities.shape == (means.shape[0],)
+    if grad_sinks is not None:
+        assert all(k in grad_sinks for k in ("means", "quats", "scales", "opacities", "shs"))
+    out = _FusedView.apply(means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
+                           eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, grad_sinks)
+    rc, ra, radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets = out[:12]
+    comps = out[12] if len(out) > 12 else None
+    if rc.grad_fn is not None:
+        rc.grad_fn.means2d_ref = weakref.ref(means2d)
+    meta = {"camera_ids": None, "gaussian_ids": None, "radii": radii, "means2d": means2d, "depths": depths,
+            "conics": conics, "opacities": op_c, "compensations": comps, "colors": colors4,
+            "tile_width": math.ceil(width / float(tile_size)), "tile_height": math.ceil(height / float(tile_size)),
+            "tiles_per_gauss": tpg, "isect_ids": isect_ids, "flatten_ids": flatten_ids,
+            "isect_offsets": isect_offsets, "width": width, "height": height, "tile_size": tile_size,
+            "n_cameras": 1}
+    return rc, ra, meta
+
+
+# ------------------------------------------------------------------------------------------
 # rasterization(): the fused high-level entry (imported by the reference, see header)
 # ------------------------------------------------------------------------------------------
 def rasterization(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, colors: Tensor,
@@ -451,6 +630,19 @@ def rasterization(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tenso
     N = means.shape[0]
     C = viewmats.shape[0]
     assert opacities.shape == (N,), opacities.shape
+    if (C == 1 and sh_degree is not None and colors.dim() == 3 and colors.shape[1] in (4, 16)
+            and render_mode in ("RGB+D", "RGB+ED") and backgrounds is None and max_hit == 0
+            and camera_model == "pinhole"):
+        # the reference renderer's configuration: one autograd node per camera pass
+        campos = torch.inverse(viewmats)[0, :3, 3]
+        render_colors, render_alphas, meta = fused_view(
+            means, quats, scales, opacities, colors, viewmats, Ks, campos, width, height, sh_degree,
+            eps2d=eps2d, near_plane=near_plane, far_plane=far_plane, radius_clip=radius_clip,
+            antialiased=(rasterize_mode == "antialiased"), tile_size=tile_size, absgrad=absgrad)
+        if render_mode == "RGB+ED":
+            render_colors = torch.cat([render_colors[..., :-1],
+                                       render_colors[..., -1:] / render_alphas.clamp(min=1e-10)], dim=-1)
+        return render_colors, render_alphas, meta
     radii, means2d, depths, conics, comps = fully_fused_projection(
         means, None, quats, scales, viewmats, Ks, width, height, eps2d=eps2d, near_plane=near_plane,
         far_plane=far_plane, radius_clip=radius_clip, calc_compensations=(rasterize_mode == "antialiased"),

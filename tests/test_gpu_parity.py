@@ -357,19 +357,21 @@ def test_absgrad_matches_per_pixel_sum(S, dev):
 
 
 # ------------------------------------------------------------------------------ whole pipeline
-def _pipeline_gpu(S, dev, s, V, K, W, H, deg, train=True):
+def _pipeline_gpu(S, dev, s, V, K, W, H, deg, train=True, fused=True):
     from street_crafter_b200.renderer import render_kernel_gsplat
     c = {k: v.to(dev) for k, v in s.items()}
     for k in c:
         c[k].requires_grad_(train)
     cam_center = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
     out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None],
-                               V[None].to(dev), K[None].to(dev), cam_center, W, H, deg, train=train)
+                               V[None].to(dev), K[None].to(dev), cam_center, W, H, deg, train=train, fused=fused)
     return c, out
 
 
-def test_full_sequence_cfg1_forward_and_backward(S, dev):
-    """BASELINE.json configs[0]: 100k Gaussians, SH deg 3, one 960x640 camera, fwd+bwd."""
+@pytest.mark.parametrize("fused", [True, False])
+def test_full_sequence_cfg1_forward_and_backward(S, dev, fused):
+    """BASELINE.json configs[0]: 100k Gaussians, SH deg 3, one 960x640 camera, fwd+bwd; through
+    the single-node fused path and through the reference's five-op sequence."""
     n, W, H, deg = 100000, 960, 640, 3
     s = make_gaussians(n, sh_degree=deg, seed=0)
     V, K = make_camera(W, H)
@@ -383,7 +385,7 @@ def test_full_sequence_cfg1_forward_and_backward(S, dev):
     v_rc[..., 3] *= 0.02  # depth channel is O(50): keep its share of the loss comparable
     ((rc_w * v_rc).sum() + (ra_w * v_ra).sum()).backward()
 
-    c, out = _pipeline_gpu(S, dev, s, V, K, W, H, deg)
+    c, out = _pipeline_gpu(S, dev, s, V, K, W, H, deg, fused=fused)
     aux = out["aux"]
     for k in ("radii", "tiles_per_gauss", "isect_ids", "flatten_ids", "isect_offsets"):
         assert torch.equal(aux[k].cpu(), aux_w[k]), f"{k} not bit-exact"
@@ -399,7 +401,42 @@ def test_full_sequence_cfg1_forward_and_backward(S, dev):
     assert out["visibility_filter"].dtype == torch.bool and out["radii"].dtype == torch.float32
 
 
-def test_grad_sinks_match_autograd_accumulation(S, dev):
+@pytest.mark.parametrize("deg,antialiasing", [(3, True), (1, True), (3, False)])
+def test_fused_view_equals_five_op_sequence(S, dev, deg, antialiasing):
+    """the single-node path computes the same tensors as the op-by-op sequence: forward
+    bit-identical (same kernels, the glue folded in), gradients equal to rounding"""
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    n, W, H = 40000, 640, 400
+    s = make_gaussians(n, sh_degree=deg, seed=11)
+    V, K = make_camera(W, H, yaw_deg=10.0)
+    g = torch.Generator().manual_seed(2)
+    v_rc = torch.randn(1, H, W, 4, generator=g).to(dev)
+    v_ra = torch.randn(1, H, W, 1, generator=g).to(dev)
+    v_rc[..., 3] *= 0.02
+    res = []
+    for fused in (False, True):
+        c = {k: v.to(dev).requires_grad_(True) for k, v in s.items()}
+        cc = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
+        out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None],
+                                   V[None].to(dev), K[None].to(dev), cc, W, H, deg, antialiasing=antialiasing,
+                                   fused=fused)
+        torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc, v_ra])
+        res.append((c, out))
+    (c0, o0), (c1, o1) = res
+    for k in ("radii", "means2d", "depths", "conics", "isect_ids", "flatten_ids", "isect_offsets", "colors",
+              "opacities"):
+        assert torch.equal(o0["aux"][k], o1["aux"][k]), k
+    assert torch.equal(o0["render_colors"], o1["render_colors"]) and torch.equal(o0["render_alphas"],
+                                                                                 o1["render_alphas"])
+    for k in ("means", "quats", "scales", "opacities", "shs"):
+        assert_grad_close(c1[k].grad, c0[k].grad.cpu(), f"fused v_{k}")
+    vp0, vp1 = o0["viewspace_points"], o1["viewspace_points"]
+    assert_grad_close(vp1.grad, vp0.grad.cpu(), "viewspace grad")
+    assert_grad_close(vp1.absgrad, vp0.absgrad.cpu(), "viewspace absgrad")
+
+
+@pytest.mark.parametrize("fused", [True, False])
+def test_grad_sinks_match_autograd_accumulation(S, dev, fused):
     """gradient-arena mode (projection / SH backward += into the flat arena) == plain autograd
     accumulation over several views"""
     from street_crafter_b200.parallel import GaussianArena
@@ -418,7 +455,8 @@ def test_grad_sinks_match_autograd_accumulation(S, dev):
         for (V, K), a, b in zip(cams, v_rc, v_ra):
             cc = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
-                                       V[None].to(dev), K[None].to(dev), cc, W, H, deg, grad_sinks=sinks)
+                                       V[None].to(dev), K[None].to(dev), cc, W, H, deg, grad_sinks=sinks,
+                                       fused=fused)
             torch.autograd.backward([out["render_colors"], out["render_alphas"]], [a, b])
         for name, off, numel, shape in arena.layout:
             assert getattr(arena, name).grad.data_ptr() == arena.grads.data_ptr() + 4 * off, name
