@@ -229,7 +229,7 @@ def run_ours(args):
 
     import street_crafter_b200 as S
     from street_crafter_b200 import _lib, rendering
-    from street_crafter_b200.parallel import GaussianArena, allreduce_gradients
+    from street_crafter_b200.parallel import GaussianArena, HostViewFeeder, allreduce_gradients
     from street_crafter_b200.renderer import render_kernel_gsplat
     from tools.scene import make_camera, make_gaussians
 
@@ -276,15 +276,18 @@ def run_ours(args):
         if world > 1:
             allreduce_gradients(arena)
 
+    feeder = HostViewFeeder(dev)
+
     def step_e2e():
-        """host buffers in, loss out: camera + target image H2D, L1 loss, backward, loss D2H"""
+        """host buffers in, loss out: camera + target image H2D (staged on a side stream so that
+        view v+1's copies overlap view v's render), L1 loss, backward, loss D2H"""
         arena.zero_grad()
+        staged = [feeder.stage((host_V[v], host_K[v], host_C[v], host_gt[v])) for v in range(n_views)]
         losses = []
         for v in range(n_views):
-            Vd = host_V[v].to(dev, non_blocking=True)
-            Kd = host_K[v].to(dev, non_blocking=True)
-            Cd = host_C[v].to(dev, non_blocking=True)
-            gt = host_gt[v].to(dev, non_blocking=True)
+            tensors, ready = staged[v]
+            feeder.acquire(tensors, ready)
+            Vd, Kd, Cd, gt = tensors
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
                                        Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks)
             loss = (out["rgb"] - gt).abs().mean() + 0.01 * out["acc"].mean()

@@ -51,3 +51,19 @@ constexpr int SC_NUM_SMS = 148;  // B200
 #define SC_T_STOP 1e-4f
 #define SC_EIGEN_FLOOR 0.01f
 #define SC_JAC_PAD 0.3f
+
+// Lanes of the (full) warp whose 8-bit digit equals this lane's, built from 8 ballots.  The
+// hardware match.any iterates over the distinct values in the warp (up to 32 rounds on random
+// digits); the ballots are fixed-latency and independent across keys, so they pipeline.
+#ifdef __CUDACC__
+__device__ __forceinline__ unsigned sc_match_digit8(unsigned d) {
+    unsigned peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) {
+        const bool bit = (d >> b) & 1u;
+        const unsigned bal = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? bal : ~bal;
+    }
+    return peers;
+}
+#endif

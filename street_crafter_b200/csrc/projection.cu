@@ -592,7 +592,7 @@ isect_emit_hist_kernel(int64_t N, int64_t V, const float2* __restrict__ means2d,
             if (in) atomicAdd(&s_hist[0][(hi32 >> (pp.shift[0] - 32)) & ((1u << pp.nbits[0]) - 1u)], 1u);
             for (int p = 1; p < pp.passes; ++p) {
                 const uint32_t d = (hi32 >> (pp.shift[p] - 32)) & ((1u << pp.nbits[p]) - 1u);
-                const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu);
+                const unsigned peers = sc_match_digit8(d) & __ballot_sync(0xffffffffu, in);
                 if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
             }
         }
@@ -725,7 +725,7 @@ struct IsectWs {
 };
 IsectWs isect_ws_layout(int64_t CN, int64_t n_tiles_total) {
     IsectWs L;
-    L.plan32 = sc_sort_make_plan(CN, 0, 32);
+    L.plan32 = sc_sort_make_plan(CN, 0, 32, 4);
     L.cc_tiles = sc_div_up(CN, CC_TILE);
     L.sg_tiles = sc_div_up(CN, SG_TILE);
     // n_isects < 2^31 (int32 flatten positions) bounds the number of emit blocks
@@ -805,7 +805,7 @@ extern "C" int sc_isect_emit_sorted(int64_t N, int C, const float* means2d, cons
     const int64_t CN = N * C;
     const IsectWs L = isect_ws_layout(CN, (int64_t)tile_width * tile_height);
     SC_CHECK_ARG(sc_div_up(n_isects, EMIT_OUT) <= L.first_cap, "n_isects exceeds the entry table");
-    const ScSortPlan plan = sc_sort_make_plan(n_isects, 32, 32 + tile_n_bits + cam_bits);
+    const ScSortPlan plan = sc_sort_make_plan(n_isects, 32, 32 + tile_n_bits + cam_bits, 8);
     if (sort_workspace_bytes < plan.total) {
         sc_set_error("sort workspace too small: %lld < %lld", (long long)sort_workspace_bytes,
                      (long long)plan.total);

@@ -100,10 +100,18 @@ constexpr int RADIX = SC_SORT_RADIX;
 static_assert(RADIX == (1 << RADIX_BITS), "radix");
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
-constexpr int SORT_KPT = 16;
-constexpr int SORT_TILE = SORT_THREADS * SORT_KPT;  // 4096 pairs
+// keys per thread (tile = 256 * KPT pairs), per key width; overridable for tools/sort_variants.sh.
+// Small tiles = more resident CTAs and a shorter per-tile critical path (the ranking loop is
+// KPT dependent steps): the passes are latency-bound, not bandwidth-bound.
+#ifndef SC_SORT_KPT_U32
+#define SC_SORT_KPT_U32 8
+#endif
+#ifndef SC_SORT_KPT_U64
+#define SC_SORT_KPT_U64 16
+#endif
+template <typename KeyT> struct SortCfg { static constexpr int KPT = sizeof(KeyT) == 4 ? SC_SORT_KPT_U32 : SC_SORT_KPT_U64; };
+constexpr int sort_min_blocks(int kpt) { return kpt >= 16 ? 3 : kpt >= 8 ? 5 : 8; }
 constexpr int MAX_PASSES = SC_SORT_MAX_PASSES;
-constexpr int SORT_MIN_BLOCKS = 3;  // caps registers at 85/thread: 3 CTAs (24 warps) per SM
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_INC = 2u << 30;
 constexpr uint32_t FLAG_MASK = 3u << 30;
@@ -111,6 +119,7 @@ constexpr uint32_t VAL_MASK = ~FLAG_MASK;
 
 template <typename KeyT>
 struct SortSmem {
+    static constexpr int SORT_TILE = SORT_THREADS * SortCfg<KeyT>::KPT;
     KeyT keys[SORT_TILE];
     uint32_t vals[SORT_TILE];
     uint32_t warp_hist[SORT_WARPS][RADIX];
@@ -142,7 +151,7 @@ sort_histogram_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* 
         const unsigned act = __ballot_sync(0xffffffffu, in);
         for (int p = 0; p < pp.passes; ++p) {
             const uint32_t d = (uint32_t)(k >> pp.shift[p]) & ((1u << pp.nbits[p]) - 1u);
-            const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu) & act;
+            const unsigned peers = sc_match_digit8(d) & act;  // d < 256; lanes past the end are masked by act
             if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p * RADIX + d], (uint32_t)__popc(peers));
         }
     }
@@ -173,7 +182,7 @@ sort_hist_scan_kernel(uint32_t* __restrict__ hist) {
 }
 
 template <typename KeyT>
-__global__ void __launch_bounds__(SORT_THREADS, SORT_MIN_BLOCKS)
+__global__ void __launch_bounds__(SORT_THREADS, sort_min_blocks(SortCfg<KeyT>::KPT))
 onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* __restrict__ keys_in,
                      const uint32_t* __restrict__ vals_in,
                      KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int nbits,
@@ -182,6 +191,8 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
                      uint32_t* __restrict__ ticket) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SortSmem<KeyT>& sm = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
+    constexpr int SORT_KPT = SortCfg<KeyT>::KPT;
+    constexpr int SORT_TILE = SortSmem<KeyT>::SORT_TILE;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const uint32_t dmask = (1u << nbits) - 1u;
 
@@ -203,12 +214,16 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
         const int local = warp_base + i * 32 + lane;
         key[i] = (local < n_valid) ? __ldg(keys_in + tile_base + local) : (KeyT)~(KeyT)0;
     }
-    // ---- stable warp-level ranking
+    // ---- stable warp-level ranking: the peer masks of all keys first (independent ballots that
+    // pipeline), then the short serial chain through the warp histogram
     const uint32_t lt_mask = (1u << lane) - 1u;
+    uint32_t peers_of[SORT_KPT];
+#pragma unroll
+    for (int i = 0; i < SORT_KPT; ++i) peers_of[i] = sc_match_digit8((uint32_t)(key[i] >> shift) & dmask);
 #pragma unroll
     for (int i = 0; i < SORT_KPT; ++i) {
         const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t peers = peers_of[i];
         const uint32_t pre = sm.warp_hist[w][d];
         rank[i] = (uint16_t)(pre + __popc(peers & lt_mask));
         __syncwarp();
@@ -346,7 +361,7 @@ int radix_sort_pairs(int64_t n, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out
     SC_CHECK_ARG(begin_bit >= 0 && end_bit > begin_bit && end_bit <= (int)sizeof(KeyT) * 8, "bit range");
     if (n == 0) return 0;
     SC_CHECK_ARG(keys_in && vals_in && keys_out && vals_out && workspace, "null pointer");
-    const ScSortPlan plan = sc_sort_make_plan(n, begin_bit, end_bit);
+    const ScSortPlan plan = sc_sort_make_plan(n, begin_bit, end_bit, (int)sizeof(KeyT));
     if (workspace_bytes < plan.total) {
         sc_set_error("sort workspace too small: %lld < %lld", (long long)workspace_bytes, (long long)plan.total);
         return SC_ERR_WORKSPACE;
@@ -361,8 +376,12 @@ int radix_sort_pairs(int64_t n, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out
 }  // namespace
 
 // passes of <= 8 bits over [begin_bit, end_bit), widths balanced (14 bits -> 7+7, not 8+6)
-ScSortPlan sc_sort_make_plan(int64_t n_max, int begin_bit, int end_bit) {
+ScSortPlan sc_sort_make_plan(int64_t n_max, int begin_bit, int end_bit, int key_bytes) {
     ScSortPlan p;
+    // key_bytes 0: the smaller tile of the two key widths (workspace upper bound)
+    const int kpt = key_bytes == 4 ? SC_SORT_KPT_U32 : key_bytes == 8 ? SC_SORT_KPT_U64
+                  : (SC_SORT_KPT_U32 < SC_SORT_KPT_U64 ? SC_SORT_KPT_U32 : SC_SORT_KPT_U64);
+    const int64_t SORT_TILE = (int64_t)SORT_THREADS * kpt;
     const int bits = end_bit - begin_bit;
     p.pp.passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
     int shift = begin_bit, left = bits;
@@ -427,7 +446,7 @@ extern "C" int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out,
     return SC_OK;
 }
 
-extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return sc_sort_make_plan(n, 0, 64).total; }
+extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return sc_sort_make_plan(n, 0, 64, 0).total; }
 
 extern "C" int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
                                    uint32_t* vals_out, int begin_bit, int end_bit, void* workspace,

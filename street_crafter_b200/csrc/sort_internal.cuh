@@ -24,7 +24,8 @@ struct ScSortPlan {
     int64_t total;
 };
 
-ScSortPlan sc_sort_make_plan(int64_t n_max, int begin_bit, int end_bit);
+// key_bytes: 4 or 8 (tile size differs per key width); 0 = workspace upper bound for either
+ScSortPlan sc_sort_make_plan(int64_t n_max, int begin_bit, int end_bit, int key_bytes);
 
 // accumulate the digit histograms of `keys` into ws + hist_off (workspace control region zeroed
 // by the caller).  n_dev (nullable) overrides n_max with a device-resident count <= n_max.

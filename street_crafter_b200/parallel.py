@@ -84,3 +84,33 @@ def allreduce_densification_stats(xyz_gradient_accum: Tensor, denom: Tensor, max
         dist.all_reduce(xyz_gradient_accum, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(denom, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX, group=group)
+
+
+class HostViewFeeder:
+    """Stages per-view host inputs (pinned camera matrices, target images) onto the device on a
+    side stream, so that the copies of view v+1 overlap the render of view v.  Usage:
+
+        feeder = HostViewFeeder(device)
+        staged = [feeder.stage(host_tensors_of_view) for view in views]   # enqueue all copies
+        for tensors, ready in staged:
+            feeder.acquire(tensors, ready)    # compute stream waits for THIS view's copies only
+            ... render / loss / backward with `tensors` ...
+    """
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.stream = torch.cuda.Stream(self.device)
+
+    def stage(self, host_tensors: Sequence[Tensor]):
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))  # order after prior use of freed blocks
+        with torch.cuda.stream(self.stream):
+            dev = [t.to(self.device, non_blocking=True) for t in host_tensors]
+            ready = torch.cuda.Event()
+            ready.record(self.stream)
+        return dev, ready
+
+    def acquire(self, dev_tensors: Sequence[Tensor], ready) -> None:
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ready)
+        for t in dev_tensors:
+            t.record_stream(cur)  # the caching allocator must not recycle them under the compute stream

@@ -6,7 +6,9 @@ minf = float(sys.argv[3]) if len(sys.argv) > 3 else 0.004
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "-k", f"regex:{kre}"],
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
-hi = next(i for i, r in enumerate(rows) if "Source" in r and "Address" in r)
+import os
+_his = [i for i, r in enumerate(rows) if "Source" in r and "Address" in r]
+hi = _his[int(os.environ.get("KIDX", "0"))]  # KIDX selects the n-th captured launch that matches
 hdr = rows[hi]
 i_src, i_s, i_ex = hdr.index("Source"), hdr.index("Warp Stall Sampling (All Samples)"), hdr.index("Instructions Executed")
 data = []
