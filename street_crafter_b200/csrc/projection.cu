@@ -592,7 +592,8 @@ isect_emit_hist_kernel(int64_t N, int64_t V, const float2* __restrict__ means2d,
             if (in) atomicAdd(&s_hist[0][(hi32 >> (pp.shift[0] - 32)) & ((1u << pp.nbits[0]) - 1u)], 1u);
             for (int p = 1; p < pp.passes; ++p) {
                 const uint32_t d = (hi32 >> (pp.shift[p] - 32)) & ((1u << pp.nbits[p]) - 1u);
-                const unsigned peers = sc_match_digit8(d) & __ballot_sync(0xffffffffu, in);
+                // neighbouring slots share the high digits: match.any resolves in one or two rounds here
+                const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu);
                 if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
             }
         }
@@ -605,23 +606,38 @@ isect_emit_hist_kernel(int64_t N, int64_t V, const float2* __restrict__ means2d,
 }
 
 // ------------------------------------------------------------------ offsets (A4)
+// 4 consecutive keys per thread (two 16-byte loads); only the high words (camera | tile) matter
 __global__ void __launch_bounds__(256)
 isect_offset_encode_kernel(int64_t n_isects, const int64_t* __restrict__ isect_ids, int n_tiles_total,
                            int n_tiles, int tile_n_bits, int32_t* __restrict__ offsets) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_isects) return;
-    const int64_t mask = ((int64_t)1 << tile_n_bits) - 1;
-    const int64_t k = __ldg(isect_ids + i);
-    const int64_t slot = (k >> (32 + tile_n_bits)) * n_tiles + ((k >> 32) & mask);
-    if (i == 0) {
-        for (int64_t s = 0; s <= slot; ++s) offsets[s] = 0;
+    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i0 >= n_isects) return;
+    const uint32_t mask = (1u << tile_n_bits) - 1u;
+    uint32_t hi[4];
+    if (i0 + 4 <= n_isects) {
+        const int4 a = __ldg(reinterpret_cast<const int4*>(isect_ids + i0));
+        const int4 b = __ldg(reinterpret_cast<const int4*>(isect_ids + i0 + 2));
+        hi[0] = (uint32_t)a.y; hi[1] = (uint32_t)a.w; hi[2] = (uint32_t)b.y; hi[3] = (uint32_t)b.w;
     } else {
-        const int64_t kp = __ldg(isect_ids + i - 1);
-        const int64_t slot_p = (kp >> (32 + tile_n_bits)) * n_tiles + ((kp >> 32) & mask);
-        for (int64_t s = slot_p + 1; s <= slot; ++s) offsets[s] = (int32_t)i;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            hi[k] = (i0 + k < n_isects) ? (uint32_t)(__ldg(isect_ids + i0 + k) >> 32) : 0u;
     }
-    if (i == n_isects - 1) {
-        for (int64_t s = slot + 1; s < n_tiles_total; ++s) offsets[s] = (int32_t)n_isects;
+    int64_t slot_p = -1;  // slot of the previous key (-1 before the first)
+    if (i0 > 0) {
+        const uint32_t hp = (uint32_t)(__ldg(isect_ids + i0 - 1) >> 32);
+        slot_p = (int64_t)(hp >> tile_n_bits) * n_tiles + (hp & mask);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int64_t i = i0 + k;
+        if (i < n_isects) {
+            const int64_t slot = (int64_t)(hi[k] >> tile_n_bits) * n_tiles + (hi[k] & mask);
+            for (int64_t s = slot_p + 1; s <= slot; ++s) offsets[s] = (int32_t)i;  // i == 0: zeros up to slot
+            slot_p = slot;
+            if (i == n_isects - 1)
+                for (int64_t s = slot + 1; s < n_tiles_total; ++s) offsets[s] = (int32_t)n_isects;
+        }
     }
 }
 
@@ -848,7 +864,8 @@ extern "C" int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids
         return SC_OK;
     }
     SC_CHECK_ARG(isect_ids, "null pointer");
-    isect_offset_encode_kernel<<<(unsigned)sc_div_up(n_isects, 256), 256, 0, (cudaStream_t)stream>>>(
+    SC_CHECK_ARG(((uintptr_t)isect_ids & 15) == 0, "16-byte alignment of isect_ids");
+    isect_offset_encode_kernel<<<(unsigned)sc_div_up(n_isects, 1024), 256, 0, (cudaStream_t)stream>>>(
         n_isects, isect_ids, n_tiles * C, n_tiles, tile_n_bits, offsets);
     SC_CHECK_LAUNCH("isect_offset_encode_kernel");
     return SC_OK;

@@ -12,7 +12,7 @@ namespace {
 
 constexpr int PB_THREADS = 128;
 
-__global__ void __launch_bounds__(PB_THREADS)
+__global__ void __launch_bounds__(PB_THREADS, 4)
 projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const float* __restrict__ quats,
                       const float* __restrict__ scales, const float* __restrict__ viewmats,
                       const float* __restrict__ Ks, int width, int height, float eps2d,
@@ -47,6 +47,16 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
         if (v_means) { old_p[0] = v_means[g * 3 + 0]; old_p[1] = v_means[g * 3 + 1]; old_p[2] = v_means[g * 3 + 2]; }
         if (v_scales) { old_s[0] = v_scales[g * 3 + 0]; old_s[1] = v_scales[g * 3 + 1]; old_s[2] = v_scales[g * 3 + 2]; }
         if (v_quats) old_q = reinterpret_cast<const float4*>(v_quats)[g];
+    }
+    // camera 0's upstream gradients are fetched NOW (one DRAM round trip together with the
+    // parameters) instead of after the forward recompute; further cameras load in the loop
+    float pf_conic[3] = {0.f, 0.f, 0.f}, pf_m2[2] = {0.f, 0.f}, pf_z = 0.f, pf_comp = 0.f;
+    if (__ldg(radii + g) > 0) {
+        pf_conic[0] = __ldg(v_conics + g * 3 + 0); pf_conic[1] = __ldg(v_conics + g * 3 + 1);
+        pf_conic[2] = __ldg(v_conics + g * 3 + 2);
+        pf_m2[0] = __ldg(v_means2d + g * 2 + 0); pf_m2[1] = __ldg(v_means2d + g * 2 + 1);
+        pf_z = __ldg(v_depths + g * vd_stride);
+        if (v_comps) pf_comp = __ldg(v_comps + g);
     }
     // ---- forward recompute: rotation, M = R diag(s), Sigma
     const float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
@@ -129,17 +139,18 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
         const float rdet2 = rdet * rdet;
 
         // ---- upstream gradients
-        const float va = __ldg(v_conics + o * 3 + 0), vb = __ldg(v_conics + o * 3 + 1),
-                    vc = __ldg(v_conics + o * 3 + 2);
-        const float vmx = __ldg(v_means2d + o * 2 + 0), vmy = __ldg(v_means2d + o * 2 + 1);
-        const float vz_up = __ldg(v_depths + o * vd_stride);
+        const bool c0 = cam == 0;
+        const float va = c0 ? pf_conic[0] : __ldg(v_conics + o * 3 + 0), vb = c0 ? pf_conic[1] : __ldg(v_conics + o * 3 + 1),
+                    vc = c0 ? pf_conic[2] : __ldg(v_conics + o * 3 + 2);
+        const float vmx = c0 ? pf_m2[0] : __ldg(v_means2d + o * 2 + 0), vmy = c0 ? pf_m2[1] : __ldg(v_means2d + o * 2 + 1);
+        const float vz_up = c0 ? pf_z : __ldg(v_depths + o * vd_stride);
         // conic = (b11, -v01, b00) / det
         float g_b00 = va * (-b11 * b11 * rdet2) + vb * (v01 * b11 * rdet2) + vc * (rdet - b00 * b11 * rdet2);
         float g_b11 = va * (rdet - b11 * b00 * rdet2) + vb * (v01 * b00 * rdet2) + vc * (-b00 * b00 * rdet2);
         float g_v01 = va * (2.f * b11 * v01 * rdet2) + vb * (-rdet - 2.f * v01 * v01 * rdet2) +
                       vc * (2.f * b00 * v01 * rdet2);
         if (v_comps) {
-            float vcomp = __ldg(v_comps + o);
+            float vcomp = c0 ? pf_comp : __ldg(v_comps + o);
             const float ratio = det_orig * rdet;
             if (opacities) {
                 const float v_prod = vcomp;

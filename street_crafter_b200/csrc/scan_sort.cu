@@ -109,8 +109,17 @@ constexpr int SORT_WARPS = SORT_THREADS / 32;
 #ifndef SC_SORT_KPT_U64
 #define SC_SORT_KPT_U64 16
 #endif
-template <typename KeyT> struct SortCfg { static constexpr int KPT = sizeof(KeyT) == 4 ? SC_SORT_KPT_U32 : SC_SORT_KPT_U64; };
-constexpr int sort_min_blocks(int kpt) { return kpt >= 16 ? 3 : kpt >= 8 ? 5 : 8; }
+#ifndef SC_SORT_MINB_U32
+#define SC_SORT_MINB_U32 3  // resident CTAs per SM the register budget is capped for (no spills beats
+                            // more warps: tools/sort_variants.sh)
+#endif
+#ifndef SC_SORT_MINB_U64
+#define SC_SORT_MINB_U64 2
+#endif
+template <typename KeyT> struct SortCfg {
+    static constexpr int KPT = sizeof(KeyT) == 4 ? SC_SORT_KPT_U32 : SC_SORT_KPT_U64;
+    static constexpr int MINB = sizeof(KeyT) == 4 ? SC_SORT_MINB_U32 : SC_SORT_MINB_U64;
+};
 constexpr int MAX_PASSES = SC_SORT_MAX_PASSES;
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_INC = 2u << 30;
@@ -151,7 +160,7 @@ sort_histogram_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* 
         const unsigned act = __ballot_sync(0xffffffffu, in);
         for (int p = 0; p < pp.passes; ++p) {
             const uint32_t d = (uint32_t)(k >> pp.shift[p]) & ((1u << pp.nbits[p]) - 1u);
-            const unsigned peers = sc_match_digit8(d) & act;  // d < 256; lanes past the end are masked by act
+            const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu) & act;
             if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p * RADIX + d], (uint32_t)__popc(peers));
         }
     }
@@ -182,7 +191,7 @@ sort_hist_scan_kernel(uint32_t* __restrict__ hist) {
 }
 
 template <typename KeyT>
-__global__ void __launch_bounds__(SORT_THREADS, sort_min_blocks(SortCfg<KeyT>::KPT))
+__global__ void __launch_bounds__(SORT_THREADS, SortCfg<KeyT>::MINB)
 onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* __restrict__ keys_in,
                      const uint32_t* __restrict__ vals_in,
                      KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int nbits,
@@ -230,6 +239,13 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
         if ((peers & lt_mask) == 0) sm.warp_hist[w][d] = pre + __popc(peers);
         __syncwarp();
     }
+    // values: issued now so that their DRAM latency hides under the look-back below
+    uint32_t val[SORT_KPT];
+#pragma unroll
+    for (int i = 0; i < SORT_KPT; ++i) {
+        const int local = warp_base + i * 32 + lane;
+        val[i] = (local < n_valid) ? __ldg(vals_in + tile_base + local) : 0u;
+    }
     __syncthreads();
 
     // ---- per digit (thread == digit): warp-exclusive offsets, tile count, look-back
@@ -243,7 +259,9 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
             acc += c;
         }
         const uint32_t count = acc;
-        // publish aggregate, then resolve exclusive prefix over previous tiles
+        // publish aggregate, then resolve exclusive prefix over previous tiles.  The walk reads
+        // FOUR predecessors per round trip (independent loads), consumes them in order and
+        // re-polls from the first one that is not published yet.
         volatile uint32_t* my = lookback + (size_t)tile * RADIX + d;
         uint32_t excl = 0;
         if (tile == 0) {
@@ -251,13 +269,22 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
         } else {
             *my = count | FLAG_AGG;
             int64_t t = (int64_t)tile - 1;
-            while (true) {
-                const uint32_t v = lookback[(size_t)t * RADIX + d];
-                const uint32_t f = v & FLAG_MASK;
-                if (f == 0) continue;  // not yet published: spin
-                excl += v & VAL_MASK;
-                if (f == FLAG_INC) break;
-                --t;
+            bool done = false;
+            while (!done) {
+                uint32_t v[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) v[u] = (t - u >= 0) ? lookback[(size_t)(t - u) * RADIX + d] : (2u << 30);
+                int used = 0;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t f = v[u] & FLAG_MASK;
+                    if (!done && used == u && f != 0) {
+                        excl += v[u] & VAL_MASK;
+                        used = u + 1;
+                        done = f == FLAG_INC;
+                    }
+                }
+                t -= used;
             }
             *my = (excl + count) | FLAG_INC;
         }
@@ -291,7 +318,7 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
 #pragma unroll
     for (int i = 0; i < SORT_KPT; ++i) {
         const int local = warp_base + i * 32 + lane;
-        if (local < n_valid) sm.vals[rank[i]] = __ldg(vals_in + tile_base + local);
+        if (local < n_valid) sm.vals[rank[i]] = val[i];
     }
     __syncthreads();
     // ---- coalesced write-out: consecutive threads -> consecutive slots of a digit run

@@ -334,6 +334,8 @@ def isect_offset_encode(isect_ids: Tensor, n_cameras: int, tile_width: int, tile
     if not isect_ids.is_cuda:
         raise RuntimeError("isect_ids must be a CUDA tensor: street_crafter_b200 has no CPU path")
     isect_ids = isect_ids.contiguous()
+    if isect_ids.data_ptr() % 16:
+        isect_ids = isect_ids.clone()  # the kernel reads two keys per 16-byte load
     dev = isect_ids.device
     offsets = torch.empty((n_cameras, tile_height, tile_width), dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
