@@ -30,6 +30,12 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# torchrun exports OMP_NUM_THREADS=1; the reference arm (rank 0 only) and the N=1 cpu_baseline leg
+# time the CPU oracle on ALL host cores, so undo that before torch initialises its thread pools
+if "reference" in sys.argv or int(os.environ.get("WORLD_SIZE", "1")) == 1:
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+    os.environ.pop("MKL_NUM_THREADS", None)
+
 import torch  # noqa: E402
 
 N_GAUSS = 2_000_000
@@ -132,8 +138,40 @@ class ClockSampler:
 
     def __init__(self, index):
         self.rows, self.proc, self.index = [], None, index
+        self.nvml, self.stop_flag, self.samples = None, False, []
+
+    def _nvml_loop(self):
+        import pynvml as nv
+        h = self.nvml
+        R = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+             "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        while not self.stop_flag:
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+                try:
+                    mask = nv.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                self.samples.append((sm, mx, [k for k, bit in R.items() if mask & bit]))
+            except Exception:
+                break
+            time.sleep(0.002)
 
     def start(self):
+        # in-process NVML polling (every ~2 ms: the timed region is only tens of ms long);
+        # nvidia-smi -lms as the fallback
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].isdigit() else self.index
+            self.nvml = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.t = threading.Thread(target=self._nvml_loop, daemon=True)
+            self.t.start()
+            return
+        except Exception:
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -148,6 +186,14 @@ class ClockSampler:
             self.rows.append([x.strip() for x in line.split(",")])
 
     def stop(self):
+        if self.nvml is not None:
+            self.stop_flag = True
+            self.t.join(timeout=1)
+            sm = [s[0] for s in self.samples]
+            mx = [s[1] for s in self.samples]
+            reasons = sorted({r for s in self.samples for r in s[2]})
+            return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                    "reasons": reasons, "samples": len(sm), "source": "nvml"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -167,7 +213,7 @@ class ClockSampler:
             except Exception:
                 pass
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvidia-smi"}
 
 
 class StageTimer:
@@ -427,7 +473,7 @@ def run_ours(args):
         t_roof += (44.0 * Ic * 2 + 24.0 * P + 28.0 * P) * n_views / (hbm_peak * 1e9) * 0  # compositing bytes hide under FP32
 
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:  # rank 0 at N=1 only (tier rule 4)
             n_s, W_s, H_s = 100_000, 960, 640
             t_cpu, cores = time_cpu_oracle(n_s, W_s, H_s, reps=1)
             cpu = {"value": W_s * H_s / t_cpu / 1e6, "unit": "Mpix/s", "cores": cores, "kind": "port",
