@@ -1,6 +1,6 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, a short bench, the ncu launch list and one --set full
-# capture of the compositing + sort kernels.  Usage (from the repo root):
+# One gpurun call: GPU parity tests, the bench, the ncu launch list of the same bench command and
+# one --set full capture of one launch of every hot kernel.  Usage (from the repo root):
 #   gpurun --timeout 1500 -- 'bash tools/gpu_check.sh [tag]'
 TAG=${1:-r01}
 mkdir -p gpurun_out
@@ -8,14 +8,16 @@ python -m pytest tests -m gpu -x -q > gpurun_out/${TAG}_pytest.log 2>&1
 echo "pytest exit $?" | tee -a gpurun_out/${TAG}_pytest.log
 tail -3 gpurun_out/${TAG}_pytest.log
 python bench.py --steps 10 --warmup 3 > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err
-echo "bench exit $?"; tail -c 600 gpurun_out/${TAG}_bench.json
+echo "bench exit $?"; tail -c 400 gpurun_out/${TAG}_bench.json
 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
     --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline \
     > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
+# per camera pass the filter matches 12 launches (projection fwd, 4+2 onesweep, emit, SH fwd, the two
+# compositing kernels, SH bwd, projection bwd): skip 6 warm-up passes, capture one pass
 ncu --set full --clock-control none --import-source on \
-    -k regex:'rasterize_|onesweep' -s 24 -c 6 -o gpurun_out/${TAG}_prof -f \
+    -k regex:'rasterize_|onesweep|sh_bwd|sh_fwd|projection_|isect_emit' -s 72 -c 12 -o gpurun_out/${TAG}_prof -f \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
-ls -la gpurun_out | tail -20
+ls -la gpurun_out | tail -12
