@@ -275,6 +275,7 @@ def run_ours(args):
 
     import street_crafter_b200 as S
     from street_crafter_b200 import _lib, rendering
+    from street_crafter_b200.losses import photometric_loss_render
     from street_crafter_b200.parallel import GaussianArena, HostViewFeeder, allreduce_gradients
     from street_crafter_b200.renderer import render_kernel_gsplat
     from tools.scene import make_camera, make_gaussians
@@ -326,7 +327,7 @@ def run_ours(args):
 
     def step_e2e():
         """host buffers in, loss out: camera + target image H2D (staged on a side stream so that
-        view v+1's copies overlap view v's render), L1 loss, backward, loss D2H"""
+        view v+1's copies overlap view v's render), the reference's L1 + SSIM loss, backward, loss D2H"""
         arena.zero_grad()
         staged = [feeder.stage((host_V[v], host_K[v], host_C[v], host_gt[v])) for v in range(n_views)]
         losses = []
@@ -336,7 +337,9 @@ def run_ours(args):
             Vd, Kd, Cd, gt = tensors
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
                                        Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks)
-            loss = (out["rgb"] - gt).abs().mean() + 0.01 * out["acc"].mean()
+            # the reference's training loss (train.py:183-186 without the LPIPS network):
+            # 0.8 * L1 + 0.2 * (1 - SSIM), fused forward + backward on the compositor's output
+            loss = photometric_loss_render(out["render_colors"], gt, None, 0.2, 1.0)[0]
             loss.backward()
             losses.append(loss.detach())
         if world > 1:
@@ -437,7 +440,10 @@ def run_ours(args):
         ach_fwd = flop_fwd / n_views / (t_fwd * 1e-3) / 1e12 if t_fwd else None
         roofline = {"kernel": "rasterize_bwd_kernel<4>", "bound": "fp32", "achieved": ach_bwd,
                     "peak": fp32_peak, "unit": "TFLOP/s", "frac": (ach_bwd / fp32_peak) if ach_bwd else None,
-                    "traffic": None,
+                    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this
+                    # workload (ncu --set full capture, profiles/r01n_ncu_summary.txt): the kernel is
+                    # compute-bound, its HBM traffic is ~2 % of peak
+                    "traffic": 87.96e6, "traffic_source": "profiles/r01n_ncu_summary.txt",
                     "peak_source": "sc_probe_fp32 FMA probe run in this process (no tensor cores on this path)",
                     "ms_per_launch": t_bwd, "alg_flop_per_launch": flop_bwd / n_views,
                     "visited_pairs_per_launch": visited / n_views,
@@ -490,7 +496,8 @@ def run_ours(args):
                        "parallelism": f"view-sharded x{world}, flat-arena gradient all-reduce" if world > 1 else "single GPU"},
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h,
-                    "what": "pinned host camera matrices + target images -> device, render, L1 loss, backward, loss -> host"},
+                    "what": "pinned host camera matrices + target images -> device (side stream), render, "
+                            "0.8*L1 + 0.2*(1-SSIM) loss (fused kernels), backward, loss -> host"},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,

@@ -182,6 +182,25 @@ int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int 
                      const float* v_render_alphas, float* v_means2d, float* v_means2d_abs,
                      float* v_conics, float* v_colors, float* v_opacities, void* stream);
 
+/* ---- N3: fused photometric loss --------------------------------------- */
+/* loss = (1 - lambda_dssim) * lambda_l1 * L1 + lambda_dssim * (1 - SSIM)
+ * (street_gaussian/utils/loss_utils.py:21-38, :84-131 combined as at train.py:183-186; no LPIPS).
+ * image element (c, y, x), c < 3, lives at image[c * channel_stride + (y * W + x) * pixel_stride]
+ * (the compositor's [H,W,4] output: strides 1 / 4; a contiguous [3,H,W] tensor: H*W / 1);
+ * gt[3,H,W] contiguous; mask[H,W] u8 nullable (reference: l1 over masked pixels, SSIM on inputs
+ * zeroed outside the mask).  out3 = {loss, L1, SSIM} (device floats).  The backward reads the
+ * upstream scalar from DEVICE memory (nullable = 1) and WRITES d loss / d image for the three
+ * channels with the given output strides.  workspace >= sc_photometric_workspace_bytes, kept
+ * between the two calls. */
+int64_t sc_photometric_workspace_bytes(int H, int W);
+int sc_photometric_fwd(int H, int W, const float* image, int64_t channel_stride, int64_t pixel_stride,
+                       const float* gt, const uint8_t* mask, float lambda_dssim, float lambda_l1,
+                       void* workspace, int64_t workspace_bytes, float* out3, void* stream);
+int sc_photometric_bwd(int H, int W, const float* image, int64_t channel_stride, int64_t pixel_stride,
+                       const float* gt, const uint8_t* mask, float lambda_dssim, float lambda_l1,
+                       const void* workspace, const float* upstream, float* v_image,
+                       int64_t v_channel_stride, int64_t v_pixel_stride, void* stream);
+
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,
  * as the reference's FLT_MAX placeholders overflow).  Never synchronises (scene bounds stay

@@ -28,6 +28,7 @@ SOURCES = {
     "scan_sort.cu": [],
     "rasterize.cu": ["--use_fast_math"],
     "knn.cu": [],
+    "loss.cu": [],
     "probe.cu": ["--use_fast_math"],
 }
 

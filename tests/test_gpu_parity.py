@@ -592,3 +592,66 @@ def test_point_rasterizer_max_hit(S, dev):
     assert_image_close(alpha[0], wa[0, ..., 0], "lidar alpha")
     nolimit, _ = G.rasterize_to_pixels(m2, cn, cols, torch.ones(1, N), W, H, 16, off, flat)
     assert (nolimit - want).abs().max() > 1e-3, "max_hit must matter in this scene"
+
+
+# ------------------------------------------------------------------------------ photometric loss (N3)
+LOSS_TOL = 2e-5   # fp32 kernel vs float64 reference values (loss terms are O(0.1..1))
+
+
+def test_photometric_loss_vs_reference_golden(S, dev):
+    """fused L1 + SSIM kernels against the reference's own l1_loss / ssim outputs
+    (tests/golden/loss_l1_ssim.npz, made by importing /root/reference/.../loss_utils.py)"""
+    import numpy as np
+    from street_crafter_b200 import losses as L
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_l1_ssim.npz"))
+    for name in ("a", "b", "c"):
+        img = torch.from_numpy(z[f"{name}_img"]).float().to(dev).requires_grad_(True)
+        gt = torch.from_numpy(z[f"{name}_gt"]).float().to(dev)
+        mask = torch.from_numpy(z[f"{name}_mask"]).to(dev) if z[f"{name}_mask"].size else None
+        loss, l1, s = L.photometric_loss(img, gt, mask, lambda_dssim=0.2, lambda_l1=1.0)
+        loss.backward()
+        assert abs(float(l1) - float(z[f"{name}_l1"])) < LOSS_TOL, name
+        assert abs(float(s) - float(z[f"{name}_ssim"])) < LOSS_TOL, name
+        assert abs(float(loss.detach()) - float(z[f"{name}_loss"])) < LOSS_TOL, name
+        want = torch.from_numpy(z[f"{name}_grad"])
+        assert_grad_close(img.grad, want, f"loss grad {name}")
+        # the reference's names
+        assert abs(float(L.l1_loss(img.detach(), gt, mask)) - float(z[f"{name}_l1"])) < LOSS_TOL
+        assert abs(float(L.ssim(img.detach(), gt, mask=mask)) - float(z[f"{name}_ssim"])) < LOSS_TOL
+
+
+@pytest.mark.parametrize("H,W,use_mask", [(97, 131, True), (128, 160, False), (5, 7, True)])
+def test_photometric_loss_vs_oracle_and_layouts(S, dev, H, W, use_mask):
+    """ragged sizes (partial tiles, images smaller than the window), the strided `rgb` view of
+    the compositor's output and the direct [1,H,W,4] entry all give the oracle's values"""
+    from oracle import loss_torch as LO
+    from street_crafter_b200 import losses as L
+    g = torch.Generator().manual_seed(H * 1000 + W)
+    rc = torch.rand(1, H, W, 4, generator=g)
+    gt = (0.5 * torch.rand(3, H, W, generator=g) + 0.5 * rc[0, ..., :3].permute(2, 0, 1)).contiguous()
+    mask = (torch.rand(1, H, W, generator=g) > 0.25) if use_mask else None
+    img_w = rc[0, ..., :3].permute(2, 0, 1).double().requires_grad_(True)
+    loss_w, l1_w, s_w = LO.photometric_loss(img_w, gt.double(), mask, 0.2, 1.0)
+    (3.0 * loss_w).backward()
+    md = mask.to(dev) if mask is not None else None
+    # (1) strided view, as the renderer returns it
+    rc1 = rc.to(dev).requires_grad_(True)
+    img = rc1[..., :-1][0].permute(2, 0, 1)
+    loss, l1, s = L.photometric_loss(img, gt.to(dev), md, 0.2, 1.0)
+    (3.0 * loss).backward()
+    assert abs(float(loss.detach()) - float(loss_w)) < LOSS_TOL and abs(float(s) - float(s_w)) < LOSS_TOL
+    assert abs(float(l1) - float(l1_w)) < LOSS_TOL
+    assert_grad_close(rc1.grad[0, ..., :3].permute(2, 0, 1), img_w.grad, "grad via rgb view")
+    assert (rc1.grad[..., 3] == 0).all()
+    # (2) direct entry on render_colors
+    rc2 = rc.to(dev).requires_grad_(True)
+    loss2, _, _ = L.photometric_loss_render(rc2, gt.to(dev), md, 0.2, 1.0)
+    (3.0 * loss2).backward()
+    assert abs(float(loss2.detach()) - float(loss_w)) < LOSS_TOL
+    assert_grad_close(rc2.grad[0, ..., :3].permute(2, 0, 1), img_w.grad, "grad via render_colors")
+    assert (rc2.grad[..., 3] == 0).all()
+    # (3) contiguous [3,H,W]
+    img3 = rc[0, ..., :3].permute(2, 0, 1).contiguous().to(dev).requires_grad_(True)
+    loss3, _, _ = L.photometric_loss(img3, gt.to(dev), md, 0.2, 1.0)
+    (3.0 * loss3).backward()
+    assert_grad_close(img3.grad, img_w.grad, "grad contiguous")

@@ -265,3 +265,23 @@ def test_cpu_tensors_raise():
     with pytest.raises(RuntimeError):
         S.fully_fused_projection(torch.zeros(4, 3), None, torch.ones(4, 4), torch.ones(4, 3),
                                  torch.eye(4)[None], torch.eye(3)[None], 32, 32)
+
+
+# ------------------------------------------------------------------------------ photometric loss (N3)
+def test_loss_oracle_matches_reference_golden():
+    """oracle/loss_torch.py against outputs of the reference's own l1_loss / ssim
+    (tests/golden/loss_l1_ssim.npz, generated by tools/make_golden_loss.py importing
+    /root/reference/street_gaussian/utils/loss_utils.py)"""
+    import numpy as np
+    from oracle import loss_torch as LO
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "loss_l1_ssim.npz"))
+    for name in ("a", "b", "c"):
+        img = torch.from_numpy(z[f"{name}_img"]).requires_grad_(True)
+        gt = torch.from_numpy(z[f"{name}_gt"])
+        mask = torch.from_numpy(z[f"{name}_mask"]) if z[f"{name}_mask"].size else None
+        loss, l1, s = LO.photometric_loss(img, gt, mask, lambda_dssim=0.2, lambda_l1=1.0)
+        loss.backward()
+        assert abs(float(l1) - float(z[f"{name}_l1"])) < 1e-12
+        assert abs(float(s) - float(z[f"{name}_ssim"])) < 1e-10
+        assert abs(float(loss) - float(z[f"{name}_loss"])) < 1e-10
+        assert np.abs(img.grad.numpy() - z[f"{name}_grad"]).max() < 1e-10
