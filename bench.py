@@ -329,16 +329,20 @@ def run_ours(args):
         """host buffers in, loss out: camera + target image H2D (staged on a side stream so that
         view v+1's copies overlap view v's render), the reference's L1 + SSIM loss, backward, loss D2H"""
         arena.zero_grad()
-        staged = [feeder.stage((host_V[v], host_K[v], host_C[v], host_gt[v])) for v in range(n_views)]
+        # camera matrices first (tiny, needed before the render), target images after them (needed
+        # only at the loss): the first view's render overlaps its own image copy
+        staged_cam = [feeder.stage((host_V[v], host_K[v], host_C[v])) for v in range(n_views)]
+        staged_gt = [feeder.stage((host_gt[v],)) for v in range(n_views)]
         losses = []
         for v in range(n_views):
-            tensors, ready = staged[v]
-            feeder.acquire(tensors, ready)
-            Vd, Kd, Cd, gt = tensors
+            feeder.acquire(*staged_cam[v])
+            Vd, Kd, Cd = staged_cam[v][0]
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
                                        Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks)
             # the reference's training loss (train.py:183-186 without the LPIPS network):
             # 0.8 * L1 + 0.2 * (1 - SSIM), fused forward + backward on the compositor's output
+            feeder.acquire(*staged_gt[v])
+            gt = staged_gt[v][0][0]
             loss = photometric_loss_render(out["render_colors"], gt, None, 0.2, 1.0)[0]
             loss.backward()
             losses.append(loss.detach())

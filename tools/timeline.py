@@ -1,5 +1,5 @@
 """GPU timeline of one bench step (torch.profiler / CUPTI): kernel time, idle gaps and who
-precedes them.   python tools/timeline.py [steps]"""
+precedes them.   python tools/timeline.py [steps] [e2e]   (e2e: host inputs + the fused loss)"""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -26,6 +26,27 @@ def step():
         out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities, V, K, cc,
                                    W, H, deg, grad_sinks=sinks)
         torch.autograd.backward([out["render_colors"], out["render_alphas"]], [a, b])
+
+if len(sys.argv) > 2 and sys.argv[2] == "e2e":
+    from street_crafter_b200.losses import photometric_loss_render
+    from street_crafter_b200.parallel import HostViewFeeder
+    feeder = HostViewFeeder(dev)
+    host = [(c[0].cpu().pin_memory(), c[1].cpu().pin_memory(), c[2].cpu().pin_memory(),
+             torch.rand(3, H, W).pin_memory()) for c in cams]
+
+    def step():
+        arena.zero_grad()
+        staged = [feeder.stage(h) for h in host]
+        losses = []
+        for tensors, ready in staged:
+            feeder.acquire(tensors, ready)
+            Vd, Kd, Cd, gt = tensors
+            out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities, Vd, Kd,
+                                       Cd, W, H, deg, grad_sinks=sinks)
+            loss = photometric_loss_render(out["render_colors"], gt, None, 0.2, 1.0)[0]
+            loss.backward()
+            losses.append(loss.detach())
+        return torch.stack(losses).cpu()
 
 for _ in range(3):
     step()
