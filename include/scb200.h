@@ -15,6 +15,11 @@
  *                               data_processor/utils/render_utils.py:150-177)
  *   sc_knn3_mean_dist2         simple_knn._C.distCUDA2         submodules/simple-knn/spatial.cu:16-25,
  *                                                              simple_knn.cu:186-222
+ *   sc_isect_prepare/emit_sorted   the same isect_tiles(sort=True) as two calls around its one host read-back
+ *   sc_*_opacity, sc_sh_*_view     the kernels above with the renderer's glue folded in
+ *                                  (street_gaussian_renderer.py:233-238, :256-266)
+ *   sc_photometric_fwd/bwd     loss_utils.l1_loss + ssim       street_gaussian/utils/loss_utils.py:21-38, :96-131,
+ *                                                              combined as in train.py:183-186
  *
  * Conventions: all pointers are DEVICE pointers unless named host_*; row-major contiguous
  * fp32 / int32 / int64 arrays; `stream` is a cudaStream_t passed as void*; nothing here
