@@ -299,114 +299,129 @@ struct ShT {
     static constexpr int STRIDE = K3 + 4;   // floats per padded row
     static constexpr int TILE_FLOATS = 32 * STRIDE;
 };
-constexpr int SHT_WARPS = 8;
+#ifndef SC_SH_WARPS
+#define SC_SH_WARPS 8
+#endif
+constexpr int SHT_WARPS = SC_SH_WARPS;
+#ifndef SC_SH_MINB_FWD
+#define SC_SH_MINB_FWD 3  // resident CTAs per SM the register budget is capped for
+#endif
+#ifndef SC_SH_MINB_BWD
+#define SC_SH_MINB_BWD 3
+#endif
 
-// coalesced: the chunk's n*Q float4 <-> padded rows; only Gaussians in `vis`
+// coalesced: the chunk's n*Q float4 -> padded rows; only Gaussians in `vis`.  The copies are
+// asynchronous (cp.async, 16 B each, no staging registers): all Q of a lane are in flight at
+// once; sht_wait() is called right before the rows are read.
 template <int K>
-__device__ __forceinline__ void sht_load(const float4* __restrict__ src4, int n, unsigned vis, float* tile,
-                                         int lane) {
+__device__ __forceinline__ void sht_issue(const float4* __restrict__ src4, unsigned vis, float* tile, int lane) {
     constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
-    constexpr int UB = Q < 6 ? Q : 6;  // loads in flight per lane
+    if (vis) {
 #pragma unroll
-    for (int u0 = 0; u0 < Q; u0 += UB) {
-        float4 v[UB];
-        bool on[UB];
-#pragma unroll
-        for (int u = 0; u < UB; ++u) {
-            const int i = lane + 32 * (u0 + u);
+        for (int u = 0; u < Q; ++u) {
+            const int i = lane + 32 * u;
             const int gl = i / Q;
-            on[u] = (u0 + u < Q) && (gl < n) && ((vis >> gl) & 1u);
-            if (on[u]) v[u] = __ldg(src4 + i);
-        }
-#pragma unroll
-        for (int u = 0; u < UB; ++u) {
-            const int i = lane + 32 * (u0 + u);
-            const int gl = i / Q;
-            if (on[u]) *reinterpret_cast<float4*>(tile + gl * STRIDE + 4 * (i - gl * Q)) = v[u];
+            if ((vis >> gl) & 1u) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(tile + gl * STRIDE + 4 * (i - gl * Q));
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src4 + i) : "memory");
+            }
         }
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
 }
 
+__device__ __forceinline__ void sht_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Per warp: chunks of 32 consecutive Gaussians.  The per-lane inputs (mask, position, upstream
+// gradient) of the NEXT chunk are requested before the current chunk's coefficient copies are
+// waited for, so a chunk exposes one DRAM round trip (its coefficient span, all Q float4 of a
+// lane in flight at once); 24 resident warps per SM overlap those.  (A two-tile software
+// pipeline per warp was measured slower: its shared memory halves the resident warps.)
 template <int K, int DEG>
-__global__ void __launch_bounds__(SHT_WARPS * 32, 3)
+__global__ void __launch_bounds__(SHT_WARPS * 32, SC_SH_MINB_FWD)
 sh_fwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restrict__ coeffs4,
                 const uint8_t* __restrict__ masks, float* __restrict__ colors, ShView vw) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NB = (DEG + 1) * (DEG + 1);
-    constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
+    constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE, TILE = ShT<K>::TILE_FLOATS;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    float* tile = smem + wib * ShT<K>::TILE_FLOATS;
+    float* tile = smem + wib * TILE;
     const int64_t n_chunks = (M + 31) >> 5;
     const float cx = vw.campos ? __ldg(vw.campos + 0) : 0.f, cy = vw.campos ? __ldg(vw.campos + 1) : 0.f,
                 cz = vw.campos ? __ldg(vw.campos + 2) : 0.f;
-    for (int64_t chunk = (int64_t)blockIdx.x * SHT_WARPS + wib; chunk < n_chunks;
-         chunk += (int64_t)gridDim.x * SHT_WARPS) {
-        const int64_t g0 = chunk << 5;
-        const int n = (int)min((int64_t)32, M - g0);
-        const int64_t g = g0 + lane;
-        const bool live = (lane < n) && (vw.radii ? __ldg(vw.radii + g) > 0 : (masks == nullptr || __ldg(masks + g) != 0));
-        const unsigned vis = __ballot_sync(0xffffffffu, live);
+    struct LaneIn { bool m; float x, y, z, d; };
+    auto fetch = [&](int64_t chunk) {
+        LaneIn in{false, 0.f, 0.f, 0.f, 0.f};
+        const int64_t g = (chunk << 5) + lane;
+        if (chunk < n_chunks && g < M) {
+            in.m = vw.radii ? __ldg(vw.radii + g) > 0 : (masks == nullptr || __ldg(masks + g) != 0);
+            in.x = __ldg(dirs + g * 3 + 0) - cx; in.y = __ldg(dirs + g * 3 + 1) - cy;
+            in.z = __ldg(dirs + g * 3 + 2) - cz;
+            if (vw.depths) in.d = __ldg(vw.depths + g);
+        }
+        return in;
+    };
+    const int64_t first = (int64_t)blockIdx.x * SHT_WARPS + wib, step = (int64_t)gridDim.x * SHT_WARPS;
+    if (first >= n_chunks) return;
+    LaneIn cur = fetch(first);
+    for (int64_t chunk = first; chunk < n_chunks; chunk += step) {
+        sht_issue<K>(coeffs4 + (chunk << 5) * Q, __ballot_sync(0xffffffffu, cur.m), tile, lane);
+        const LaneIn nxt = fetch(chunk + step);
+        const int64_t g = (chunk << 5) + lane;
         float r = 0.f, gg = 0.f, b = 0.f;
-        if (vis) {
-            float x = 0.f, y = 0.f, z = 0.f;
-            if (live) {
-                x = __ldg(dirs + g * 3 + 0) - cx; y = __ldg(dirs + g * 3 + 1) - cy;
-                z = __ldg(dirs + g * 3 + 2) - cz;
-            }
-            sht_load<K>(coeffs4 + g0 * Q, n, vis, tile, lane);
-            __syncwarp();
-            if (live) {
-                const float inv = 1.0f / fmaxf(sqrtf(x * x + y * y + z * z), 1e-12f);
-                float Y[25];
-                sh_basis<DEG>(x * inv, y * inv, z * inv, Y);
-                const float4* row = reinterpret_cast<const float4*>(tile + lane * STRIDE);
-                float acc[3] = {0.f, 0.f, 0.f};
+        float Y[25];
+        if (cur.m) {
+            const float inv = 1.0f / fmaxf(sqrtf(cur.x * cur.x + cur.y * cur.y + cur.z * cur.z), 1e-12f);
+            sh_basis<DEG>(cur.x * inv, cur.y * inv, cur.z * inv, Y);
+        }
+        sht_wait();
+        __syncwarp();
+        if (cur.m) {
+            const float4* row = reinterpret_cast<const float4*>(tile + lane * STRIDE);
+            float acc[3] = {0.f, 0.f, 0.f};
 #pragma unroll
-                for (int q = 0; q < Q; ++q) {
-                    if (4 * q < NB * 3) {  // float4s wholly beyond the used degree are skipped
-                        const float4 c = row[q];
-                        const float cv[4] = {c.x, c.y, c.z, c.w};
+            for (int q = 0; q < Q; ++q) {
+                if (4 * q < NB * 3) {  // float4s wholly beyond the used degree are skipped
+                    const float4 c = row[q];
+                    const float cv[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int e = 4 * q + j;
-                            if (e < NB * 3) acc[e % 3] = fmaf(Y[e / 3], cv[j], acc[e % 3]);
-                        }
+                    for (int j = 0; j < 4; ++j) {
+                        const int e = 4 * q + j;
+                        if (e < NB * 3) acc[e % 3] = fmaf(Y[e / 3], cv[j], acc[e % 3]);
                     }
                 }
-                r = acc[0]; gg = acc[1]; b = acc[2];
             }
-            __syncwarp();
+            r = acc[0]; gg = acc[1]; b = acc[2];
         }
-        if (lane < n) {
+        __syncwarp();  // the tile is overwritten by the next chunk's copies
+        if (g < M) {
             if (vw.depths) {
                 // view mode (A5 + A6 fused): clamp_min(colour + 0.5, 0) and the depth channel
                 reinterpret_cast<float4*>(colors)[g] = make_float4(fmaxf(r + 0.5f, 0.f), fmaxf(gg + 0.5f, 0.f),
-                                                                   fmaxf(b + 0.5f, 0.f), __ldg(vw.depths + g));
+                                                                   fmaxf(b + 0.5f, 0.f), cur.d);
             } else {
                 colors[g * 3 + 0] = r; colors[g * 3 + 1] = gg; colors[g * 3 + 2] = b;
             }
         }
+        cur = nxt;
     }
 }
 
 template <int K, int DEG>
-__global__ void __launch_bounds__(SHT_WARPS * 32, 3)
+__global__ void __launch_bounds__(SHT_WARPS * 32, SC_SH_MINB_BWD)
 sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restrict__ coeffs4,
                 const uint8_t* __restrict__ masks, const float* __restrict__ v_colors,
                 float4* __restrict__ v_coeffs4, float* __restrict__ v_dirs, int accumulate, ShView vw) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NB = (DEG + 1) * (DEG + 1);
-    constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE;
+    constexpr int Q = ShT<K>::Q, STRIDE = ShT<K>::STRIDE, TILE = ShT<K>::TILE_FLOATS;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    float* tile = smem + wib * ShT<K>::TILE_FLOATS;
+    float* tile = smem + wib * TILE;
     const int64_t n_chunks = (M + 31) >> 5;
     const bool want_dirs = v_dirs != nullptr;
     const int vs = vw.vc_stride;
     const float cx = vw.campos ? __ldg(vw.campos + 0) : 0.f, cy = vw.campos ? __ldg(vw.campos + 1) : 0.f,
                 cz = vw.campos ? __ldg(vw.campos + 2) : 0.f;
-    // per-lane inputs of a chunk (mask, direction, upstream colour gradient) are fetched one
-    // chunk AHEAD, unconditionally, so that the only DRAM latency a chunk exposes is its
-    // coefficient span
     struct LaneIn { bool m; float x, y, z, r, g, b; };
     auto fetch = [&](int64_t chunk) {
         LaneIn in{false, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -417,7 +432,7 @@ sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restr
             in.z = __ldg(dirs + g * 3 + 2) - cz;
             if (vs == 4) {
                 // view mode: one 16-byte load per row; unconditional (a load gated on the mask
-                // would make this prefetch wait for the mask's DRAM round trip)
+                // would wait for the mask's DRAM round trip)
                 const float4 v = __ldg(reinterpret_cast<const float4*>(v_colors) + g);
                 in.r = v.x; in.g = v.y; in.b = v.z;
                 if (vw.colors_fwd) {  // backward of clamp_min(colour + 0.5, 0)
@@ -430,17 +445,20 @@ sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restr
         }
         return in;
     };
-    const int64_t chunk_step = (int64_t)gridDim.x * SHT_WARPS;
-    LaneIn nxt = fetch((int64_t)blockIdx.x * SHT_WARPS + wib);
-    for (int64_t chunk = (int64_t)blockIdx.x * SHT_WARPS + wib; chunk < n_chunks; chunk += chunk_step) {
+    const int64_t first = (int64_t)blockIdx.x * SHT_WARPS + wib, step = (int64_t)gridDim.x * SHT_WARPS;
+    if (first >= n_chunks) return;
+    LaneIn cur = fetch(first);
+    for (int64_t chunk = first; chunk < n_chunks; chunk += step) {
+        const unsigned vis = __ballot_sync(0xffffffffu, cur.m);
+        sht_issue<K>(coeffs4 + (chunk << 5) * Q, want_dirs ? vis : 0u, tile, lane);
+        const LaneIn nxt = fetch(chunk + step);
         const int64_t g0 = chunk << 5;
         const int n = (int)min((int64_t)32, M - g0);
         const int64_t g = g0 + lane;
-        const LaneIn cur = nxt;
-        nxt = fetch(chunk + chunk_step);
-        const bool live = (lane < n) && cur.m;
-        const unsigned vis = __ballot_sync(0xffffffffu, live);
+        const bool live = cur.m;
         float4* dst4 = v_coeffs4 + g0 * Q;
+        sht_wait();
+        __syncwarp();
         if (!vis) {
             // nothing visible in the chunk: zeros, or untouched in accumulate mode
             if (!accumulate) {
@@ -451,83 +469,84 @@ sh_bwd_t_kernel(int64_t M, const float* __restrict__ dirs, const float4* __restr
                 }
                 if (want_dirs && lane < n) { v_dirs[g * 3] = 0.f; v_dirs[g * 3 + 1] = 0.f; v_dirs[g * 3 + 2] = 0.f; }
             }
-            continue;
-        }
-        float x = cur.x, y = cur.y, z = cur.z, inv = 0.f;
-        const float vc[3] = {live ? cur.r : 0.f, live ? cur.g : 0.f, live ? cur.b : 0.f};
-        if (want_dirs) sht_load<K>(coeffs4 + g0 * Q, n, vis, tile, lane);
-        float Y[25];
-        if (live) {
-            inv = 1.0f / fmaxf(sqrtf(x * x + y * y + z * z), 1e-12f);
-            x *= inv; y *= inv; z *= inv;
-            sh_basis<DEG>(x, y, z, Y);
-        }
-        float gx = 0.f, gy = 0.f, gz = 0.f;
-        float4* row = reinterpret_cast<float4*>(tile + lane * STRIDE);
-        if (want_dirs) {
-            __syncwarp();
+        } else {
+            float x = cur.x, y = cur.y, z = cur.z, inv = 0.f;
+            const float vc[3] = {live ? cur.r : 0.f, live ? cur.g : 0.f, live ? cur.b : 0.f};
             if (live) {
-                float s[25];
+                inv = 1.0f / fmaxf(sqrtf(x * x + y * y + z * z), 1e-12f);
+                x *= inv; y *= inv; z *= inv;
+            }
+            float gx = 0.f, gy = 0.f, gz = 0.f;
+            float4* row = reinterpret_cast<float4*>(tile + lane * STRIDE);
+            if (want_dirs) {
+                if (live) {
+                    float s[25];
 #pragma unroll
-                for (int k = 0; k < NB; ++k) s[k] = 0.f;
+                    for (int k = 0; k < NB; ++k) s[k] = 0.f;
 #pragma unroll
-                for (int q = 0; q < Q; ++q) {
-                    if (4 * q < NB * 3) {
-                        const float4 c = row[q];
-                        const float cv[4] = {c.x, c.y, c.z, c.w};
+                    for (int q = 0; q < Q; ++q) {
+                        if (4 * q < NB * 3) {
+                            const float4 c = row[q];
+                            const float cv[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int e = 4 * q + j;
-                            if (e < NB * 3) s[e / 3] = fmaf(cv[j], vc[e % 3], s[e / 3]);
+                            for (int j = 0; j < 4; ++j) {
+                                const int e = 4 * q + j;
+                                if (e < NB * 3) s[e / 3] = fmaf(cv[j], vc[e % 3], s[e / 3]);
+                            }
                         }
                     }
+                    float ax, ay, az;
+                    sh_basis_vjp<DEG>(x, y, z, s, ax, ay, az);
+                    const float dp = ax * x + ay * y + az * z;
+                    gx = (ax - x * dp) * inv; gy = (ay - y * dp) * inv; gz = (az - z * dp) * inv;
                 }
-                float ax, ay, az;
-                sh_basis_vjp<DEG>(x, y, z, s, ax, ay, az);
-                const float dp = ax * x + ay * y + az * z;
-                gx = (ax - x * dp) * inv; gy = (ay - y * dp) * inv; gz = (az - z * dp) * inv;
+                __syncwarp();
+            }
+            // v_coeffs rows: Y_k * v_colour, zeros beyond the used degree and for masked Gaussians
+            // (the basis is evaluated here, after the direction gradient, so that Y[] and s[] are
+            // never live together)
+            if (lane < n) {
+                float Y[25];
+                sh_basis<DEG>(x, y, z, Y);
+#pragma unroll
+                for (int q = 0; q < Q; ++q) {
+                    float o[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int e = 4 * q + j;
+                        o[j] = (live && e < NB * 3) ? Y[e / 3 < NB ? e / 3 : 0] * vc[e % 3] : 0.f;
+                    }
+                    row[q] = make_float4(o[0], o[1], o[2], o[3]);
+                }
             }
             __syncwarp();
-        }
-        // v_coeffs rows: Y_k * v_colour, zeros beyond the used degree and for masked Gaussians
-        if (lane < n) {
-#pragma unroll
-            for (int q = 0; q < Q; ++q) {
-                float o[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int e = 4 * q + j;
-                    o[j] = (live && e < NB * 3) ? Y[e / 3 < NB ? e / 3 : 0] * vc[e % 3] : 0.f;
-                }
-                row[q] = make_float4(o[0], o[1], o[2], o[3]);
-            }
-        }
-        __syncwarp();
-        if (accumulate) {
-            // red.global.add.v4.f32: fire-and-forget, no read of the running sums
-#pragma unroll
-            for (int u = 0; u < Q; ++u) {
-                const int i = lane + 32 * u;
-                const int gl = i / Q;
-                if ((gl < n) && ((vis >> gl) & 1u))
-                    atomicAdd(dst4 + i, *reinterpret_cast<const float4*>(tile + gl * STRIDE + 4 * (i - gl * Q)));
-            }
-        } else {
-#pragma unroll
-            for (int u = 0; u < Q; ++u) {
-                const int i = lane + 32 * u;
-                const int gl = i / Q;
-                if (gl < n) dst4[i] = *reinterpret_cast<const float4*>(tile + gl * STRIDE + 4 * (i - gl * Q));
-            }
-        }
-        __syncwarp();
-        if (want_dirs && lane < n) {
             if (accumulate) {
-                if (live) { atomicAdd(v_dirs + g * 3 + 0, gx); atomicAdd(v_dirs + g * 3 + 1, gy); atomicAdd(v_dirs + g * 3 + 2, gz); }
+                // red.global.add.v4.f32: fire-and-forget, no read of the running sums
+#pragma unroll
+                for (int u = 0; u < Q; ++u) {
+                    const int i = lane + 32 * u;
+                    const int gl = i / Q;
+                    if ((gl < n) && ((vis >> gl) & 1u))
+                        atomicAdd(dst4 + i, *reinterpret_cast<const float4*>(tile + gl * STRIDE + 4 * (i - gl * Q)));
+                }
             } else {
-                v_dirs[g * 3 + 0] = gx; v_dirs[g * 3 + 1] = gy; v_dirs[g * 3 + 2] = gz;
+#pragma unroll
+                for (int u = 0; u < Q; ++u) {
+                    const int i = lane + 32 * u;
+                    const int gl = i / Q;
+                    if (gl < n) dst4[i] = *reinterpret_cast<const float4*>(tile + gl * STRIDE + 4 * (i - gl * Q));
+                }
+            }
+            if (want_dirs && lane < n) {
+                if (accumulate) {
+                    if (live) { atomicAdd(v_dirs + g * 3 + 0, gx); atomicAdd(v_dirs + g * 3 + 1, gy); atomicAdd(v_dirs + g * 3 + 2, gz); }
+                } else {
+                    v_dirs[g * 3 + 0] = gx; v_dirs[g * 3 + 1] = gy; v_dirs[g * 3 + 2] = gz;
+                }
             }
         }
+        __syncwarp();  // the tile is overwritten by the next chunk's copies
+        cur = nxt;
     }
 }
 

@@ -20,7 +20,7 @@ if [ "$1" = build ]; then
 else
   mkdir -p gpurun_out
   for so in $D/_variants/libscb200_*.so; do
-    echo "== $so"; SCB200_LIB=$PWD/$so python tools/sort_bench.py 2>&1 | grep "n=   626000\|n= 11400000"
+    echo "== $so"; SCB200_LIB=$PWD/$so python tools/sort_bench.py 2>&1 | grep "n=   626000\|REAL\|u64 n=\|u32 n="
     SCB200_LIB=$PWD/$so python tools/timeline.py 2 2>&1 | grep "steps:\|onesweep_pass_kernel<"
   done | tee gpurun_out/sort_variants.log
 fi
