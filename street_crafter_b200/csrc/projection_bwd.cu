@@ -12,32 +12,25 @@ namespace {
 
 constexpr int PB_THREADS = 128;
 
-__global__ void __launch_bounds__(PB_THREADS, 4)
-projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const float* __restrict__ quats,
-                      const float* __restrict__ scales, const float* __restrict__ viewmats,
-                      const float* __restrict__ Ks, int width, int height, float eps2d,
-                      const int32_t* __restrict__ radii, const float* __restrict__ v_means2d,
-                      const float* __restrict__ v_depths, const float* __restrict__ v_conics,
-                      const float* __restrict__ v_comps, float* __restrict__ v_means,
-                      float* __restrict__ v_quats, float* __restrict__ v_scales, int accumulate,
-                      int vd_stride, const float* __restrict__ opacities, float* __restrict__ v_opacities, int use_comp) {
+#ifndef SC_PB_SPAN
+#define SC_PB_SPAN 4  // Gaussians per thread in the visibility scan (a CTA owns PB_THREADS * SPAN of them)
+#endif
+constexpr int PB_SPAN = SC_PB_SPAN;
+constexpr int PB_CHUNK = PB_THREADS * PB_SPAN;
+
+// one Gaussian some camera sees
+__device__ __forceinline__ void
+pb_gaussian(const int64_t g, int64_t N, int C, const float* __restrict__ means, const float* __restrict__ quats,
+            const float* __restrict__ scales, const float* __restrict__ viewmats,
+            const float* __restrict__ Ks, int width, int height, float eps2d,
+            const int32_t* __restrict__ radii, const float* __restrict__ v_means2d,
+            const float* __restrict__ v_depths, const float* __restrict__ v_conics,
+            const float* __restrict__ v_comps, float* __restrict__ v_means,
+            float* __restrict__ v_quats, float* __restrict__ v_scales, int accumulate,
+            int vd_stride, const float* __restrict__ opacities, float* __restrict__ v_opacities, int use_comp) {
     // fused-opacity mode (opacities != nullptr): the rasterizer consumed opacity * compensation
     // (plain opacity without compensations), `v_comps` holds the gradient w.r.t. THAT product:
     //   v_compensation = v_prod * opacity,  v_opacity (+)= sum_cam v_prod * compensation
-    const int64_t g = (int64_t)blockIdx.x * PB_THREADS + threadIdx.x;
-    if (g >= N) return;
-    // Gaussians no camera sees: nothing to compute (zeros, or untouched in accumulate mode)
-    bool seen = false;
-    for (int cam = 0; cam < C; ++cam) seen |= __ldg(radii + (int64_t)cam * N + g) > 0;
-    if (!seen) {
-        if (!accumulate) {
-            if (v_means) { v_means[g * 3 + 0] = 0.f; v_means[g * 3 + 1] = 0.f; v_means[g * 3 + 2] = 0.f; }
-            if (v_scales) { v_scales[g * 3 + 0] = 0.f; v_scales[g * 3 + 1] = 0.f; v_scales[g * 3 + 2] = 0.f; }
-            if (v_quats) reinterpret_cast<float4*>(v_quats)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (v_opacities) v_opacities[g] = 0.f;
-        }
-        return;
-    }
     const float occ = opacities ? __ldg(opacities + g) : 1.0f;
     float v_occ = 0.f;
     // accumulate mode: fetch the running sums now, so their latency hides under the math
@@ -51,7 +44,7 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
     // camera 0's upstream gradients are fetched NOW (one DRAM round trip together with the
     // parameters) instead of after the forward recompute; further cameras load in the loop
     float pf_conic[3] = {0.f, 0.f, 0.f}, pf_m2[2] = {0.f, 0.f}, pf_z = 0.f, pf_comp = 0.f;
-    if (__ldg(radii + g) > 0) {
+    {  // unconditional (valid rows; unused if camera 0 does not see g): no dependent round trip
         pf_conic[0] = __ldg(v_conics + g * 3 + 0); pf_conic[1] = __ldg(v_conics + g * 3 + 1);
         pf_conic[2] = __ldg(v_conics + g * 3 + 2);
         pf_m2[0] = __ldg(v_means2d + g * 2 + 0); pf_m2[1] = __ldg(v_means2d + g * 2 + 1);
@@ -268,6 +261,67 @@ projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const f
     if (v_opacities) v_opacities[g] = (accumulate ? v_opacities[g] : 0.f) + v_occ;
 }
 
+// A CTA owns PB_CHUNK consecutive Gaussians.  Typically a third of them is seen by a camera, so
+// a thread-per-Gaussian mapping would run the ~600-instruction VJP with a third of the lanes:
+// the CTA first scans the radii, compacts the ids of the visible Gaussians (order preserved, so
+// neighbouring threads still touch neighbouring rows) and then runs the VJP with full warps.
+__global__ void __launch_bounds__(PB_THREADS, 4)
+projection_bwd_kernel(int64_t N, int C, const float* __restrict__ means, const float* __restrict__ quats,
+                      const float* __restrict__ scales, const float* __restrict__ viewmats,
+                      const float* __restrict__ Ks, int width, int height, float eps2d,
+                      const int32_t* __restrict__ radii, const float* __restrict__ v_means2d,
+                      const float* __restrict__ v_depths, const float* __restrict__ v_conics,
+                      const float* __restrict__ v_comps, float* __restrict__ v_means,
+                      float* __restrict__ v_quats, float* __restrict__ v_scales, int accumulate,
+                      int vd_stride, const float* __restrict__ opacities, float* __restrict__ v_opacities, int use_comp) {
+    __shared__ uint16_t s_list[PB_CHUNK];
+    __shared__ int s_wsum[PB_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t base = (int64_t)blockIdx.x * PB_CHUNK;
+    // thread t scans Gaussians base + t, base + t + PB_THREADS, ... (coalesced); list position =
+    // round-major, so the list is NOT globally ascending but each round's ids are
+    int32_t r[PB_SPAN];
+#pragma unroll
+    for (int k = 0; k < PB_SPAN; ++k) {
+        const int64_t g = base + k * PB_THREADS + tid;
+        r[k] = 0;
+        if (g < N) {
+            r[k] = __ldg(radii + g);
+            for (int cam = 1; cam < C; ++cam) r[k] = max(r[k], __ldg(radii + (int64_t)cam * N + g));
+        }
+    }
+    int round_base = 0;
+#pragma unroll
+    for (int k = 0; k < PB_SPAN; ++k) {
+        const int64_t g = base + k * PB_THREADS + tid;
+        const bool seen = r[k] > 0;
+        if (!seen && g < N && !accumulate) {
+            // Gaussians no camera sees: zeros (untouched in accumulate mode)
+            if (v_means) { v_means[g * 3 + 0] = 0.f; v_means[g * 3 + 1] = 0.f; v_means[g * 3 + 2] = 0.f; }
+            if (v_scales) { v_scales[g * 3 + 0] = 0.f; v_scales[g * 3 + 1] = 0.f; v_scales[g * 3 + 2] = 0.f; }
+            if (v_quats) reinterpret_cast<float4*>(v_quats)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (v_opacities) v_opacities[g] = 0.f;
+        }
+        const unsigned b = __ballot_sync(0xffffffffu, seen);
+        if (lane == 0) s_wsum[wid] = __popc(b);
+        __syncthreads();
+        int off = round_base;
+#pragma unroll
+        for (int w = 0; w < PB_THREADS / 32; ++w) {
+            const int c = s_wsum[w];
+            if (w < wid) off += c;
+            round_base += c;
+        }
+        if (seen) s_list[off + __popc(b & ((1u << lane) - 1u))] = (uint16_t)(k * PB_THREADS + tid);
+        __syncthreads();
+    }
+    const int total = round_base;
+    for (int i = tid; i < total; i += PB_THREADS)
+        pb_gaussian(base + s_list[i], N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, radii,
+                    v_means2d, v_depths, v_conics, v_comps, v_means, v_quats, v_scales, accumulate, vd_stride,
+                    opacities, v_opacities, use_comp);
+}
+
 }  // namespace
 
 static int projection_bwd_launch(int64_t N, int C, const float* means, const float* quats, const float* scales,
@@ -282,7 +336,7 @@ static int projection_bwd_launch(int64_t N, int C, const float* means, const flo
                  "null pointer");
     SC_CHECK_ARG(((uintptr_t)quats & 15) == 0 && (!v_quats || ((uintptr_t)v_quats & 15) == 0),
                  "16-byte alignment of quats");
-    projection_bwd_kernel<<<(unsigned)sc_div_up(N, PB_THREADS), PB_THREADS, 0, (cudaStream_t)stream>>>(
+    projection_bwd_kernel<<<(unsigned)sc_div_up(N, PB_CHUNK), PB_THREADS, 0, (cudaStream_t)stream>>>(
         N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, radii, v_means2d, v_depths,
         v_conics, v_compensations, v_means, v_quats, v_scales, accumulate, vd_stride, opacities, v_opacities,
         use_comp);
