@@ -297,7 +297,7 @@ def run_ours(args):
     proxy = _LibProxy(_lib.lib)
     stage_fns = ["sc_projection_fwd_opacity", "sc_projection_bwd_opacity", "sc_sh_fwd_view", "sc_sh_bwd_view",
                  "sc_isect_prepare",
-                 "sc_isect_emit_sorted", "sc_isect_offset_encode", "sc_rasterize_fwd", "sc_rasterize_bwd"]
+                 "sc_isect_emit_sorted", "sc_isect_offset_encode", "sc_rasterize_fwd_depth", "sc_rasterize_bwd"]
     timer.wrap(proxy, stage_fns)
     rendering.lib = proxy
 
@@ -461,7 +461,7 @@ def run_ours(args):
             ms, cnt = stages.get(name, (0.0, 0))
             return (ms / cnt) if cnt else None
         t_bwd = per_launch("sc_rasterize_bwd")
-        t_fwd = per_launch("sc_rasterize_fwd")
+        t_fwd = per_launch("sc_rasterize_fwd_depth")
         # one launch = one camera; flop_* are sums over the 3 cameras
         ach_bwd = flop_bwd / n_views / (t_bwd * 1e-3) / 1e12 if t_bwd else None
         ach_fwd = flop_fwd / n_views / (t_fwd * 1e-3) / 1e12 if t_fwd else None
@@ -493,7 +493,7 @@ def run_ours(args):
                 gbs = alg_bytes[nme] / (ms / cnt * 1e-3) / 1e9
                 row.update({"alg_GB_per_call": alg_bytes[nme] / 1e9, "achieved_GBs": gbs, "frac_hbm": gbs / hbm_peak})
             stage_table[nme] = row
-        stage_table["sc_rasterize_fwd"].update({"achieved_TFLOPs": ach_fwd,
+        stage_table["sc_rasterize_fwd_depth"].update({"achieved_TFLOPs": ach_fwd,
                                                 "frac_fp32": (ach_fwd / fp32_peak) if ach_fwd else None})
         stage_table["sc_rasterize_bwd"].update({"achieved_TFLOPs": ach_bwd,
                                                 "frac_fp32": (ach_bwd / fp32_peak) if ach_bwd else None})

@@ -80,7 +80,9 @@ int sc_sh_bwd(int64_t M, int K, int degree, const float* dirs, const float* coef
 /* "View mode" of the same kernels, used by the fused renderer path (rows A2, A5, A6 of
  * SURVEY.md section 8 folded into their producers; K = 4 or 16):
  *   sc_projection_fwd_opacity: additionally opacities_out[C,N] = opacities[N] * compensation
- *     (plain opacity when compensations == NULL);
+ *     (plain opacity when compensations == NULL) and, both nullable, the renderer's result-packing
+ *     outputs (row A11, street_gaussian_renderer.py:293-294): visibility[C,N] u8 = radii > 0 and
+ *     radii_norm[C,N] = float(radii) * (1 / max(height, width));
  *   sc_sh_fwd_view: dirs = means - campos (campos: DEVICE float[3]), mask = radii > 0,
  *     colors4[M,4] = (clamp_min(colour + 0.5, 0), depths[M]);
  *   sc_sh_bwd_view: upstream v_colors4[M,4], clamp mask from the saved colors4_fwd; v_means
@@ -91,7 +93,8 @@ int sc_projection_fwd_opacity(int64_t N, int C, const float* means, const float*
                               const float* opacities, const float* viewmats, const float* Ks, int width,
                               int height, float eps2d, float near_plane, float far_plane, float radius_clip,
                               int32_t* radii, float* means2d, float* depths, float* conics,
-                              float* compensations, float* opacities_out, void* stream);
+                              float* compensations, float* opacities_out, uint8_t* visibility,
+                              float* radii_norm, void* stream);
 int sc_projection_bwd_opacity(int64_t N, int C, const float* means, const float* quats, const float* scales,
                               const float* opacities, const float* viewmats, const float* Ks, int width,
                               int height, float eps2d, const int32_t* radii, const float* v_means2d,
@@ -178,6 +181,15 @@ int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int width, int 
                      const int32_t* flatten_ids, int max_hit, float* render_colors,
                      float* render_alphas, int32_t* last_ids, float* final_T, uint64_t* stats,
                      void* stream);
+/* sc_rasterize_fwd for the RGB + depth layout (CH = 4, no background, no max_hit) that also writes the
+ * renderer's depth map depth_norm[C,H,W] = render_colors[..., 3] / max(render_alphas, 1e-10)
+ * (row A11, street_gaussian_renderer.py:283; IEEE division). */
+int sc_rasterize_fwd_depth(int C, int64_t N, int64_t n_isects, int width, int height, int tile_size,
+                           const float* means2d, const float* conics, const float* colors4,
+                           const float* opacities, const int32_t* isect_offsets, const int32_t* flatten_ids,
+                           float* render_colors, float* render_alphas, float* depth_norm, int32_t* last_ids,
+                           float* final_T, uint64_t* stats, void* stream);
+
 /* gradient buffers must be ZEROED by the caller; v_means2d_abs nullable. */
 int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
                      int tile_size, const float* means2d, const float* conics, const float* colors,

@@ -70,7 +70,8 @@ projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* _
                       float far_plane, float radius_clip, int32_t* __restrict__ radii,
                       float* __restrict__ means2d, float* __restrict__ depths,
                       float* __restrict__ conics, float* __restrict__ comps,
-                      const float* __restrict__ opacities, float* __restrict__ op_out) {
+                      const float* __restrict__ opacities, float* __restrict__ op_out,
+                      uint8_t* __restrict__ vis_out, float* __restrict__ radii_norm, float inv_max_dim) {
     // stage the two 12-byte-stride arrays through shared memory so that global loads are
     // full-line float4 accesses (AoS [N,3] would otherwise be 3 strided scalar loads)
     __shared__ float s_means[PROJ_THREADS * 3];
@@ -175,6 +176,10 @@ projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* _
         if (comps) comps[o] = o_comp;
         // A2 fused: opacity * compensation (plain opacity in classic mode)
         if (op_out) op_out[o] = comps ? __ldg(opacities + g) * o_comp : __ldg(opacities + g);
+        // A11 fused: the renderer's `visibility_filter` (radii > 0) and `radii` (radii / max(H, W),
+        // which torch evaluates as float(radii) * (1 / max)) (street_gaussian_renderer.py:293-294)
+        if (vis_out) vis_out[o] = radius_i > 0 ? 1 : 0;
+        if (radii_norm) radii_norm[o] = (float)radius_i * inv_max_dim;
     }
     s_conics[tid * 3 + 0] = o_a;
     s_conics[tid * 3 + 1] = o_b;
@@ -647,7 +652,8 @@ static int projection_fwd_launch(int64_t N, int C, const float* means, const flo
                                  const float* viewmats, const float* Ks, int width, int height, float eps2d,
                                  float near_plane, float far_plane, float radius_clip, int32_t* radii,
                                  float* means2d, float* depths, float* conics, float* compensations,
-                                 const float* opacities, float* op_out, void* stream) {
+                                 const float* opacities, float* op_out, uint8_t* vis_out, float* radii_norm,
+                                 void* stream) {
     SC_CHECK_ARG(N >= 0 && C >= 1, "N, C");
     SC_CHECK_ARG(width > 0 && height > 0, "image size");
     if (N == 0) return SC_OK;
@@ -661,7 +667,8 @@ static int projection_fwd_launch(int64_t N, int C, const float* means, const flo
     dim3 grid((unsigned)sc_div_up(N, PROJ_THREADS), (unsigned)C);
     projection_fwd_kernel<<<grid, PROJ_THREADS, 0, (cudaStream_t)stream>>>(
         N, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip,
-        radii, means2d, depths, conics, compensations, opacities, op_out);
+        radii, means2d, depths, conics, compensations, opacities, op_out, vis_out, radii_norm,
+        1.0f / (float)(width > height ? width : height));
     SC_CHECK_LAUNCH("projection_fwd_kernel");
     return SC_OK;
 }
@@ -673,7 +680,7 @@ extern "C" int sc_projection_fwd(int64_t N, int C, const float* means, const flo
                                  float* conics, float* compensations, void* stream) {
     return projection_fwd_launch(N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
                                  far_plane, radius_clip, radii, means2d, depths, conics, compensations, nullptr,
-                                 nullptr, stream);
+                                 nullptr, nullptr, nullptr, stream);
 }
 
 extern "C" int sc_projection_fwd_opacity(int64_t N, int C, const float* means, const float* quats,
@@ -681,11 +688,12 @@ extern "C" int sc_projection_fwd_opacity(int64_t N, int C, const float* means, c
                                          const float* Ks, int width, int height, float eps2d, float near_plane,
                                          float far_plane, float radius_clip, int32_t* radii, float* means2d,
                                          float* depths, float* conics, float* compensations,
-                                         float* opacities_out, void* stream) {
+                                         float* opacities_out, uint8_t* visibility, float* radii_norm,
+                                         void* stream) {
     SC_CHECK_ARG(opacities && opacities_out, "null pointer");
     return projection_fwd_launch(N, C, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane,
                                  far_plane, radius_clip, radii, means2d, depths, conics, compensations,
-                                 opacities, opacities_out, stream);
+                                 opacities, opacities_out, visibility, radii_norm, stream);
 }
 
 extern "C" int sc_isect_count(int64_t CN, const float* means2d, const int32_t* radii, const float* depths,

@@ -210,7 +210,8 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                      const float* __restrict__ backgrounds, const int32_t* __restrict__ isect_offsets,
                      const int32_t* __restrict__ flatten_ids, int max_hit, float* __restrict__ render_colors,
                      float* __restrict__ render_alphas, int32_t* __restrict__ last_ids,
-                     float* __restrict__ final_T, unsigned long long* __restrict__ stats) {
+                     float* __restrict__ final_T, unsigned long long* __restrict__ stats,
+                     float* __restrict__ depth_norm) {
     __shared__ __align__(16) WarpSmem<CH, false> smem[WARPS_PER_CTA];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t n_slots = (int64_t)n_cams * tile_w * tile_h;
@@ -340,6 +341,9 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                     o.z += T[r] * __ldg(backgrounds + cam * 4 + 2); o.w += T[r] * __ldg(backgrounds + cam * 4 + 3);
                 }
                 reinterpret_cast<float4*>(render_colors)[pix_id] = o;
+                // A11 fused: the renderer's depth map, render_colors[..., 3] / clamp(alpha, 1e-10)
+                // (street_gaussian_renderer.py:283), IEEE division like the torch op it replaces
+                if (depth_norm) depth_norm[pix_id] = __fdiv_rn(o.w, fmaxf(1.0f - T[r], 1e-10f));
             } else {
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
@@ -592,14 +596,14 @@ int launch_fwd(int C, int64_t n_isects, int width, int height, const float* mean
                const float* colors, const float* opacities, const float* backgrounds,
                const int32_t* isect_offsets, const int32_t* flatten_ids, int max_hit, float* render_colors,
                float* render_alphas, int32_t* last_ids, float* final_T, unsigned long long* stats,
-               cudaStream_t st) {
+               float* depth_norm, cudaStream_t st) {
     const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
     const unsigned grid = (unsigned)sc_div_up((int64_t)C * tile_w * tile_h, WARPS_PER_CTA);
 #define FWD_LAUNCH(ST, MH)                                                                              \
     rasterize_fwd_kernel<CH, ST, MH><<<grid, WARPS_PER_CTA * 32, 0, st>>>(                              \
         n_isects, C, width, height, tile_w, tile_h, reinterpret_cast<const float2*>(means2d), conics,    \
         colors, opacities, backgrounds, isect_offsets, flatten_ids, max_hit, render_colors,             \
-        render_alphas, last_ids, final_T, stats)
+        render_alphas, last_ids, final_T, stats, depth_norm)
     if (stats) {
         if (max_hit > 0) FWD_LAUNCH(true, true); else FWD_LAUNCH(true, false);
     } else {
@@ -629,12 +633,12 @@ int launch_bwd(int C, int64_t n_isects, int width, int height, const float* mean
 
 }  // namespace
 
-extern "C" int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
+static int rasterize_fwd_entry(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
                                 int tile_size, const float* means2d, const float* conics, const float* colors,
                                 const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
                                 const int32_t* flatten_ids, int max_hit, float* render_colors,
                                 float* render_alphas, int32_t* last_ids, float* final_T, uint64_t* stats,
-                                void* stream) {
+                                float* depth_norm, void* stream) {
     SC_CHECK_ARG(C >= 1 && N >= 0 && n_isects >= 0 && width > 0 && height > 0, "sizes");
     SC_CHECK_ARG(n_isects < (1ll << 31), "n_isects must fit int32");
     if (tile_size != TILE) {
@@ -644,10 +648,11 @@ extern "C" int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int 
     SC_CHECK_ARG(isect_offsets && render_colors && render_alphas, "null pointer");
     SC_CHECK_ARG(n_isects == 0 || (means2d && conics && colors && opacities && flatten_ids), "null pointer");
     SC_CHECK_ARG(CH != 4 || ((uintptr_t)render_colors & 15) == 0, "16-byte alignment of render_colors");
+    SC_CHECK_ARG(depth_norm == nullptr || CH == 4, "depth_norm needs the RGB+depth layout (CH = 4)");
     cudaStream_t st = (cudaStream_t)stream;
 #define ARGS C, n_isects, width, height, means2d, conics, colors, opacities, backgrounds, isect_offsets, \
              flatten_ids, max_hit, render_colors, render_alphas, last_ids, final_T,                       \
-             reinterpret_cast<unsigned long long*>(stats), st
+             reinterpret_cast<unsigned long long*>(stats), depth_norm, st
     switch (CH) {
         case 1: return launch_fwd<1>(ARGS);
         case 2: return launch_fwd<2>(ARGS);
@@ -659,6 +664,29 @@ extern "C" int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int 
 #undef ARGS
     sc_set_error("unsupported channel count %d (supported 1..5)", CH);
     return SC_ERR_UNSUPPORTED;
+}
+
+extern "C" int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
+                                int tile_size, const float* means2d, const float* conics, const float* colors,
+                                const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
+                                const int32_t* flatten_ids, int max_hit, float* render_colors,
+                                float* render_alphas, int32_t* last_ids, float* final_T, uint64_t* stats,
+                                void* stream) {
+    return rasterize_fwd_entry(C, N, n_isects, CH, width, height, tile_size, means2d, conics, colors, opacities,
+                               backgrounds, isect_offsets, flatten_ids, max_hit, render_colors, render_alphas,
+                               last_ids, final_T, stats, nullptr, stream);
+}
+
+extern "C" int sc_rasterize_fwd_depth(int C, int64_t N, int64_t n_isects, int width, int height, int tile_size,
+                                      const float* means2d, const float* conics, const float* colors4,
+                                      const float* opacities, const int32_t* isect_offsets,
+                                      const int32_t* flatten_ids, float* render_colors, float* render_alphas,
+                                      float* depth_norm, int32_t* last_ids, float* final_T, uint64_t* stats,
+                                      void* stream) {
+    SC_CHECK_ARG(depth_norm, "null pointer");
+    return rasterize_fwd_entry(C, N, n_isects, 4, width, height, tile_size, means2d, conics, colors4, opacities,
+                               nullptr, isect_offsets, flatten_ids, 0, render_colors, render_alphas, last_ids,
+                               final_T, stats, depth_norm, stream);
 }
 
 extern "C" int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,

@@ -37,7 +37,7 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
             grad_sinks=grad_sinks)
         radii, means2d = meta["radii"], meta["means2d"]
         rendered_color = render_colors[..., :-1]
-        rendered_depth = render_colors[..., -1:] / render_alphas.clamp(min=1e-10)
+        rendered_depth = meta["depth_norm"]  # render_colors[..., -1:] / render_alphas.clamp(min=1e-10), in-kernel
         if not train:
             rendered_color = torch.clamp(rendered_color, 0.0, 1.0)
         return {
@@ -45,8 +45,8 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
             "acc": render_alphas[..., 0],
             "depth": rendered_depth[..., 0],
             "viewspace_points": means2d,
-            "visibility_filter": radii[0] > 0,
-            "radii": radii[0] / float(max(height, width)),
+            "visibility_filter": meta["visibility"][0],     # radii[0] > 0, written by the projection kernel
+            "radii": meta["radii_norm"][0],                  # radii[0] / float(max(height, width)), likewise
             "render_colors": render_colors,
             "render_alphas": render_alphas,
             "aux": dict(radii=radii, means2d=means2d, depths=meta["depths"], conics=meta["conics"],

@@ -495,12 +495,16 @@ class _FusedView(torch.autograd.Function):
         comps = torch.empty((1, N), dtype=torch.float32, device=dev) if antialiased else None
         op_c = torch.empty((1, N), dtype=torch.float32, device=dev)
         colors4 = torch.empty((1, N, 4), dtype=torch.float32, device=dev)
+        # the renderer's result packing (row A11), written by the producing kernels
+        vis = torch.empty((1, N), dtype=torch.bool, device=dev)
+        radii_norm = torch.empty((1, N), dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             check(lib.sc_projection_fwd_opacity(N, 1, _p(means), _p(quats), _p(scales), _p(opacities),
                                                 _p(viewmats), _p(Ks), int(width), int(height), float(eps2d),
                                                 float(near_plane), float(far_plane), float(radius_clip),
                                                 _p(radii), _p(means2d), _p(depths), _p(conics), _p(comps),
-                                                _p(op_c), st), "sc_projection_fwd_opacity")
+                                                _p(op_c), _p(vis), _p(radii_norm), st),
+                  "sc_projection_fwd_opacity")
         tile_width = math.ceil(width / float(tile_size))
         tile_height = math.ceil(height / float(tile_size))
         with torch.cuda.device(dev):
@@ -516,33 +520,44 @@ class _FusedView(torch.autograd.Function):
             render_alphas = torch.empty((1, height, width, 1), dtype=torch.float32, device=dev)
             last_ids = torch.empty((1, height, width), dtype=torch.int32, device=dev)
             final_T = torch.empty((1, height, width), dtype=torch.float32, device=dev)
-            check(lib.sc_rasterize_fwd(1, N, flatten_ids.numel(), 4, width, height, tile_size, _p(means2d),
-                                       _p(conics), _p(colors4), _p(op_c), None, _p(isect_offsets),
-                                       _p(flatten_ids), 0, _p(render_colors), _p(render_alphas), _p(last_ids),
-                                       _p(final_T), _p(_STATS["buf"]), st), "sc_rasterize_fwd")
+            depth_norm = torch.empty((1, height, width, 1), dtype=torch.float32, device=dev)
+            check(lib.sc_rasterize_fwd_depth(1, N, flatten_ids.numel(), width, height, tile_size, _p(means2d),
+                                             _p(conics), _p(colors4), _p(op_c), _p(isect_offsets),
+                                             _p(flatten_ids), _p(render_colors), _p(render_alphas),
+                                             _p(depth_norm), _p(last_ids), _p(final_T), _p(_STATS["buf"]), st),
+                  "sc_rasterize_fwd_depth")
         ctx.save_for_backward(means, quats, scales, opacities, shs, viewmats, Ks, campos, radii, means2d, conics,
-                              colors4, op_c, isect_offsets, flatten_ids, last_ids, final_T)
+                              colors4, op_c, isect_offsets, flatten_ids, last_ids, final_T, render_alphas,
+                              depth_norm)
         ctx.cfg = (int(width), int(height), int(tile_size), float(eps2d), bool(antialiased), bool(absgrad),
                    int(sh_degree))
         ctx.sinks = sinks
         ctx.means2d_ref = None  # weakref to the returned means2d: receives .grad / .absgrad in backward
         ctx.set_materialize_grads(False)  # no zero-filled "gradients" for the auxiliary outputs
-        aux = (radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets)
+        aux = (radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets, vis,
+               radii_norm)
         ctx.mark_non_differentiable(*aux)
         if comps is not None:
             ctx.mark_non_differentiable(comps)
-        return (render_colors, render_alphas) + aux + ((comps,) if comps is not None else ())
+        return (render_colors, render_alphas, depth_norm) + aux + ((comps,) if comps is not None else ())
 
     @staticmethod
-    def backward(ctx, v_render_colors, v_render_alphas, *_unused):
+    def backward(ctx, v_render_colors, v_render_alphas, v_depth_norm, *_unused):
         (means, quats, scales, opacities, shs, viewmats, Ks, campos, radii, means2d, conics, colors4, op_c,
-         isect_offsets, flatten_ids, last_ids, final_T) = ctx.saved_tensors
+         isect_offsets, flatten_ids, last_ids, final_T, render_alphas, depth_norm) = ctx.saved_tensors
         width, height, tile_size, eps2d, antialiased, absgrad, sh_degree = ctx.cfg
         N, Kc = shs.shape[0], shs.shape[1]
         dev = means.device
         st = _stream()
         v_render_colors = _grad_or_zeros(v_render_colors, (1, height, width, 4), dev)
         v_render_alphas = _grad_or_zeros(v_render_alphas, (1, height, width, 1), dev)
+        if v_depth_norm is not None:
+            # depth_norm = rc[..., 3] / clamp_min(alpha, 1e-10) (only when a depth loss is attached):
+            # d/d rc_d = 1 / ac,  d/d alpha = -depth_norm / ac where alpha >= 1e-10
+            ac = render_alphas.clamp(min=1e-10)
+            v_render_colors = v_render_colors.clone()
+            v_render_colors[..., 3:] += v_depth_norm / ac
+            v_render_alphas = v_render_alphas - v_depth_norm * depth_norm / ac * (render_alphas >= 1e-10)
         sizes = [4 * N, 2 * N, 2 * N if absgrad else 0, 3 * N, N]  # colours first: 16-byte aligned rows
         arena = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)  # one memset for all five
         v_colors4, v_means2d, v_abs, v_conics, v_opc = torch.split(arena, sizes)
@@ -595,8 +610,9 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
         assert all(k in grad_sinks for k in ("means", "quats", "scales", "opacities", "shs"))
     out = _FusedView.apply(means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
                            eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, grad_sinks)
-    rc, ra, radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets = out[:12]
-    comps = out[12] if len(out) > 12 else None
+    (rc, ra, depth_norm, radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets,
+     vis, radii_norm) = out[:15]
+    comps = out[15] if len(out) > 15 else None
     if rc.grad_fn is not None:
         rc.grad_fn.means2d_ref = weakref.ref(means2d)
     meta = {"camera_ids": None, "gaussian_ids": None, "radii": radii, "means2d": means2d, "depths": depths,
@@ -604,7 +620,10 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
             "tile_width": math.ceil(width / float(tile_size)), "tile_height": math.ceil(height / float(tile_size)),
             "tiles_per_gauss": tpg, "isect_ids": isect_ids, "flatten_ids": flatten_ids,
             "isect_offsets": isect_offsets, "width": width, "height": height, "tile_size": tile_size,
-            "n_cameras": 1}
+            "n_cameras": 1,
+            # result packing of the reference renderer (street_gaussian_renderer.py:283, :293-294),
+            # produced by the kernels: depth / clamp(alpha), radii > 0, radii / max(H, W)
+            "depth_norm": depth_norm, "visibility": vis, "radii_norm": radii_norm}
     return rc, ra, meta
 
 

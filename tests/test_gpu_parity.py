@@ -430,9 +430,39 @@ def test_fused_view_equals_five_op_sequence(S, dev, deg, antialiasing):
                                                                                  o1["render_alphas"])
     for k in ("means", "quats", "scales", "opacities", "shs"):
         assert_grad_close(c1[k].grad, c0[k].grad.cpu(), f"fused v_{k}")
+    # the renderer's result packing (depth / clamp(alpha), radii > 0, radii / max(H, W)) is written by
+    # the kernels on the single-node path and by torch ops on the op-by-op path: identical bits
+    for k in ("rgb", "acc", "depth", "visibility_filter", "radii"):
+        assert o0[k].shape == o1[k].shape and o0[k].dtype == o1[k].dtype, k
+        assert torch.equal(o0[k], o1[k]), k
     vp0, vp1 = o0["viewspace_points"], o1["viewspace_points"]
     assert_grad_close(vp1.grad, vp0.grad.cpu(), "viewspace grad")
     assert_grad_close(vp1.absgrad, vp0.absgrad.cpu(), "viewspace absgrad")
+
+
+def test_fused_view_depth_loss_gradient(S, dev):
+    """a loss on the renderer's normalised depth map flows through the in-kernel division exactly
+    as through the torch ops of the op-by-op path"""
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    n, W, H, deg = 20000, 320, 200, 3
+    s = make_gaussians(n, sh_degree=deg, seed=13)
+    V, K = make_camera(W, H, yaw_deg=-5.0)
+    g = torch.Generator().manual_seed(3)
+    w_depth = torch.rand(1, H, W, generator=g).to(dev)
+    w_rgb = torch.randn(3, H, W, generator=g).to(dev)
+    res = []
+    for fused in (False, True):
+        c = {k: v.to(dev).requires_grad_(True) for k, v in s.items()}
+        cc = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
+        out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None],
+                                   V[None].to(dev), K[None].to(dev), cc, W, H, deg, fused=fused)
+        loss = (out["depth"] * w_depth).sum() * 1e-3 + (out["rgb"] * w_rgb).sum() + out["acc"].sum() * 0.1
+        loss.backward()
+        res.append((c, out, loss.item()))
+    (c0, o0, l0), (c1, o1, l1) = res
+    assert abs(l0 - l1) <= 1e-5 * abs(l0)
+    for k in ("means", "quats", "scales", "opacities", "shs"):
+        assert_grad_close(c1[k].grad, c0[k].grad.cpu(), f"depth-loss v_{k}")
 
 
 @pytest.mark.parametrize("fused", [True, False])
