@@ -190,7 +190,8 @@ int sc_rasterize_fwd_depth(int C, int64_t N, int64_t n_isects, int width, int he
                            float* render_colors, float* render_alphas, float* depth_norm, int32_t* last_ids,
                            float* final_T, uint64_t* stats, void* stream);
 
-/* gradient buffers must be ZEROED by the caller; v_means2d_abs nullable. */
+/* gradient buffers must be ZEROED by the caller; v_means2d_abs nullable; v_render_alphas nullable
+ * (= no gradient flows into the alpha map). */
 int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
                      int tile_size, const float* means2d, const float* conics, const float* colors,
                      const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
@@ -207,8 +208,9 @@ int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int 
  * gt[3,H,W] contiguous; mask[H,W] u8 nullable (reference: l1 over masked pixels, SSIM on inputs
  * zeroed outside the mask).  out3 = {loss, L1, SSIM} (device floats).  The backward reads the
  * upstream scalar from DEVICE memory (nullable = 1) and WRITES d loss / d image for the three
- * channels with the given output strides.  workspace >= sc_photometric_workspace_bytes, kept
- * between the two calls. */
+ * channels with the given output strides, plus zeros for `zero_extra_channels` further channels
+ * (3, 4, ... at the same strides: the depth channel of the compositor's interleaved output).
+ * workspace >= sc_photometric_workspace_bytes, kept between the two calls. */
 int64_t sc_photometric_workspace_bytes(int H, int W);
 int sc_photometric_fwd(int H, int W, const float* image, int64_t channel_stride, int64_t pixel_stride,
                        const float* gt, const uint8_t* mask, float lambda_dssim, float lambda_l1,
@@ -216,7 +218,8 @@ int sc_photometric_fwd(int H, int W, const float* image, int64_t channel_stride,
 int sc_photometric_bwd(int H, int W, const float* image, int64_t channel_stride, int64_t pixel_stride,
                        const float* gt, const uint8_t* mask, float lambda_dssim, float lambda_l1,
                        const void* workspace, const float* upstream, float* v_image,
-                       int64_t v_channel_stride, int64_t v_pixel_stride, void* stream);
+                       int64_t v_channel_stride, int64_t v_pixel_stride, int zero_extra_channels,
+                       void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

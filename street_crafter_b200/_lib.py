@@ -54,7 +54,7 @@ SIGNATURES = {
     "sc_photometric_workspace_bytes": (_i64, [_i32, _i32]),
     "sc_photometric_fwd": (_i32, [_i32, _i32, _ptr, _i64, _i64, _ptr, _ptr, _f32, _f32, _ptr, _i64, _ptr, _ptr]),
     "sc_photometric_bwd": (_i32, [_i32, _i32, _ptr, _i64, _i64, _ptr, _ptr, _f32, _f32, _ptr, _ptr, _ptr, _i64,
-                                  _i64, _ptr]),
+                                  _i64, _i32, _ptr]),
     "sc_knn_workspace_bytes": (_i64, [_i64]),
     "sc_knn3_mean_dist2": (_i32, [_i64, _ptr, _ptr, _ptr, _i64, _ptr]),
     "sc_probe_fp32": (_i32, [_i32, _i32, _i32, _i32, _ptr, _ptr]),

@@ -185,7 +185,7 @@ __global__ void __launch_bounds__(256)
 photometric_bwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt, const uint8_t* __restrict__ mask,
                        const float* __restrict__ dmaps, const double* __restrict__ sums,
                        const float* __restrict__ upstream, float lambda_dssim, float lambda_l1,
-                       float* __restrict__ v_img, int64_t v_cs, int64_t v_ps) {
+                       float* __restrict__ v_img, int64_t v_cs, int64_t v_ps, int zero_extra) {
     __shared__ float s_d[9][LH][LH + 1];   // [map * 3 + channel], with halo
     __shared__ float s_h[9][LH][LT + 1];
     const int tid = threadIdx.x;
@@ -249,6 +249,10 @@ photometric_bwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt, 
                          w_l1 * (d > 0.f ? 1.f : d < 0.f ? -1.f : 0.f);
                 }
                 v_img[c * v_cs + p * v_ps] = gr;
+                // channels beyond RGB of an interleaved gradient (the compositor's depth channel) get
+                // their zeros here instead of a separate fill of the whole buffer
+                if (c == 0)
+                    for (int e = 0; e < zero_extra; ++e) v_img[(3 + e) * v_cs + p * v_ps] = 0.f;
             }
         }
     }
@@ -288,17 +292,18 @@ extern "C" int sc_photometric_bwd(int H, int W, const float* image, int64_t chan
                                   int64_t pixel_stride, const float* gt, const uint8_t* mask,
                                   float lambda_dssim, float lambda_l1, const void* workspace,
                                   const float* upstream, float* v_image, int64_t v_channel_stride,
-                                  int64_t v_pixel_stride, void* stream) {
+                                  int64_t v_pixel_stride, int zero_extra_channels, void* stream) {
     SC_CHECK_ARG(H > 0 && W > 0 && channel_stride > 0 && pixel_stride > 0 && v_channel_stride > 0 &&
                      v_pixel_stride > 0, "sizes / strides");
     SC_CHECK_ARG(image && gt && workspace && v_image, "null pointer");
+    SC_CHECK_ARG(zero_extra_channels >= 0 && zero_extra_channels <= 8, "zero_extra_channels");
     const unsigned char* ws = (const unsigned char*)workspace;
     const int64_t maps_bytes = sc_align_up((int64_t)9 * H * W * 4, 256);
     dim3 grid((unsigned)sc_div_up(W, LT), (unsigned)sc_div_up(H, LT));
     photometric_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
         H, W, ImgView{image, channel_stride, pixel_stride}, gt, mask, (const float*)ws,
         (const double*)(ws + maps_bytes), upstream, lambda_dssim, lambda_l1, v_image, v_channel_stride,
-        v_pixel_stride);
+        v_pixel_stride, zero_extra_channels);
     SC_CHECK_LAUNCH("photometric_bwd_kernel");
     return SC_OK;
 }

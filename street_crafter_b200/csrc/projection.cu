@@ -12,7 +12,10 @@
 
 namespace {
 
-constexpr int PROJ_THREADS = 256;
+#ifndef SC_PROJ_THREADS
+#define SC_PROJ_THREADS 128
+#endif
+constexpr int PROJ_THREADS = SC_PROJ_THREADS;
 
 struct Cam {
     float W[3][3];
@@ -63,51 +66,52 @@ __device__ __forceinline__ void quat_scale_to_covar(const float4 q, const float 
     S[5] = (M[2][0] * M[2][0] + M[2][1] * M[2][1]) + M[2][2] * M[2][2];
 }
 
-__global__ void __launch_bounds__(PROJ_THREADS)
-projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* __restrict__ quats,
-                      const float* __restrict__ scales, const float* __restrict__ viewmats,
-                      const float* __restrict__ Ks, int width, int height, float eps2d, float near_plane,
-                      float far_plane, float radius_clip, int32_t* __restrict__ radii,
-                      float* __restrict__ means2d, float* __restrict__ depths,
-                      float* __restrict__ conics, float* __restrict__ comps,
-                      const float* __restrict__ opacities, float* __restrict__ op_out,
-                      uint8_t* __restrict__ vis_out, float* __restrict__ radii_norm, float inv_max_dim) {
-    // stage the two 12-byte-stride arrays through shared memory so that global loads are
-    // full-line float4 accesses (AoS [N,3] would otherwise be 3 strided scalar loads)
-    __shared__ float s_means[PROJ_THREADS * 3];
-    __shared__ float s_scales[PROJ_THREADS * 3];
-    __shared__ float s_conics[PROJ_THREADS * 3];
-    const int cam = blockIdx.y;
-    const int64_t base = (int64_t)blockIdx.x * PROJ_THREADS;
-    const int tid = threadIdx.x;
-    const int64_t n_here = min((int64_t)PROJ_THREADS, N - base);
-    {
-        const int64_t f0 = base * 3;           // float offset, multiple of 768 -> 16B aligned
-        const int nf = (int)n_here * 3;
-        const int nf4 = nf >> 2;
-        const float4* m4 = reinterpret_cast<const float4*>(means + f0);
-        const float4* s4 = reinterpret_cast<const float4*>(scales + f0);
-        if (tid < nf4) {
-            reinterpret_cast<float4*>(s_means)[tid] = __ldg(m4 + tid);
-            reinterpret_cast<float4*>(s_scales)[tid] = __ldg(s4 + tid);
-        }
-        const int rem = nf - (nf4 << 2);
-        if (tid < rem) {
-            s_means[(nf4 << 2) + tid] = __ldg(means + f0 + (nf4 << 2) + tid);
-            s_scales[(nf4 << 2) + tid] = __ldg(scales + f0 + (nf4 << 2) + tid);
-        }
-    }
-    __syncthreads();
-    const int64_t g = base + tid;
-    const bool active = g < N;
+#ifndef SC_PF_SPAN
+#define SC_PF_SPAN 2  // Gaussians per thread in the pre-cull scan (a CTA owns PROJ_THREADS * SPAN of them)
+#endif
+constexpr int PF_SPAN = SC_PF_SPAN;
+constexpr int PF_CHUNK = PROJ_THREADS * PF_SPAN;
+
+struct ProjOut {
+    int32_t* __restrict__ radii;
+    float* __restrict__ means2d;
+    float* __restrict__ depths;
+    float* __restrict__ conics;
+    float* __restrict__ comps;
+    const float* __restrict__ opacities;
+    float* __restrict__ op_out;
+    uint8_t* __restrict__ vis_out;
+    float* __restrict__ radii_norm;
+    float inv_max_dim;
+};
+
+__device__ __forceinline__ void proj_store(const ProjOut& O, int64_t o, int64_t g, int32_t radius_i, float mx,
+                                           float my, float z, float a, float b, float c, float comp) {
+    O.radii[o] = radius_i;
+    reinterpret_cast<float2*>(O.means2d)[o] = make_float2(mx, my);
+    O.depths[o] = z;
+    O.conics[o * 3 + 0] = a; O.conics[o * 3 + 1] = b; O.conics[o * 3 + 2] = c;
+    if (O.comps) O.comps[o] = comp;
+    // A2 fused: opacity * compensation (plain opacity in classic mode)
+    if (O.op_out) O.op_out[o] = O.comps ? __ldg(O.opacities + g) * comp : __ldg(O.opacities + g);
+    // A11 fused: the renderer's `visibility_filter` (radii > 0) and `radii` (radii / max(H, W),
+    // which torch evaluates as float(radii) * (1 / max)) (street_gaussian_renderer.py:293-294)
+    if (O.vis_out) O.vis_out[o] = radius_i > 0 ? 1 : 0;
+    if (O.radii_norm) O.radii_norm[o] = (float)radius_i * O.inv_max_dim;
+}
+
+// the full chain for one Gaussian that survived the pre-cull (canonical IEEE op order)
+__device__ __forceinline__ void
+proj_one(int64_t g, int64_t o, const Cam& c, const float* __restrict__ means, const float* __restrict__ quats,
+         const float* __restrict__ scales, int width, int height, float eps2d, float near_plane, float far_plane,
+         float radius_clip, const ProjOut& O) {
     int32_t radius_i = 0;
     float o_mx = 0.f, o_my = 0.f, o_z = 0.f, o_a = 0.f, o_b = 0.f, o_c = 0.f, o_comp = 0.f;
-    if (active) {
-        const Cam c = load_cam(viewmats + cam * 16, Ks + cam * 9);
-        const float px = s_means[tid * 3 + 0], py = s_means[tid * 3 + 1], pz = s_means[tid * 3 + 2];
+    {
+        const float px = __ldg(means + g * 3 + 0), py = __ldg(means + g * 3 + 1), pz = __ldg(means + g * 3 + 2);
         const float4 q = __ldg(reinterpret_cast<const float4*>(quats) + g);
         float S[6];
-        quat_scale_to_covar(q, s_scales[tid * 3 + 0], s_scales[tid * 3 + 1], s_scales[tid * 3 + 2], S);
+        quat_scale_to_covar(q, __ldg(scales + g * 3 + 0), __ldg(scales + g * 3 + 1), __ldg(scales + g * 3 + 2), S);
         const float Sm[3][3] = {{S[0], S[1], S[2]}, {S[1], S[3], S[4]}, {S[2], S[4], S[5]}};
         const float xc = ((c.W[0][0] * px + c.W[0][1] * py) + c.W[0][2] * pz) + c.t[0];
         const float yc = ((c.W[1][0] * px + c.W[1][1] * py) + c.W[1][2] * pz) + c.t[1];
@@ -168,36 +172,85 @@ projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* _
             o_comp = comp;
         }
     }
-    const int64_t o = (int64_t)cam * N + g;
-    if (active) {
-        radii[o] = radius_i;
-        reinterpret_cast<float2*>(means2d)[o] = make_float2(o_mx, o_my);
-        depths[o] = o_z;
-        if (comps) comps[o] = o_comp;
-        // A2 fused: opacity * compensation (plain opacity in classic mode)
-        if (op_out) op_out[o] = comps ? __ldg(opacities + g) * o_comp : __ldg(opacities + g);
-        // A11 fused: the renderer's `visibility_filter` (radii > 0) and `radii` (radii / max(H, W),
-        // which torch evaluates as float(radii) * (1 / max)) (street_gaussian_renderer.py:293-294)
-        if (vis_out) vis_out[o] = radius_i > 0 ? 1 : 0;
-        if (radii_norm) radii_norm[o] = (float)radius_i * inv_max_dim;
+    proj_store(O, o, g, radius_i, o_mx, o_my, o_z, o_a, o_b, o_c, o_comp);
+}
+
+// A CTA owns PF_CHUNK consecutive Gaussians of one camera.  On a street scene two thirds of them
+// are culled, most because they lie outside the frustum: each thread first runs a cheap
+// CONSERVATIVE test on PF_SPAN Gaussians (exact depth test; lateral test against an upper bound
+// of the radius: lambda_max(cov2d) <= max(scale)^2 |J|^2 + eps), writes the all-zero rows of the
+// ones it rejects (coalesced) and compacts the ids of the rest, which then run the full chain
+// with full warps.  A Gaussian rejected here is rejected by the full chain too, so the outputs
+// are bit-identical to evaluating every Gaussian.
+__global__ void __launch_bounds__(PROJ_THREADS)
+projection_fwd_kernel(int64_t N, const float* __restrict__ means, const float* __restrict__ quats,
+                      const float* __restrict__ scales, const float* __restrict__ viewmats,
+                      const float* __restrict__ Ks, int width, int height, float eps2d, float near_plane,
+                      float far_plane, float radius_clip, ProjOut O) {
+    __shared__ uint16_t s_list[PF_CHUNK];
+    __shared__ int s_wsum[PROJ_THREADS / 32];
+    const int cam = blockIdx.y;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int64_t base = (int64_t)blockIdx.x * PF_CHUNK;
+    const Cam c = load_cam(viewmats + cam * 16, Ks + cam * 9);
+    const float Wf = (float)width, Hf = (float)height;
+    // |tx / z| and |ty / z| never exceed these (the Jacobian clamp of the full chain)
+    const float Lx = fmaxf((Wf - c.cx) / c.fx, c.cx / c.fx) + SC_JAC_PAD * (0.5f * Wf / c.fx);
+    const float Ly = fmaxf((Hf - c.cy) / c.fy, c.cy / c.fy) + SC_JAC_PAD * (0.5f * Hf / c.fy);
+    // |W|_2^2 <= |W|_1 |W|_inf (1 for a rotation up to this bound's slack; holds for any view matrix)
+    float w1 = 0.f, winf = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        w1 = fmaxf(w1, fabsf(c.W[0][i]) + fabsf(c.W[1][i]) + fabsf(c.W[2][i]));
+        winf = fmaxf(winf, fabsf(c.W[i][0]) + fabsf(c.W[i][1]) + fabsf(c.W[i][2]));
     }
-    s_conics[tid * 3 + 0] = o_a;
-    s_conics[tid * 3 + 1] = o_b;
-    s_conics[tid * 3 + 2] = o_c;
-    __syncthreads();
-    {
-        // coalesced float4 write-back of the [.,3] conics
-        float* dst = conics + ((int64_t)cam * N + base) * 3;
-        const int nf = (int)n_here * 3;
-        const bool aligned = ((((int64_t)cam * N + base) * 3) & 3) == 0;
-        if (aligned) {
-            const int nf4 = nf >> 2;
-            if (tid < nf4) reinterpret_cast<float4*>(dst)[tid] = reinterpret_cast<float4*>(s_conics)[tid];
-            const int rem = nf - (nf4 << 2);
-            if (tid < rem) dst[(nf4 << 2) + tid] = s_conics[(nf4 << 2) + tid];
-        } else {
-            for (int i = tid; i < nf; i += PROJ_THREADS) dst[i] = s_conics[i];
+    const float jac2 = 1.02f * (w1 * winf) * (c.fx * c.fx * (1.0f + Lx * Lx) + c.fy * c.fy * (1.0f + Ly * Ly));
+    bool keep[PF_SPAN];
+#pragma unroll
+    for (int k = 0; k < PF_SPAN; ++k) {
+        const int64_t g = base + k * PROJ_THREADS + tid;
+        keep[k] = false;
+        if (g < N) {
+            const float px = __ldg(means + g * 3 + 0), py = __ldg(means + g * 3 + 1), pz = __ldg(means + g * 3 + 2);
+            const float smax = fmaxf(fmaxf(fabsf(__ldg(scales + g * 3 + 0)), fabsf(__ldg(scales + g * 3 + 1))),
+                                     fabsf(__ldg(scales + g * 3 + 2)));
+            const float xc = ((c.W[0][0] * px + c.W[0][1] * py) + c.W[0][2] * pz) + c.t[0];
+            const float yc = ((c.W[1][0] * px + c.W[1][1] * py) + c.W[1][2] * pz) + c.t[1];
+            const float zc = ((c.W[2][0] * px + c.W[2][1] * py) + c.W[2][2] * pz) + c.t[2];
+            bool dead = !((zc > near_plane) && (zc < far_plane));  // exactly the full chain's depth test
+            if (!dead && zc > 0.0f) {
+                const float mx = (c.fx * xc) / zc + c.cx;  // same expressions as the full chain
+                const float my = (c.fy * yc) / zc + c.cy;
+                // lambda_max(cov2d + eps I) <= smax^2 (|J0|^2 + |J1|^2) + 2 eps + 0.1, radius = ceil(3 sqrt(.))
+                const float lam = (smax * smax) * (jac2 / (zc * zc)) + (2.0f * eps2d + 0.1f);
+                const float rub = 3.0f * sqrtf(lam) * 1.001f + 2.0f;
+                dead = (mx + rub <= 0.0f) || (mx - rub >= Wf) || (my + rub <= 0.0f) || (my - rub >= Hf);
+            }
+            keep[k] = !dead;
+            if (dead) proj_store(O, (int64_t)cam * N + g, g, 0, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f);
         }
+    }
+    int round_base = 0;
+#pragma unroll
+    for (int k = 0; k < PF_SPAN; ++k) {
+        const unsigned b = __ballot_sync(0xffffffffu, keep[k]);
+        if (lane == 0) s_wsum[wid] = __popc(b);
+        __syncthreads();
+        int off = round_base;
+#pragma unroll
+        for (int w = 0; w < PROJ_THREADS / 32; ++w) {
+            const int cnt = s_wsum[w];
+            if (w < wid) off += cnt;
+            round_base += cnt;
+        }
+        if (keep[k]) s_list[off + __popc(b & ((1u << lane) - 1u))] = (uint16_t)(k * PROJ_THREADS + tid);
+        __syncthreads();
+    }
+    const int total = round_base;
+    for (int i = tid; i < total; i += PROJ_THREADS) {
+        const int64_t g = base + s_list[i];
+        proj_one(g, (int64_t)cam * N + g, c, means, quats, scales, width, height, eps2d, near_plane, far_plane,
+                 radius_clip, O);
     }
 }
 
@@ -664,11 +717,11 @@ static int projection_fwd_launch(int64_t N, int C, const float* means, const flo
                      ((uintptr_t)quats & 15) == 0 && ((uintptr_t)means2d & 7) == 0 &&
                      ((uintptr_t)conics & 15) == 0,
                  "16-byte alignment of means/quats/scales/conics");
-    dim3 grid((unsigned)sc_div_up(N, PROJ_THREADS), (unsigned)C);
+    dim3 grid((unsigned)sc_div_up(N, PF_CHUNK), (unsigned)C);
+    const ProjOut O{radii, means2d, depths, conics, compensations, opacities, op_out, vis_out, radii_norm,
+                    1.0f / (float)(width > height ? width : height)};
     projection_fwd_kernel<<<grid, PROJ_THREADS, 0, (cudaStream_t)stream>>>(
-        N, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip,
-        radii, means2d, depths, conics, compensations, opacities, op_out, vis_out, radii_norm,
-        1.0f / (float)(width > height ? width : height));
+        N, means, quats, scales, viewmats, Ks, width, height, eps2d, near_plane, far_plane, radius_clip, O);
     SC_CHECK_LAUNCH("projection_fwd_kernel");
     return SC_OK;
 }

@@ -454,7 +454,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             v_rc[r][c] = inside ? v_render_colors[pix_id * CH + c] : 0.f;
             if (backgrounds) bg_dot += __ldg(backgrounds + cam * CH + c) * v_rc[r][c];
         }
-        const float v_ra = inside ? v_render_alphas[pix_id] : 0.f;
+        const float v_ra = (inside && v_render_alphas) ? v_render_alphas[pix_id] : 0.f;  // nullable: zeros
         R[r] = Tf * (bg_dot - v_ra);
     }
     // the tile never used an entry past max(last id): start there
@@ -703,7 +703,7 @@ extern "C" int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int 
     }
     if (n_isects == 0 || N == 0) return SC_OK;
     SC_CHECK_ARG(means2d && conics && colors && opacities && isect_offsets && flatten_ids && final_T &&
-                     last_ids && v_render_colors && v_render_alphas && v_means2d && v_conics && v_colors &&
+                     last_ids && v_render_colors && v_means2d && v_conics && v_colors &&
                      v_opacities,
                  "null pointer");
     cudaStream_t st = (cudaStream_t)stream;

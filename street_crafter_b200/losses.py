@@ -77,20 +77,25 @@ class _Photometric(torch.autograd.Function):
         up = v_loss.to(torch.float32).contiguous()
         # gradient in the layout of `image`: a strided view of the compositor's [H,W,CH] output
         # gets a [H,W,CH] buffer (extra channels zero), a contiguous image a contiguous one
+        zero_extra = 0
         if st[1] > 1:
-            g_full = torch.zeros((H, W, st[1]), dtype=torch.float32, device=dev)
+            # channels beyond RGB (the depth channel) are zeroed by the kernel, not by a fill
+            interleaved = st[0] == 1 and st[1] - 3 <= 8
+            g_full = (torch.empty if interleaved else torch.zeros)((H, W, st[1]), dtype=torch.float32, device=dev)
             g = g_full.permute(2, 0, 1)[:3] if st[0] == 1 else None
+            zero_extra = st[1] - 3 if interleaved else 0
         else:
             g_full = torch.empty((3, H, W), dtype=torch.float32, device=dev)
             g = g_full if st[0] == H * W else None
         if g is None:  # unusual strides: dense [3,H,W] gradient
             g_full = torch.empty((3, H, W), dtype=torch.float32, device=dev)
             g = g_full
+            zero_extra = 0
         vs = _strides_chw(g)
         with torch.cuda.device(dev):
             check(lib.sc_photometric_bwd(H, W, image.data_ptr(), st[0], st[1], gt.data_ptr(),
                                          m8.data_ptr() if has_mask else None, lambda_dssim, lambda_l1,
-                                         ws.data_ptr(), up.data_ptr(), g.data_ptr(), vs[0], vs[1],
+                                         ws.data_ptr(), up.data_ptr(), g.data_ptr(), vs[0], vs[1], zero_extra,
                                          torch.cuda.current_stream().cuda_stream), "sc_photometric_bwd")
         if ctx.base_shape is not None:
             assert g_full.dim() == 3 and g_full.shape[-1] == ctx.base_shape[-1]

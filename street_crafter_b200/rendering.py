@@ -402,7 +402,8 @@ class _RasterizeToPixels(torch.autograd.Function):
         CH = colors.shape[-1]
         dev = means2d.device
         v_render_colors = _grad_or_zeros(v_render_colors, (C, height, width, CH), dev)
-        v_render_alphas = _grad_or_zeros(v_render_alphas, (C, height, width, 1), dev)
+        if v_render_alphas is not None:  # None: the kernel takes a null pointer (no gradient into alpha)
+            v_render_alphas = _f32c(v_render_alphas, "grad")
         # one zero-filled arena for all five gradient outputs (a single memset launch)
         n2, n3, nc, n1 = C * N * 2, C * N * 3, C * N * CH, C * N
         sizes = [n2, n2 if absgrad else 0, n3, nc, n1]
@@ -550,14 +551,16 @@ class _FusedView(torch.autograd.Function):
         dev = means.device
         st = _stream()
         v_render_colors = _grad_or_zeros(v_render_colors, (1, height, width, 4), dev)
-        v_render_alphas = _grad_or_zeros(v_render_alphas, (1, height, width, 1), dev)
+        if v_render_alphas is not None:  # None: no gradient into the alpha map, the kernel takes a null pointer
+            v_render_alphas = _f32c(v_render_alphas, "grad")
         if v_depth_norm is not None:
             # depth_norm = rc[..., 3] / clamp_min(alpha, 1e-10) (only when a depth loss is attached):
             # d/d rc_d = 1 / ac,  d/d alpha = -depth_norm / ac where alpha >= 1e-10
             ac = render_alphas.clamp(min=1e-10)
             v_render_colors = v_render_colors.clone()
             v_render_colors[..., 3:] += v_depth_norm / ac
-            v_render_alphas = v_render_alphas - v_depth_norm * depth_norm / ac * (render_alphas >= 1e-10)
+            v_a = -v_depth_norm * depth_norm / ac * (render_alphas >= 1e-10)
+            v_render_alphas = v_a if v_render_alphas is None else v_render_alphas + v_a
         sizes = [4 * N, 2 * N, 2 * N if absgrad else 0, 3 * N, N]  # colours first: 16-byte aligned rows
         arena = torch.zeros(sum(sizes), dtype=torch.float32, device=dev)  # one memset for all five
         v_colors4, v_means2d, v_abs, v_conics, v_opc = torch.split(arena, sizes)
