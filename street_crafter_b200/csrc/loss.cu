@@ -36,7 +36,8 @@ struct ImgView {        // element (c, y, x) of an image lives at base[c * cs + 
     int64_t cs, ps;
 };
 
-__device__ __forceinline__ float block_sum_256(float v, float* s_red) {
+template <int WARPS>
+__device__ __forceinline__ float block_sum(float v, float* s_red) {
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -45,7 +46,7 @@ __device__ __forceinline__ float block_sum_256(float v, float* s_red) {
     __syncthreads();
     float t = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) t += s_red[i];
+    for (int i = 0; i < WARPS; ++i) t += s_red[i];
     return t;
 }
 
@@ -55,23 +56,26 @@ __device__ __forceinline__ float block_sum_256(float v, float* s_red) {
 // loads per output instead of 11 per tap set.
 constexpr int HSEG = 8;   // outputs per horizontal task
 constexpr int VSEG = 4;   // outputs per vertical task
+constexpr int LPAD = LT + 1;  // odd row stride: the horizontal tasks of a warp walk down the rows
+// forward CTA: 192 threads = the 3 * 4 * 16 vertical tasks exactly (the horizontal pass has 156)
+constexpr int LF_THREADS = 3 * (LT / VSEG) * LT;
 
 // sums[0] = sum ssim, sums[1] = sum |x - y| over mask (all channels), sums[2] = masked pixels,
 // counter: CTAs done; out[0..2] = loss, L1, SSIM
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(LF_THREADS)
 photometric_fwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt,
                        const uint8_t* __restrict__ mask, float* __restrict__ dmaps, double* __restrict__ sums,
                        unsigned* __restrict__ counter, float lambda_dssim, float lambda_l1,
                        float* __restrict__ out) {
     __shared__ float s_x[3][LH][LH + 1], s_y[3][LH][LH + 1];
-    __shared__ float s_h[3][5][LH][LT + 1];
+    __shared__ float s_h[3][5][LH][LPAD];
     __shared__ float s_red[8];
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
     const int64_t HW = (int64_t)H * W;
     const bool hwc4 = img.cs == 1 && img.ps == 4 && (((uintptr_t)img.base) & 15) == 0;
     float l1_part = 0.f, cnt_part = 0.f;
-    for (int i = tid; i < LH * LH; i += 256) {
+    for (int i = tid; i < LH * LH; i += LF_THREADS) {
         const int hy = i / LH, hx = i - hy * LH;
         const int y = y0 + hy - LR, x = x0 + hx - LR;
         float a[3] = {0.f, 0.f, 0.f}, b[3] = {0.f, 0.f, 0.f};
@@ -98,21 +102,25 @@ photometric_fwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt,
         for (int c = 0; c < 3; ++c) { s_x[c][hy][hx] = a[c]; s_y[c][hy][hx] = b[c]; }
     }
     __syncthreads();
-    // horizontal pass, all channels: 3 * 26 * 2 tasks
-    for (int t = tid; t < 3 * LH * (LT / HSEG); t += 256) {
-        const int c = t / (LH * 2), r = (t - c * LH * 2) >> 1, c0 = (t & 1) * HSEG;
-        float xa[HSEG + 10], ya[HSEG + 10];
+    // horizontal pass, all channels: 3 * 26 * 2 tasks.  The products x^2, y^2, xy are formed once
+    // per staged value, so every tap is one FMA per moment map.
+    for (int t = tid; t < 3 * LH * (LT / HSEG); t += LF_THREADS) {
+        // consecutive lanes take consecutive halo rows (odd strides 27 / 17: no bank conflicts)
+        const int ch = t / LH, r = t - ch * LH, c = ch >> 1, c0 = (ch & 1) * HSEG;
+        float xa[HSEG + 10], ya[HSEG + 10], xx[HSEG + 10], yy[HSEG + 10], xy[HSEG + 10];
 #pragma unroll
-        for (int j = 0; j < HSEG + 10; ++j) { xa[j] = s_x[c][r][c0 + j]; ya[j] = s_y[c][r][c0 + j]; }
+        for (int j = 0; j < HSEG + 10; ++j) {
+            xa[j] = s_x[c][r][c0 + j]; ya[j] = s_y[c][r][c0 + j];
+            xx[j] = xa[j] * xa[j]; yy[j] = ya[j] * ya[j]; xy[j] = xa[j] * ya[j];
+        }
 #pragma unroll
         for (int o = 0; o < HSEG; ++o) {
             float hx_ = 0.f, hy_ = 0.f, hxx = 0.f, hyy = 0.f, hxy = 0.f;
 #pragma unroll
             for (int k = 0; k < 11; ++k) {
-                const float w = c_win[k], a = xa[o + k], b = ya[o + k];
-                const float wa = w * a, wb = w * b;
-                hx_ += wa; hy_ += wb;
-                hxx = fmaf(wa, a, hxx); hyy = fmaf(wb, b, hyy); hxy = fmaf(wa, b, hxy);
+                const float w = c_win[k];
+                hx_ = fmaf(w, xa[o + k], hx_); hy_ = fmaf(w, ya[o + k], hy_);
+                hxx = fmaf(w, xx[o + k], hxx); hyy = fmaf(w, yy[o + k], hyy); hxy = fmaf(w, xy[o + k], hxy);
             }
             s_h[c][0][r][c0 + o] = hx_; s_h[c][1][r][c0 + o] = hy_; s_h[c][2][r][c0 + o] = hxx;
             s_h[c][3][r][c0 + o] = hyy; s_h[c][4][r][c0 + o] = hxy;
@@ -121,7 +129,7 @@ photometric_fwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt,
     __syncthreads();
     // vertical pass + SSIM: 3 * 4 * 16 tasks, 4 rows each
     float ssim_part = 0.f;
-    if (tid < 3 * (LT / VSEG) * LT) {
+    {
         const int c = tid / ((LT / VSEG) * LT), rem = tid - c * (LT / VSEG) * LT;
         const int r0 = (rem >> 4) * VSEG, col = rem & 15;
         float acc[VSEG][5];
@@ -159,9 +167,9 @@ photometric_fwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt,
             }
         }
     }
-    const float bs = block_sum_256(ssim_part, s_red);
-    const float bl = block_sum_256(l1_part, s_red);
-    const float bc = block_sum_256(cnt_part, s_red);
+    const float bs = block_sum<LF_THREADS / 32>(ssim_part, s_red);
+    const float bl = block_sum<LF_THREADS / 32>(l1_part, s_red);
+    const float bc = block_sum<LF_THREADS / 32>(cnt_part, s_red);
     if (tid == 0) {
         atomicAdd(sums + 0, (double)bs);
         atomicAdd(sums + 1, (double)bl);
@@ -187,7 +195,7 @@ photometric_bwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt, 
                        const float* __restrict__ upstream, float lambda_dssim, float lambda_l1,
                        float* __restrict__ v_img, int64_t v_cs, int64_t v_ps, int zero_extra) {
     __shared__ float s_d[9][LH][LH + 1];   // [map * 3 + channel], with halo
-    __shared__ float s_h[9][LH][LT + 1];
+    __shared__ float s_h[9][LH][LPAD];
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * LT, y0 = blockIdx.y * LT;
     const int64_t HW = (int64_t)H * W;
@@ -205,7 +213,7 @@ photometric_bwd_kernel(int H, int W, ImgView img, const float* __restrict__ gt, 
     }
     __syncthreads();
     for (int t = tid; t < 9 * LH * (LT / HSEG); t += 256) {
-        const int m = t / (LH * 2), r = (t - m * LH * 2) >> 1, c0 = (t & 1) * HSEG;
+        const int mh = t / LH, r = t - mh * LH, m = mh >> 1, c0 = (mh & 1) * HSEG;  // lanes walk down the rows
         float v[HSEG + 10];
 #pragma unroll
         for (int j = 0; j < HSEG + 10; ++j) v[j] = s_d[m][r][c0 + j];
@@ -281,7 +289,7 @@ extern "C" int sc_photometric_fwd(int H, int W, const float* image, int64_t chan
     const int64_t maps_bytes = sc_align_up((int64_t)9 * H * W * 4, 256);
     SC_CUDA(cudaMemsetAsync(ws + maps_bytes, 0, 256, st));
     dim3 grid((unsigned)sc_div_up(W, LT), (unsigned)sc_div_up(H, LT));
-    photometric_fwd_kernel<<<grid, 256, 0, st>>>(H, W, ImgView{image, channel_stride, pixel_stride}, gt, mask,
+    photometric_fwd_kernel<<<grid, LF_THREADS, 0, st>>>(H, W, ImgView{image, channel_stride, pixel_stride}, gt, mask,
                                                  (float*)ws, (double*)(ws + maps_bytes),
                                                  (unsigned*)(ws + maps_bytes + 32), lambda_dssim, lambda_l1, out3);
     SC_CHECK_LAUNCH("photometric_fwd_kernel");
