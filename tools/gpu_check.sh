@@ -14,10 +14,14 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv \
     --log-file gpurun_out/${TAG}_launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline \
     > gpurun_out/${TAG}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
-# per camera pass the filter matches 12 launches (projection fwd, 4+2 onesweep, emit, SH fwd, the two
+# per camera pass the filter matches 13 launches (projection fwd, 4+2 onesweep, emit, SH fwd, the two
 # compositing kernels, SH bwd, projection bwd): skip 6 warm-up passes, capture one pass
 ncu --set full --clock-control none --import-source on \
-    -k regex:'rasterize_|onesweep|sh_bwd|sh_fwd|projection_|isect_emit' -s 72 -c 12 -o gpurun_out/${TAG}_prof -f \
+    -k regex:'rasterize_|onesweep|sh_bwd|sh_fwd|projection_|isect_emit' -s 78 -c 13 -o gpurun_out/${TAG}_prof -f \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/${TAG}_ncu_full.log 2>&1
 echo "ncu full exit $?"
+# the loss kernels run in the e2e leg only: capture them from the stand-alone loss tool
+ncu --set full --clock-control none --import-source on -k regex:photometric -s 6 -c 2 \
+    -o gpurun_out/${TAG}_loss -f python tools/loss_bench.py > gpurun_out/${TAG}_ncu_loss.log 2>&1
+echo "ncu loss exit $?"
 ls -la gpurun_out | tail -12

@@ -34,8 +34,10 @@ if os.path.exists(lc):
     for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
         out.write(f"{v[1]:10.1f} us {100*v[1]/tot:5.1f}% n={v[0]:4d} avg={v[1]/v[0]:8.1f} us  {k}\n")
 
-rep = os.path.join(ROOT, "gpurun_out", f"{tag}_prof.ncu-rep")
-if os.path.exists(rep):
+for rep in (os.path.join(ROOT, "gpurun_out", f"{tag}_prof.ncu-rep"),
+            os.path.join(ROOT, "gpurun_out", f"{tag}_loss.ncu-rep")):
+    if not os.path.exists(rep):
+        continue
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
@@ -53,11 +55,19 @@ if os.path.exists(rep):
             "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
             "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
             "smsp__thread_inst_executed_per_inst_executed.ratio"]
-    out.write(f"\n# ncu --set full --clock-control none ({tag}); one block per captured launch\n")
+    stall = [h for h in hdr if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("not_issued")]
+    out.write(f"\n# ncu --set full --clock-control none ({os.path.basename(rep)}); one block per captured launch\n")
     for r in rows[2:]:
         out.write("-----\n" + r[idx["Kernel Name"]][:90] + "\n")
         for w in want:
             if w in idx:
                 out.write(f"  {w:66s} {r[idx[w]]:>18s} {units[idx[w]]}\n")
+        try:
+            sv = sorted(((float(r[idx[h]].replace(",", "")), h.replace("smsp__pcsamp_warps_issue_stalled_", ""))
+                         for h in stall), reverse=True)
+            tot = sum(v for v, _ in sv) or 1.0
+            out.write("  warp-state samples: " + ", ".join(f"{n} {100*v/tot:.0f}%" for v, n in sv[:7]) + "\n")
+        except ValueError:
+            pass
 out.close()
 print(open(os.path.join(ROOT, "profiles", f"{tag}_ncu_summary.txt")).read()[-3000:])
