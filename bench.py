@@ -284,6 +284,10 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # the image exports NCCL_DEBUG=VERSION, which makes NCCL print a banner on STDOUT: keep stdout to
+        # the one JSON line (an explicit INFO / TRACE request is left alone)
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
 
     import street_crafter_b200 as S
