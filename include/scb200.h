@@ -20,6 +20,8 @@
  *                                  (street_gaussian_renderer.py:233-238, :256-266)
  *   sc_photometric_fwd/bwd     loss_utils.l1_loss + ssim       street_gaussian/utils/loss_utils.py:21-38, :96-131,
  *                                                              combined as in train.py:183-186
+ *   sc_densification_stats     set_max_radii2D + add_densification_stats
+ *                                                              street_gaussian/models/street_gaussian_model.py:486-519
  *
  * Conventions: all pointers are DEVICE pointers unless named host_*; row-major contiguous
  * fp32 / int32 / int64 arrays; `stream` is a cudaStream_t passed as void*; nothing here
@@ -220,6 +222,17 @@ int sc_photometric_bwd(int H, int W, const float* image, int64_t channel_stride,
                        const void* workspace, const float* upstream, float* v_image,
                        int64_t v_channel_stride, int64_t v_pixel_stride, int zero_extra_channels,
                        void* stream);
+
+/* N3, second half: the per-iteration densification statistics in one pass
+ * (street_gaussian/models/street_gaussian_model.py:486-497 set_max_radii2D, :503-519
+ * add_densification_stats with absgrad, called at train.py:283-284).  For every Gaussian with
+ * visibility != 0:  xyz_gradient_accum[i,0] += |absgrad_i * 0.5 * (W,H)|,
+ * xyz_gradient_accum[i,1] += |grad_i * 0.5 * (W,H)|, denom[i] += 1,
+ * max_radii2D[i] = max(max_radii2D[i], radii[i]).  All arrays fp32, visibility u8 / bool. */
+int sc_densification_stats(int64_t N, const float* means2d_absgrad /*[N,2]*/, const float* means2d_grad /*[N,2]*/,
+                           const uint8_t* visibility /*[N]*/, const float* radii /*[N]*/, int width, int height,
+                           float* xyz_gradient_accum /*[N,2]*/, float* denom /*[N]*/, float* max_radii2D /*[N]*/,
+                           void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

@@ -29,6 +29,7 @@ SOURCES = {
     "rasterize.cu": ["--use_fast_math"],
     "knn.cu": [],
     "loss.cu": [],
+    "densify.cu": [],
     "probe.cu": ["--use_fast_math"],
 }
 

@@ -685,3 +685,46 @@ def test_photometric_loss_vs_oracle_and_layouts(S, dev, H, W, use_mask):
     loss3, _, _ = L.photometric_loss(img3, gt.to(dev), md, 0.2, 1.0)
     (3.0 * loss3).backward()
     assert_grad_close(img3.grad, img_w.grad, "grad contiguous")
+
+
+# ------------------------------------------------------------------------ densification statistics (N3)
+@pytest.mark.gpu
+def test_densification_stats_vs_reference_golden(S, dev):
+    import numpy as np
+    from street_crafter_b200.densify import densification_stats
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "densify_stats.npz"))
+    f = lambda k: torch.from_numpy(z[k]).float().to(dev)
+    vp = torch.zeros(1, z["grad"].shape[1], 2, device=dev)
+    vp.grad, vp.absgrad = f("grad"), f("absgrad")
+    acc, den, mr = f("accum_in").contiguous(), f("denom_in").contiguous(), f("max_radii2D_in").contiguous()
+    densification_stats(vp, torch.from_numpy(z["vis"]).to(dev), f("radii"), int(z["W"]), int(z["H"]), acc, den, mr)
+    assert torch.allclose(acc.cpu().double(), torch.from_numpy(z["accum_out"]), rtol=2e-6, atol=1e-7)
+    assert torch.equal(den.cpu().double(), torch.from_numpy(z["denom_out"]))
+    assert torch.equal(mr.cpu(), torch.from_numpy(z["max_radii2D_out"]).float())
+
+
+@pytest.mark.gpu
+def test_densification_stats_after_render_vs_oracle(S, dev):
+    """the call sequence of train.py:283-284 on a real render: statistics from the renderer's own
+    viewspace_points / visibility_filter / radii equal the oracle's, untouched where invisible"""
+    from oracle.densify_torch import densification_stats as oracle_stats
+    from street_crafter_b200.densify import densification_stats
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    n, W, H, deg = 30000, 480, 320, 3
+    s = make_gaussians(n, sh_degree=deg, seed=17)
+    V, K = make_camera(W, H, yaw_deg=8.0)
+    c = {k: v.to(dev).requires_grad_(True) for k, v in s.items()}
+    cc = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
+    out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None],
+                               V[None].to(dev), K[None].to(dev), cc, W, H, deg)
+    (out["rgb"].square().sum() + out["acc"].sum()).backward()
+    g = torch.Generator().manual_seed(4)
+    acc0, den0, mr0 = torch.rand(n, 2, generator=g), torch.randint(0, 3, (n, 1), generator=g).float(), torch.rand(n, generator=g) * 0.01
+    acc, den, mr = acc0.to(dev), den0.to(dev), mr0.to(dev)
+    vp = out["viewspace_points"]
+    densification_stats(vp, out["visibility_filter"], out["radii"], W, H, acc, den, mr)
+    w_acc, w_den, w_mr = oracle_stats(vp.grad.cpu(), vp.absgrad.cpu(), out["visibility_filter"].cpu(), out["radii"].cpu(),
+                                      W, H, acc0.clone(), den0.clone(), mr0.clone())
+    assert out["visibility_filter"].sum().item() > 1000
+    assert torch.allclose(acc.cpu(), w_acc, rtol=2e-6, atol=1e-9)
+    assert torch.equal(den.cpu(), w_den) and torch.equal(mr.cpu(), w_mr)

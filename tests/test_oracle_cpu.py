@@ -285,3 +285,19 @@ def test_loss_oracle_matches_reference_golden():
         assert abs(float(s) - float(z[f"{name}_ssim"])) < 1e-10
         assert abs(float(loss) - float(z[f"{name}_loss"])) < 1e-10
         assert np.abs(img.grad.numpy() - z[f"{name}_grad"]).max() < 1e-10
+
+
+def test_densify_oracle_matches_reference_golden():
+    """oracle/densify_torch.py against vectors produced by EXECUTING the reference's own
+    set_max_radii2D / add_densification_stats (tools/make_golden_densify.py)"""
+    import numpy as np
+    from oracle.densify_torch import densification_stats
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "densify_stats.npz"))
+    t = lambda k: torch.from_numpy(z[k])
+    acc, den, mr = densification_stats(t("grad"), t("absgrad"), t("vis"), t("radii"), int(z["W"]), int(z["H"]),
+                                       t("accum_in").clone(), t("denom_in").clone(), t("max_radii2D_in").clone())
+    assert torch.allclose(acc, t("accum_out"), rtol=1e-12, atol=0)
+    assert torch.equal(den, t("denom_out")) and torch.equal(mr, t("max_radii2D_out"))
+    # Gaussians outside the visibility filter are untouched
+    inv = ~t("vis")
+    assert torch.equal(acc[inv], t("accum_in")[inv]) and torch.equal(den[inv], t("denom_in")[inv])
