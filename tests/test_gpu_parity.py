@@ -722,7 +722,9 @@ def test_densification_stats_after_render_vs_oracle(S, dev):
     acc0, den0, mr0 = torch.rand(n, 2, generator=g), torch.randint(0, 3, (n, 1), generator=g).float(), torch.rand(n, generator=g) * 0.01
     acc, den, mr = acc0.to(dev), den0.to(dev), mr0.to(dev)
     vp = out["viewspace_points"]
-    densification_stats(vp, out["visibility_filter"], out["radii"], W, H, acc, den, mr)
+    half = n // 2  # two "models" of the scene graph: rows [0, half) and [half, n)
+    densification_stats(vp, out["visibility_filter"], out["radii"], W, H, acc[:half], den[:half], mr[:half], 0, half)
+    densification_stats(vp, out["visibility_filter"], out["radii"], W, H, acc[half:], den[half:], mr[half:], half, n)
     w_acc, w_den, w_mr = oracle_stats(vp.grad.cpu(), vp.absgrad.cpu(), out["visibility_filter"].cpu(), out["radii"].cpu(),
                                       W, H, acc0.clone(), den0.clone(), mr0.clone())
     assert out["visibility_filter"].sum().item() > 1000
