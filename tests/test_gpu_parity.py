@@ -730,3 +730,65 @@ def test_densification_stats_after_render_vs_oracle(S, dev):
     assert out["visibility_filter"].sum().item() > 1000
     assert torch.allclose(acc.cpu(), w_acc, rtol=2e-6, atol=1e-9)
     assert torch.equal(den.cpu(), w_den) and torch.equal(mr.cpu(), w_mr)
+
+
+# ------------------------------------------------------- BASELINE configs[2] / configs[4] at FULL size
+def test_cfg3_lidar_frame_scale_properties(S, dev):
+    """configs[2]: 5 M LiDAR points splatted to a 1024x576 frame with max_hit = 10 — too large for the
+    oracle, so size-independent properties: binning structure, alpha range, the hit cap only ever removes
+    contributions, and a cap above the longest per-pixel list changes nothing."""
+    from street_crafter_b200 import rendering as R
+    P, W, H = 5_000_000, 1024, 576
+    xyz, rgb = make_lidar_points(P, seed=3)
+    xyz, rgb = xyz.to(dev), rgb.to(dev)
+    V, K = make_camera(W, H)
+    V, K = V.to(dev), K.to(dev)
+    quats = torch.zeros(P, 4, device=dev); quats[:, 0] = 1
+    scales = torch.full((P, 3), 0.02, device=dev)
+    radii, m2, dep, con, _ = R.fully_fused_projection(xyz, None, quats, scales, V[None], K[None], W, H,
+                                                      near_plane=1.0, far_plane=100.0)
+    tw, th = math.ceil(W / 16), math.ceil(H / 16)
+    tpg, ids, flat = R.isect_tiles(m2, radii, dep, 16, tw, th, n_cameras=1)
+    off = R.isect_offset_encode(ids, 1, tw, th)
+    I = ids.numel()
+    assert I == int(tpg.sum()) and I > 500_000
+    assert bool((ids[1:] >= ids[:-1]).all())
+    offs = torch.cat([off.reshape(-1).long(), torch.tensor([I], device=dev)])
+    assert torch.equal(torch.bincount(ids >> 32, minlength=off.numel()), offs[1:] - offs[:-1])
+    assert bool((radii[0][flat.long()] > 0).all()), "only visible points are binned"
+    cols = torch.cat([rgb, dep[0][:, None]], -1)[None]
+    op = torch.ones(1, P, device=dev)
+    outs = {}
+    for mh in (0, 10, 1 << 20):
+        outs[mh] = R.rasterize_to_pixels(m2, con, cols, op, W, H, 16, off, flat, max_hit=mh)
+    (rc0, ra0), (rc10, ra10), (rcb, rab) = outs[0], outs[10], outs[1 << 20]
+    for t in (rc0, ra0, rc10, ra10):
+        assert bool(torch.isfinite(t).all())
+    assert float(ra10.min()) >= 0.0 and float(ra10.max()) <= 1.0
+    assert bool((ra10 <= ra0 + 1e-6).all()), "the hit cap only removes contributions"
+    assert bool((ra10 < ra0 - 1e-3).any()), "and it does bite somewhere at this density"
+    assert torch.equal(rcb, rc0) and torch.equal(rab, ra0), "a cap above the longest list is the uncapped render"
+    # front-to-back depth: the blended depth lies inside the near/far range wherever the pixel is covered
+    cov = ra10[0, ..., 0] > 0.5
+    d = (rc10[0, ..., 3] / ra10[0, ..., 0].clamp(min=1e-10))[cov]
+    assert cov.float().mean().item() > 0.2 and float(d.min()) >= 1.0 - 1e-3 and float(d.max()) <= 100.0 + 1e-3
+
+
+def test_cfg5_knn_5m_subset_exact(S, dev):
+    """configs[4]: distCUDA2 on 5 M points; 512 random queries are checked against an exhaustive search over
+    all 5 M points (the property every output must satisfy: mean squared distance to the 3 nearest OTHER points)"""
+    P = 5_000_000
+    xyz, _ = make_lidar_points(P, seed=5)
+    p = xyz.to(dev)
+    got = S.distCUDA2(p)
+    assert got.shape == (P,) and bool(torch.isfinite(got).all()) and float(got.min()) >= 0.0
+    g = torch.Generator().manual_seed(9)
+    q = torch.randint(0, P, (512,), generator=g).to(dev)
+    best = torch.full((512, 4), float("inf"), device=dev)
+    for a in range(0, P, 500_000):
+        blk = p[a:a + 500_000]
+        d2 = ((p[q][:, None, :] - blk[None, :, :]) ** 2).sum(-1)          # [512, 500k]
+        best = torch.cat([best, d2.topk(4, dim=1, largest=False).values], 1).topk(4, dim=1, largest=False).values
+    want = best[:, 1:].mean(1)                                             # drop the self match (0)
+    assert float(best[:, 0].max()) == 0.0
+    assert torch.allclose(got[q], want, rtol=1e-5, atol=1e-12), (got[q] - want).abs().max()
