@@ -176,23 +176,38 @@ __device__ __forceinline__ int stage_round(int first, int step, int n_cand, int 
 
 // tuning knobs (overridable with -D for the sweeps of tools/raster_variants.sh)
 #ifndef SC_FWD_MIN_CTAS
-#define SC_FWD_MIN_CTAS 4  // register cap 128 -> 16 warps per SM: no spills beats more warps (tools/raster_variants.sh)
+#define SC_FWD_MIN_CTAS 16  // CTAs of ONE warp: register cap 128 -> 16 warps per SM; no spills beats more warps
 #endif
 #ifndef SC_BWD_MIN_CTAS
-#define SC_BWD_MIN_CTAS 4  // register cap 128 -> 16 warps per SM
+#define SC_BWD_MIN_CTAS 16  // register cap 128 -> 16 warps per SM (a 96-register build with 20 warps measured 5 % slower)
 #endif
-constexpr int WARPS_PER_CTA = 4;  // independent tiles per CTA (no inter-warp communication)
+#ifndef SC_WARPS_PER_CTA
+#define SC_WARPS_PER_CTA 1  // one tile per CTA: the finest grain for the hardware's CTA scheduler (tile cost varies 100x)
+#endif
+constexpr int WARPS_PER_CTA = SC_WARPS_PER_CTA;  // independent tiles per CTA (no inter-warp communication)
 constexpr int FWD_MIN_CTAS = SC_FWD_MIN_CTAS;
 constexpr int BWD_MIN_CTAS = SC_BWD_MIN_CTAS;
 
-template <int CH, bool WITH_GID>
+#ifndef SC_BWD_BATCH
+#define SC_BWD_BATCH 64
+#endif
+#ifndef SC_BWD_VRC_SMEM
+#define SC_BWD_VRC_SMEM 1  // the backward keeps the per-pixel upstream colour gradient in shared memory (32 registers
+                           // freed for the scheduler; one conflict-free LDS.128 per contributing pixel pair)
+#endif
+constexpr int BATCH_BWD = SC_BWD_BATCH;
+constexpr bool BWD_VRC_SMEM = SC_BWD_VRC_SMEM != 0;
+
+template <int CH, bool WITH_GID, int NBATCH = BATCH>
 struct WarpSmem {
-    StagedA A[BATCH];
-    StagedB B[BATCH];
-    float C[BATCH * CH];
-    int G[WITH_GID ? BATCH : 1];
+    StagedA A[NBATCH];
+    StagedB B[NBATCH];
+    float C[NBATCH * CH];
+    int G[WITH_GID ? NBATCH : 1];
     int P[PPT][32];  // per-pixel list positions touched only on rare events (kept out of registers)
     float Rd[WITH_GID ? NRED : 1][RED_STRIDE];  // backward: transposed per-lane partials
+    float4 V[(WITH_GID && BWD_VRC_SMEM && CH == 4) ? PPT : 1]
+            [(WITH_GID && BWD_VRC_SMEM && CH == 4) ? 32 : 1];  // backward: upstream colour gradients
 };
 
 // ------------------------------------------------------------------------------- forward
@@ -418,12 +433,13 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                      float* __restrict__ v_means2d_abs, float* __restrict__ v_conics,
                      float* __restrict__ v_colors, float* __restrict__ v_opacities) {
     static_assert(CH <= 5, "slots 0..4 hold v_colors");
-    __shared__ __align__(16) WarpSmem<CH, true> smem[WARPS_PER_CTA];
+    __shared__ __align__(16) WarpSmem<CH, true, BATCH_BWD> smem[WARPS_PER_CTA];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t n_slots = (int64_t)n_cams * tile_w * tile_h;
     const int64_t tslot = (int64_t)blockIdx.x * WARPS_PER_CTA + wib;
     if (tslot >= n_slots) return;
-    WarpSmem<CH, true>& sm = smem[wib];
+    WarpSmem<CH, true, BATCH_BWD>& sm = smem[wib];
+    constexpr bool VSM = BWD_VRC_SMEM && CH == 4;
     const int cam = (int)(tslot / (tile_w * tile_h));
     const int tile_id = (int)(tslot - (int64_t)cam * tile_w * tile_h);
     const int tyi = tile_id / tile_w, txi = tile_id - tyi * tile_w;
@@ -435,7 +451,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 
     // per-pixel state: T (running transmittance, walking back), R = <v_rc, colour behind> -
     // T_final * v_ra (+ T_final * <bg, v_rc>), so that v_alpha = <v_rc,col> * T - R / (1-alpha)
-    float T[PPT], R[PPT], v_rc[PPT][CH], pyv[PPT];
+    float T[PPT], R[PPT], v_rc[VSM ? 1 : PPT][CH], pyv[PPT];
     int tile_last = -1;
 #pragma unroll
     for (int r = 0; r < PPT; ++r) {
@@ -449,10 +465,17 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
         T[r] = Tf;
         pyv[r] = SC_DEAD_Y;
         float bg_dot = 0.f;
+        float vin[CH];
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
-            v_rc[r][c] = inside ? v_render_colors[pix_id * CH + c] : 0.f;
-            if (backgrounds) bg_dot += __ldg(backgrounds + cam * CH + c) * v_rc[r][c];
+            vin[c] = inside ? v_render_colors[pix_id * CH + c] : 0.f;
+            if (backgrounds) bg_dot += __ldg(backgrounds + cam * CH + c) * vin[c];
+        }
+        if constexpr (VSM) {
+            sm.V[r][lane] = make_float4(vin[0], vin[1], vin[2], vin[3]);
+        } else {
+#pragma unroll
+            for (int c = 0; c < CH; ++c) v_rc[r][c] = vin[c];
         }
         const float v_ra = (inside && v_render_alphas) ? v_render_alphas[pix_id] : 0.f;  // nullable: zeros
         R[r] = Tf * (bg_dot - v_ra);
@@ -486,7 +509,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
     int next = tile_last;  // candidates are taken from here downwards
     while (next >= range_start) {
         int count = 0;
-        while (count <= BATCH - ROUND && next >= range_start) {
+        while (count <= BATCH_BWD - ROUND && next >= range_start) {
             count = stage_round<CH, true>(next, -1, min(ROUND, next - range_start + 1), count, lane, X0, Y0,
                                           means2d, conics, colors, opacities, flatten_ids, sm.A, sm.B, sm.C,
                                           sm.G);
@@ -550,10 +573,18 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                             T[r] *= ra;
                             const float fac = a * T[r];
                             float d = 0.f;
+                            float vr[CH];
+                            if constexpr (VSM) {
+                                const float4 v4 = sm.V[r][lane];
+                                vr[0] = v4.x; vr[1] = v4.y; vr[2] = v4.z; vr[3] = v4.w;
+                            } else {
+#pragma unroll
+                                for (int c = 0; c < CH; ++c) vr[c] = v_rc[r][c];
+                            }
 #pragma unroll
                             for (int c = 0; c < CH; ++c) {
-                                d = fmaf(col[c], v_rc[r][c], d);
-                                vc[c] = fmaf(fac, v_rc[r][c], vc[c]);
+                                d = fmaf(col[c], vr[c], d);
+                                vc[c] = fmaf(fac, vr[c], vc[c]);
                             }
                             const float v_alpha = d * T[r] - R[r] * ra;
                             R[r] = fmaf(d, fac, R[r]);
