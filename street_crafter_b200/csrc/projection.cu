@@ -579,6 +579,11 @@ isect_scan_kernel(const int64_t* __restrict__ totals, const uint32_t* __restrict
 }
 
 // emit with the entry table and the fused sort histogram (see the pipeline header above)
+#ifndef SC_EMIT_ILP
+#define SC_EMIT_ILP 2
+#endif
+constexpr int EMIT_ILP = SC_EMIT_ILP;  // output slots per lane and iteration (independent search chains)
+
 __global__ void __launch_bounds__(EMIT_THREADS)
 isect_emit_hist_kernel(int64_t N, int64_t V, const float2* __restrict__ means2d,
                        const int32_t* __restrict__ radii, const float* __restrict__ depths,
@@ -627,32 +632,50 @@ isect_emit_hist_kernel(int64_t N, int64_t V, const float2* __restrict__ means2d,
         __syncthreads();
         const int qlo = (int)(max(p0, chunk_first) - p0);
         const int qhi = (int)(min(p1, chunk_end) - p0);
-        // all lanes of a warp iterate together (the histogram uses warp votes)
-        for (int qb = qlo + (tid & ~31); qb < qhi; qb += EMIT_THREADS) {
-            const int q = qb + lane;
-            const bool in = q < qhi;
-            uint32_t hi32 = 0;
-            if (in) {
-                int t = 0;
+        // all lanes of a warp iterate together (the histogram uses warp votes); EMIT_ILP slots per
+        // lane and iteration, so that the two dependent chains (8-step search over the staged entries,
+        // integer divide) interleave
+        for (int qb = qlo + (tid & ~31); qb < qhi; qb += EMIT_ILP * EMIT_THREADS) {
+            int q[EMIT_ILP], t[EMIT_ILP];
+            bool in[EMIT_ILP];
+            uint32_t hi32[EMIT_ILP];
 #pragma unroll
-                for (int step = EMIT_THREADS / 2; step >= 1; step >>= 1)
-                    if (s_start[t + step] <= q) t += step;
-                const int k = q - s_start[t];
-                const int w = s_w[t];
-                const int ty = s_y0[t] + k / w;
-                const int tx = s_x0[t] + k % w;
-                hi32 = (uint32_t)(s_camhi[t] | (ty * tw + tx));
-                isect_ids[p0 + q] = (int64_t)(((uint64_t)hi32 << 32) | (uint64_t)s_dbits[t]);
-                flatten_ids[p0 + q] = s_id[t];
+            for (int u = 0; u < EMIT_ILP; ++u) {
+                q[u] = qb + u * EMIT_THREADS + lane;
+                in[u] = q[u] < qhi;
+                t[u] = 0;
+                hi32[u] = 0u;
             }
-            // pass 0 digits of neighbouring slots are consecutive tiles (distinct): plain atomics;
-            // higher digits are shared by most of the warp: one atomic per distinct digit
-            if (in) atomicAdd(&s_hist[0][(hi32 >> (pp.shift[0] - 32)) & ((1u << pp.nbits[0]) - 1u)], 1u);
-            for (int p = 1; p < pp.passes; ++p) {
-                const uint32_t d = (hi32 >> (pp.shift[p] - 32)) & ((1u << pp.nbits[p]) - 1u);
-                // neighbouring slots share the high digits: match.any resolves in one or two rounds here
-                const unsigned peers = __match_any_sync(0xffffffffu, in ? d : 0xffffffffu);
-                if (in && (peers & lt_mask) == 0) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
+#pragma unroll
+            for (int step = EMIT_THREADS / 2; step >= 1; step >>= 1) {
+#pragma unroll
+                for (int u = 0; u < EMIT_ILP; ++u)
+                    if (s_start[t[u] + step] <= q[u]) t[u] += step;
+            }
+#pragma unroll
+            for (int u = 0; u < EMIT_ILP; ++u) {
+                if (in[u]) {
+                    const int k = q[u] - s_start[t[u]];
+                    const int w = s_w[t[u]];
+                    const int ty = s_y0[t[u]] + k / w;
+                    const int tx = s_x0[t[u]] + k % w;
+                    hi32[u] = (uint32_t)(s_camhi[t[u]] | (ty * tw + tx));
+                    isect_ids[p0 + q[u]] = (int64_t)(((uint64_t)hi32[u] << 32) | (uint64_t)s_dbits[t[u]]);
+                    flatten_ids[p0 + q[u]] = s_id[t[u]];
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < EMIT_ILP; ++u) {
+                if (u > 0 && qb + u * EMIT_THREADS >= qhi) break;  // warp-uniform
+                // pass 0 digits of neighbouring slots are consecutive tiles (distinct): plain atomics;
+                // higher digits are shared by most of the warp: one atomic per distinct digit
+                if (in[u]) atomicAdd(&s_hist[0][(hi32[u] >> (pp.shift[0] - 32)) & ((1u << pp.nbits[0]) - 1u)], 1u);
+                for (int p = 1; p < pp.passes; ++p) {
+                    const uint32_t d = (hi32[u] >> (pp.shift[p] - 32)) & ((1u << pp.nbits[p]) - 1u);
+                    // neighbouring slots share the high digits: match.any resolves in one or two rounds here
+                    const unsigned peers = __match_any_sync(0xffffffffu, in[u] ? d : 0xffffffffu);
+                    if (in[u] && (peers & lt_mask) == 0) atomicAdd(&s_hist[p][d], (uint32_t)__popc(peers));
+                }
             }
         }
     }
