@@ -116,7 +116,7 @@ def run_reference(args):
     dt = (time.perf_counter() - t0) / args.steps
     mpix = W * H / dt / 1e6
     sample = f"{n} Gaussians SH3, one {W}x{H} camera, fwd+bwd (torch CPU oracle, same scene generator)"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "3DGS fwd+bwd Mpix/s", "value": mpix, "unit": "Mpix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -124,7 +124,7 @@ def run_reference(args):
         "cpu_baseline": {"value": mpix, "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": mpix, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }))
+    })
 
 
 # ------------------------------------------------------------------------------------------
@@ -284,10 +284,9 @@ def run_ours(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # the image exports NCCL_DEBUG=VERSION, which makes NCCL print a banner on STDOUT: keep stdout to
-        # the one JSON line (an explicit INFO / TRACE request is left alone)
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"
+        # the image exports NCCL_DEBUG=VERSION and NCCL writes its banner / debug lines to STDOUT: send them
+        # to stderr so that stdout carries the one JSON line only
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
     import street_crafter_b200 as S
@@ -544,11 +543,31 @@ def run_ours(args):
         dist.barrier()
         dist.destroy_process_group()
     if result is not None:
-        print(json.dumps(result))
+        emit(result)
+
+
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """libraries (NCCL's version banner, torchrun's notices) write to fd 1: point it at stderr for the
+    run and keep the real stdout for the ONE JSON line"""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(result):
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(result), flush=True)
 
 
 def main():
     args = parse()
+    _quiet_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:
