@@ -792,3 +792,49 @@ def test_cfg5_knn_5m_subset_exact(S, dev):
     want = best[:, 1:].mean(1)                                             # drop the self match (0)
     assert float(best[:, 0].max()) == 0.0
     assert torch.allclose(got[q], want, rtol=1e-5, atol=1e-12), (got[q] - want).abs().max()
+
+
+# ------------------------------------------------------------------------------ degenerate inputs
+@pytest.mark.parametrize("case", ["nothing_visible", "single_gaussian", "odd_image"])
+@pytest.mark.parametrize("fused", [True, False])
+def test_renderer_degenerate_inputs(S, dev, case, fused):
+    """empty binning (every Gaussian behind the camera), N = 1, and an image that is not a multiple of the
+    tile size, through the whole renderer + backward on both call paths: finite results, same as the oracle"""
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    deg = 3
+    if case == "nothing_visible":
+        n, W, H = 500, 160, 96
+        s = make_gaussians(n, sh_degree=deg, seed=5)
+        s["means"][:, 2] = -s["means"][:, 2].abs() - 1.0       # all behind the camera
+    elif case == "single_gaussian":
+        n, W, H = 1, 64, 48
+        s = make_gaussians(n, sh_degree=deg, seed=6)
+        s["means"][0] = torch.tensor([0.05, -0.02, 4.0])
+        s["scales"][0] = torch.tensor([0.05, 0.08, 0.03])
+    else:
+        n, W, H = 3000, 333, 211
+        s = make_gaussians(n, sh_degree=deg, seed=7, scale_mean=0.3)
+    V, K = make_camera(W, H)
+    c = {k: v.to(dev).requires_grad_(True) for k, v in s.items()}
+    cc = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
+    out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None],
+                               V[None].to(dev), K[None].to(dev), cc, W, H, deg, fused=fused)
+    assert out["rgb"].shape == (3, H, W) and out["acc"].shape == (1, H, W) and out["depth"].shape == (1, H, W)
+    loss = out["rgb"].square().sum() + out["acc"].sum() + out["depth"].sum() * 1e-2
+    loss.backward()
+    for k in ("means", "quats", "scales", "opacities", "shs"):
+        g = c[k].grad
+        assert g is not None and bool(torch.isfinite(g).all()), k
+    vis = out["visibility_filter"]
+    if case == "nothing_visible":
+        assert int(vis.sum()) == 0 and out["aux"]["isect_ids"].numel() == 0
+        assert float(out["acc"].detach().abs().max()) == 0.0 and float(out["rgb"].detach().abs().max()) == 0.0
+        assert all(float(c[k].grad.abs().max()) == 0.0 for k in ("means", "quats", "scales", "opacities", "shs"))
+    else:
+        assert int(vis.sum()) >= 1
+    # oracle on the same inputs (forward image)
+    o = {k: v.detach().cpu() for k, v in c.items()}
+    want_rc, want_ra = G.render_reference_sequence(o["means"], o["quats"], o["scales"], o["opacities"], o["shs"], V, K,
+                                                   W, H, deg)[:2]
+    assert_image_close(out["render_colors"].cpu(), want_rc.detach(), "degenerate render")
+    assert_image_close(out["render_alphas"].cpu(), want_ra.detach(), "degenerate alpha")
