@@ -20,6 +20,7 @@
  *                                  (street_gaussian_renderer.py:233-238, :256-266)
  *   sc_photometric_fwd/bwd     loss_utils.l1_loss + ssim       street_gaussian/utils/loss_utils.py:21-38, :96-131,
  *                                                              combined as in train.py:183-186
+ *   sc_compact_rows            prune_optimizer / prune_points  street_gaussian/models/gaussian_model.py:363-382, :416-431
  *   sc_densification_stats     set_max_radii2D + add_densification_stats
  *                                                              street_gaussian/models/street_gaussian_model.py:486-519
  *
@@ -233,6 +234,19 @@ int sc_densification_stats(int64_t N, const float* means2d_absgrad /*[N,2]*/, co
                            const uint8_t* visibility /*[N]*/, const float* radii /*[N]*/, int width, int height,
                            float* xyz_gradient_accum /*[N,2]*/, float* denom /*[N]*/, float* max_radii2D /*[N]*/,
                            void* stream);
+
+/* N4 (prune / clone / split half): order-preserving compaction of up to SC_COMPACT_MAX_ARRAYS
+ * row-major fp32 arrays that share one keep mask — parameters, Adam exp_avg / exp_avg_sq and the
+ * densification statistics of every attribute in ONE launch
+ * (street_gaussian/models/gaussian_model.py:363-382 prune_optimizer, :416-431 prune_points; the same
+ * gather serves the `[selected_pts_mask]` selections of densify_and_clone / densify_and_split).
+ * keep[N] u8 / bool; dest_index[N] i64 = exclusive prefix sum of keep (sc_exclusive_scan_i32);
+ * src / dst / row_floats are HOST arrays of n_arrays entries (device pointers inside);
+ * dst[a] must hold sum(keep) rows of row_floats[a] floats. */
+#define SC_COMPACT_MAX_ARRAYS 32
+int sc_compact_rows(int64_t N, const uint8_t* keep, const int64_t* dest_index, int n_arrays,
+                    const float* const* host_src, float* const* host_dst, const int* host_row_floats,
+                    void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

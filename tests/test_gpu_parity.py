@@ -838,3 +838,36 @@ def test_renderer_degenerate_inputs(S, dev, case, fused):
                                                    W, H, deg)[:2]
     assert_image_close(out["render_colors"].cpu(), want_rc.detach(), "degenerate render")
     assert_image_close(out["render_alphas"].cpu(), want_ra.detach(), "degenerate alpha")
+
+
+# ------------------------------------------------------------------------ prune / select compaction (N4)
+def test_prune_state_vs_reference_golden(S, dev):
+    """parameters, Adam moments and statistics after the reference's own prune_points == one compaction launch"""
+    from street_crafter_b200.compaction import prune_state
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "prune_points.npz"))
+    names = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation", "semantic")
+    stats = ("xyz_gradient_accum", "denom", "max_radii2D")
+    d = lambda k: torch.from_numpy(z[k]).to(dev)
+    keep = ~d("mask")
+    p, m, v, st = prune_state(keep, {k: d(f"in_{k}") for k in names}, {k: d(f"in_m_{k}") for k in names},
+                              {k: d(f"in_v_{k}") for k in names}, {k: d(f"in_{k}") for k in stats})
+    for k in names:
+        for got, key in ((p[k], f"out_{k}"), (m[k], f"out_m_{k}"), (v[k], f"out_v_{k}")):
+            assert got.shape == z[key].shape and torch.equal(got.cpu(), torch.from_numpy(z[key])), key
+    for k in stats:
+        assert torch.equal(st[k].cpu(), torch.from_numpy(z[f"out_{k}"])), k
+
+
+@pytest.mark.parametrize("N,frac", [(0, 0.5), (1, 1.0), (1, 0.0), (4097, 0.0), (4097, 1.0), (300001, 0.37), (2_000_000, 0.9)])
+def test_compact_rows_matches_boolean_indexing(S, dev, N, frac):
+    """bit-exact against t[keep] for ragged row widths, empty / full masks and the cfg2 Gaussian count"""
+    from street_crafter_b200.compaction import compact_rows
+    g = torch.Generator().manual_seed(N + 1)
+    keep = (torch.rand(N, generator=g) < frac).to(dev)
+    ts = [torch.randn((N,) + s, generator=g).to(dev) for s in ((3,), (4,), (), (16, 3), (1,), (2,))]
+    if N >= 1_000_000:
+        ts = ts + [t.clone() for t in ts] + [t.clone() for t in ts]       # params + two Adam moments: 18 arrays
+    out = compact_rows(keep, ts)
+    assert len(out) == len(ts)
+    for o, t in zip(out, ts):
+        assert o.shape == t[keep].shape and torch.equal(o, t[keep])

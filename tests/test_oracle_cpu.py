@@ -301,3 +301,22 @@ def test_densify_oracle_matches_reference_golden():
     # Gaussians outside the visibility filter are untouched
     inv = ~t("vis")
     assert torch.equal(acc[inv], t("accum_in")[inv]) and torch.equal(den[inv], t("denom_in")[inv])
+
+
+PRUNE_NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation", "semantic")
+PRUNE_STATS = ("xyz_gradient_accum", "denom", "max_radii2D")
+
+
+def test_prune_oracle_matches_reference_golden():
+    """oracle/prune_torch.py against vectors produced by EXECUTING the reference's prune_optimizer /
+    prune_points on a real Adam optimizer (tools/make_golden_prune.py)"""
+    import numpy as np
+    from oracle.prune_torch import prune_points
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "prune_points.npz"))
+    t = lambda k: torch.from_numpy(z[k])
+    p, m, v, st = prune_points(t("mask"), {k: t(f"in_{k}") for k in PRUNE_NAMES}, {k: t(f"in_m_{k}") for k in PRUNE_NAMES},
+                               {k: t(f"in_v_{k}") for k in PRUNE_NAMES}, {k: t(f"in_{k}") for k in PRUNE_STATS})
+    for k in PRUNE_NAMES:
+        assert torch.equal(p[k], t(f"out_{k}")) and torch.equal(m[k], t(f"out_m_{k}")) and torch.equal(v[k], t(f"out_v_{k}")), k
+    for k in PRUNE_STATS:
+        assert torch.equal(st[k], t(f"out_{k}")), k
