@@ -485,9 +485,9 @@ def run_ours(args):
         roofline = {"kernel": "rasterize_bwd_kernel<4>", "bound": "fp32", "achieved": ach_bwd,
                     "peak": fp32_peak, "unit": "TFLOP/s", "frac": (ach_bwd / fp32_peak) if ach_bwd else None,
                     # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this
-                    # workload (ncu --set full capture, profiles/r01z_ncu_summary.txt): the kernel is
+                    # workload (ncu --set full capture, profiles/r01_final_ncu_summary.txt): the kernel is
                     # compute-bound, its HBM traffic is ~2 % of peak
-                    "traffic": 88.60e6, "traffic_source": "profiles/r01z_ncu_summary.txt",
+                    "traffic": 88.50e6, "traffic_source": "profiles/r01_final_ncu_summary.txt",
                     "peak_source": "sc_probe_fp32 FMA probe run in this process (no tensor cores on this path)",
                     "ms_per_launch": t_bwd, "alg_flop_per_launch": flop_bwd / n_views,
                     "visited_pairs_per_launch": visited / n_views,
