@@ -27,6 +27,8 @@
 #include <stdlib.h>
 #include "common.cuh"
 
+#include <type_traits>
+
 namespace {
 
 constexpr int TILE = 16;
@@ -38,6 +40,7 @@ constexpr unsigned FULL = 0xffffffffu;
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr float LOG2_ALPHA_FLOOR = -7.994353436858858f;  // log2(1/255)
+constexpr float LO_NOCAP = -0.0016f;  // log2(opacity) below this (opacity < 0.9989): alpha stays below SC_ALPHA_CAP = 0.999
 constexpr float CULL_MARGIN = 1e-3f;  // slack of the conservative cull (log2 units of alpha)
 
 constexpr int NRED = 13;         // reduced values per (tile, Gaussian) in the backward pass
@@ -280,6 +283,8 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             load_colors<CH>(sm.C, t, col);
             // two halves of 4 row pairs: one warp-uniform branch each, the 4 pixel chains inside
             // are branch-free so that they interleave
+            auto halves = [&](auto nocap_tag) {
+            constexpr bool NOCAP = decltype(nocap_tag)::value;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if ((B.rmask >> (4 * h)) & 0xfu) {
@@ -297,7 +302,9 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const int r = 4 * h + q;
-                            a[q] = ok[q] ? fminf(SC_ALPHA_CAP, exp2f(B.lo - s2[q])) : 0.f;
+                            // (an opacity below the cap can never reach it: ok implies s2 >= 0; warp-uniform)
+                            const float au = exp2f(B.lo - s2[q]);
+                            a[q] = ok[q] ? (NOCAP ? au : fminf(SC_ALPHA_CAP, au)) : 0.f;
                             next_T[q] = fmaf(-a[q], T[r], T[r]);
                             // a == 0 leaves T (> 1e-4 for every pixel, live or not) unchanged
                             any_stop |= next_T[q] <= SC_T_STOP;
@@ -341,6 +348,8 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                     }
                 }
             }
+            };
+            if (B.lo <= LO_NOCAP) halves(std::true_type{}); else halves(std::false_type{});
         }
         __syncwarp();
     }
@@ -548,6 +557,11 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             bool any_entry = false;
             // two halves of 4 row pairs: one warp-uniform branch each; the 4 pixel chains inside
             // are branch-free so that they interleave
+            // A Gaussian whose opacity is below the cap can never reach it (ok implies s2 >= 0, so
+            // alpha <= opacity): its chains drop the clamp and the "not clamped" predicate.  The
+            // choice is per Gaussian, i.e. warp-uniform; both instances are the same code otherwise.
+            auto halves = [&](auto nocap_tag) {
+            constexpr bool NOCAP = decltype(nocap_tag)::value;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 if ((B.rmask >> (4 * h)) & 0xfu) {
@@ -568,7 +582,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                             // a dead pixel has dy = -inf: keep it out of the moment sums
                             const float dy = ok[q] ? dyq[q] : 0.f;
                             const float au = exp2f(B.lo - s2[q]);
-                            const float a = ok[q] ? fminf(SC_ALPHA_CAP, au) : 0.f;
+                            const float a = ok[q] ? (NOCAP ? au : fminf(SC_ALPHA_CAP, au)) : 0.f;
                             const float ra = __fdividef(1.0f, 1.0f - a);  // MUFU.RCP; exactly 1 when the pair is not used
                             T[r] *= ra;
                             const float fac = a * T[r];
@@ -588,7 +602,8 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                             }
                             const float v_alpha = d * T[r] - R[r] * ra;
                             R[r] = fmaf(d, fac, R[r]);
-                            const float w = (ok[q] && au <= SC_ALPHA_CAP) ? -au * v_alpha : 0.f;
+                            // a clamped alpha passes no gradient; unclamped: -a * v_alpha is already 0 when !ok
+                            const float w = NOCAP ? -a * v_alpha : ((ok[q] && au <= SC_ALPHA_CAP) ? -au * v_alpha : 0.f);
                             const float wdy = w * dy;
                             sw += w;
                             swy += wdy;
@@ -599,6 +614,8 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                     }
                 }
             }
+            };
+            if (B.lo <= LO_NOCAP) halves(std::true_type{}); else halves(std::false_type{});
             if (!any_entry) continue;  // warp-uniform
             float v[NRED];
 #pragma unroll
