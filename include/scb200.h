@@ -23,6 +23,7 @@
  *   sc_compact_rows            prune_optimizer / prune_points  street_gaussian/models/gaussian_model.py:363-382, :416-431
  *   sc_densification_stats     set_max_radii2D + add_densification_stats
  *                                                              street_gaussian/models/street_gaussian_model.py:486-519
+ *   sc_densify_classify/move   densify_and_prune (clone + split + prune)  street_gaussian/models/gaussian_model.py:433-551
  *
  * Conventions: all pointers are DEVICE pointers unless named host_*; row-major contiguous
  * fp32 / int32 / int64 arrays; `stream` is a cudaStream_t passed as void*; nothing here
@@ -247,6 +248,36 @@ int sc_densification_stats(int64_t N, const float* means2d_absgrad /*[N,2]*/, co
 int sc_compact_rows(int64_t N, const uint8_t* keep, const int64_t* dest_index, int n_arrays,
                     const float* const* host_src, float* const* host_dst, const int* host_row_floats,
                     void* stream);
+
+/* N4 (clone / split half): the whole densification cycle of
+ * street_gaussian/models/gaussian_model.py:521-551 densify_and_prune (densify_and_clone :493-519,
+ * densify_and_split :452-491, cat_optimizer :384-408, prune_points :416-431) as classify -> scan -> move.
+ * sc_densify_classify writes four 0/1 segments flags[4N] = [stay | clone | child | split-selected]
+ * (stay: kept original; clone: surviving copy; child: split row whose children survive the final prune) and
+ * the number of clone-SELECTED rows (for the reference's scalar_dict) to *n_clone_selected (device).
+ * Thresholds are the float32 values the reference compares against: clone_max_scale = percent_dense * extent,
+ * split_min_scale = float32(percent_dense) * float32(extent), big_ws_scale = extent * percent_big_ws (used when
+ * prune_big != 0, i.e. max_screen_size is set), split_shrink = 0.8 * n_copies.
+ * The caller runs sc_exclusive_scan_i32 over the 4N flags (dest_index[4N+1]) and reads the segment totals;
+ * sc_densify_move then writes, for every array of the table, the output rows
+ * [stay | clones | children of copy 0 | children of copy 1 ...] (n_stay + n_clone + n_copies * n_child rows):
+ * kind PARAM rows are copied everywhere, MOMENT rows are copied to `stay` rows and zero elsewhere, the XYZ
+ * array gets R(rotation) (noise * exp(scaling)) + xyz for children, the SCALING array log(exp(s) / split_shrink).
+ * noise[n_copies * n_split, 3] is the standard-normal draw of torch.normal (row c * n_split + k belongs to copy
+ * c of the k-th split-selected row).  Table arrays are HOST arrays as in sc_compact_rows. */
+#define SC_DENSIFY_PARAM 0
+#define SC_DENSIFY_MOMENT 1
+#define SC_DENSIFY_XYZ 2
+#define SC_DENSIFY_SCALING 3
+int sc_densify_classify(int64_t N, const float* xyz_gradient_accum /*[N,2]*/, const float* denom /*[N]*/,
+                        const float* scaling /*[N,3]*/, const float* opacity /*[N]*/, float max_grad,
+                        float clone_max_scale, float split_min_scale, float min_opacity, int prune_big,
+                        float big_ws_scale, float split_shrink, int32_t* flags /*[4N]*/,
+                        int32_t* n_clone_selected /*[1]*/, void* stream);
+int sc_densify_move(int64_t N, const int32_t* flags /*[4N]*/, const int64_t* dest_index /*[4N+1]*/,
+                    int64_t n_child, int64_t n_split, int n_copies, const float* noise, const float* scaling,
+                    const float* rotation, float split_shrink, int n_arrays, const float* const* host_src,
+                    float* const* host_dst, const int* host_row_floats, const int* host_kinds, void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

@@ -30,6 +30,7 @@ SOURCES = {
     "knn.cu": [],
     "loss.cu": [],
     "densify.cu": [],
+    "densify_cycle.cu": [],
     "compact.cu": [],
     "probe.cu": ["--use_fast_math"],
 }

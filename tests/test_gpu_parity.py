@@ -871,3 +871,79 @@ def test_compact_rows_matches_boolean_indexing(S, dev, N, frac):
     assert len(out) == len(ts)
     for o, t in zip(out, ts):
         assert o.shape == t[keep].shape and torch.equal(o, t[keep])
+
+
+# ------------------------------------------------------------------------ densification cycle (N4, clone / split)
+DENSIFY_NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation", "semantic")
+
+
+def _assert_cycle_equal(got, want, tag, exact_all=False):
+    """got / want: (params, exp_avg, exp_avg_sq).  Copied rows are bit-exact; the split children's xyz (free
+    summation order of the 3x3 product) and log-scales (exp / log of two math libraries) within 2e-6."""
+    for gi, wi, what in zip(got, want, ("param", "exp_avg", "exp_avg_sq")):
+        for k in wi:
+            g, w = gi[k].cpu(), wi[k].cpu()
+            assert g.shape == w.shape, (tag, what, k, g.shape, w.shape)
+            if what == "param" and k in ("xyz", "scaling") and not exact_all:
+                assert (g - w).abs().max() <= 2e-6 * max(1.0, float(w.abs().max())), (tag, k, float((g - w).abs().max()))
+            else:
+                assert torch.equal(g, w), (tag, what, k)
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_densify_cycle_vs_reference_golden(S, dev, tag):
+    """parameters, Adam moments, statistics and scalar_dict after the reference's own densify_and_prune (clone +
+    split + prune on a real Adam optimizer, tests/golden/densify_cycle.npz) == classify + scan + one move launch"""
+    from street_crafter_b200.densify import densify_and_prune
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "densify_cycle.npz"))
+    d = lambda k: torch.from_numpy(z[f"{tag}_{k}"]).to(dev)
+    max_grad, min_opacity, extent, mss, pd, pbw = [float(x) for x in z[f"{tag}_cfg"]]
+    p, m, v, st, sc = densify_and_prune({k: d(f"in_{k}") for k in DENSIFY_NAMES}, {k: d(f"in_m_{k}") for k in DENSIFY_NAMES},
+                                        {k: d(f"in_v_{k}") for k in DENSIFY_NAMES}, d("in_xyz_gradient_accum"),
+                                        d("in_denom"), max_grad, min_opacity, extent, mss or None, pd, pbw,
+                                        noise=d("noise"))
+    assert [sc[k] for k in ("points_total", "points_clone", "points_split", "points_pruned")] == z[f"{tag}_scalars"].tolist()
+    want = tuple({k: torch.from_numpy(z[f"{tag}_out_{pre}{k}"]) for k in DENSIFY_NAMES} for pre in ("", "m_", "v_"))
+    _assert_cycle_equal((p, m, v), want, tag)
+    for k in ("xyz_gradient_accum", "denom", "max_radii2D"):
+        assert st[k].shape == z[f"{tag}_out_{k}"].shape and not st[k].any(), k
+
+
+@pytest.mark.parametrize("N,mss", [(1, 20), (31, None), (4097, 20), (300_001, 20), (2_000_000, 20)])
+def test_densify_cycle_vs_oracle(S, dev, N, mss):
+    """ragged sizes up to the cfg2 Gaussian count against the pinned oracle run on the same device tensors (torch's
+    own exp / log / sigmoid kernels), same noise; row counts and every copied value bit-exact"""
+    from oracle.densify_cycle_torch import densify_and_prune as oracle_cycle
+    from street_crafter_b200.densify import densify_and_prune
+    g = torch.Generator().manual_seed(N)
+    extent, max_grad, min_op = 20.0, 0.0002, 0.005
+    shapes = {"xyz": (3,), "f_dc": (1, 3), "f_rest": (15, 3), "opacity": (1,), "scaling": (3,), "rotation": (4,)}
+    params = {k: torch.randn((N,) + s, generator=g).to(dev) for k, s in shapes.items()}
+    params["scaling"] = (math.log(0.01 * extent) + 0.8 * torch.randn(N, 3, generator=g)).to(dev)
+    params["opacity"] = (2.5 * torch.randn(N, 1, generator=g) - 1.0).to(dev)
+    m = {k: torch.randn((N,) + s, generator=g).to(dev) for k, s in shapes.items()}
+    v = {k: torch.rand((N,) + s, generator=g).to(dev) for k, s in shapes.items() if k != "f_rest"}   # one group without exp_avg_sq
+    denom = torch.randint(0, 4, (N, 1), generator=g).float().to(dev)
+    accum = (torch.rand(N, 2, generator=g) * 2.5 * max_grad).to(dev) * denom.clamp(min=1)
+    p1, m1, v1, st, sc = densify_and_prune(params, m, v, accum, denom, max_grad, min_op, extent, mss,
+                                           generator=torch.Generator(device=dev).manual_seed(7))
+    noise = torch.randn((2 * sc["points_split"], 3), device=dev, generator=torch.Generator(device=dev).manual_seed(7))
+    p0, m0, v0, sc0 = oracle_cycle(params, m, {**v, "f_rest": torch.zeros_like(m["f_rest"])}, accum, denom, noise,
+                                   max_grad, min_op, extent, mss)
+    v0.pop("f_rest")
+    assert sc == sc0, (sc, sc0)
+    _assert_cycle_equal((p1, m1, v1), (p0, m0, v0), N)
+    n = p1["xyz"].shape[0]
+    assert st["xyz_gradient_accum"].shape == (n, 2) and st["denom"].shape == (n, 1) and st["max_radii2D"].shape == (n,)
+    if N >= 4097:
+        assert sc["points_clone"] > 0 and sc["points_split"] > 0 and sc["points_pruned"] > 0
+
+
+def test_densify_cycle_empty_and_cpu_raises(S, dev):
+    from street_crafter_b200.densify import densify_and_prune
+    shapes = {"xyz": (3,), "opacity": (1,), "scaling": (3,), "rotation": (4,)}
+    p = {k: torch.zeros((0,) + s, device=dev) for k, s in shapes.items()}
+    out = densify_and_prune(p, {}, {}, torch.zeros(0, 2, device=dev), torch.zeros(0, 1, device=dev), 2e-4, 5e-3, 10.0, 20)
+    assert out[0]["xyz"].shape == (0, 3) and out[4]["points_total"] == 0
+    with pytest.raises(RuntimeError):
+        densify_and_prune({k: t.cpu() for k, t in p.items()}, {}, {}, torch.zeros(0, 2), torch.zeros(0, 1), 2e-4, 5e-3, 10.0, 20)

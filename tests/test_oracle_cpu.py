@@ -320,3 +320,31 @@ def test_prune_oracle_matches_reference_golden():
         assert torch.equal(p[k], t(f"out_{k}")) and torch.equal(m[k], t(f"out_m_{k}")) and torch.equal(v[k], t(f"out_v_{k}")), k
     for k in PRUNE_STATS:
         assert torch.equal(st[k], t(f"out_{k}")), k
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_densify_cycle_oracle_matches_reference_golden(tag):
+    """oracle/densify_cycle_torch.py against vectors produced by EXECUTING the reference's densify_and_prune
+    (clone + split + prune, with cat_optimizer / prune_optimizer on a real Adam optimizer;
+    tools/make_golden_densify_cycle.py).  Case b has max_screen_size=None (no big-point pruning)."""
+    import numpy as np
+    from oracle.densify_cycle_torch import densify_and_prune, n_split
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "densify_cycle.npz"))
+    t = lambda k: torch.from_numpy(z[f"{tag}_{k}"])
+    max_grad, min_opacity, extent, mss, pd, pbw = [float(x) for x in z[f"{tag}_cfg"]]
+    params = {k: t(f"in_{k}") for k in PRUNE_NAMES}
+    assert 2 * n_split(params, t("in_xyz_gradient_accum"), t("in_denom"), max_grad, extent, pd) == t("noise").shape[0]
+    p, m, v, sc = densify_and_prune(params, {k: t(f"in_m_{k}") for k in PRUNE_NAMES},
+                                    {k: t(f"in_v_{k}") for k in PRUNE_NAMES}, t("in_xyz_gradient_accum"),
+                                    t("in_denom"), t("noise"), max_grad, min_opacity, extent, mss or None, pd, pbw)
+    assert [sc[k] for k in ("points_total", "points_clone", "points_split", "points_pruned")] == z[f"{tag}_scalars"].tolist()
+    for k in PRUNE_NAMES:
+        assert p[k].shape == t(f"out_{k}").shape, k
+        if k == "xyz":      # the only arithmetic with a free summation order (bmm)
+            assert (p[k] - t(f"out_{k}")).abs().max() < 1e-6
+        else:
+            assert torch.equal(p[k], t(f"out_{k}")), k
+        assert torch.equal(m[k], t(f"out_m_{k}")) and torch.equal(v[k], t(f"out_v_{k}")), k
+    n = p["xyz"].shape[0]
+    for k in PRUNE_STATS:
+        assert z[f"{tag}_out_{k}"].shape[0] == n and not z[f"{tag}_out_{k}"].any(), k
