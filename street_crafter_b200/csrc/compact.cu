@@ -19,28 +19,51 @@ struct RowTable {
     int n;
 };
 
-// One flat grid over all arrays: a CTA finds its array in the (<= 32 entry) prefix table; a thread moves one
-// 4-float piece of one row (a float4 when the row width and both bases allow it).
+// One flat grid over all arrays: a CTA finds its array in the (<= 32 entry) prefix table.  A thread moves one float4
+// of one row when the row width and both bases allow it (width < 0 in the table marks the other case), else one
+// float per access with consecutive lanes on consecutive floats of the flattened array — ragged widths (xyz 3,
+// f_rest 45) still move whole sectors, where 4-float strided pieces per thread made the L2 fill every partially
+// written sector from DRAM.
+constexpr int COMPACT_EPT = 4;   // element mode: floats per thread (a CTA covers 1024 consecutive floats)
+
 __global__ void __launch_bounds__(256)
 compact_rows_kernel(int64_t N, const uint8_t* __restrict__ keep, const int64_t* __restrict__ dest, RowTable T) {
     int a = 0;
     while (a < T.n - 1 && blockIdx.x >= T.block_end[a]) ++a;
     const unsigned b0 = a ? T.block_end[a - 1] : 0u;
-    const int w = T.width[a];
-    const int pieces = (w + 3) >> 2;
-    const int64_t idx = (int64_t)(blockIdx.x - b0) * 256 + threadIdx.x;
-    const int64_t row = idx / pieces;
-    if (row >= N || !keep[row]) return;
-    const int c = (int)(idx - row * pieces) * 4;
-    const float* s = T.src[a] + row * w + c;
-    float* d = T.dst[a] + __ldg(dest + row) * w + c;
-    if (((w & 3) == 0) && ((((uintptr_t)T.src[a]) | ((uintptr_t)T.dst[a])) & 15) == 0) {
-        *reinterpret_cast<float4*>(d) = __ldg(reinterpret_cast<const float4*>(s));
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            if (c + k < w) d[k] = __ldg(s + k);
+    const float* __restrict__ src = T.src[a];
+    float* __restrict__ dst = T.dst[a];
+    if (T.width[a] > 0) {
+        const int w = T.width[a], pieces = w >> 2;
+        const int64_t idx = (int64_t)(blockIdx.x - b0) * 256 + threadIdx.x;
+        const int64_t row = idx / pieces;
+        if (row >= N || !keep[row]) return;
+        const int c = (int)(idx - row * pieces) * 4;
+        *reinterpret_cast<float4*>(dst + __ldg(dest + row) * w + c) =
+            __ldg(reinterpret_cast<const float4*>(src + row * w + c));
+        return;
     }
+    const int w = -T.width[a];
+    const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * COMPACT_EPT);
+    const int64_t row0 = base / w, total = N * w;
+    const int rem0 = (int)(base - row0 * w);
+    // all loads of the four elements are independent of each other (the source is read whether or not the row is
+    // kept: ~all rows are) and issue before the first store
+    float v[COMPACT_EPT];
+    int64_t shift[COMPACT_EPT];
+    bool k[COMPACT_EPT];
+#pragma unroll
+    for (int j = 0; j < COMPACT_EPT; ++j) {
+        const int64_t e = base + j * 256 + threadIdx.x;
+        const bool in = e < total;
+        const int64_t row = row0 + (rem0 + j * 256 + (int)threadIdx.x) / w;
+        v[j] = in ? __ldg(src + e) : 0.f;
+        k[j] = in && keep[row];
+        shift[j] = in ? (__ldg(dest + row) - row) * w : 0;
+    }
+#pragma unroll
+    for (int j = 0; j < COMPACT_EPT; ++j)
+        if (k[j]) dst[base + j * 256 + threadIdx.x + shift[j]] = v[j];
 }
 
 }  // namespace
@@ -56,8 +79,10 @@ extern "C" int sc_compact_rows(int64_t N, const uint8_t* keep, const int64_t* de
     for (int a = 0; a < SC_COMPACT_MAX_ARRAYS; ++a) {
         if (a < n_arrays) {
             SC_CHECK_ARG(src[a] && dst[a] && row_floats[a] > 0, "array table entry");
-            T.src[a] = src[a]; T.dst[a] = dst[a]; T.width[a] = row_floats[a];
-            blocks += sc_div_up(N * ((row_floats[a] + 3) / 4), 256);
+            const int w = row_floats[a];
+            const bool vec = (w & 3) == 0 && ((((uintptr_t)src[a]) | ((uintptr_t)dst[a])) & 15) == 0;
+            T.src[a] = src[a]; T.dst[a] = dst[a]; T.width[a] = vec ? w : -w;
+            blocks += vec ? sc_div_up(N * (w / 4), 256) : sc_div_up(N * w, 256 * COMPACT_EPT);
             SC_CHECK_ARG(blocks < (1ll << 31), "N * row width");
         } else {
             T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1;

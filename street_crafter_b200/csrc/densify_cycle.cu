@@ -60,82 +60,108 @@ struct MoveTable {
     const float* src[SC_COMPACT_MAX_ARRAYS];
     float* dst[SC_COMPACT_MAX_ARRAYS];
     int width[SC_COMPACT_MAX_ARRAYS];
-    int kind[SC_COMPACT_MAX_ARRAYS];
+    int kind[SC_COMPACT_MAX_ARRAYS];        // SC_DENSIFY_* | MOVE_VEC
     unsigned block_end[SC_COMPACT_MAX_ARRAYS];
     int n;
 };
+constexpr int MOVE_VEC = 16;        // row width a multiple of 4 floats and both bases 16-byte aligned
+constexpr int MOVE_EPT = 4;         // element mode: floats per thread (a CTA covers 1024 consecutive floats)
 
-__device__ __forceinline__ void store_piece(float* d, const float v[4], int c, int w, bool vec) {
-    if (vec) {
-        *reinterpret_cast<float4*>(d) = make_float4(v[0], v[1], v[2], v[3]);
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            if (c + k < w) d[k] = v[k];
-    }
+struct SplitCtx {
+    int64_t n_child, n_split;
+    int n_copies;
+    const float* noise;
+    const float* scaling;
+    const float* rotation;
+    float shrink;
+};
+
+// c-th child value of one xyz component (row k of R(q) times (z * std), plus the parent's component)
+__device__ __forceinline__ float child_xyz(const SplitCtx& S, int64_t row, int64_t rank, int cp, int k, float v) {
+    const float qw = __ldg(S.rotation + 4 * row), qx = __ldg(S.rotation + 4 * row + 1),
+                qy = __ldg(S.rotation + 4 * row + 2), qz = __ldg(S.rotation + 4 * row + 3);
+    const float nrm = sqrtf(qw * qw + qx * qx + qy * qy + qz * qz);                  // general_utils.py:126-128
+    const float r = qw / nrm, x = qx / nrm, y = qy / nrm, z = qz / nrm;
+    float R0, R1, R2;                                                                // :137-145
+    if (k == 0) { R0 = 1.f - 2.f * (y * y + z * z); R1 = 2.f * (x * y - r * z); R2 = 2.f * (x * z + r * y); }
+    else if (k == 1) { R0 = 2.f * (x * y + r * z); R1 = 1.f - 2.f * (x * x + z * z); R2 = 2.f * (y * z - r * x); }
+    else { R0 = 2.f * (x * z - r * y); R1 = 2.f * (y * z + r * x); R2 = 1.f - 2.f * (x * x + y * y); }
+    const float* zn = S.noise + 3 * (cp * S.n_split + rank);
+    const float p0 = __ldg(zn) * expf(__ldg(S.scaling + 3 * row)),                   // gaussian_model.py:469-470
+                p1 = __ldg(zn + 1) * expf(__ldg(S.scaling + 3 * row + 1)),
+                p2 = __ldg(zn + 2) * expf(__ldg(S.scaling + 3 * row + 2));
+    return (R0 * p0 + R1 * p1 + R2 * p2) + v;                                        // :472
 }
 
-// One flat grid over all arrays (as compact_rows_kernel): a thread owns one 4-float piece of one INPUT row and
-// writes it to every output row that descends from it.
+// One flat grid over all arrays (as compact_rows_kernel).  Every input float is read once, fully coalesced, and
+// written to every output row that descends from its row: a float4 per thread when the row width allows it,
+// otherwise one float per thread and access (consecutive lanes = consecutive floats of the flattened array, so
+// ragged widths such as f_rest's 45 floats still move whole sectors; strided 4-float pieces per thread made
+// the L2 fill every partially written sector from DRAM and doubled the read traffic).
 __global__ void __launch_bounds__(256)
-densify_move_kernel(int64_t N, const int32_t* __restrict__ flags, const int64_t* __restrict__ dest, int64_t n_child,
-                    int64_t n_split, int n_copies, const float* __restrict__ noise, const float* __restrict__ scaling,
-                    const float* __restrict__ rotation, float split_shrink, MoveTable T) {
+densify_move_kernel(int64_t N, const int32_t* __restrict__ flags, const int64_t* __restrict__ dest, SplitCtx S,
+                    MoveTable T) {
     int a = 0;
     while (a < T.n - 1 && blockIdx.x >= T.block_end[a]) ++a;
     const unsigned b0 = a ? T.block_end[a - 1] : 0u;
-    const int w = T.width[a], kind = T.kind[a];
-    const int pieces = (w + 3) >> 2;
-    const int64_t idx = (int64_t)(blockIdx.x - b0) * 256 + threadIdx.x;
-    const int64_t row = idx / pieces;
-    if (row >= N) return;
-    const bool stay = flags[row], clone = flags[N + row], child = flags[2 * N + row];
-    if (!stay && !clone && !child) return;
-    const int c = (int)(idx - row * pieces) * 4;
-    const bool vec = ((w & 3) == 0) && ((((uintptr_t)T.src[a]) | ((uintptr_t)T.dst[a])) & 15) == 0;
-    const float* s = T.src[a] + row * w + c;
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
-    if (vec) {
-        const float4 t = __ldg(reinterpret_cast<const float4*>(s));
-        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            if (c + k < w) v[k] = __ldg(s + k);
-    }
-    const float zero[4] = {0.f, 0.f, 0.f, 0.f};
+    const int w = T.width[a], kind = T.kind[a] & 15;
     const bool moment = kind == SC_DENSIFY_MOMENT;
-    if (stay) store_piece(T.dst[a] + __ldg(dest + row) * w + c, v, c, w, vec);
-    if (clone) store_piece(T.dst[a] + __ldg(dest + N + row) * w + c, moment ? zero : v, c, w, vec);
-    if (child) {
-        const int64_t d0 = __ldg(dest + 2 * N + row);
-        const int64_t rank = __ldg(dest + 3 * N + row) - __ldg(dest + 3 * N);   // among the split-selected rows
-        float R[9], sd[3];
-        if (kind == SC_DENSIFY_XYZ) {   // width 3: this thread holds the whole row
-            const float qw = __ldg(rotation + 4 * row), qx = __ldg(rotation + 4 * row + 1),
-                        qy = __ldg(rotation + 4 * row + 2), qz = __ldg(rotation + 4 * row + 3);
-            const float nrm = sqrtf(qw * qw + qx * qx + qy * qy + qz * qz);      // general_utils.py:126-128
-            const float r = qw / nrm, x = qx / nrm, y = qy / nrm, z = qz / nrm;
-            R[0] = 1.f - 2.f * (y * y + z * z); R[1] = 2.f * (x * y - r * z); R[2] = 2.f * (x * z + r * y);
-            R[3] = 2.f * (x * y + r * z); R[4] = 1.f - 2.f * (x * x + z * z); R[5] = 2.f * (y * z - r * x);
-            R[6] = 2.f * (x * z - r * y); R[7] = 2.f * (y * z + r * x); R[8] = 1.f - 2.f * (x * x + y * y);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) sd[k] = expf(__ldg(scaling + 3 * row + k));
+    const float* __restrict__ src = T.src[a];
+    float* __restrict__ dst = T.dst[a];
+    if (T.kind[a] & MOVE_VEC) {     // PARAM / MOMENT only
+        const int pieces = w >> 2;
+        const int64_t idx = (int64_t)(blockIdx.x - b0) * 256 + threadIdx.x;
+        const int64_t row = idx / pieces;
+        if (row >= N) return;
+        const bool stay = flags[row], clone = flags[N + row], child = flags[2 * N + row];
+        if (!stay && !clone && !child) return;
+        const int c = (int)(idx - row * pieces) * 4;
+        const float4 v = __ldg(reinterpret_cast<const float4*>(src + row * w + c));
+        const float4 o = moment ? make_float4(0.f, 0.f, 0.f, 0.f) : v;
+        if (stay) *reinterpret_cast<float4*>(dst + __ldg(dest + row) * w + c) = v;
+        if (clone) *reinterpret_cast<float4*>(dst + __ldg(dest + N + row) * w + c) = o;
+        if (child) {
+            const int64_t d0 = __ldg(dest + 2 * N + row);
+            for (int cp = 0; cp < S.n_copies; ++cp)
+                *reinterpret_cast<float4*>(dst + (d0 + cp * S.n_child) * w + c) = o;
         }
-        for (int cp = 0; cp < n_copies; ++cp) {
-            float o[4] = {v[0], v[1], v[2], v[3]};
-            if (moment) {
-                o[0] = o[1] = o[2] = o[3] = 0.f;
-            } else if (kind == SC_DENSIFY_XYZ) {
-                const float* zn = noise + 3 * (cp * n_split + rank);
-                const float p0 = __ldg(zn) * sd[0], p1 = __ldg(zn + 1) * sd[1], p2 = __ldg(zn + 2) * sd[2];  // :469-470
+        return;
+    }
+    const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * MOVE_EPT);
+    const int64_t row0 = base / w;
+    const int rem0 = (int)(base - row0 * w);
+    const int64_t total = N * w;
+    // all loads of the four elements are independent of each other (the source is read whether or not its row
+    // survives: ~all rows do) and issue before the first store
+    float v[MOVE_EPT];
+    int64_t row[MOVE_EPT];
+    int col[MOVE_EPT], f[MOVE_EPT];
 #pragma unroll
-                for (int k = 0; k < 3; ++k) o[k] = (R[3 * k] * p0 + R[3 * k + 1] * p1 + R[3 * k + 2] * p2) + v[k];  // :472
-            } else if (kind == SC_DENSIFY_SCALING) {
+    for (int j = 0; j < MOVE_EPT; ++j) {
+        const int64_t e = base + j * 256 + threadIdx.x;
+        const bool in = e < total;
+        const int dr = (rem0 + j * 256 + (int)threadIdx.x) / w;
+        row[j] = row0 + dr;
+        col[j] = rem0 + j * 256 + (int)threadIdx.x - dr * w;
+        v[j] = in ? __ldg(src + e) : 0.f;
+        f[j] = in ? (flags[row[j]] | (flags[N + row[j]] << 1) | (flags[2 * N + row[j]] << 2)) : 0;
+    }
 #pragma unroll
-                for (int k = 0; k < 4; ++k) o[k] = logf(expf(v[k]) / split_shrink);                                  // :473
+    for (int j = 0; j < MOVE_EPT; ++j) {
+        if (!f[j]) continue;
+        const int c = col[j];
+        const float o = moment ? 0.f : v[j];
+        if (f[j] & 1) dst[__ldg(dest + row[j]) * w + c] = v[j];
+        if (f[j] & 2) dst[__ldg(dest + N + row[j]) * w + c] = o;
+        if (f[j] & 4) {
+            const int64_t d0 = __ldg(dest + 2 * N + row[j]);
+            const int64_t rank = __ldg(dest + 3 * N + row[j]) - __ldg(dest + 3 * N);   // among the split-selected rows
+            for (int cp = 0; cp < S.n_copies; ++cp) {
+                float oc = o;
+                if (kind == SC_DENSIFY_XYZ) oc = child_xyz(S, row[j], rank, cp, c, v[j]);
+                else if (kind == SC_DENSIFY_SCALING) oc = logf(expf(v[j]) / S.shrink);                   // :473
+                dst[(d0 + cp * S.n_child) * w + c] = oc;
             }
-            store_piece(T.dst[a] + (d0 + cp * n_child) * w + c, o, c, w, vec);
         }
     }
 }
@@ -173,22 +199,22 @@ extern "C" int sc_densify_move(int64_t N, const int32_t* flags, const int64_t* d
     int64_t blocks = 0;
     for (int a = 0; a < SC_COMPACT_MAX_ARRAYS; ++a) {
         if (a < n_arrays) {
-            SC_CHECK_ARG(src[a] && dst[a] && row_floats[a] > 0, "array table entry");
-            SC_CHECK_ARG(kinds[a] >= SC_DENSIFY_PARAM && kinds[a] <= SC_DENSIFY_SCALING, "array kind");
-            if (kinds[a] == SC_DENSIFY_XYZ || kinds[a] == SC_DENSIFY_SCALING)
-                SC_CHECK_ARG(row_floats[a] == 3, "xyz / scaling rows are 3 floats");
-            if (kinds[a] == SC_DENSIFY_XYZ && n_split > 0) SC_CHECK_ARG(noise && scaling && rotation, "split inputs");
-            T.src[a] = src[a]; T.dst[a] = dst[a]; T.width[a] = row_floats[a]; T.kind[a] = kinds[a];
-            blocks += sc_div_up(N * ((row_floats[a] + 3) / 4), 256);
+            const int w = row_floats[a], k = kinds[a];
+            SC_CHECK_ARG(src[a] && dst[a] && w > 0, "array table entry");
+            SC_CHECK_ARG(k >= SC_DENSIFY_PARAM && k <= SC_DENSIFY_SCALING, "array kind");
+            if (k == SC_DENSIFY_XYZ || k == SC_DENSIFY_SCALING) SC_CHECK_ARG(w == 3, "xyz / scaling rows are 3 floats");
+            if (k == SC_DENSIFY_XYZ && n_split > 0) SC_CHECK_ARG(noise && scaling && rotation, "split inputs");
+            const bool vec = (w & 3) == 0 && ((((uintptr_t)src[a]) | ((uintptr_t)dst[a])) & 15) == 0;
+            T.src[a] = src[a]; T.dst[a] = dst[a]; T.width[a] = w; T.kind[a] = k | (vec ? MOVE_VEC : 0);
+            blocks += vec ? sc_div_up(N * (w / 4), 256) : sc_div_up(N * w, 256 * MOVE_EPT);
             SC_CHECK_ARG(blocks < (1ll << 31), "N * row width");
         } else {
             T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1; T.kind[a] = 0;
         }
         T.block_end[a] = (unsigned)blocks;
     }
-    densify_move_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(N, flags, dest_index, n_child, n_split,
-                                                                          n_copies, noise, scaling, rotation,
-                                                                          split_shrink, T);
+    SplitCtx S{n_child, n_split, n_copies, noise, scaling, rotation, split_shrink};
+    densify_move_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(N, flags, dest_index, S, T);
     SC_CHECK_LAUNCH("densify_move_kernel");
     return SC_OK;
 }

@@ -1,5 +1,6 @@
-"""Times the prune compaction on the cfg2 Gaussian set: 2 M rows of (means 3 | quats 4 | scales 3 | opacity 1 |
-SH 48) floats for the parameters and both Adam moments (15 arrays, 708 B / Gaussian), 90 % kept, against the
+"""Times the prune compaction on the cfg2 Gaussian set: 2 M rows of (xyz 3 | f_dc 1x3 | f_rest 15x3 |
+opacity 1 | scaling 3 | rotation 4) floats — the reference's own shapes, ragged widths included — for the
+parameters and both Adam moments (18 arrays, 708 B / Gaussian), 90 % kept, against the
 same prune done with torch boolean indexing (what the reference does).   python tools/compact_bench.py"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -9,7 +10,7 @@ dev = torch.device("cuda:0")
 N = 2_000_000
 g = torch.Generator().manual_seed(0)
 keep = (torch.rand(N, generator=g) < 0.9).to(dev)
-ts = [torch.randn((N,) + s, device=dev) for _ in range(3) for s in ((3,), (4,), (3,), (1,), (16, 3))]
+ts = [torch.randn((N,) + s, device=dev) for _ in range(3) for s in ((3,), (1, 3), (15, 3), (1,), (3,), (4,))]
 def t_ms(fn, reps=5):
     fn(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
