@@ -258,8 +258,9 @@ int sc_compact_rows(int64_t N, const uint8_t* keep, const int64_t* dest_index, i
  * Thresholds are the float32 values the reference compares against: clone_max_scale = percent_dense * extent,
  * split_min_scale = float32(percent_dense) * float32(extent), big_ws_scale = extent * percent_big_ws (used when
  * prune_big != 0, i.e. max_screen_size is set), split_shrink = 0.8 * n_copies.
- * The caller runs sc_exclusive_scan_i32 over the 4N flags (dest_index[4N+1]) and reads the segment totals;
- * sc_densify_move then writes, for every array of the table, the output rows
+ * The caller runs sc_exclusive_scan_i32 over the 4N flags (dest_index[4N+1]) and reads the segment totals
+ * (n_stay, n_clone, n_child, n_split); sc_densify_move (two launches: the source-row index of the appended rows
+ * into index_workspace, then the move) writes, for every array of the table, the output rows
  * [stay | clones | children of copy 0 | children of copy 1 ...] (n_stay + n_clone + n_copies * n_child rows):
  * kind PARAM rows are copied everywhere, MOMENT rows are copied to `stay` rows and zero elsewhere, the XYZ
  * array gets R(rotation) (noise * exp(scaling)) + xyz for children, the SCALING array log(exp(s) / split_shrink).
@@ -275,9 +276,11 @@ int sc_densify_classify(int64_t N, const float* xyz_gradient_accum /*[N,2]*/, co
                         float big_ws_scale, float split_shrink, int32_t* flags /*[4N]*/,
                         int32_t* n_clone_selected /*[1]*/, void* stream);
 int sc_densify_move(int64_t N, const int32_t* flags /*[4N]*/, const int64_t* dest_index /*[4N+1]*/,
-                    int64_t n_child, int64_t n_split, int n_copies, const float* noise, const float* scaling,
-                    const float* rotation, float split_shrink, int n_arrays, const float* const* host_src,
-                    float* const* host_dst, const int* host_row_floats, const int* host_kinds, void* stream);
+                    int64_t n_stay, int64_t n_clone, int64_t n_child, int64_t n_split, int n_copies,
+                    const float* noise, const float* scaling, const float* rotation, float split_shrink,
+                    int32_t* index_workspace /*[n_clone + 2 n_child]*/, int n_arrays,
+                    const float* const* host_src, float* const* host_dst, const int* host_row_floats,
+                    const int* host_kinds, void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

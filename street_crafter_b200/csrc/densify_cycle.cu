@@ -61,20 +61,41 @@ struct MoveTable {
     float* dst[SC_COMPACT_MAX_ARRAYS];
     int width[SC_COMPACT_MAX_ARRAYS];
     int kind[SC_COMPACT_MAX_ARRAYS];        // SC_DENSIFY_* | MOVE_VEC
-    unsigned block_end[SC_COMPACT_MAX_ARRAYS];
+    unsigned block_end[2 * SC_COMPACT_MAX_ARRAYS];   // entry 2a: the `stay` scatter of array a, 2a+1: its appended rows
     int n;
 };
 constexpr int MOVE_VEC = 16;        // row width a multiple of 4 floats and both bases 16-byte aligned
 constexpr int MOVE_EPT = 4;         // element mode: floats per thread (a CTA covers 1024 consecutive floats)
 
 struct SplitCtx {
-    int64_t n_child, n_split;
+    int64_t n_stay, n_clone, n_child, n_split;
     int n_copies;
     const float* noise;
     const float* scaling;
     const float* rotation;
     float shrink;
+    const int32_t* clone_src;   // [n_clone]  source row of every surviving clone
+    const int32_t* child_src;   // [n_child]  source row of every surviving split row
+    const int32_t* child_rank;  // [n_child]  its rank among the split-SELECTED rows (indexes the noise)
 };
+
+// Source rows of the appended blocks, in output order (the inverse of the scan): lets the move kernel GATHER the
+// clones and children with fully coalesced stores.  (Scattering them from the source side wrote every 12..180-byte
+// row at a different time from its neighbours; the L2 filled the partially written sectors from DRAM and the
+// kernel read twice its input.)
+__global__ void __launch_bounds__(256)
+densify_index_kernel(int64_t N, const int32_t* __restrict__ flags, const int64_t* __restrict__ dest, int64_t n_stay,
+                     int64_t n_clone, int32_t* __restrict__ clone_src, int32_t* __restrict__ child_src,
+                     int32_t* __restrict__ child_rank) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    if (flags[N + i]) clone_src[__ldg(dest + N + i) - n_stay] = (int32_t)i;
+    if (flags[2 * N + i]) {
+        const int64_t r = __ldg(dest + 2 * N + i) - n_stay - n_clone;
+        child_src[r] = (int32_t)i;
+        child_rank[r] = (int32_t)(__ldg(dest + 3 * N + i) - __ldg(dest + 3 * N));
+    }
+}
 
 // c-th child value of one xyz component (row k of R(q) times (z * std), plus the parent's component)
 __device__ __forceinline__ float child_xyz(const SplitCtx& S, int64_t row, int64_t rank, int cp, int k, float v) {
@@ -93,77 +114,82 @@ __device__ __forceinline__ float child_xyz(const SplitCtx& S, int64_t row, int64
     return (R0 * p0 + R1 * p1 + R2 * p2) + v;                                        // :472
 }
 
-// One flat grid over all arrays (as compact_rows_kernel).  Every input float is read once, fully coalesced, and
-// written to every output row that descends from its row: a float4 per thread when the row width allows it,
-// otherwise one float per thread and access (consecutive lanes = consecutive floats of the flattened array, so
-// ragged widths such as f_rest's 45 floats still move whole sectors; strided 4-float pieces per thread made
-// the L2 fill every partially written sector from DRAM and doubled the read traffic).
+// One flat grid over all arrays, two CTA ranges per array.
+//  * `stay` rows: an order-preserving compaction exactly like compact_rows_kernel — a float4 per thread when the
+//    row width allows it, otherwise one float per lane access over the flattened array (ragged widths such as
+//    f_rest's 45 floats still move whole sectors).
+//  * appended rows [clones | children of copy 0 | copy 1 ...]: one float per lane access over the flattened OUTPUT
+//    block, source row looked up in the index lists; moments get zeros (no read at all).
 __global__ void __launch_bounds__(256)
 densify_move_kernel(int64_t N, const int32_t* __restrict__ flags, const int64_t* __restrict__ dest, SplitCtx S,
                     MoveTable T) {
-    int a = 0;
-    while (a < T.n - 1 && blockIdx.x >= T.block_end[a]) ++a;
-    const unsigned b0 = a ? T.block_end[a - 1] : 0u;
+    int t = 0;
+    while (t < 2 * T.n - 1 && blockIdx.x >= T.block_end[t]) ++t;
+    const unsigned b0 = t ? T.block_end[t - 1] : 0u;
+    const int a = t >> 1;
     const int w = T.width[a], kind = T.kind[a] & 15;
-    const bool moment = kind == SC_DENSIFY_MOMENT;
     const float* __restrict__ src = T.src[a];
     float* __restrict__ dst = T.dst[a];
-    if (T.kind[a] & MOVE_VEC) {     // PARAM / MOMENT only
-        const int pieces = w >> 2;
-        const int64_t idx = (int64_t)(blockIdx.x - b0) * 256 + threadIdx.x;
-        const int64_t row = idx / pieces;
-        if (row >= N) return;
-        const bool stay = flags[row], clone = flags[N + row], child = flags[2 * N + row];
-        if (!stay && !clone && !child) return;
-        const int c = (int)(idx - row * pieces) * 4;
-        const float4 v = __ldg(reinterpret_cast<const float4*>(src + row * w + c));
-        const float4 o = moment ? make_float4(0.f, 0.f, 0.f, 0.f) : v;
-        if (stay) *reinterpret_cast<float4*>(dst + __ldg(dest + row) * w + c) = v;
-        if (clone) *reinterpret_cast<float4*>(dst + __ldg(dest + N + row) * w + c) = o;
-        if (child) {
-            const int64_t d0 = __ldg(dest + 2 * N + row);
-            for (int cp = 0; cp < S.n_copies; ++cp)
-                *reinterpret_cast<float4*>(dst + (d0 + cp * S.n_child) * w + c) = o;
+    if (t & 1) {    // appended rows, output side
+        const int64_t total = (S.n_clone + S.n_copies * S.n_child) * w;
+        const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * MOVE_EPT);
+        const int64_t row0 = base / w;
+        const int rem0 = (int)(base - row0 * w);
+        float* __restrict__ out = dst + S.n_stay * w;
+#pragma unroll
+        for (int j = 0; j < MOVE_EPT; ++j) {
+            const int64_t e = base + j * 256 + threadIdx.x;
+            if (e >= total) break;
+            if (kind == SC_DENSIFY_MOMENT) { out[e] = 0.f; continue; }               // cat_optimizer :396-397
+            const int L = rem0 + j * 256 + (int)threadIdx.x;
+            const int dr = L / w, c = L - dr * w;
+            const int64_t orow = row0 + dr;
+            if (orow < S.n_clone) {
+                out[e] = __ldg(src + (int64_t)__ldg(S.clone_src + orow) * w + c);
+            } else {
+                const int64_t q = orow - S.n_clone;
+                const int cp = (int)(q / S.n_child);
+                const int64_t r = q - cp * S.n_child;
+                const int64_t row = __ldg(S.child_src + r);
+                const float v = __ldg(src + row * w + c);
+                float o = v;
+                if (kind == SC_DENSIFY_XYZ) o = child_xyz(S, row, __ldg(S.child_rank + r), cp, c, v);
+                else if (kind == SC_DENSIFY_SCALING) o = logf(expf(v) / S.shrink);   // :473
+                out[e] = o;
+            }
         }
         return;
     }
+    if (T.kind[a] & MOVE_VEC) {
+        const int pieces = w >> 2;
+        const int64_t idx = (int64_t)(blockIdx.x - b0) * 256 + threadIdx.x;
+        const int64_t row = idx / pieces;
+        if (row >= N || !flags[row]) return;
+        const int c = (int)(idx - row * pieces) * 4;
+        *reinterpret_cast<float4*>(dst + __ldg(dest + row) * w + c) =
+            __ldg(reinterpret_cast<const float4*>(src + row * w + c));
+        return;
+    }
     const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * MOVE_EPT);
-    const int64_t row0 = base / w;
+    const int64_t row0 = base / w, total = N * w;
     const int rem0 = (int)(base - row0 * w);
-    const int64_t total = N * w;
     // all loads of the four elements are independent of each other (the source is read whether or not its row
-    // survives: ~all rows do) and issue before the first store
+    // stays: ~all rows do) and issue before the first store
     float v[MOVE_EPT];
-    int64_t row[MOVE_EPT];
-    int col[MOVE_EPT], f[MOVE_EPT];
+    int64_t shift[MOVE_EPT];
+    bool k[MOVE_EPT];
 #pragma unroll
     for (int j = 0; j < MOVE_EPT; ++j) {
         const int64_t e = base + j * 256 + threadIdx.x;
         const bool in = e < total;
-        const int dr = (rem0 + j * 256 + (int)threadIdx.x) / w;
-        row[j] = row0 + dr;
-        col[j] = rem0 + j * 256 + (int)threadIdx.x - dr * w;
+        const int64_t row = row0 + (rem0 + j * 256 + (int)threadIdx.x) / w;
         v[j] = in ? __ldg(src + e) : 0.f;
-        f[j] = in ? (flags[row[j]] | (flags[N + row[j]] << 1) | (flags[2 * N + row[j]] << 2)) : 0;
+        k[j] = in && flags[row];
+        shift[j] = in ? (__ldg(dest + row) - row) * w : 0;
     }
 #pragma unroll
-    for (int j = 0; j < MOVE_EPT; ++j) {
-        if (!f[j]) continue;
-        const int c = col[j];
-        const float o = moment ? 0.f : v[j];
-        if (f[j] & 1) dst[__ldg(dest + row[j]) * w + c] = v[j];
-        if (f[j] & 2) dst[__ldg(dest + N + row[j]) * w + c] = o;
-        if (f[j] & 4) {
-            const int64_t d0 = __ldg(dest + 2 * N + row[j]);
-            const int64_t rank = __ldg(dest + 3 * N + row[j]) - __ldg(dest + 3 * N);   // among the split-selected rows
-            for (int cp = 0; cp < S.n_copies; ++cp) {
-                float oc = o;
-                if (kind == SC_DENSIFY_XYZ) oc = child_xyz(S, row[j], rank, cp, c, v[j]);
-                else if (kind == SC_DENSIFY_SCALING) oc = logf(expf(v[j]) / S.shrink);                   // :473
-                dst[(d0 + cp * S.n_child) * w + c] = oc;
-            }
-        }
-    }
+    for (int j = 0; j < MOVE_EPT; ++j)
+        if (k[j]) dst[base + j * 256 + threadIdx.x + shift[j]] = v[j];
 }
 
 }  // namespace
@@ -186,14 +212,26 @@ extern "C" int sc_densify_classify(int64_t N, const float* xyz_gradient_accum, c
     return SC_OK;
 }
 
-extern "C" int sc_densify_move(int64_t N, const int32_t* flags, const int64_t* dest_index, int64_t n_child,
-                               int64_t n_split, int n_copies, const float* noise, const float* scaling,
-                               const float* rotation, float split_shrink, int n_arrays, const float* const* src,
-                               float* const* dst, const int* row_floats, const int* kinds, void* stream) {
-    SC_CHECK_ARG(N >= 0 && n_arrays >= 0 && n_arrays <= SC_COMPACT_MAX_ARRAYS && n_copies >= 1, "sizes");
-    SC_CHECK_ARG(n_child >= 0 && n_split >= n_child, "child / split counts");
+extern "C" int sc_densify_move(int64_t N, const int32_t* flags, const int64_t* dest_index, int64_t n_stay,
+                               int64_t n_clone, int64_t n_child, int64_t n_split, int n_copies, const float* noise,
+                               const float* scaling, const float* rotation, float split_shrink, int32_t* index_ws,
+                               int n_arrays, const float* const* src, float* const* dst, const int* row_floats,
+                               const int* kinds, void* stream) {
+    SC_CHECK_ARG(N >= 0 && N < (1ll << 31) && n_arrays >= 0 && n_arrays <= SC_COMPACT_MAX_ARRAYS && n_copies >= 1,
+                 "sizes");
+    SC_CHECK_ARG(n_stay >= 0 && n_clone >= 0 && n_child >= 0 && n_split >= n_child && n_stay + n_split <= N,
+                 "stay / clone / child / split counts");
     if (N == 0 || n_arrays == 0) return SC_OK;
     SC_CHECK_ARG(flags && dest_index && src && dst && row_floats && kinds, "null pointer");
+    const int64_t n_app = n_clone + (int64_t)n_copies * n_child;
+    SC_CHECK_ARG(n_app == 0 || index_ws, "index workspace");
+    SplitCtx S{n_stay, n_clone, n_child, n_split, n_copies, noise, scaling, rotation, split_shrink,
+               index_ws, index_ws + n_clone, index_ws + n_clone + n_child};
+    if (n_app > 0) {
+        densify_index_kernel<<<(unsigned)sc_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(
+            N, flags, dest_index, n_stay, n_clone, index_ws, index_ws + n_clone, index_ws + n_clone + n_child);
+        SC_CHECK_LAUNCH("densify_index_kernel");
+    }
     MoveTable T;
     T.n = n_arrays;
     int64_t blocks = 0;
@@ -206,14 +244,17 @@ extern "C" int sc_densify_move(int64_t N, const int32_t* flags, const int64_t* d
             if (k == SC_DENSIFY_XYZ && n_split > 0) SC_CHECK_ARG(noise && scaling && rotation, "split inputs");
             const bool vec = (w & 3) == 0 && ((((uintptr_t)src[a]) | ((uintptr_t)dst[a])) & 15) == 0;
             T.src[a] = src[a]; T.dst[a] = dst[a]; T.width[a] = w; T.kind[a] = k | (vec ? MOVE_VEC : 0);
-            blocks += vec ? sc_div_up(N * (w / 4), 256) : sc_div_up(N * w, 256 * MOVE_EPT);
+            blocks += n_stay == 0 ? 0 : (vec ? sc_div_up(N * (w / 4), 256) : sc_div_up(N * w, 256 * MOVE_EPT));
+            T.block_end[2 * a] = (unsigned)blocks;
+            blocks += sc_div_up(n_app * w, 256 * MOVE_EPT);
             SC_CHECK_ARG(blocks < (1ll << 31), "N * row width");
         } else {
             T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1; T.kind[a] = 0;
+            T.block_end[2 * a] = (unsigned)blocks;
         }
-        T.block_end[a] = (unsigned)blocks;
+        T.block_end[2 * a + 1] = (unsigned)blocks;
     }
-    SplitCtx S{n_child, n_split, n_copies, noise, scaling, rotation, split_shrink};
+    if (blocks == 0) return SC_OK;
     densify_move_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(N, flags, dest_index, S, T);
     SC_CHECK_LAUNCH("densify_move_kernel");
     return SC_OK;

@@ -110,6 +110,7 @@ def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp
         noise = noise.contiguous()
         assert noise.is_cuda and noise.dtype == torch.float32 and tuple(noise.shape) == (n_copies * n_split, 3), noise.shape
         n_out = n_stay + n_clone + n_copies * n_child
+        index_ws = torch.empty(max(1, n_clone + 2 * n_child), dtype=torch.int32, device=dev)
         outs = [torch.empty((n_out,) + tuple(t.shape[1:]), dtype=torch.float32, device=dev) for t, _ in table]
         for a in range(0, len(table), MAX_ARRAYS):
             part, part_o = table[a:a + MAX_ARRAYS], outs[a:a + MAX_ARRAYS]
@@ -119,9 +120,9 @@ def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp
             w_arr = (C.c_int * n)(*[max(1, t[0].numel()) for t, _ in part])
             k_arr = (C.c_int * n)(*[k for _, k in part])
             if n_out:
-                check(lib.sc_densify_move(N, flags.data_ptr(), dest.data_ptr(), n_child, n_split, n_copies,
-                                          noise.data_ptr(), scaling.data_ptr(), rotation.data_ptr(), shrink, n,
-                                          src_arr, dst_arr, w_arr, k_arr, st), "sc_densify_move")
+                check(lib.sc_densify_move(N, flags.data_ptr(), dest.data_ptr(), n_stay, n_clone, n_child, n_split,
+                                          n_copies, noise.data_ptr(), scaling.data_ptr(), rotation.data_ptr(), shrink,
+                                          index_ws.data_ptr(), n, src_arr, dst_arr, w_arr, k_arr, st), "sc_densify_move")
     it = iter(outs)
     new_p = {k: next(it) for k in names}
     new_m = {k: next(it) for k in names if k in exp_avg}
