@@ -257,7 +257,8 @@ int sc_compact_rows(int64_t N, const uint8_t* keep, const int64_t* dest_index, i
  * the number of clone-SELECTED rows (for the reference's scalar_dict) to *n_clone_selected (device).
  * Thresholds are the float32 values the reference compares against: clone_max_scale = percent_dense * extent,
  * split_min_scale = float32(percent_dense) * float32(extent), big_ws_scale = extent * percent_big_ws (used when
- * prune_big != 0, i.e. max_screen_size is set), split_shrink = 0.8 * n_copies.
+ * prune_big != 0, i.e. max_screen_size is set), split_shrink = 0.8 * n_copies; grad_column picks
+ * xyz_gradient_accum[:, 0] (the base model) or [:, 1] (`densify_grad_abs_bkgd`, gaussian_model_bkgd.py:102-105).
  * The caller runs sc_exclusive_scan_i32 over the 4N flags (dest_index[4N+1]) and reads the segment totals
  * (n_stay, n_clone, n_child, n_split); sc_densify_move (two launches: the source-row index of the appended rows
  * into index_workspace, then the move) writes, for every array of the table, the output rows
@@ -273,7 +274,7 @@ int sc_compact_rows(int64_t N, const uint8_t* keep, const int64_t* dest_index, i
 int sc_densify_classify(int64_t N, const float* xyz_gradient_accum /*[N,2]*/, const float* denom /*[N]*/,
                         const float* scaling /*[N,3]*/, const float* opacity /*[N]*/, float max_grad,
                         float clone_max_scale, float split_min_scale, float min_opacity, int prune_big,
-                        float big_ws_scale, float split_shrink, int32_t* flags /*[4N]*/,
+                        float big_ws_scale, float split_shrink, int grad_column /*0 | 1*/, int32_t* flags /*[4N]*/,
                         int32_t* n_clone_selected /*[1]*/, void* stream);
 int sc_densify_move(int64_t N, const int32_t* flags /*[4N]*/, const int64_t* dest_index /*[4N+1]*/,
                     int64_t n_stay, int64_t n_clone, int64_t n_child, int64_t n_split, int n_copies,

@@ -44,13 +44,13 @@ def n_split(params, xyz_gradient_accum, denom, max_grad, extent, percent_dense=0
 
 
 def densify_and_prune(params, exp_avg, exp_avg_sq, xyz_gradient_accum, denom, noise, max_grad, min_opacity, extent,
-                      max_screen_size, percent_dense=0.01, percent_big_ws=0.1, n_copies=2):
+                      max_screen_size, percent_dense=0.01, percent_big_ws=0.1, n_copies=2, grad_column=0):
     """dicts of fp32 tensors (any one device) keyed xyz / f_dc / f_rest / opacity / scaling / rotation (/ semantic).
     -> (params, exp_avg, exp_avg_sq, scalars dict) after the cycle; the three statistics are all-zero afterwards
     (:546-548) and are not returned."""
     params, m, v = dict(params), dict(exp_avg), dict(exp_avg_sq)
     n0 = params["xyz"].shape[0]
-    grads = xyz_gradient_accum[:, 0:1] / denom.reshape(-1, 1)            # :522
+    grads = xyz_gradient_accum[:, grad_column:grad_column + 1] / denom.reshape(-1, 1)   # :522 (gaussian_model_bkgd.py:102-105 for column 1)
     grads[grads.isnan()] = 0.0                                           # :523
     scalars = {"points_total": n0}
     # clone :493-519

@@ -28,7 +28,8 @@ SIGNATURES = {
     "sc_projection_fwd_opacity": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _f32, _f32,
                                          _f32, _f32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_compact_rows": (_i32, [_i64, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr]),
-    "sc_densify_classify": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _f32, _f32, _f32, _f32, _i32, _f32, _f32, _ptr, _ptr, _ptr]),
+    "sc_densify_classify": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _f32, _f32, _f32, _f32, _i32, _f32, _f32, _i32, _ptr, _ptr,
+                                   _ptr]),
     "sc_densify_move": (_i32, [_i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr, _f32, _ptr, _i32, _ptr, _ptr,
                                _ptr, _ptr, _ptr]),
     "sc_densification_stats": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _ptr, _ptr, _ptr]),

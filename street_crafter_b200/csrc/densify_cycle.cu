@@ -23,7 +23,7 @@ namespace {
 
 struct ClassifyParams {
     float max_grad, clone_max_scale, split_min_scale, min_opacity, big_ws_scale, split_shrink;
-    int prune_big;
+    int prune_big, grad_column;
 };
 
 __global__ void __launch_bounds__(256)
@@ -33,7 +33,8 @@ densify_classify_kernel(int64_t N, const float2* __restrict__ accum, const float
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool clone_sel = false;
     if (i < N) {
-        float g = __ldg(&accum[i].x) / __ldg(denom + i);                       // :522
+        const float2 ac = __ldg(accum + i);
+        float g = (P.grad_column ? ac.y : ac.x) / __ldg(denom + i);            // :522 (column 1: the actor / background models' abs-grad option)
         if (g != g) g = 0.0f;                                                  // :523
         const float s0 = __ldg(scaling + 3 * i), s1 = __ldg(scaling + 3 * i + 1), s2 = __ldg(scaling + 3 * i + 2);
         const float e0 = expf(s0), e1 = expf(s1), e2 = expf(s2);
@@ -197,15 +198,15 @@ densify_move_kernel(int64_t N, const int32_t* __restrict__ flags, const int64_t*
 extern "C" int sc_densify_classify(int64_t N, const float* xyz_gradient_accum, const float* denom,
                                    const float* scaling, const float* opacity, float max_grad, float clone_max_scale,
                                    float split_min_scale, float min_opacity, int prune_big, float big_ws_scale,
-                                   float split_shrink, int32_t* flags, int32_t* n_clone_selected, void* stream) {
+                                   float split_shrink, int grad_column, int32_t* flags, int32_t* n_clone_selected, void* stream) {
     SC_CHECK_ARG(N >= 0 && 4 * N < (1ll << 31) * 256, "sizes");
     SC_CHECK_ARG(n_clone_selected, "null pointer");
     SC_CUDA(cudaMemsetAsync(n_clone_selected, 0, sizeof(int32_t), (cudaStream_t)stream));
     if (N == 0) return SC_OK;
     SC_CHECK_ARG(xyz_gradient_accum && denom && scaling && opacity && flags, "null pointer");
     SC_CHECK_ARG(((uintptr_t)xyz_gradient_accum & 7) == 0, "8-byte alignment of xyz_gradient_accum");
-    SC_CHECK_ARG(split_shrink > 0.f, "split_shrink");
-    ClassifyParams P{max_grad, clone_max_scale, split_min_scale, min_opacity, big_ws_scale, split_shrink, prune_big};
+    SC_CHECK_ARG(split_shrink > 0.f && (grad_column == 0 || grad_column == 1), "split_shrink / grad_column");
+    ClassifyParams P{max_grad, clone_max_scale, split_min_scale, min_opacity, big_ws_scale, split_shrink, prune_big, grad_column};
     densify_classify_kernel<<<(unsigned)sc_div_up(N, 256), 256, 0, (cudaStream_t)stream>>>(
         N, reinterpret_cast<const float2*>(xyz_gradient_accum), denom, scaling, opacity, P, flags, n_clone_selected);
     SC_CHECK_LAUNCH("densify_classify_kernel");

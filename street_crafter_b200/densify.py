@@ -54,7 +54,8 @@ _KINDS = {"xyz": 2, "scaling": 3}        # SC_DENSIFY_XYZ / SC_DENSIFY_SCALING; 
 def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp_avg_sq: Dict[str, Tensor],
                       xyz_gradient_accum: Tensor, denom: Tensor, max_grad: float, min_opacity: float, extent: float,
                       max_screen_size, percent_dense: float = 0.01, percent_big_ws: float = 0.1, n_copies: int = 2,
-                      noise: Optional[Tensor] = None, generator: Optional[torch.Generator] = None):
+                      noise: Optional[Tensor] = None, generator: Optional[torch.Generator] = None,
+                      grad_column: int = 0):
     """The reference's `GaussianModel.densify_and_prune(max_grad, min_opacity, prune_big_points, extent,
     max_screen_size)` (/root/reference/street_gaussian/models/gaussian_model.py:521-551: densify_and_clone
     :493-519, densify_and_split :452-491, cat_optimizer :384-408, prune_points :416-431) on plain tensors, as
@@ -65,6 +66,8 @@ def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp
     a parameter without optimizer state is simply absent from the moment dicts.  `noise` [n_copies*n_split, 3]
     replaces the standard-normal draw behind `torch.normal(mean=0, std=stds)` (:469-470); by default it is drawn
     here with `torch.randn` on the device — the same Philox stream the reference's call consumes.
+    `grad_column=1` takes the gradients from `xyz_gradient_accum[:, 1]` (the background / actor models'
+    `densify_grad_abs_*` option, gaussian_model_bkgd.py:102-105).
     -> (params, exp_avg, exp_avg_sq, stats, scalars): stats = the three zeroed statistics (:546-548),
     scalars = the reference's `scalar_dict` (points_total / clone / split / pruned)."""
     xyz, scaling, rotation, opacity = params["xyz"], params["scaling"], params["rotation"], params["opacity"]
@@ -95,7 +98,7 @@ def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp
         n_clone_sel = dest[4 * N + 1:].view(torch.int32)
         check(lib.sc_densify_classify(N, xyz_gradient_accum.data_ptr(), denom.data_ptr(), scaling.data_ptr(),
                                       opacity.data_ptr(), max_grad, clone_max, split_min, min_opacity,
-                                      1 if max_screen_size else 0, big_ws, shrink, flags.data_ptr(),
+                                      1 if max_screen_size else 0, big_ws, shrink, int(grad_column), flags.data_ptr(),
                                       n_clone_sel.data_ptr(), st), "sc_densify_classify")
         ws_bytes = int(lib.sc_scan_workspace_bytes(4 * N))
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)

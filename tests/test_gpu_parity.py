@@ -909,8 +909,8 @@ def test_densify_cycle_vs_reference_golden(S, dev, tag):
         assert st[k].shape == z[f"{tag}_out_{k}"].shape and not st[k].any(), k
 
 
-@pytest.mark.parametrize("N,mss", [(1, 20), (31, None), (4097, 20), (300_001, 20), (2_000_000, 20)])
-def test_densify_cycle_vs_oracle(S, dev, N, mss):
+@pytest.mark.parametrize("N,mss,col", [(1, 20, 0), (31, None, 0), (4097, 20, 1), (300_001, 20, 0), (2_000_000, 20, 0)])
+def test_densify_cycle_vs_oracle(S, dev, N, mss, col):
     """ragged sizes up to the cfg2 Gaussian count against the pinned oracle run on the same device tensors (torch's
     own exp / log / sigmoid kernels), same noise; row counts and every copied value bit-exact"""
     from oracle.densify_cycle_torch import densify_and_prune as oracle_cycle
@@ -926,10 +926,10 @@ def test_densify_cycle_vs_oracle(S, dev, N, mss):
     denom = torch.randint(0, 4, (N, 1), generator=g).float().to(dev)
     accum = (torch.rand(N, 2, generator=g) * 2.5 * max_grad).to(dev) * denom.clamp(min=1)
     p1, m1, v1, st, sc = densify_and_prune(params, m, v, accum, denom, max_grad, min_op, extent, mss,
-                                           generator=torch.Generator(device=dev).manual_seed(7))
+                                           generator=torch.Generator(device=dev).manual_seed(7), grad_column=col)
     noise = torch.randn((2 * sc["points_split"], 3), device=dev, generator=torch.Generator(device=dev).manual_seed(7))
     p0, m0, v0, sc0 = oracle_cycle(params, m, {**v, "f_rest": torch.zeros_like(m["f_rest"])}, accum, denom, noise,
-                                   max_grad, min_op, extent, mss)
+                                   max_grad, min_op, extent, mss, grad_column=col)
     v0.pop("f_rest")
     assert sc == sc0, (sc, sc0)
     _assert_cycle_equal((p1, m1, v1), (p0, m0, v0), N)

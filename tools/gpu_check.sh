@@ -24,4 +24,11 @@ echo "ncu full exit $?"
 ncu --set full --clock-control none --import-source on -k regex:photometric -s 6 -c 2 \
     -o gpurun_out/${TAG}_loss -f python tools/loss_bench.py > gpurun_out/${TAG}_ncu_loss.log 2>&1
 echo "ncu loss exit $?"
+# the densification-cycle / compaction kernels from their stand-alone tools
+python tools/densify_bench.py > gpurun_out/${TAG}_densify.log 2>&1; python tools/compact_bench.py >> gpurun_out/${TAG}_densify.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'densify_|compact_rows' -s 3 -c 3 \
+    -o gpurun_out/${TAG}_densify -f python tools/densify_bench.py > gpurun_out/${TAG}_ncu_densify.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'compact_rows' -s 1 -c 1 \
+    -o gpurun_out/${TAG}_compact -f python tools/compact_bench.py > gpurun_out/${TAG}_ncu_compact.log 2>&1
+echo "ncu densify exit $?"; cat gpurun_out/${TAG}_densify.log | tail -3
 ls -la gpurun_out | tail -12
