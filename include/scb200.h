@@ -23,6 +23,7 @@
  *   sc_compact_rows            prune_optimizer / prune_points  street_gaussian/models/gaussian_model.py:363-382, :416-431
  *   sc_densification_stats     set_max_radii2D + add_densification_stats
  *                                                              street_gaussian/models/street_gaussian_model.py:486-519
+ *   sc_assemble_fwd/bwd        StreetGaussianModel.get_xyz / get_rotation  street_gaussian/models/street_gaussian_model.py:296-364
  *   sc_densify_classify/move   densify_and_prune (clone + split + prune)  street_gaussian/models/gaussian_model.py:433-551
  *
  * Conventions: all pointers are DEVICE pointers unless named host_*; row-major contiguous
@@ -282,6 +283,32 @@ int sc_densify_move(int64_t N, const int32_t* flags /*[4N]*/, const int64_t* des
                     int32_t* index_workspace /*[n_clone + 2 n_child]*/, int n_arrays,
                     const float* const* host_src, float* const* host_dst, const int* host_row_floats,
                     const int* host_kinds, void* stream);
+
+/* N2 (geometric half): scene-graph assembly of the projection kernel's `means` / `quats` inputs —
+ * StreetGaussianModel.get_xyz / get_rotation (street_gaussian/models/street_gaussian_model.py:296-364) with
+ * quaternion_to_matrix / quaternion_raw_multiply (street_gaussian/utils/general_utils.py:125-146, :245-264) —
+ * over the concatenation of up to SC_ASSEMBLE_MAX_SEGMENTS models per call.  Segment s covers output rows
+ * [seg_start[s], seg_start[s+1]) (global row numbers: a scene with more segments is assembled by several calls
+ * on the same outputs).  pose_rot[s] == NULL: plain segment (background, sky): xyz copied, rotation
+ * F.normalize'd.  Otherwise an actor under the rigid pose (pose_rot[s][4] RAW wxyz, pose_trans[s][3], device
+ * pointers): xyz_w = R(pose_rot / |pose_rot|) x' + t, rot_w = normalize(pose_rot (x) q), where rows with
+ * flip[s][k] != 0 mirror x along flip_axis and pre-multiply q by flip_quat (host float[4]) — the training-time
+ * symmetry prior (:313-318, :347-350).  All table arrays are HOST arrays of device pointers.
+ * sc_assemble_bwd writes the gradients of every segment's own arrays (v_xyz[s][n_s,3], v_rot[s][n_s,4]; NULL =
+ * not wanted) and ACCUMULATES the tracked-pose gradients into v_pose_rot[s][4] / v_pose_trans[s][3] (NULL = pose
+ * not optimised; the caller zeroes them). */
+#define SC_ASSEMBLE_MAX_SEGMENTS 32
+int sc_assemble_fwd(int n_segments, const int64_t* host_seg_start /*[n_segments+1]*/, const float* const* host_xyz,
+                    const float* const* host_rot, const float* const* host_pose_rot,
+                    const float* const* host_pose_trans, const uint8_t* const* host_flip, int flip_axis,
+                    const float* host_flip_quat /*[4]*/, float* out_xyz /*[N,3]*/, float* out_rot /*[N,4]*/,
+                    void* stream);
+int sc_assemble_bwd(int n_segments, const int64_t* host_seg_start, const float* const* host_xyz,
+                    const float* const* host_rot, const float* const* host_pose_rot,
+                    const float* const* host_pose_trans, const uint8_t* const* host_flip, int flip_axis,
+                    const float* host_flip_quat, const float* v_out_xyz /*[N,3]*/, const float* v_out_rot /*[N,4]*/,
+                    float* const* host_v_xyz, float* const* host_v_rot, float* const* host_v_pose_rot,
+                    float* const* host_v_pose_trans, void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

@@ -32,6 +32,8 @@ SIGNATURES = {
                                    _ptr]),
     "sc_densify_move": (_i32, [_i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr, _f32, _ptr, _i32, _ptr, _ptr,
                                _ptr, _ptr, _ptr]),
+    "sc_assemble_fwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr]),
+    "sc_assemble_bwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_densification_stats": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "sc_rasterize_fwd_depth": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                       _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),

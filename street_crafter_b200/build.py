@@ -31,6 +31,7 @@ SOURCES = {
     "loss.cu": [],
     "densify.cu": [],
     "densify_cycle.cu": [],
+    "assemble.cu": [],
     "compact.cu": [],
     "probe.cu": ["--use_fast_math"],
 }

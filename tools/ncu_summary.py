@@ -35,7 +35,9 @@ if os.path.exists(lc):
         out.write(f"{v[1]:10.1f} us {100*v[1]/tot:5.1f}% n={v[0]:4d} avg={v[1]/v[0]:8.1f} us  {k}\n")
 
 for rep in (os.path.join(ROOT, "gpurun_out", f"{tag}_prof.ncu-rep"),
-            os.path.join(ROOT, "gpurun_out", f"{tag}_loss.ncu-rep")):
+            os.path.join(ROOT, "gpurun_out", f"{tag}_loss.ncu-rep"),
+            os.path.join(ROOT, "gpurun_out", f"{tag}_densify.ncu-rep"),
+            os.path.join(ROOT, "gpurun_out", f"{tag}_compact.ncu-rep")):
     if not os.path.exists(rep):
         continue
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
