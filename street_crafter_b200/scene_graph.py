@@ -1,0 +1,118 @@
+"""Scene-graph assembly of the projection kernel's `means` / `quats` inputs (SURVEY.md section 8(f) row N2,
+geometric half): the reference's `StreetGaussianModel.get_xyz` / `get_rotation`
+(/root/reference/street_gaussian/models/street_gaussian_model.py:296-364) — per-model cat, flip-mask clone /
+masked index, quaternion_to_matrix + einsum, two quaternion_raw_multiply and two normalize, each with its autograd
+node — as ONE forward and ONE backward kernel over the concatenated Gaussian set (csrc/assemble.cu).  No CPU path."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional, Sequence
+
+import torch
+from torch import Tensor
+
+from ._lib import check, lib
+
+MAX_SEGMENTS = 32      # SC_ASSEMBLE_MAX_SEGMENTS
+FLIP_QUAT_Y = (0.0, 0.0, 1.0, 0.0)   # matrix_to_quaternion(diag(-1, 1, -1)), street_gaussian_model.py:55-58
+
+
+def _tables(segs, starts, flip_quat):
+    n = len(segs)
+    ptr = lambda t: t.data_ptr() if t is not None and t.numel() else None
+    arr = lambda xs: (C.c_void_p * n)(*xs)
+    return ((C.c_int64 * (n + 1))(*starts), arr([ptr(s[0]) for s in segs]), arr([ptr(s[1]) for s in segs]),
+            arr([s[2].data_ptr() if s[2] is not None else None for s in segs]),
+            arr([s[3].data_ptr() if s[3] is not None else None for s in segs]), arr([ptr(s[4]) for s in segs]),
+            (C.c_float * 4)(*flip_quat))
+
+
+class _Assemble(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, meta, *tensors):
+        kinds, flips, flip_axis, flip_quat = meta
+        dev = tensors[0].device
+        segs, it = [], iter(tensors)
+        for actor, flip in zip(kinds, flips):
+            xyz, rot = next(it).contiguous(), next(it).contiguous()
+            pr, pt = (next(it).contiguous(), next(it).contiguous()) if actor else (None, None)
+            segs.append((xyz, rot, pr, pt, flip))
+        starts = [0]
+        for s in segs:
+            starts.append(starts[-1] + s[0].shape[0])
+        N = starts[-1]
+        out_xyz = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        out_rot = torch.empty((N, 4), dtype=torch.float32, device=dev)
+        st = torch.cuda.current_stream().cuda_stream
+        with torch.cuda.device(dev):
+            for a in range(0, len(segs), MAX_SEGMENTS):
+                part = segs[a:a + MAX_SEGMENTS]
+                t = _tables(part, starts[a:a + len(part) + 1], flip_quat)
+                check(lib.sc_assemble_fwd(len(part), t[0], t[1], t[2], t[3], t[4], t[5], flip_axis, t[6],
+                                          out_xyz.data_ptr(), out_rot.data_ptr(), st), "sc_assemble_fwd")
+        ctx.segs, ctx.starts, ctx.meta = segs, starts, meta
+        return out_xyz, out_rot
+
+    @staticmethod
+    def backward(ctx, v_xyz, v_rot):
+        kinds, flips, flip_axis, flip_quat = ctx.meta
+        segs, starts = ctx.segs, ctx.starts
+        dev = segs[0][0].device
+        v_xyz = (v_xyz if v_xyz is not None else torch.zeros((starts[-1], 3), device=dev)).float().contiguous()
+        v_rot = (v_rot if v_rot is not None else torch.zeros((starts[-1], 4), device=dev)).float().contiguous()
+        need = iter(ctx.needs_input_grad[1:])
+        grads, gsegs = [None], []
+        for (xyz, rot, pr, pt, _), actor in zip(segs, kinds):
+            gx = torch.empty_like(xyz) if next(need) else None
+            gr = torch.empty_like(rot) if next(need) else None
+            gpr = gpt = None
+            if actor:
+                gpr = torch.zeros(4, dtype=torch.float32, device=dev) if next(need) else None
+                gpt = torch.zeros(3, dtype=torch.float32, device=dev) if next(need) else None
+            gsegs.append((gx, gr, gpr, gpt))
+            grads += [gx, gr] + ([gpr.view_as(pr) if gpr is not None else None,
+                                  gpt.view_as(pt) if gpt is not None else None] if actor else [])
+        st = torch.cuda.current_stream().cuda_stream
+        ptr = lambda t: t.data_ptr() if t is not None and t.numel() else None
+        with torch.cuda.device(dev):
+            for a in range(0, len(segs), MAX_SEGMENTS):
+                part, gpart = segs[a:a + MAX_SEGMENTS], gsegs[a:a + MAX_SEGMENTS]
+                n = len(part)
+                t = _tables(part, starts[a:a + n + 1], flip_quat)
+                g = [(C.c_void_p * n)(*[ptr(gs[j]) for gs in gpart]) for j in range(4)]
+                check(lib.sc_assemble_bwd(n, t[0], t[1], t[2], t[3], t[4], t[5], flip_axis, t[6], v_xyz.data_ptr(),
+                                          v_rot.data_ptr(), g[0], g[1], g[2], g[3], st), "sc_assemble_bwd")
+        return tuple(grads)
+
+
+def assemble_xyz_rotation(segments: Sequence[Dict[str, Optional[Tensor]]], flip_quat: Sequence[float] = FLIP_QUAT_Y,
+                          flip_axis: int = 1):
+    """segments, in scene-graph order (background, visible actors, sky — `parse_camera`,
+    street_gaussian_model.py:216-243): dicts with `xyz` [n,3] and `rotation` [n,4] (the model's RAW `_rotation`);
+    actors add `pose_rot` [4] (ActorPose.get_tracking_rotation, raw wxyz), `pose_trans` [3] and optionally `flip`
+    [n] bool (the training-time flip mask, :262-271).  -> (`get_xyz` [N,3], `get_rotation` [N,4]), differentiable
+    w.r.t. every float input (tracked poses included)."""
+    if not segments:
+        raise ValueError("assemble_xyz_rotation needs at least one segment")
+    kinds, flips, tensors = [], [], []
+    for s in segments:
+        xyz, rot = s["xyz"], s["rotation"]
+        if not (xyz.is_cuda and rot.is_cuda):
+            raise RuntimeError("assemble_xyz_rotation needs CUDA tensors: street_crafter_b200 has no CPU path")
+        assert xyz.dtype == torch.float32 and rot.dtype == torch.float32 and xyz.shape[1:] == (3,) and \
+            rot.shape == (xyz.shape[0], 4), (xyz.shape, rot.shape)
+        actor = s.get("pose_rot") is not None
+        kinds.append(actor)
+        tensors += [xyz, rot]
+        flip = None
+        if actor:
+            pr, pt = s["pose_rot"], s["pose_trans"]
+            assert pr.numel() == 4 and pt.numel() == 3 and pr.is_cuda and pt.is_cuda
+            tensors += [pr, pt]
+            if s.get("flip") is not None:
+                flip = s["flip"]
+                flip = (flip if flip.dtype == torch.bool else flip != 0).reshape(-1).contiguous().view(torch.uint8)
+                assert flip.numel() == xyz.shape[0] and flip.is_cuda
+        flips.append(flip)
+    meta = (tuple(kinds), tuple(flips), int(flip_axis), tuple(float(v) for v in flip_quat))
+    return _Assemble.apply(meta, *tensors)

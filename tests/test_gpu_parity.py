@@ -947,3 +947,73 @@ def test_densify_cycle_empty_and_cpu_raises(S, dev):
     assert out[0]["xyz"].shape == (0, 3) and out[4]["points_total"] == 0
     with pytest.raises(RuntimeError):
         densify_and_prune({k: t.cpu() for k, t in p.items()}, {}, {}, torch.zeros(0, 2), torch.zeros(0, 1), 2e-4, 5e-3, 10.0, 20)
+
+
+# ------------------------------------------------------------------------ scene-graph assembly (N2, geometric half)
+def _assemble_loss_and_grads(fn, segs, w_xyz, w_rot):
+    xyz, rot = fn(segs)
+    ((xyz * w_xyz).sum() + (rot * w_rot).sum()).backward()
+    grads = []
+    for s in segs:
+        for k in ("xyz", "rotation", "pose_rot", "pose_trans"):
+            t = s.get(k)
+            if t is not None:
+                grads.append((s["name"], k, (t.grad if t.grad is not None else torch.zeros_like(t)).detach().clone()))
+                t.grad = None
+    return xyz.detach(), rot.detach(), grads
+
+
+def test_assemble_vs_reference_golden(S, dev):
+    """get_xyz / get_rotation values and autograd gradients (Gaussian parameters AND tracked poses) of the reference's
+    own property bodies (tests/golden/assemble.npz: background + 3 actors incl. an empty one + sky, flips) == one
+    forward + one backward kernel.  Values within 1e-5, gradients within 1e-4 relative to their scale."""
+    from street_crafter_b200.scene_graph import assemble_xyz_rotation
+    from test_oracle_cpu import _assemble_golden_segments
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "assemble.npz"))
+    segs = _assemble_golden_segments(z, to=lambda t: t.to(dev))
+    fq, ax = [float(v) for v in z["flip_quat"]], int(z["flip_axis"])
+    xyz, rot, grads = _assemble_loss_and_grads(lambda s: assemble_xyz_rotation(s, fq, ax), segs,
+                                               torch.from_numpy(z["w_xyz"]).to(dev), torch.from_numpy(z["w_rot"]).to(dev))
+    assert (xyz.cpu() - torch.from_numpy(z["out_xyz"])).abs().max() < 1e-5
+    assert (rot.cpu() - torch.from_numpy(z["out_rot"])).abs().max() < 1e-5
+    key = {"xyz": "v_xyz", "rotation": "v_rot", "pose_rot": "v_pose_rot", "pose_trans": "v_pose_trans"}
+    for name, k, g in grads:
+        want = torch.from_numpy(z[f"{name}_{key[k]}"])
+        assert g.shape == want.shape, (name, k)
+        if want.numel():
+            assert (g.cpu() - want).abs().max() <= 1e-4 * max(1.0, float(want.abs().max())), (name, k)
+
+
+@pytest.mark.parametrize("n_bkgd,n_actors,n_per_actor,n_sky", [(1000, 2, 300, 0), (0, 40, 257, 50), (1_900_000, 20, 5000, 100_000)])
+def test_assemble_vs_oracle(S, dev, n_bkgd, n_actors, n_per_actor, n_sky):
+    """cfg2-like scene graph (1.9 M background + 20 actors x 5000 + sky) and a 41-segment graph (two kernel calls)
+    against the pinned oracle run with autograd on the same device tensors"""
+    from oracle.assemble_torch import assemble as oracle_assemble
+    from street_crafter_b200.scene_graph import FLIP_QUAT_Y, assemble_xyz_rotation
+    g = torch.Generator().manual_seed(n_actors)
+    leaf = lambda *s, k=1.0: (torch.randn(*s, generator=g) * k).to(dev).requires_grad_(True)
+    segs = []
+    if n_bkgd:
+        segs.append({"name": "background", "xyz": leaf(n_bkgd, 3, k=30.0), "rotation": leaf(n_bkgd, 4)})
+    for a in range(n_actors):
+        n = n_per_actor + a
+        segs.append({"name": f"obj_{a:03d}", "xyz": leaf(n, 3, k=2.0), "rotation": leaf(n, 4), "pose_rot": leaf(4),
+                     "pose_trans": leaf(3, k=20.0),
+                     "flip": None if a % 3 == 2 else (torch.rand(n, generator=g) < 0.5).to(dev)})
+    if n_sky:
+        segs.append({"name": "sky", "xyz": leaf(n_sky, 3, k=100.0), "rotation": leaf(n_sky, 4)})
+    N = sum(s["xyz"].shape[0] for s in segs)
+    w_xyz, w_rot = torch.randn(N, 3, generator=g).to(dev), torch.randn(N, 4, generator=g).to(dev)
+    fq = torch.tensor(FLIP_QUAT_Y, device=dev)
+    x0, r0, g0 = _assemble_loss_and_grads(lambda s: oracle_assemble(s, fq, 1), segs, w_xyz, w_rot)
+    x1, r1, g1 = _assemble_loss_and_grads(lambda s: assemble_xyz_rotation(s), segs, w_xyz, w_rot)
+    assert x1.shape == (N, 3) and r1.shape == (N, 4)
+    assert (x1 - x0).abs().max() <= 1e-5 * max(1.0, float(x0.abs().max())) and (r1 - r0).abs().max() < 1e-5
+    for (name, k, a), (_, _, b) in zip(g1, g0):
+        assert (a - b).abs().max() <= 2e-4 * max(1.0, float(b.abs().max())), (name, k, float((a - b).abs().max()))
+
+
+def test_assemble_cpu_raises(S, dev):
+    from street_crafter_b200.scene_graph import assemble_xyz_rotation
+    with pytest.raises(RuntimeError):
+        assemble_xyz_rotation([{"xyz": torch.zeros(4, 3), "rotation": torch.ones(4, 4)}])

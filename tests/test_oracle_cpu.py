@@ -348,3 +348,37 @@ def test_densify_cycle_oracle_matches_reference_golden(tag):
     n = p["xyz"].shape[0]
     for k in PRUNE_STATS:
         assert z[f"{tag}_out_{k}"].shape[0] == n and not z[f"{tag}_out_{k}"].any(), k
+
+
+def _assemble_golden_segments(z, to=lambda t: t, grad=True):
+    segs = []
+    for name in z["names"]:
+        name = str(name)
+        mk = lambda k: to(torch.from_numpy(z[f"{name}_{k}"])).requires_grad_(grad)
+        s = {"name": name, "xyz": mk("xyz"), "rotation": mk("rot")}
+        if name.startswith("obj_"):
+            s.update(pose_rot=mk("pose_rot"), pose_trans=mk("pose_trans"), flip=to(torch.from_numpy(z[f"{name}_flip"])))
+        segs.append(s)
+    return segs
+
+
+def test_assemble_oracle_matches_reference_golden():
+    """oracle/assemble_torch.py against values and autograd gradients produced by EXECUTING the reference's
+    StreetGaussianModel.get_xyz / get_rotation (tools/make_golden_assemble.py)"""
+    import numpy as np
+    from oracle.assemble_torch import assemble
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "assemble.npz"))
+    segs = _assemble_golden_segments(z)
+    xyz, rot = assemble(segs, torch.from_numpy(z["flip_quat"]), int(z["flip_axis"]))
+    assert torch.allclose(xyz, torch.from_numpy(z["out_xyz"]), atol=1e-6, rtol=1e-6)
+    assert torch.allclose(rot, torch.from_numpy(z["out_rot"]), atol=1e-6, rtol=1e-6)
+    ((xyz * torch.from_numpy(z["w_xyz"])).sum() + (rot * torch.from_numpy(z["w_rot"])).sum()).backward()
+    for s in segs:
+        n = s["name"]
+        for key, t in (("v_xyz", s["xyz"]), ("v_rot", s["rotation"]), ("v_pose_rot", s.get("pose_rot")),
+                       ("v_pose_trans", s.get("pose_trans"))):
+            if t is None:
+                continue
+            got = t.grad if t.grad is not None else torch.zeros_like(t)
+            want = torch.from_numpy(z[f"{n}_{key}"])
+            assert torch.allclose(got, want, atol=2e-5, rtol=1e-5), (n, key, float((got - want).abs().max()))

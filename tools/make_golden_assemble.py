@@ -1,0 +1,89 @@
+"""Generates tests/golden/assemble.npz by EXECUTING the reference's own `StreetGaussianModel.get_xyz` /
+`get_rotation` property bodies (/root/reference/street_gaussian/models/street_gaussian_model.py:296-364) with
+`quaternion_to_matrix` / `quaternion_raw_multiply` / `matrix_to_quaternion` and its helpers
+(/root/reference/street_gaussian/utils/general_utils.py) — cut out of the reference files with `ast` (unmodified,
+nothing copied into this repository) and bound to a stand-in scene graph: background + 3 actors (one without
+flips, one empty) + sky, training mode with a 50 % flip mask, tracked poses as autograd leaves.  Outputs AND the
+autograd gradients of a fixed random linear functional are stored.       python tools/make_golden_assemble.py"""
+import ast
+import os
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = "/root/reference/street_gaussian/models/street_gaussian_model.py"
+SRC_U = "/root/reference/street_gaussian/utils/general_utils.py"
+
+
+def load():
+    tree_u = ast.parse(open(SRC_U).read())
+    want_u = ("quaternion_to_matrix", "quaternion_raw_multiply", "matrix_to_quaternion", "_sqrt_positive_part")
+    fu = [n for n in tree_u.body if isinstance(n, ast.FunctionDef) and n.name in want_u]
+    assert len(fu) == len(want_u)
+    for f in fu:
+        f.decorator_list = []        # @torch.jit.script needs the source file; eager execution is the same math
+    ns = {"torch": torch, "F": torch.nn.functional, "cfg": types.SimpleNamespace(mode="train")}
+    exec(compile(ast.Module(body=fu, type_ignores=[]), SRC_U, "exec"), ns)
+    tree = ast.parse(open(SRC).read())
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "StreetGaussianModel")
+    fm = [n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name in ("get_xyz", "get_rotation")]
+    assert len(fm) == 2
+    for f in fm:
+        f.decorator_list = []        # call the property bodies as plain methods
+    exec(compile(ast.Module(body=fm, type_ignores=[]), SRC, "exec"), ns)
+    return ns
+
+
+class Leaf:
+    """One model of the scene graph: raw parameters, the reference's getters (gaussian_model.py:229-235)."""
+
+    def __init__(self, n, g):
+        self._xyz = (torch.randn(n, 3, generator=g) * 3).requires_grad_(True)
+        self._rotation = (torch.randn(n, 4, generator=g) * 1.7).requires_grad_(True)
+
+    get_xyz = property(lambda s: s._xyz)
+    get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))
+
+
+if __name__ == "__main__":
+    ns = load()
+    g = torch.Generator().manual_seed(41)
+    sizes = {"background": 37, "obj_000": 19, "obj_001": 0, "obj_002": 33, "sky": 11}
+    m = types.SimpleNamespace(**{k: Leaf(n, g) for k, n in sizes.items()})
+    m.graph_obj_list = ["obj_000", "obj_001", "obj_002"]
+    m.get_visibility = lambda name: True
+    m.flip_axis = 1                                                           # street_gaussian_model.py:55-58
+    fm = torch.eye(3) * -1
+    fm[m.flip_axis, m.flip_axis] = 1
+    m.flip_matrix = ns["matrix_to_quaternion"](fm.unsqueeze(0))
+    pose_rot = {k: (torch.randn(4, generator=g)).requires_grad_(True) for k in m.graph_obj_list}   # RAW (not unit)
+    pose_trans = {k: (torch.randn(3, generator=g) * 10).requires_grad_(True) for k in m.graph_obj_list}
+    # parse_camera :245-271
+    m.obj_rots = torch.cat([pose_rot[k].expand(sizes[k], -1) for k in m.graph_obj_list], 0)
+    m.obj_trans = torch.cat([pose_trans[k].unsqueeze(0).expand(sizes[k], -1) for k in m.graph_obj_list], 0)
+    flips = {"obj_000": torch.rand(sizes["obj_000"], generator=g) < 0.5, "obj_001": torch.zeros(0, dtype=torch.bool),
+             "obj_002": torch.zeros(sizes["obj_002"], dtype=torch.bool)}
+    m.flip_mask = torch.cat([flips[k] for k in m.graph_obj_list], 0)
+    xyz = ns["get_xyz"](m)
+    rot = ns["get_rotation"](m)
+    n = sum(sizes.values())
+    assert xyz.shape == (n, 3) and rot.shape == (n, 4)
+    w_xyz, w_rot = torch.randn(n, 3, generator=g), torch.randn(n, 4, generator=g)
+    ((xyz * w_xyz).sum() + (rot * w_rot).sum()).backward()
+    out = {"names": np.array(list(sizes)), "sizes": np.array(list(sizes.values())), "flip_quat": m.flip_matrix[0].numpy(),
+           "flip_axis": np.array(m.flip_axis), "out_xyz": xyz.detach().numpy(), "out_rot": rot.detach().numpy(),
+           "w_xyz": w_xyz.numpy(), "w_rot": w_rot.numpy()}
+    for k in sizes:
+        leaf = getattr(m, k)
+        out[f"{k}_xyz"], out[f"{k}_rot"] = leaf._xyz.detach().numpy(), leaf._rotation.detach().numpy()
+        out[f"{k}_v_xyz"], out[f"{k}_v_rot"] = leaf._xyz.grad.numpy(), leaf._rotation.grad.numpy()
+    for k in m.graph_obj_list:
+        out[f"{k}_pose_rot"], out[f"{k}_pose_trans"] = pose_rot[k].detach().numpy(), pose_trans[k].detach().numpy()
+        z4, z3 = torch.zeros(4), torch.zeros(3)
+        out[f"{k}_v_pose_rot"] = (pose_rot[k].grad if pose_rot[k].grad is not None else z4).numpy()
+        out[f"{k}_v_pose_trans"] = (pose_trans[k].grad if pose_trans[k].grad is not None else z3).numpy()
+        out[f"{k}_flip"] = flips[k].numpy()
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "assemble.npz"), **out)
+    print(len(out), "arrays;", n, "Gaussians; flip quaternion", out["flip_quat"], "; flipped", int(m.flip_mask.sum()))
