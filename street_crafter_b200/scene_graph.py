@@ -61,14 +61,20 @@ class _Assemble(torch.autograd.Function):
         v_xyz = (v_xyz if v_xyz is not None else torch.zeros((starts[-1], 3), device=dev)).float().contiguous()
         v_rot = (v_rot if v_rot is not None else torch.zeros((starts[-1], 4), device=dev)).float().contiguous()
         need = iter(ctx.needs_input_grad[1:])
+        # three allocations for all segments: per-Gaussian gradients are row slices of two [N, .] buffers, the pose
+        # gradients rows of one zeroed [S, 7] buffer (the kernel accumulates into them)
+        N = starts[-1]
+        all_gx = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        all_gr = torch.empty((N, 4), dtype=torch.float32, device=dev)
+        all_gp = torch.zeros((len(segs), 7), dtype=torch.float32, device=dev)
         grads, gsegs = [None], []
-        for (xyz, rot, pr, pt, _), actor in zip(segs, kinds):
-            gx = torch.empty_like(xyz) if next(need) else None
-            gr = torch.empty_like(rot) if next(need) else None
+        for i, ((xyz, rot, pr, pt, _), actor) in enumerate(zip(segs, kinds)):
+            gx = all_gx[starts[i]:starts[i + 1]] if next(need) else None
+            gr = all_gr[starts[i]:starts[i + 1]] if next(need) else None
             gpr = gpt = None
             if actor:
-                gpr = torch.zeros(4, dtype=torch.float32, device=dev) if next(need) else None
-                gpt = torch.zeros(3, dtype=torch.float32, device=dev) if next(need) else None
+                gpr = all_gp[i, :4] if next(need) else None
+                gpt = all_gp[i, 4:] if next(need) else None
             gsegs.append((gx, gr, gpr, gpt))
             grads += [gx, gr] + ([gpr.view_as(pr) if gpr is not None else None,
                                   gpt.view_as(pt) if gpt is not None else None] if actor else [])
