@@ -24,6 +24,7 @@
  *   sc_densification_stats     set_max_radii2D + add_densification_stats
  *                                                              street_gaussian/models/street_gaussian_model.py:486-519
  *   sc_assemble_fwd/bwd        StreetGaussianModel.get_xyz / get_rotation  street_gaussian/models/street_gaussian_model.py:296-364
+ *   sc_assemble_act_fwd/bwd    StreetGaussianModel.get_scaling / get_opacity  street_gaussian/models/street_gaussian_model.py:273-294, :389-407
  *   sc_densify_classify/move   densify_and_prune (clone + split + prune)  street_gaussian/models/gaussian_model.py:433-551
  *
  * Conventions: all pointers are DEVICE pointers unless named host_*; row-major contiguous
@@ -309,6 +310,19 @@ int sc_assemble_bwd(int n_segments, const int64_t* host_seg_start, const float* 
                     const float* host_flip_quat, const float* v_out_xyz /*[N,3]*/, const float* v_out_rot /*[N,4]*/,
                     float* const* host_v_xyz, float* const* host_v_rot, float* const* host_v_pose_rot,
                     float* const* host_v_pose_trans, void* stream);
+
+/* N2, activations of the concatenated set: StreetGaussianModel.get_scaling (street_gaussian_model.py:273-294) =
+ * cat of exp(_scaling) per model (clamped to clamp_max[s] for the sky model, gaussian_model_sky.py:63-66; pass
+ * +inf otherwise) and get_opacity (:389-407) = cat of sigmoid(_opacity).  Same segment convention as
+ * sc_assemble_fwd; host_clamp_max is a HOST float[n_segments].  The backward recomputes the activations from
+ * the raw parameters and writes every segment's own gradient arrays (NULL = not wanted). */
+int sc_assemble_act_fwd(int n_segments, const int64_t* host_seg_start, const float* const* host_scaling /*[n_s,3]*/,
+                        const float* const* host_opacity /*[n_s]*/, const float* host_clamp_max,
+                        float* out_scaling /*[N,3]*/, float* out_opacity /*[N]*/, void* stream);
+int sc_assemble_act_bwd(int n_segments, const int64_t* host_seg_start, const float* const* host_scaling,
+                        const float* const* host_opacity, const float* host_clamp_max,
+                        const float* v_out_scaling /*[N,3]*/, const float* v_out_opacity /*[N]*/,
+                        float* const* host_v_scaling, float* const* host_v_opacity, void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

@@ -44,3 +44,17 @@ def assemble(segments, flip_quat, flip_axis=1):
         xyzs.append(x)
         rots.append(q)
     return torch.cat(xyzs, 0), torch.cat(rots, 0)
+
+
+def assemble_activations(segments):
+    """segments: dicts with raw `scaling` [n,3], `opacity` [n,1] and, for the sky model, `scaling_clamp_max`.
+    -> (get_scaling [N,3], get_opacity [N,1]): street_gaussian_model.py:273-294, :389-407 over the per-model
+    activations (gaussian_model.py:215-227, :251-252; gaussian_model_sky.py:63-66)."""
+    scs, ops = [], []
+    for s in segments:
+        sc = torch.exp(s["scaling"])
+        if s.get("scaling_clamp_max") is not None:
+            sc = torch.clamp(sc, max=float(s["scaling_clamp_max"]))
+        scs.append(sc)
+        ops.append(torch.sigmoid(s["opacity"]))
+    return torch.cat(scs, 0), torch.cat(ops, 0)

@@ -236,6 +236,76 @@ int fill_table(SegTable& T, int n_segments, const int64_t* seg_start, const floa
     return SC_OK;
 }
 
+// ---- activations of the concatenated set: get_scaling (:273-294) and get_opacity (:389-407) -------------------
+// scaling_w = min(exp(scaling), clamp_max)   (clamp_max = +inf except for the sky model, gaussian_model_sky.py:63-66)
+// opacity_w = sigmoid(opacity)               (gaussian_model.py:215-220, :226-227, :251-252)
+struct ActTable {
+    int64_t start[SC_ASSEMBLE_MAX_SEGMENTS + 1];
+    const float* scaling[SC_ASSEMBLE_MAX_SEGMENTS];
+    const float* opacity[SC_ASSEMBLE_MAX_SEGMENTS];
+    float* v_scaling[SC_ASSEMBLE_MAX_SEGMENTS];     // backward only
+    float* v_opacity[SC_ASSEMBLE_MAX_SEGMENTS];
+    float clamp_max[SC_ASSEMBLE_MAX_SEGMENTS];
+    int n;
+};
+
+__device__ __forceinline__ int find_act_segment(const ActTable& T, int64_t i) {
+    int s = 0;
+    while (s < T.n - 1 && i >= T.start[s + 1]) ++s;
+    return s;
+}
+
+__global__ void __launch_bounds__(256)
+assemble_act_fwd_kernel(ActTable T, float* __restrict__ out_scaling, float* __restrict__ out_opacity) {
+    const int64_t i = T.start[0] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T.start[T.n]) return;
+    const int s = find_act_segment(T, i);
+    const int64_t k = i - T.start[s];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) out_scaling[3 * i + c] = fminf(expf(__ldg(T.scaling[s] + 3 * k + c)), T.clamp_max[s]);
+    out_opacity[i] = 1.f / (1.f + expf(-__ldg(T.opacity[s] + k)));
+}
+
+__global__ void __launch_bounds__(256)
+assemble_act_bwd_kernel(ActTable T, const float* __restrict__ v_out_scaling, const float* __restrict__ v_out_opacity) {
+    const int64_t i = T.start[0] + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T.start[T.n]) return;
+    const int s = find_act_segment(T, i);
+    const int64_t k = i - T.start[s];
+    if (T.v_scaling[s]) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float e = expf(__ldg(T.scaling[s] + 3 * k + c));
+            T.v_scaling[s][3 * k + c] = e <= T.clamp_max[s] ? __ldg(v_out_scaling + 3 * i + c) * e : 0.f;   // clamp passes x <= max
+        }
+    }
+    if (T.v_opacity[s]) {
+        const float o = 1.f / (1.f + expf(-__ldg(T.opacity[s] + k)));
+        T.v_opacity[s][k] = __ldg(v_out_opacity + i) * ((1.f - o) * o);
+    }
+}
+
+int fill_act_table(ActTable& T, int n_segments, const int64_t* seg_start, const float* const* scaling,
+                   const float* const* opacity, const float* clamp_max, float* const* v_scaling,
+                   float* const* v_opacity) {
+    SC_CHECK_ARG(n_segments >= 1 && n_segments <= SC_ASSEMBLE_MAX_SEGMENTS, "segment count");
+    SC_CHECK_ARG(seg_start && scaling && opacity && clamp_max, "null table");
+    T.n = n_segments;
+    for (int s = 0; s < SC_ASSEMBLE_MAX_SEGMENTS; ++s) {
+        const bool in = s < n_segments;
+        if (in) {
+            SC_CHECK_ARG(seg_start[s + 1] >= seg_start[s], "segment starts must not decrease");
+            SC_CHECK_ARG(seg_start[s + 1] == seg_start[s] || (scaling[s] && opacity[s]), "segment arrays");
+        }
+        T.scaling[s] = in ? scaling[s] : nullptr; T.opacity[s] = in ? opacity[s] : nullptr;
+        T.clamp_max[s] = in ? clamp_max[s] : 0.f;
+        T.v_scaling[s] = (in && v_scaling) ? v_scaling[s] : nullptr;
+        T.v_opacity[s] = (in && v_opacity) ? v_opacity[s] : nullptr;
+    }
+    for (int s = 0; s <= SC_ASSEMBLE_MAX_SEGMENTS; ++s) T.start[s] = seg_start[s <= n_segments ? s : n_segments];
+    return SC_OK;
+}
+
 }  // namespace
 
 extern "C" int sc_assemble_fwd(int n_segments, const int64_t* seg_start, const float* const* xyz,
@@ -274,5 +344,35 @@ extern "C" int sc_assemble_bwd(int n_segments, const int64_t* seg_start, const f
     }
     assemble_bwd_kernel<<<(unsigned)sc_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(T, G, v_out_xyz, v_out_rot);
     SC_CHECK_LAUNCH("assemble_bwd_kernel");
+    return SC_OK;
+}
+
+extern "C" int sc_assemble_act_fwd(int n_segments, const int64_t* seg_start, const float* const* scaling,
+                                   const float* const* opacity, const float* clamp_max, float* out_scaling,
+                                   float* out_opacity, void* stream) {
+    ActTable T;
+    const int rc = fill_act_table(T, n_segments, seg_start, scaling, opacity, clamp_max, nullptr, nullptr);
+    if (rc != SC_OK) return rc;
+    const int64_t n = T.start[T.n] - T.start[0];
+    if (n == 0) return SC_OK;
+    SC_CHECK_ARG(out_scaling && out_opacity, "outputs");
+    assemble_act_fwd_kernel<<<(unsigned)sc_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(T, out_scaling, out_opacity);
+    SC_CHECK_LAUNCH("assemble_act_fwd_kernel");
+    return SC_OK;
+}
+
+extern "C" int sc_assemble_act_bwd(int n_segments, const int64_t* seg_start, const float* const* scaling,
+                                   const float* const* opacity, const float* clamp_max, const float* v_out_scaling,
+                                   const float* v_out_opacity, float* const* v_scaling, float* const* v_opacity,
+                                   void* stream) {
+    SC_CHECK_ARG(v_scaling && v_opacity, "null gradient table");
+    ActTable T;
+    const int rc = fill_act_table(T, n_segments, seg_start, scaling, opacity, clamp_max, v_scaling, v_opacity);
+    if (rc != SC_OK) return rc;
+    const int64_t n = T.start[T.n] - T.start[0];
+    if (n == 0) return SC_OK;
+    SC_CHECK_ARG(v_out_scaling && v_out_opacity, "upstream gradients");
+    assemble_act_bwd_kernel<<<(unsigned)sc_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(T, v_out_scaling, v_out_opacity);
+    SC_CHECK_LAUNCH("assemble_act_bwd_kernel");
     return SC_OK;
 }

@@ -122,3 +122,75 @@ def assemble_xyz_rotation(segments: Sequence[Dict[str, Optional[Tensor]]], flip_
         flips.append(flip)
     meta = (tuple(kinds), tuple(flips), int(flip_axis), tuple(float(v) for v in flip_quat))
     return _Assemble.apply(meta, *tensors)
+
+
+class _AssembleAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, clamp_max, *tensors):
+        dev = tensors[0].device
+        segs = [(tensors[i].contiguous(), tensors[i + 1].contiguous()) for i in range(0, len(tensors), 2)]
+        starts = [0]
+        for s in segs:
+            starts.append(starts[-1] + s[0].shape[0])
+        N = starts[-1]
+        out_s = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        out_o = torch.empty((N, 1), dtype=torch.float32, device=dev)
+        st = torch.cuda.current_stream().cuda_stream
+        with torch.cuda.device(dev):
+            for a in range(0, len(segs), MAX_SEGMENTS):
+                t = _AssembleAct._tables(segs[a:a + MAX_SEGMENTS], starts[a:a + MAX_SEGMENTS + 1], clamp_max[a:a + MAX_SEGMENTS])
+                check(lib.sc_assemble_act_fwd(t[0], t[1], t[2], t[3], t[4], out_s.data_ptr(), out_o.data_ptr(), st),
+                      "sc_assemble_act_fwd")
+        ctx.segs, ctx.starts, ctx.clamp_max = segs, starts, clamp_max
+        return out_s, out_o
+
+    @staticmethod
+    def _tables(part, starts, clamp):
+        n = len(part)
+        ptr = lambda t: t.data_ptr() if t is not None and t.numel() else None
+        return (n, (C.c_int64 * (n + 1))(*starts), (C.c_void_p * n)(*[ptr(s[0]) for s in part]),
+                (C.c_void_p * n)(*[ptr(s[1]) for s in part]), (C.c_float * n)(*clamp))
+
+    @staticmethod
+    def backward(ctx, v_s, v_o):
+        segs, starts, clamp_max = ctx.segs, ctx.starts, ctx.clamp_max
+        dev, N = segs[0][0].device, starts[-1]
+        v_s = (v_s if v_s is not None else torch.zeros((N, 3), device=dev)).float().contiguous()
+        v_o = (v_o if v_o is not None else torch.zeros((N, 1), device=dev)).float().contiguous()
+        all_gs = torch.empty((N, 3), dtype=torch.float32, device=dev)
+        all_go = torch.empty((N,), dtype=torch.float32, device=dev)
+        need = iter(ctx.needs_input_grad[1:])
+        gsegs = []
+        for i, (sc, op) in enumerate(segs):
+            gs = all_gs[starts[i]:starts[i + 1]] if next(need) else None
+            go = all_go[starts[i]:starts[i + 1]].view_as(op) if next(need) else None
+            gsegs.append((gs, go))
+        st = torch.cuda.current_stream().cuda_stream
+        ptr = lambda t: t.data_ptr() if t is not None and t.numel() else None
+        with torch.cuda.device(dev):
+            for a in range(0, len(segs), MAX_SEGMENTS):
+                part, gpart = segs[a:a + MAX_SEGMENTS], gsegs[a:a + MAX_SEGMENTS]
+                t = _AssembleAct._tables(part, starts[a:a + len(part) + 1], clamp_max[a:a + MAX_SEGMENTS])
+                g = [(C.c_void_p * len(part))(*[ptr(gs[j]) for gs in gpart]) for j in range(2)]
+                check(lib.sc_assemble_act_bwd(t[0], t[1], t[2], t[3], t[4], v_s.data_ptr(), v_o.data_ptr(), g[0], g[1], st),
+                      "sc_assemble_act_bwd")
+        return (None,) + tuple(x for gs in gsegs for x in gs)
+
+
+def assemble_scaling_opacity(segments: Sequence[Dict[str, Optional[Tensor]]]):
+    """segments in scene-graph order: dicts with the models' RAW `scaling` [n,3] (log) and `opacity` [n,1] (logit);
+    the sky model adds `scaling_clamp_max` (its sphere radius, gaussian_model_sky.py:63-66).
+    -> (`get_scaling` [N,3], `get_opacity` [N,1]) of street_gaussian_model.py:273-294 / :389-407, differentiable."""
+    if not segments:
+        raise ValueError("assemble_scaling_opacity needs at least one segment")
+    tensors, clamp = [], []
+    for s in segments:
+        sc, op = s["scaling"], s["opacity"]
+        if not (sc.is_cuda and op.is_cuda):
+            raise RuntimeError("assemble_scaling_opacity needs CUDA tensors: street_crafter_b200 has no CPU path")
+        assert sc.dtype == torch.float32 and op.dtype == torch.float32 and sc.shape[1:] == (3,) and \
+            op.numel() == sc.shape[0], (sc.shape, op.shape)
+        tensors += [sc, op]
+        cm = s.get("scaling_clamp_max")
+        clamp.append(float("inf") if cm is None else float(cm))
+    return _AssembleAct.apply(tuple(clamp), *tensors)

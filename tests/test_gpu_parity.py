@@ -950,12 +950,12 @@ def test_densify_cycle_empty_and_cpu_raises(S, dev):
 
 
 # ------------------------------------------------------------------------ scene-graph assembly (N2, geometric half)
-def _assemble_loss_and_grads(fn, segs, w_xyz, w_rot):
+def _assemble_loss_and_grads(fn, segs, w_xyz, w_rot, keys=("xyz", "rotation", "pose_rot", "pose_trans")):
     xyz, rot = fn(segs)
     ((xyz * w_xyz).sum() + (rot * w_rot).sum()).backward()
     grads = []
     for s in segs:
-        for k in ("xyz", "rotation", "pose_rot", "pose_trans"):
+        for k in keys:
             t = s.get(k)
             if t is not None:
                 grads.append((s["name"], k, (t.grad if t.grad is not None else torch.zeros_like(t)).detach().clone()))
@@ -1017,3 +1017,39 @@ def test_assemble_cpu_raises(S, dev):
     from street_crafter_b200.scene_graph import assemble_xyz_rotation
     with pytest.raises(RuntimeError):
         assemble_xyz_rotation([{"xyz": torch.zeros(4, 3), "rotation": torch.ones(4, 4)}])
+
+
+def test_assemble_activations_vs_reference_golden(S, dev):
+    """get_scaling / get_opacity (sky model clamped) of the reference's own property bodies, values and gradients"""
+    from street_crafter_b200.scene_graph import assemble_scaling_opacity
+    from test_oracle_cpu import _assemble_golden_segments
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "assemble.npz"))
+    segs = _assemble_golden_segments(z, to=lambda t: t.to(dev))
+    sca, opa, grads = _assemble_loss_and_grads(assemble_scaling_opacity, segs, torch.from_numpy(z["w_scaling"]).to(dev),
+                                               torch.from_numpy(z["w_opacity"]).to(dev), keys=("scaling", "opacity"))
+    want_s, want_o = torch.from_numpy(z["out_scaling"]), torch.from_numpy(z["out_opacity"])
+    assert sca.shape == want_s.shape and opa.shape == want_o.shape
+    assert ((sca.cpu() - want_s).abs() <= 2e-6 * want_s.abs()).all() and (opa.cpu() - want_o).abs().max() < 1e-6
+    for name, k, g in grads:
+        want = torch.from_numpy(z[f"{name}_v_{k}"])
+        assert g.shape == want.shape, (name, k)
+        if want.numel():
+            assert (g.cpu() - want).abs().max() <= 1e-5 * max(1.0, float(want.abs().max())), (name, k)
+
+
+def test_assemble_activations_vs_oracle_cfg2(S, dev):
+    """1.9 M background + 40 actors (two kernel calls) + clamped sky against torch's own exp / sigmoid / clamp"""
+    from oracle.assemble_torch import assemble_activations
+    from street_crafter_b200.scene_graph import assemble_scaling_opacity
+    g = torch.Generator().manual_seed(5)
+    leaf = lambda *s, k=1.0, b=0.0: (torch.randn(*s, generator=g) * k + b).to(dev).requires_grad_(True)
+    sizes = [1_900_000] + [2500 + a for a in range(40)] + [100_000]
+    segs = [{"name": str(i), "scaling": leaf(n, 3, b=-2.0), "opacity": leaf(n, 1, k=2.5)} for i, n in enumerate(sizes)]
+    segs[-1]["scaling_clamp_max"] = 0.2
+    N = sum(sizes)
+    w_s, w_o = torch.randn(N, 3, generator=g).to(dev), torch.randn(N, 1, generator=g).to(dev)
+    s0, o0, g0 = _assemble_loss_and_grads(assemble_activations, segs, w_s, w_o, keys=("scaling", "opacity"))
+    s1, o1, g1 = _assemble_loss_and_grads(assemble_scaling_opacity, segs, w_s, w_o, keys=("scaling", "opacity"))
+    assert ((s1 - s0).abs() <= 2e-6 * s0.abs()).all() and (o1 - o0).abs().max() < 1e-6
+    for (name, k, a), (_, _, b) in zip(g1, g0):
+        assert (a - b).abs().max() <= 1e-5 * max(1.0, float(b.abs().max())), (name, k)

@@ -355,7 +355,9 @@ def _assemble_golden_segments(z, to=lambda t: t, grad=True):
     for name in z["names"]:
         name = str(name)
         mk = lambda k: to(torch.from_numpy(z[f"{name}_{k}"])).requires_grad_(grad)
-        s = {"name": name, "xyz": mk("xyz"), "rotation": mk("rot")}
+        s = {"name": name, "xyz": mk("xyz"), "rotation": mk("rot"), "scaling": mk("scaling"), "opacity": mk("opacity")}
+        if name == "sky":
+            s["scaling_clamp_max"] = float(z["sky_clamp_max"])
         if name.startswith("obj_"):
             s.update(pose_rot=mk("pose_rot"), pose_trans=mk("pose_trans"), flip=to(torch.from_numpy(z[f"{name}_flip"])))
         segs.append(s)
@@ -382,3 +384,20 @@ def test_assemble_oracle_matches_reference_golden():
             got = t.grad if t.grad is not None else torch.zeros_like(t)
             want = torch.from_numpy(z[f"{n}_{key}"])
             assert torch.allclose(got, want, atol=2e-5, rtol=1e-5), (n, key, float((got - want).abs().max()))
+
+
+def test_assemble_activations_oracle_matches_reference_golden():
+    """get_scaling / get_opacity of the reference's StreetGaussianModel (sky model clamped) incl. autograd gradients"""
+    import numpy as np
+    from oracle.assemble_torch import assemble_activations
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "assemble.npz"))
+    segs = _assemble_golden_segments(z)
+    sca, opa = assemble_activations(segs)
+    assert torch.allclose(sca, torch.from_numpy(z["out_scaling"]), atol=0, rtol=1e-6)
+    assert torch.allclose(opa, torch.from_numpy(z["out_opacity"]), atol=1e-7, rtol=1e-6)
+    assert (torch.from_numpy(z["out_scaling"][-int(z["sizes"][-1]):]) == float(z["sky_clamp_max"])).any()   # the clamp is exercised
+    ((sca * torch.from_numpy(z["w_scaling"])).sum() + (opa * torch.from_numpy(z["w_opacity"])).sum()).backward()
+    for s in segs:
+        for key, t in (("v_scaling", s["scaling"]), ("v_opacity", s["opacity"])):
+            got = t.grad if t.grad is not None else torch.zeros_like(t)
+            assert torch.allclose(got, torch.from_numpy(z[f"{s['name']}_{key}"]), atol=1e-7, rtol=1e-5), (s["name"], key)

@@ -1,5 +1,7 @@
 """Generates tests/golden/assemble.npz by EXECUTING the reference's own `StreetGaussianModel.get_xyz` /
-`get_rotation` property bodies (/root/reference/street_gaussian/models/street_gaussian_model.py:296-364) with
+`get_rotation` / `get_scaling` / `get_opacity` property bodies
+(/root/reference/street_gaussian/models/street_gaussian_model.py:273-364, :389-407; the sky model's clamped
+`get_scaling`, gaussian_model_sky.py:63-66) with
 `quaternion_to_matrix` / `quaternion_raw_multiply` / `matrix_to_quaternion` and its helpers
 (/root/reference/street_gaussian/utils/general_utils.py) — cut out of the reference files with `ast` (unmodified,
 nothing copied into this repository) and bound to a stand-in scene graph: background + 3 actors (one without
@@ -28,11 +30,19 @@ def load():
     exec(compile(ast.Module(body=fu, type_ignores=[]), SRC_U, "exec"), ns)
     tree = ast.parse(open(SRC).read())
     cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "StreetGaussianModel")
-    fm = [n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name in ("get_xyz", "get_rotation")]
-    assert len(fm) == 2
+    fm = [n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name in ("get_xyz", "get_rotation", "get_scaling",
+                                                                                "get_opacity")]
+    assert len(fm) == 4
     for f in fm:
         f.decorator_list = []        # call the property bodies as plain methods
     exec(compile(ast.Module(body=fm, type_ignores=[]), SRC, "exec"), ns)
+    # the sky model's own get_scaling (clamped to its sphere radius), gaussian_model_sky.py:63-66
+    src_sky = "/root/reference/street_gaussian/models/gaussian_model_sky.py"
+    sky = next(n for n in ast.parse(open(src_sky).read()).body if isinstance(n, ast.ClassDef) and n.name == "GaussianModelSky")
+    fs = [n for n in sky.body if isinstance(n, ast.FunctionDef) and n.name == "get_scaling"]
+    assert len(fs) == 1
+    fs[0].decorator_list, fs[0].name = [], "sky_get_scaling"
+    exec(compile(ast.Module(body=fs, type_ignores=[]), src_sky, "exec"), ns)
     return ns
 
 
@@ -42,9 +52,13 @@ class Leaf:
     def __init__(self, n, g):
         self._xyz = (torch.randn(n, 3, generator=g) * 3).requires_grad_(True)
         self._rotation = (torch.randn(n, 4, generator=g) * 1.7).requires_grad_(True)
+        self._scaling = (torch.randn(n, 3, generator=g) - 1.0).requires_grad_(True)
+        self._opacity = (torch.randn(n, 1, generator=g) * 2.5).requires_grad_(True)
 
     get_xyz = property(lambda s: s._xyz)
     get_rotation = property(lambda s: torch.nn.functional.normalize(s._rotation))
+    get_scaling = property(lambda s: torch.exp(s._scaling))                  # gaussian_model.py:215, :226-227
+    get_opacity = property(lambda s: torch.sigmoid(s._opacity))              # :220, :251-252
 
 
 if __name__ == "__main__":
@@ -66,19 +80,31 @@ if __name__ == "__main__":
     flips = {"obj_000": torch.rand(sizes["obj_000"], generator=g) < 0.5, "obj_001": torch.zeros(0, dtype=torch.bool),
              "obj_002": torch.zeros(sizes["obj_002"], dtype=torch.bool)}
     m.flip_mask = torch.cat([flips[k] for k in m.graph_obj_list], 0)
+    class Sky(Leaf):                                                          # gaussian_model_sky.py:63-66
+        scaling_activation = staticmethod(torch.exp)
+        sphere_radius = torch.tensor(0.45)
+        get_scaling = property(ns["sky_get_scaling"])
+    m.sky.__class__ = Sky
     xyz = ns["get_xyz"](m)
     rot = ns["get_rotation"](m)
     n = sum(sizes.values())
     assert xyz.shape == (n, 3) and rot.shape == (n, 4)
     w_xyz, w_rot = torch.randn(n, 3, generator=g), torch.randn(n, 4, generator=g)
-    ((xyz * w_xyz).sum() + (rot * w_rot).sum()).backward()
+    sca, opa = ns["get_scaling"](m), ns["get_opacity"](m)
+    assert sca.shape == (n, 3) and opa.shape == (n, 1)
+    w_sca, w_opa = torch.randn(n, 3, generator=g), torch.randn(n, 1, generator=g)
+    ((xyz * w_xyz).sum() + (rot * w_rot).sum() + (sca * w_sca).sum() + (opa * w_opa).sum()).backward()
     out = {"names": np.array(list(sizes)), "sizes": np.array(list(sizes.values())), "flip_quat": m.flip_matrix[0].numpy(),
            "flip_axis": np.array(m.flip_axis), "out_xyz": xyz.detach().numpy(), "out_rot": rot.detach().numpy(),
-           "w_xyz": w_xyz.numpy(), "w_rot": w_rot.numpy()}
+           "w_xyz": w_xyz.numpy(), "w_rot": w_rot.numpy(), "out_scaling": sca.detach().numpy(),
+           "out_opacity": opa.detach().numpy(), "w_scaling": w_sca.numpy(), "w_opacity": w_opa.numpy(),
+           "sky_clamp_max": np.array(float(Sky.sphere_radius))}
     for k in sizes:
         leaf = getattr(m, k)
         out[f"{k}_xyz"], out[f"{k}_rot"] = leaf._xyz.detach().numpy(), leaf._rotation.detach().numpy()
         out[f"{k}_v_xyz"], out[f"{k}_v_rot"] = leaf._xyz.grad.numpy(), leaf._rotation.grad.numpy()
+        out[f"{k}_scaling"], out[f"{k}_opacity"] = leaf._scaling.detach().numpy(), leaf._opacity.detach().numpy()
+        out[f"{k}_v_scaling"], out[f"{k}_v_opacity"] = leaf._scaling.grad.numpy(), leaf._opacity.grad.numpy()
     for k in m.graph_obj_list:
         out[f"{k}_pose_rot"], out[f"{k}_pose_trans"] = pose_rot[k].detach().numpy(), pose_trans[k].detach().numpy()
         z4, z3 = torch.zeros(4), torch.zeros(3)
