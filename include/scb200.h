@@ -243,7 +243,8 @@ int sc_densification_stats(int64_t N, const float* means2d_absgrad /*[N,2]*/, co
  * densification statistics of every attribute in ONE launch
  * (street_gaussian/models/gaussian_model.py:363-382 prune_optimizer, :416-431 prune_points; the same
  * gather serves the `[selected_pts_mask]` selections of densify_and_clone / densify_and_split).
- * keep[N] u8 / bool; dest_index[N] i64 = exclusive prefix sum of keep (sc_exclusive_scan_i32);
+ * keep[N] u8 / bool; dest_index[N+1] i64 = exclusive prefix sum of keep with the total in entry N
+ * (sc_exclusive_scan_i32 with `total` = out + N);
  * src / dst / row_floats are HOST arrays of n_arrays entries (device pointers inside);
  * dst[a] must hold sum(keep) rows of row_floats[a] floats. */
 #define SC_COMPACT_MAX_ARRAYS 32

@@ -6,6 +6,7 @@
 // the keep mask and its exclusive prefix sum.  Rows keep their relative order, so parameters and
 // optimizer moments stay aligned.  HBM-bound: every kept float is read once and written once.
 #include "common.cuh"
+#include "row_move.cuh"
 
 #include "../../include/scb200.h"
 
@@ -16,6 +17,7 @@ struct RowTable {
     float* dst[SC_COMPACT_MAX_ARRAYS];
     int width[SC_COMPACT_MAX_ARRAYS];
     unsigned block_end[SC_COMPACT_MAX_ARRAYS];  // inclusive prefix of the CTAs each array owns
+    int rows_per_cta[SC_COMPACT_MAX_ARRAYS];    // > 0: ragged width staged through shared memory
     int n;
 };
 
@@ -44,6 +46,10 @@ compact_rows_kernel(int64_t N, const uint8_t* __restrict__ keep, const int64_t* 
         return;
     }
     const int w = -T.width[a];
+    if (T.rows_per_cta[a] > 0) {    // ragged width, staged through shared memory (row_move.cuh)
+        rowmove_staged_cta(N, dest, src, dst, w, T.rows_per_cta[a], blockIdx.x - b0);
+        return;
+    }
     const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * COMPACT_EPT);
     const int64_t row0 = base / w, total = N * w;
     const int rem0 = (int)(base - row0 * w);
@@ -82,10 +88,12 @@ extern "C" int sc_compact_rows(int64_t N, const uint8_t* keep, const int64_t* de
             const int w = row_floats[a];
             const bool vec = (w & 3) == 0 && ((((uintptr_t)src[a]) | ((uintptr_t)dst[a])) & 15) == 0;
             T.src[a] = src[a]; T.dst[a] = dst[a]; T.width[a] = vec ? w : -w;
-            blocks += vec ? sc_div_up(N * (w / 4), 256) : sc_div_up(N * w, 256 * COMPACT_EPT);
+            const int R = vec ? 0 : rowmove_rows_per_cta(w);
+            T.rows_per_cta[a] = R;
+            blocks += vec ? sc_div_up(N * (w / 4), 256) : R > 0 ? sc_div_up(N, R) : sc_div_up(N * w, 256 * COMPACT_EPT);
             SC_CHECK_ARG(blocks < (1ll << 31), "N * row width");
         } else {
-            T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1;
+            T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1; T.rows_per_cta[a] = 0;
         }
         T.block_end[a] = (unsigned)blocks;
     }

@@ -18,6 +18,7 @@
 //
 // Compiled WITHOUT fast math: expf / logf / the divisions are the accurate ones torch's exp / log / sigmoid use.
 #include "common.cuh"
+#include "row_move.cuh"
 
 namespace {
 
@@ -63,6 +64,7 @@ struct MoveTable {
     int width[SC_COMPACT_MAX_ARRAYS];
     int kind[SC_COMPACT_MAX_ARRAYS];        // SC_DENSIFY_* | MOVE_VEC
     unsigned block_end[2 * SC_COMPACT_MAX_ARRAYS];   // entry 2a: the `stay` scatter of array a, 2a+1: its appended rows
+    int rows_per_cta[SC_COMPACT_MAX_ARRAYS];         // > 0: ragged width, `stay` rows staged through shared memory
     int n;
 };
 constexpr int MOVE_VEC = 16;        // row width a multiple of 4 floats and both bases 16-byte aligned
@@ -171,6 +173,10 @@ densify_move_kernel(int64_t N, const int32_t* __restrict__ flags, const int64_t*
             __ldg(reinterpret_cast<const float4*>(src + row * w + c));
         return;
     }
+    if (T.rows_per_cta[a] > 0) {    // dest[0 .. N] is the scan of the `stay` flags (dest[N] = n_stay)
+        rowmove_staged_cta(N, dest, src, dst, w, T.rows_per_cta[a], blockIdx.x - b0);
+        return;
+    }
     const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * MOVE_EPT);
     const int64_t row0 = base / w, total = N * w;
     const int rem0 = (int)(base - row0 * w);
@@ -245,12 +251,14 @@ extern "C" int sc_densify_move(int64_t N, const int32_t* flags, const int64_t* d
             if (k == SC_DENSIFY_XYZ && n_split > 0) SC_CHECK_ARG(noise && scaling && rotation, "split inputs");
             const bool vec = (w & 3) == 0 && ((((uintptr_t)src[a]) | ((uintptr_t)dst[a])) & 15) == 0;
             T.src[a] = src[a]; T.dst[a] = dst[a]; T.width[a] = w; T.kind[a] = k | (vec ? MOVE_VEC : 0);
-            blocks += n_stay == 0 ? 0 : (vec ? sc_div_up(N * (w / 4), 256) : sc_div_up(N * w, 256 * MOVE_EPT));
+            const int R = vec ? 0 : rowmove_rows_per_cta(w);
+            T.rows_per_cta[a] = R;
+            blocks += n_stay == 0 ? 0 : vec ? sc_div_up(N * (w / 4), 256) : R > 0 ? sc_div_up(N, R) : sc_div_up(N * w, 256 * MOVE_EPT);
             T.block_end[2 * a] = (unsigned)blocks;
             blocks += sc_div_up(n_app * w, 256 * MOVE_EPT);
             SC_CHECK_ARG(blocks < (1ll << 31), "N * row width");
         } else {
-            T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1; T.kind[a] = 0;
+            T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1; T.kind[a] = 0; T.rows_per_cta[a] = 0;
             T.block_end[2 * a] = (unsigned)blocks;
         }
         T.block_end[2 * a + 1] = (unsigned)blocks;
