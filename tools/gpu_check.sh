@@ -30,5 +30,7 @@ ncu --set full --clock-control none --import-source on -k regex:'densify_|compac
     -o gpurun_out/${TAG}_densify -f python tools/densify_bench.py > gpurun_out/${TAG}_ncu_densify.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:'compact_rows' -s 1 -c 1 \
     -o gpurun_out/${TAG}_compact -f python tools/compact_bench.py > gpurun_out/${TAG}_ncu_compact.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'assemble_' -s 6 -c 2 \
+    -o gpurun_out/${TAG}_assemble -f python tools/assemble_bench.py > gpurun_out/${TAG}_ncu_assemble.log 2>&1
 echo "ncu densify exit $?"; cat gpurun_out/${TAG}_densify.log | tail -3
 ls -la gpurun_out | tail -12

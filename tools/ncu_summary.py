@@ -37,7 +37,8 @@ if os.path.exists(lc):
 for rep in (os.path.join(ROOT, "gpurun_out", f"{tag}_prof.ncu-rep"),
             os.path.join(ROOT, "gpurun_out", f"{tag}_loss.ncu-rep"),
             os.path.join(ROOT, "gpurun_out", f"{tag}_densify.ncu-rep"),
-            os.path.join(ROOT, "gpurun_out", f"{tag}_compact.ncu-rep")):
+            os.path.join(ROOT, "gpurun_out", f"{tag}_compact.ncu-rep"),
+            os.path.join(ROOT, "gpurun_out", f"{tag}_assemble.ncu-rep")):
     if not os.path.exists(rep):
         continue
     raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
