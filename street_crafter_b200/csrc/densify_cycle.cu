@@ -135,24 +135,39 @@ densify_move_kernel(int64_t N, const int32_t* __restrict__ flags, const int64_t*
     float* __restrict__ dst = T.dst[a];
     if (t & 1) {    // appended rows, output side
         const int64_t total = (S.n_clone + S.n_copies * S.n_child) * w;
-        const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * MOVE_EPT);
+        const int64_t base = (int64_t)(blockIdx.x - b0) * (256 * MOVE_EPT) * (kind == SC_DENSIFY_MOMENT ? 4 : 1);
         const int64_t row0 = base / w;
         const int rem0 = (int)(base - row0 * w);
         float* __restrict__ out = dst + S.n_stay * w;
+        if (kind == SC_DENSIFY_MOMENT) {    // cat_optimizer :396-397: zeros — float4 stores on 16-byte boundaries
+            const int shift = (int)((((uintptr_t)out) >> 2) & 3);          // floats past the previous boundary
+            const int64_t f0 = base + 4 * (int64_t)threadIdx.x - shift;   // base is a multiple of 4096
+#pragma unroll
+            for (int j = 0; j < MOVE_EPT; ++j) {
+                const int64_t f = f0 + (int64_t)j * 1024;                  // this thread's 4 floats: [f, f + 4)
+                if (f >= 0 && f + 3 < total) {
+                    *reinterpret_cast<float4*>(out + f) = make_float4(0.f, 0.f, 0.f, 0.f);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (f + k >= 0 && f + k < total) out[f + k] = 0.f;
+                }
+            }
+            return;
+        }
 #pragma unroll
         for (int j = 0; j < MOVE_EPT; ++j) {
             const int64_t e = base + j * 256 + threadIdx.x;
             if (e >= total) break;
-            if (kind == SC_DENSIFY_MOMENT) { out[e] = 0.f; continue; }               // cat_optimizer :396-397
             const int L = rem0 + j * 256 + (int)threadIdx.x;
             const int dr = L / w, c = L - dr * w;
             const int64_t orow = row0 + dr;
             if (orow < S.n_clone) {
                 out[e] = __ldg(src + (int64_t)__ldg(S.clone_src + orow) * w + c);
             } else {
-                const int64_t q = orow - S.n_clone;
-                const int cp = (int)(q / S.n_child);
-                const int64_t r = q - cp * S.n_child;
+                const unsigned q = (unsigned)(orow - S.n_clone), nc = (unsigned)S.n_child;   // appended rows < 2^31 (host check)
+                const int cp = (int)(q / nc);
+                const int64_t r = q - cp * nc;
                 const int64_t row = __ldg(S.child_src + r);
                 const float v = __ldg(src + row * w + c);
                 float o = v;
@@ -232,6 +247,7 @@ extern "C" int sc_densify_move(int64_t N, const int32_t* flags, const int64_t* d
     SC_CHECK_ARG(flags && dest_index && src && dst && row_floats && kinds, "null pointer");
     const int64_t n_app = n_clone + (int64_t)n_copies * n_child;
     SC_CHECK_ARG(n_app == 0 || index_ws, "index workspace");
+    SC_CHECK_ARG(n_app < (1ll << 31), "appended row count");
     SplitCtx S{n_stay, n_clone, n_child, n_split, n_copies, noise, scaling, rotation, split_shrink,
                index_ws, index_ws + n_clone, index_ws + n_clone + n_child};
     if (n_app > 0) {
@@ -255,7 +271,7 @@ extern "C" int sc_densify_move(int64_t N, const int32_t* flags, const int64_t* d
             T.rows_per_cta[a] = R;
             blocks += n_stay == 0 ? 0 : vec ? sc_div_up(N * (w / 4), 256) : R > 0 ? sc_div_up(N, R) : sc_div_up(N * w, 256 * MOVE_EPT);
             T.block_end[2 * a] = (unsigned)blocks;
-            blocks += sc_div_up(n_app * w, 256 * MOVE_EPT);
+            blocks += k == SC_DENSIFY_MOMENT ? sc_div_up(n_app * w + 3, 1024 * MOVE_EPT) : sc_div_up(n_app * w, 256 * MOVE_EPT);
             SC_CHECK_ARG(blocks < (1ll << 31), "N * row width");
         } else {
             T.src[a] = nullptr; T.dst[a] = nullptr; T.width[a] = 1; T.kind[a] = 0; T.rows_per_cta[a] = 0;
