@@ -24,6 +24,7 @@
  *   sc_densification_stats     set_max_radii2D + add_densification_stats
  *                                                              street_gaussian/models/street_gaussian_model.py:486-519
  *   sc_assemble_fwd/bwd        StreetGaussianModel.get_xyz / get_rotation  street_gaussian/models/street_gaussian_model.py:296-364
+ *   sc_assemble_features_fwd/bwd  StreetGaussianModel.get_features (Fourier DC of the actors)  street_gaussian/models/street_gaussian_model.py:366-386
  *   sc_assemble_act_fwd/bwd    StreetGaussianModel.get_scaling / get_opacity  street_gaussian/models/street_gaussian_model.py:273-294, :389-407
  *   sc_densify_classify/move   densify_and_prune (clone + split + prune)  street_gaussian/models/gaussian_model.py:433-551
  *
@@ -324,6 +325,20 @@ int sc_assemble_act_bwd(int n_segments, const int64_t* host_seg_start, const flo
                         const float* const* host_opacity, const float* host_clamp_max,
                         const float* v_out_scaling /*[N,3]*/, const float* v_out_opacity /*[N]*/,
                         float* const* host_v_scaling, float* const* host_v_opacity, void* stream);
+
+/* N2, features of the concatenated set: StreetGaussianModel.get_features (street_gaussian_model.py:366-386) —
+ * cat(f_dc, f_rest) per model (gaussian_model.py:238-241); for actors the DC colour is the inverse Fourier sum
+ * over n_fourier[s] coefficients, sum_c f_dc[:, c, :] * idft_base[s][c] (get_features_fourier,
+ * gaussian_model_actor.py:67-76; idft_base = IDFT(time, C) of street_gaussian/utils/sh_utils.py:120-130, evaluated by
+ * the host).  f_dc[s] is [n_s, n_fourier[s], 3], f_rest[s] [n_s, K-1, 3], out_features [N, K, 3];
+ * host_idft_base is a HOST float[n_segments][SC_ASSEMBLE_MAX_FOURIER] (plain segments: n_fourier 1, base 1). */
+#define SC_ASSEMBLE_MAX_FOURIER 8
+int sc_assemble_features_fwd(int n_segments, const int64_t* host_seg_start, int K, const float* const* host_f_dc,
+                             const float* const* host_f_rest, const int* host_n_fourier, const float* host_idft_base,
+                             float* out_features, void* stream);
+int sc_assemble_features_bwd(int n_segments, const int64_t* host_seg_start, int K, const int* host_n_fourier,
+                             const float* host_idft_base, const float* v_out_features, float* const* host_v_f_dc,
+                             float* const* host_v_f_rest, void* stream);
 
 /* ---- A10: distCUDA2 -------------------------------------------------------------------- */
 /* points[P,3] -> mean squared distance to the 3 nearest other points [P] (+inf if P < 4,

@@ -58,3 +58,26 @@ def assemble_activations(segments):
         scs.append(sc)
         ops.append(torch.sigmoid(s["opacity"]))
     return torch.cat(scs, 0), torch.cat(ops, 0)
+
+
+def idft(time, dim):                                                     # sh_utils.py:120-130
+    t = torch.tensor(float(time)).view(-1, 1)
+    out = torch.zeros(1, dim)
+    idx = torch.arange(dim)
+    out[:, idx[::2]] = torch.cos(torch.pi * t * idx[::2])
+    out[:, idx[1::2]] = torch.sin(torch.pi * t * (idx[1::2] + 1))
+    return out
+
+
+def assemble_features(segments):
+    """segments: dicts with `f_dc` [n,C,3], `f_rest` [n,K-1,3] and, for actors, `idft_base` [C].
+    -> get_features [N,K,3]: street_gaussian_model.py:366-386 over gaussian_model.py:238-241 (plain models) and
+    gaussian_model_actor.py:67-76 (`get_features_fourier`)."""
+    feats = []
+    for s in segments:
+        dc = s["f_dc"]
+        if s.get("idft_base") is not None:
+            base = torch.as_tensor(s["idft_base"], dtype=torch.float32, device=dc.device)
+            dc = torch.sum(dc * base[..., None], dim=1, keepdim=True)    # :72
+        feats.append(torch.cat([dc, s["f_rest"]], dim=1))                # :74 / gaussian_model.py:241
+    return torch.cat(feats, 0)

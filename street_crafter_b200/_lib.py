@@ -36,6 +36,8 @@ SIGNATURES = {
     "sc_assemble_bwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_assemble_act_fwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_assemble_act_bwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_assemble_features_fwd": (_i32, [_i32, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_assemble_features_bwd": (_i32, [_i32, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_densification_stats": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "sc_rasterize_fwd_depth": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                       _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),

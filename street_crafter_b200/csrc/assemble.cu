@@ -306,6 +306,85 @@ int fill_act_table(ActTable& T, int n_segments, const int64_t* seg_start, const 
     return SC_OK;
 }
 
+// ---- features of the concatenated set: get_features (:366-386) ------------------------------------------------
+// plain segment: cat(f_dc [n,1,3], f_rest [n,K-1,3]) (gaussian_model.py:238-241); actor segment: the DC colour is the
+// inverse Fourier sum over the actor's C coefficients, sum_c f_dc[:,c,:] * idft_base[c] (get_features_fourier,
+// gaussian_model_actor.py:67-76; idft_base = IDFT(time, C), sh_utils.py:120-130, evaluated by the host).
+// One float of the [N, K, 3] output per lane access, consecutive lanes on consecutive floats.
+struct FeatTable {
+    int64_t start[SC_ASSEMBLE_MAX_SEGMENTS + 1];
+    const float* f_dc[SC_ASSEMBLE_MAX_SEGMENTS];
+    const float* f_rest[SC_ASSEMBLE_MAX_SEGMENTS];
+    float* v_f_dc[SC_ASSEMBLE_MAX_SEGMENTS];        // backward only
+    float* v_f_rest[SC_ASSEMBLE_MAX_SEGMENTS];
+    int n_fourier[SC_ASSEMBLE_MAX_SEGMENTS];
+    float base[SC_ASSEMBLE_MAX_SEGMENTS][SC_ASSEMBLE_MAX_FOURIER];
+    int n;
+    int row;                                        // 3 K floats per output row
+};
+constexpr int FEAT_EPT = 4;
+
+template <bool BWD>
+__global__ void __launch_bounds__(256)
+assemble_feat_kernel(FeatTable T, float* __restrict__ out, const float* __restrict__ v_out) {
+    const int row = T.row;
+    const int64_t e0 = T.start[0] * row, e1 = T.start[T.n] * row;
+#pragma unroll
+    for (int j = 0; j < FEAT_EPT; ++j) {
+        const int64_t e = e0 + ((int64_t)blockIdx.x * FEAT_EPT + j) * 256 + threadIdx.x;
+        if (e >= e1) return;
+        const int64_t i = e / row;
+        const int c = (int)(e - i * row);
+        int s = 0;
+        while (s < T.n - 1 && i >= T.start[s + 1]) ++s;
+        const int64_t k = i - T.start[s];
+        const int C = T.n_fourier[s];
+        if (!BWD) {
+            float v;
+            if (c < 3) {
+                v = 0.f;
+                for (int f = 0; f < C; ++f) v += __ldg(T.f_dc[s] + (k * C + f) * 3 + c) * T.base[s][f];
+            } else {
+                v = __ldg(T.f_rest[s] + k * (row - 3) + (c - 3));
+            }
+            out[e] = v;
+        } else {
+            const float g = __ldg(v_out + e);
+            if (c < 3) {
+                if (T.v_f_dc[s])
+                    for (int f = 0; f < C; ++f) T.v_f_dc[s][(k * C + f) * 3 + c] = g * T.base[s][f];
+            } else if (T.v_f_rest[s]) {
+                T.v_f_rest[s][k * (row - 3) + (c - 3)] = g;
+            }
+        }
+    }
+}
+
+int fill_feat_table(FeatTable& T, int n_segments, const int64_t* seg_start, int K, const float* const* f_dc,
+                    const float* const* f_rest, const int* n_fourier, const float* idft_base, float* const* v_f_dc,
+                    float* const* v_f_rest) {
+    const bool fwd = v_f_dc == nullptr;     // the backward never reads the parameters
+    SC_CHECK_ARG(n_segments >= 1 && n_segments <= SC_ASSEMBLE_MAX_SEGMENTS && K >= 1 && K <= 64, "segment count / K");
+    SC_CHECK_ARG(seg_start && n_fourier && idft_base && (!fwd || (f_dc && f_rest)), "null table");
+    T.n = n_segments;
+    T.row = 3 * K;
+    for (int s = 0; s < SC_ASSEMBLE_MAX_SEGMENTS; ++s) {
+        const bool in = s < n_segments;
+        if (in) {
+            SC_CHECK_ARG(seg_start[s + 1] >= seg_start[s], "segment starts must not decrease");
+            SC_CHECK_ARG(n_fourier[s] >= 1 && n_fourier[s] <= SC_ASSEMBLE_MAX_FOURIER, "fourier dimension");
+            if (fwd) SC_CHECK_ARG(seg_start[s + 1] == seg_start[s] || (f_dc[s] && (K == 1 || f_rest[s])), "segment arrays");
+        }
+        T.f_dc[s] = (in && fwd) ? f_dc[s] : nullptr; T.f_rest[s] = (in && fwd) ? f_rest[s] : nullptr;
+        T.v_f_dc[s] = (in && v_f_dc) ? v_f_dc[s] : nullptr; T.v_f_rest[s] = (in && v_f_rest) ? v_f_rest[s] : nullptr;
+        T.n_fourier[s] = in ? n_fourier[s] : 1;
+        for (int f = 0; f < SC_ASSEMBLE_MAX_FOURIER; ++f)
+            T.base[s][f] = (in && f < n_fourier[s]) ? idft_base[s * SC_ASSEMBLE_MAX_FOURIER + f] : 0.f;
+    }
+    for (int s = 0; s <= SC_ASSEMBLE_MAX_SEGMENTS; ++s) T.start[s] = seg_start[s <= n_segments ? s : n_segments];
+    return SC_OK;
+}
+
 }  // namespace
 
 extern "C" int sc_assemble_fwd(int n_segments, const int64_t* seg_start, const float* const* xyz,
@@ -374,5 +453,38 @@ extern "C" int sc_assemble_act_bwd(int n_segments, const int64_t* seg_start, con
     SC_CHECK_ARG(v_out_scaling && v_out_opacity, "upstream gradients");
     assemble_act_bwd_kernel<<<(unsigned)sc_div_up(n, 256), 256, 0, (cudaStream_t)stream>>>(T, v_out_scaling, v_out_opacity);
     SC_CHECK_LAUNCH("assemble_act_bwd_kernel");
+    return SC_OK;
+}
+
+extern "C" int sc_assemble_features_fwd(int n_segments, const int64_t* seg_start, int K, const float* const* f_dc,
+                                        const float* const* f_rest, const int* n_fourier, const float* idft_base,
+                                        float* out_features, void* stream) {
+    FeatTable T;
+    const int rc = fill_feat_table(T, n_segments, seg_start, K, f_dc, f_rest, n_fourier, idft_base, nullptr, nullptr);
+    if (rc != SC_OK) return rc;
+    const int64_t n = (T.start[T.n] - T.start[0]) * T.row;
+    if (n == 0) return SC_OK;
+    SC_CHECK_ARG(out_features, "output");
+    const int64_t blocks = sc_div_up(n, 256 * FEAT_EPT);
+    SC_CHECK_ARG(blocks < (1ll << 31), "N * K");
+    assemble_feat_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(T, out_features, nullptr);
+    SC_CHECK_LAUNCH("assemble_feat_kernel<fwd>");
+    return SC_OK;
+}
+
+extern "C" int sc_assemble_features_bwd(int n_segments, const int64_t* seg_start, int K, const int* n_fourier,
+                                        const float* idft_base, const float* v_out_features, float* const* v_f_dc,
+                                        float* const* v_f_rest, void* stream) {
+    SC_CHECK_ARG(v_f_dc && v_f_rest, "null gradient table");
+    FeatTable T;
+    const int rc = fill_feat_table(T, n_segments, seg_start, K, nullptr, nullptr, n_fourier, idft_base, v_f_dc, v_f_rest);
+    if (rc != SC_OK) return rc;
+    const int64_t n = (T.start[T.n] - T.start[0]) * T.row;
+    if (n == 0) return SC_OK;
+    SC_CHECK_ARG(v_out_features, "upstream gradient");
+    const int64_t blocks = sc_div_up(n, 256 * FEAT_EPT);
+    SC_CHECK_ARG(blocks < (1ll << 31), "N * K");
+    assemble_feat_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(T, nullptr, v_out_features);
+    SC_CHECK_LAUNCH("assemble_feat_kernel<bwd>");
     return SC_OK;
 }

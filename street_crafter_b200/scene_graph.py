@@ -194,3 +194,83 @@ def assemble_scaling_opacity(segments: Sequence[Dict[str, Optional[Tensor]]]):
         cm = s.get("scaling_clamp_max")
         clamp.append(float("inf") if cm is None else float(cm))
     return _AssembleAct.apply(tuple(clamp), *tensors)
+
+
+MAX_FOURIER = 8        # SC_ASSEMBLE_MAX_FOURIER
+
+
+class _AssembleFeatures(torch.autograd.Function):
+    @staticmethod
+    def _tables(starts, n_fourier, bases):
+        n = len(n_fourier)
+        flat = []
+        for b in bases:
+            flat += list(b) + [0.0] * (MAX_FOURIER - len(b))
+        return n, (C.c_int64 * (n + 1))(*starts), (C.c_int * n)(*n_fourier), (C.c_float * (n * MAX_FOURIER))(*flat)
+
+    @staticmethod
+    def forward(ctx, bases, *tensors):
+        dev = tensors[0].device
+        segs = [(tensors[i].contiguous(), tensors[i + 1].contiguous()) for i in range(0, len(tensors), 2)]
+        K = segs[0][1].shape[1] + 1
+        starts = [0]
+        for dc, _ in segs:
+            starts.append(starts[-1] + dc.shape[0])
+        out = torch.empty((starts[-1], K, 3), dtype=torch.float32, device=dev)
+        st = torch.cuda.current_stream().cuda_stream
+        ptr = lambda t: t.data_ptr() if t.numel() else None
+        with torch.cuda.device(dev):
+            for a in range(0, len(segs), MAX_SEGMENTS):
+                part = segs[a:a + MAX_SEGMENTS]
+                n, c_starts, c_nf, c_base = _AssembleFeatures._tables(starts[a:a + len(part) + 1],
+                                                                     [s[0].shape[1] for s in part], bases[a:a + len(part)])
+                check(lib.sc_assemble_features_fwd(n, c_starts, K, (C.c_void_p * n)(*[ptr(s[0]) for s in part]),
+                                                   (C.c_void_p * n)(*[ptr(s[1]) for s in part]), c_nf, c_base,
+                                                   out.data_ptr(), st), "sc_assemble_features_fwd")
+        ctx.shapes, ctx.starts, ctx.bases, ctx.K = [(s[0].shape, s[1].shape) for s in segs], starts, bases, K
+        return out
+
+    @staticmethod
+    def backward(ctx, v_out):
+        v_out = v_out.float().contiguous()
+        dev, starts, K = v_out.device, ctx.starts, ctx.K
+        need = iter(ctx.needs_input_grad[1:])
+        gsegs = []
+        for dc_shape, rest_shape in ctx.shapes:
+            gdc = torch.empty(dc_shape, dtype=torch.float32, device=dev) if next(need) else None
+            grest = torch.empty(rest_shape, dtype=torch.float32, device=dev) if next(need) else None
+            gsegs.append((gdc, grest))
+        st = torch.cuda.current_stream().cuda_stream
+        ptr = lambda t: t.data_ptr() if t is not None and t.numel() else None
+        with torch.cuda.device(dev):
+            for a in range(0, len(gsegs), MAX_SEGMENTS):
+                part = gsegs[a:a + MAX_SEGMENTS]
+                n, c_starts, c_nf, c_base = _AssembleFeatures._tables(
+                    starts[a:a + len(part) + 1], [s[0][1] for s in ctx.shapes[a:a + len(part)]], ctx.bases[a:a + len(part)])
+                check(lib.sc_assemble_features_bwd(n, c_starts, K, c_nf, c_base, v_out.data_ptr(),
+                                                   (C.c_void_p * n)(*[ptr(g[0]) for g in part]),
+                                                   (C.c_void_p * n)(*[ptr(g[1]) for g in part]), st),
+                      "sc_assemble_features_bwd")
+        return (None,) + tuple(x for g in gsegs for x in g)
+
+
+def assemble_features(segments: Sequence[Dict[str, Optional[Tensor]]]):
+    """segments in scene-graph order: dicts with `f_dc` [n,C,3] and `f_rest` [n,K-1,3]; actors (C = fourier_dim) add
+    `idft_base` — the C floats `IDFT(time, C)[0]` of gaussian_model_actor.py:67-71 (plain models: C = 1, base 1).
+    -> `get_features` [N,K,3] of street_gaussian_model.py:366-386, differentiable."""
+    if not segments:
+        raise ValueError("assemble_features needs at least one segment")
+    tensors, bases = [], []
+    K = segments[0]["f_rest"].shape[1] + 1
+    for s in segments:
+        dc, rest = s["f_dc"], s["f_rest"]
+        if not (dc.is_cuda and rest.is_cuda):
+            raise RuntimeError("assemble_features needs CUDA tensors: street_crafter_b200 has no CPU path")
+        assert dc.dtype == torch.float32 and rest.dtype == torch.float32 and dc.dim() == 3 and dc.shape[2] == 3 and \
+            rest.shape == (dc.shape[0], K - 1, 3) and 1 <= dc.shape[1] <= MAX_FOURIER, (dc.shape, rest.shape)
+        base = s.get("idft_base")
+        base = [1.0] if base is None else [float(v) for v in (base.tolist() if isinstance(base, Tensor) else base)]
+        assert len(base) == dc.shape[1], (len(base), dc.shape)
+        tensors += [dc, rest]
+        bases.append(tuple(base))
+    return _AssembleFeatures.apply(tuple(bases), *tensors)

@@ -1053,3 +1053,52 @@ def test_assemble_activations_vs_oracle_cfg2(S, dev):
     assert ((s1 - s0).abs() <= 2e-6 * s0.abs()).all() and (o1 - o0).abs().max() < 1e-6
     for (name, k, a), (_, _, b) in zip(g1, g0):
         assert (a - b).abs().max() <= 1e-5 * max(1.0, float(b.abs().max())), (name, k)
+
+
+def test_assemble_features_vs_reference_golden(S, dev):
+    """get_features (Fourier DC of the actors, cat with the rest coefficients) of the reference's own bodies"""
+    from street_crafter_b200.scene_graph import assemble_features
+    from test_oracle_cpu import _assemble_golden_segments
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "assemble.npz"))
+    segs = _assemble_golden_segments(z, to=lambda t: t.to(dev))
+    fea = assemble_features(segs)
+    want = torch.from_numpy(z["out_features"])
+    assert fea.shape == want.shape and (fea.detach().cpu() - want).abs().max() < 1e-6
+    (fea * torch.from_numpy(z["w_features"]).to(dev)).sum().backward()
+    for s in segs:
+        for key, t in (("v_f_dc", s["f_dc"]), ("v_f_rest", s["f_rest"])):
+            w = torch.from_numpy(z[f"{s['name']}_{key}"])
+            got = t.grad if t.grad is not None else torch.zeros_like(t)
+            assert got.shape == w.shape, (s["name"], key)
+            if w.numel():
+                assert (got.cpu() - w).abs().max() < 1e-6, (s["name"], key)
+
+
+@pytest.mark.parametrize("K", [16, 4, 1])
+def test_assemble_features_vs_oracle_cfg2(S, dev, K):
+    """1.9 M background + 40 actors (fourier_dim 1..5, two kernel calls) + sky, SH degree 3 / 1 / 0"""
+    from oracle.assemble_torch import assemble_features as oracle_features, idft
+    from street_crafter_b200.scene_graph import assemble_features
+    g = torch.Generator().manual_seed(K)
+    leaf = lambda *s: torch.randn(*s, generator=g).to(dev).requires_grad_(True)
+    sizes = [(1_900_000 if K == 16 else 50_000, 1)] + [(2500 + a, 1 + a % 5) for a in range(40)] + [(10_000, 1)]
+    segs = []
+    for i, (n, C) in enumerate(sizes):
+        s = {"name": str(i), "f_dc": leaf(n, C, 3), "f_rest": leaf(n, K - 1, 3)}
+        if 0 < i <= 40:
+            s["idft_base"] = idft(0.1 + 0.02 * i, C)[0].tolist()
+        segs.append(s)
+    N = sum(n for n, _ in sizes)
+    w = torch.randn(N, K, 3, generator=g).to(dev)
+    res = []
+    for fn in (oracle_features, assemble_features):
+        f = fn(segs)
+        (f * w).sum().backward()
+        res.append((f.detach(), [(s["f_dc"].grad.clone(), s["f_rest"].grad.clone() if s["f_rest"].grad is not None else None) for s in segs]))
+        for s in segs:
+            s["f_dc"].grad = s["f_rest"].grad = None
+    assert res[1][0].shape == (N, K, 3) and (res[1][0] - res[0][0]).abs().max() < 2e-6
+    for (a_dc, a_r), (b_dc, b_r) in zip(res[1][1], res[0][1]):
+        assert (a_dc - b_dc).abs().max() < 2e-6
+        if b_r is not None and b_r.numel():
+            assert torch.equal(a_r, b_r)

@@ -355,7 +355,10 @@ def _assemble_golden_segments(z, to=lambda t: t, grad=True):
     for name in z["names"]:
         name = str(name)
         mk = lambda k: to(torch.from_numpy(z[f"{name}_{k}"])).requires_grad_(grad)
-        s = {"name": name, "xyz": mk("xyz"), "rotation": mk("rot"), "scaling": mk("scaling"), "opacity": mk("opacity")}
+        s = {"name": name, "xyz": mk("xyz"), "rotation": mk("rot"), "scaling": mk("scaling"), "opacity": mk("opacity"),
+             "f_dc": mk("f_dc"), "f_rest": mk("f_rest")}
+        if name.startswith("obj_"):
+            s["idft_base"] = [float(v) for v in z["actor_idft_base"]]
         if name == "sky":
             s["scaling_clamp_max"] = float(z["sky_clamp_max"])
         if name.startswith("obj_"):
@@ -401,3 +404,19 @@ def test_assemble_activations_oracle_matches_reference_golden():
         for key, t in (("v_scaling", s["scaling"]), ("v_opacity", s["opacity"])):
             got = t.grad if t.grad is not None else torch.zeros_like(t)
             assert torch.allclose(got, torch.from_numpy(z[f"{s['name']}_{key}"]), atol=1e-7, rtol=1e-5), (s["name"], key)
+
+
+def test_assemble_features_oracle_matches_reference_golden():
+    """get_features of the reference's StreetGaussianModel (actors through get_features_fourier + IDFT) incl. gradients"""
+    import numpy as np
+    from oracle.assemble_torch import assemble_features, idft
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "assemble.npz"))
+    assert torch.allclose(idft((31 - 10) / (58 - 10), 5)[0], torch.from_numpy(z["actor_idft_base"]), atol=1e-7)
+    segs = _assemble_golden_segments(z)
+    fea = assemble_features(segs)
+    assert torch.allclose(fea, torch.from_numpy(z["out_features"]), atol=1e-6, rtol=1e-6)
+    (fea * torch.from_numpy(z["w_features"])).sum().backward()
+    for s in segs:
+        for key, t in (("v_f_dc", s["f_dc"]), ("v_f_rest", s["f_rest"])):
+            got = t.grad if t.grad is not None else torch.zeros_like(t)
+            assert torch.allclose(got, torch.from_numpy(z[f"{s['name']}_{key}"]), atol=1e-6, rtol=1e-6), (s["name"], key)
