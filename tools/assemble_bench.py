@@ -36,3 +36,25 @@ ref = t_ms(lambda: step(lambda: oracle_assemble(segs, fq, 1)))
 moved = N * (56 + 84)
 print(f"assemble fwd+bwd, {N} Gaussians in {len(segs)} segments: {ours:.3f} ms ({moved/ours/1e6:.0f} GB/s algorithmic, "
       f"autograd glue included); torch op chain of the reference: {ref:.3f} ms ({ref/ours:.1f}x)")
+
+# ---- activations and features of the same scene graph (fourier_dim 1, SH degree 3) ----
+from oracle.assemble_torch import assemble_activations as oracle_act, assemble_features as oracle_feat
+from street_crafter_b200.scene_graph import assemble_features, assemble_scaling_opacity
+for s in segs:
+    n = s["xyz"].shape[0]
+    s.update(scaling=leaf(n, 3), opacity=leaf(n, 1), f_dc=leaf(n, 1, 3), f_rest=leaf(n, 15, 3))
+    if "pose_rot" in s:
+        s["idft_base"] = [1.0]
+leaves = [t for s in segs for t in s.values() if isinstance(t, torch.Tensor) and t.requires_grad]
+w_s, w_o, w_f = torch.randn(N, 3, device=dev), torch.randn(N, 1, device=dev), torch.randn(N, 16, 3, device=dev)
+def step2(fn, ws):
+    outs = fn()
+    outs = list(outs) if isinstance(outs, tuple) else [outs]
+    torch.autograd.backward(outs, ws)
+    for t in leaves: t.grad = None
+a_ours = t_ms(lambda: step2(lambda: assemble_scaling_opacity(segs), [w_s, w_o]))
+a_ref = t_ms(lambda: step2(lambda: oracle_act(segs), [w_s, w_o]))
+f_ours = t_ms(lambda: step2(lambda: assemble_features(segs), [w_f]))
+f_ref = t_ms(lambda: step2(lambda: oracle_feat(segs), [w_f]))
+print(f"scaling/opacity fwd+bwd: {a_ours:.3f} ms ({N*64/a_ours/1e6:.0f} GB/s algorithmic); torch op chain: {a_ref:.3f} ms")
+print(f"features fwd+bwd (K=16): {f_ours:.3f} ms ({N*768/f_ours/1e6:.0f} GB/s algorithmic); torch op chain: {f_ref:.3f} ms")
