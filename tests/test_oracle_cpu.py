@@ -420,3 +420,22 @@ def test_assemble_features_oracle_matches_reference_golden():
         for key, t in (("v_f_dc", s["f_dc"]), ("v_f_rest", s["f_rest"])):
             got = t.grad if t.grad is not None else torch.zeros_like(t)
             assert torch.allclose(got, torch.from_numpy(z[f"{s['name']}_{key}"]), atol=1e-6, rtol=1e-6), (s["name"], key)
+
+
+def test_scene_graph_and_densify_wrappers_have_no_cpu_path():
+    """the product wrappers of the N2 / N4 rows refuse CPU tensors before touching the library (no fallback)"""
+    from street_crafter_b200.compaction import compact_rows
+    from street_crafter_b200.densify import densify_and_prune
+    from street_crafter_b200.scene_graph import assemble_features, assemble_scaling_opacity, assemble_xyz_rotation
+    z3, z4, z1 = torch.zeros(2, 3), torch.ones(2, 4), torch.zeros(2, 1)
+    with pytest.raises(RuntimeError):
+        assemble_xyz_rotation([{"xyz": z3, "rotation": z4}])
+    with pytest.raises(RuntimeError):
+        assemble_scaling_opacity([{"scaling": z3, "opacity": z1}])
+    with pytest.raises(RuntimeError):
+        assemble_features([{"f_dc": torch.zeros(2, 1, 3), "f_rest": torch.zeros(2, 15, 3)}])
+    with pytest.raises(RuntimeError):
+        densify_and_prune({"xyz": z3, "scaling": z3, "rotation": z4, "opacity": z1}, {}, {}, torch.zeros(2, 2), z1,
+                          2e-4, 5e-3, 10.0, 20)
+    with pytest.raises(RuntimeError):
+        compact_rows(torch.ones(2, dtype=torch.bool), [z3])
