@@ -324,19 +324,26 @@ struct FeatTable {
 };
 constexpr int FEAT_EPT = 4;
 
-template <bool BWD>
+// ROW = 3 K as a compile-time constant for the reference's SH degrees 3 / 1 (row / column split by multiply-shift,
+// one 64-bit division per thread instead of one per float), 0 = any K.
+template <bool BWD, int ROW>
 __global__ void __launch_bounds__(256)
 assemble_feat_kernel(FeatTable T, float* __restrict__ out, const float* __restrict__ v_out) {
-    const int row = T.row;
+    const int row = ROW ? ROW : T.row;
     const int64_t e0 = T.start[0] * row, e1 = T.start[T.n] * row;
+    const int64_t base = e0 + (int64_t)blockIdx.x * (256 * FEAT_EPT);
+    const int64_t i0 = base / row;
+    const int rem0 = (int)(base - i0 * row);
+    int s = 0;
 #pragma unroll
     for (int j = 0; j < FEAT_EPT; ++j) {
-        const int64_t e = e0 + ((int64_t)blockIdx.x * FEAT_EPT + j) * 256 + threadIdx.x;
+        const int64_t e = base + j * 256 + threadIdx.x;
         if (e >= e1) return;
-        const int64_t i = e / row;
-        const int c = (int)(e - i * row);
-        int s = 0;
-        while (s < T.n - 1 && i >= T.start[s + 1]) ++s;
+        const unsigned L = (unsigned)(rem0 + j * 256 + (int)threadIdx.x);
+        const unsigned di = L / (unsigned)row;
+        const int c = (int)(L - di * (unsigned)row);
+        const int64_t i = i0 + di;
+        while (s < T.n - 1 && i >= T.start[s + 1]) ++s;      // i only grows with j
         const int64_t k = i - T.start[s];
         const int C = T.n_fourier[s];
         if (!BWD) {
@@ -358,6 +365,66 @@ assemble_feat_kernel(FeatTable T, float* __restrict__ out, const float* __restri
             }
         }
     }
+}
+
+// ROW a multiple of 4 floats (K = 16, 4): a thread owns one 16-byte piece of an output row — piece 0 is
+// [dc.r, dc.g, dc.b, rest[0]], piece p >= 1 is rest[4p-3 .. 4p] — float4 on the [N, K, 3] side, scalars on the
+// model side (rows of 45 / 9 floats are not 16-byte aligned).
+template <bool BWD, int ROW>
+__global__ void __launch_bounds__(256)
+assemble_feat_vec_kernel(FeatTable T, float* __restrict__ out, const float* __restrict__ v_out) {
+    constexpr int PIECES = ROW / 4;
+    const int64_t p0 = T.start[0] * PIECES, p1 = T.start[T.n] * PIECES;
+    int s = 0;
+#pragma unroll
+    for (int j = 0; j < FEAT_EPT; ++j) {
+        const int64_t P = p0 + ((int64_t)blockIdx.x * FEAT_EPT + j) * 256 + threadIdx.x;
+        if (P >= p1) return;
+        const int64_t i = P / PIECES;
+        const int p = (int)(P - i * PIECES);
+        while (s < T.n - 1 && i >= T.start[s + 1]) ++s;
+        const int64_t k = i - T.start[s];
+        const int C = T.n_fourier[s];
+        if (!BWD) {
+            const float* r = T.f_rest[s] + k * (ROW - 3) + 4 * p - 3;
+            float4 v;
+            if (p == 0) {
+                float d[3] = {0.f, 0.f, 0.f};
+                for (int f = 0; f < C; ++f) {
+                    const float b = T.base[s][f];
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) d[c] += __ldg(T.f_dc[s] + (k * C + f) * 3 + c) * b;
+                }
+                v = make_float4(d[0], d[1], d[2], __ldg(r + 3));
+            } else {
+                v = make_float4(__ldg(r), __ldg(r + 1), __ldg(r + 2), __ldg(r + 3));
+            }
+            reinterpret_cast<float4*>(out)[P] = v;
+        } else {
+            const float4 g = __ldg(reinterpret_cast<const float4*>(v_out) + P);
+            float* r = T.v_f_rest[s] ? T.v_f_rest[s] + k * (ROW - 3) + 4 * p - 3 : nullptr;
+            if (p == 0) {
+                if (T.v_f_dc[s])
+                    for (int f = 0; f < C; ++f) {
+                        const float b = T.base[s][f];
+                        float* d = T.v_f_dc[s] + (k * C + f) * 3;
+                        d[0] = g.x * b; d[1] = g.y * b; d[2] = g.z * b;
+                    }
+                if (r) r[3] = g.w;
+            } else if (r) {
+                r[0] = g.x; r[1] = g.y; r[2] = g.z; r[3] = g.w;
+            }
+        }
+    }
+}
+
+template <bool BWD>
+void launch_feat(const FeatTable& T, int64_t n_floats, float* out, const float* v_out, cudaStream_t st) {
+    const bool aligned = ((((uintptr_t)out) | ((uintptr_t)v_out)) & 15) == 0;
+    const unsigned vb = (unsigned)sc_div_up(n_floats / 4, 256 * FEAT_EPT), eb = (unsigned)sc_div_up(n_floats, 256 * FEAT_EPT);
+    if (T.row == 48 && aligned) assemble_feat_vec_kernel<BWD, 48><<<vb, 256, 0, st>>>(T, out, v_out);
+    else if (T.row == 12 && aligned) assemble_feat_vec_kernel<BWD, 12><<<vb, 256, 0, st>>>(T, out, v_out);
+    else assemble_feat_kernel<BWD, 0><<<eb, 256, 0, st>>>(T, out, v_out);
 }
 
 int fill_feat_table(FeatTable& T, int n_segments, const int64_t* seg_start, int K, const float* const* f_dc,
@@ -467,7 +534,7 @@ extern "C" int sc_assemble_features_fwd(int n_segments, const int64_t* seg_start
     SC_CHECK_ARG(out_features, "output");
     const int64_t blocks = sc_div_up(n, 256 * FEAT_EPT);
     SC_CHECK_ARG(blocks < (1ll << 31), "N * K");
-    assemble_feat_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(T, out_features, nullptr);
+    launch_feat<false>(T, n, out_features, nullptr, (cudaStream_t)stream);
     SC_CHECK_LAUNCH("assemble_feat_kernel<fwd>");
     return SC_OK;
 }
@@ -484,7 +551,7 @@ extern "C" int sc_assemble_features_bwd(int n_segments, const int64_t* seg_start
     SC_CHECK_ARG(v_out_features, "upstream gradient");
     const int64_t blocks = sc_div_up(n, 256 * FEAT_EPT);
     SC_CHECK_ARG(blocks < (1ll << 31), "N * K");
-    assemble_feat_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(T, nullptr, v_out_features);
+    launch_feat<true>(T, n, nullptr, v_out_features, (cudaStream_t)stream);
     SC_CHECK_LAUNCH("assemble_feat_kernel<bwd>");
     return SC_OK;
 }
