@@ -303,8 +303,12 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
                         image_width: int, image_height: int, tile_size: int, isect_offsets: Tensor,
                         flatten_ids: Tensor, backgrounds: Optional[Tensor] = None,
                         packed: bool = False, absgrad: bool = False, max_hit: int = 0,
-                        return_stats: bool = False):
+                        return_stats: bool = False, return_margin: bool = False):
     """-> (render_colors[C,H,W,CH], render_alphas[C,H,W,1]).
+
+    return_margin: also returns margin[C,H,W] = the smallest RELATIVE distance of any visited
+    (pixel, Gaussian) pair to one of the algorithm's hard discontinuities (alpha = 1/255 accept test,
+    T = 1e-4 stop test): the tests require every pixel that misses the image tolerance to sit on one.
 
     Per pixel centre (j+.5, i+.5), front to back over the tile's sorted list:
       sigma = .5(a dx² + c dy²) + b dx dy;  alpha = min(.999, o·exp(-sigma));
@@ -329,6 +333,7 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
     visited = 0
     contributing = 0
     tiles_c, tiles_a, tiles_pos = [], [], []
+    margin = torch.full((C, tile_h * tile_size, tile_w * tile_size), float("inf"), dtype=dt) if return_margin else None
     for c in range(C):
         for t in range(tile_h * tile_w):
             s, e = offs[c * tile_h * tile_w + t], offs[c * tile_h * tile_w + t + 1]
@@ -343,6 +348,7 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
             a, b, cc = cn[g, 0][None], cn[g, 1][None], cn[g, 2][None]
             sigma = 0.5 * (a * dx * dx + cc * dy * dy) + b * dx * dy
             alpha = torch.clamp_max(op[g][None] * torch.exp(-sigma), ALPHA_CAP)
+            raw_alpha = alpha
             keep = (sigma >= 0) & (alpha >= ALPHA_FLOOR)
             if max_hit > 0:
                 keep = keep & (torch.cumsum(keep.to(torch.int32), 1) <= max_hit)
@@ -353,6 +359,15 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
             wgt = torch.where(live, alpha * Tp, torch.zeros_like(alpha))  # [P,G]
             pix = wgt @ col[g]  # [P,CH]
             Tfin = torch.prod(torch.where(live, 1.0 - alpha, torch.ones_like(alpha)), dim=1)
+            if return_margin:
+                with torch.no_grad():
+                    visited_m = Tp > T_STOP  # pairs the front-to-back walk reaches
+                    big = torch.full_like(alpha, float("inf"))
+                    m_a = torch.where(visited_m, (raw_alpha - ALPHA_FLOOR).abs() / ALPHA_FLOOR, big)
+                    m_t = torch.where(visited_m, (Tn - T_STOP).abs() / T_STOP, big)
+                    mm = torch.minimum(m_a, m_t).min(dim=1).values
+                    margin[c, ty * tile_size:(ty + 1) * tile_size, tx * tile_size:(tx + 1) * tile_size] = \
+                        mm.reshape(tile_size, tile_size)
             if return_stats:
                 inb = ((px < image_width) & (py < image_height))[:, None]
                 nlive = live.sum(1, keepdim=True)
@@ -369,6 +384,11 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
     out_a = out_a[:, :image_height, :image_width]
     if backgrounds is not None:
         out_c = out_c + backgrounds[:, None, None, :] * (1.0 - out_a)
+    if return_margin:
+        margin = margin[:, :image_height, :image_width]
+        if return_stats:
+            return out_c, out_a, {"visited": visited, "contributing": contributing, "margin": margin}
+        return out_c, out_a, margin
     if return_stats:
         return out_c, out_a, {"visited": visited, "contributing": contributing}
     return out_c, out_a
@@ -399,10 +419,14 @@ def render_reference_sequence(means, quats, scales, opacities, shs, viewmat, K, 
     colors = spherical_harmonics(sh_degree, dirs, shs[None], masks=radii > 0)
     colors = torch.clamp_min(colors + 0.5, 0.0)
     colors = torch.cat((colors, depths[..., None]), dim=-1)
-    rc, ra = rasterize_to_pixels(means2d, conics, colors, op, width, height, tile_size,
-                                 isect_offsets, flatten_ids)
     if return_aux:
-        return rc, ra, dict(radii=radii, means2d=means2d, depths=depths, conics=conics,
+        rc, ra, margin = rasterize_to_pixels(means2d, conics, colors, op, width, height, tile_size,
+                                             isect_offsets, flatten_ids, return_margin=True)
+    else:
+        rc, ra = rasterize_to_pixels(means2d, conics, colors, op, width, height, tile_size,
+                                     isect_offsets, flatten_ids)
+    if return_aux:
+        return rc, ra, dict(margin=margin, radii=radii, means2d=means2d, depths=depths, conics=conics,
                             compensations=comps, tiles_per_gauss=tpg, isect_ids=isect_ids,
                             flatten_ids=flatten_ids, isect_offsets=isect_offsets, colors=colors,
                             opacities=op)

@@ -120,6 +120,10 @@ template <typename KeyT> struct SortCfg {
     static constexpr int KPT = sizeof(KeyT) == 4 ? SC_SORT_KPT_U32 : SC_SORT_KPT_U64;
     static constexpr int MINB = sizeof(KeyT) == 4 ? SC_SORT_MINB_U32 : SC_SORT_MINB_U64;
 };
+#ifndef SC_SORT_LB_W
+#define SC_SORT_LB_W 8
+#endif
+constexpr int LB_W = SC_SORT_LB_W;  // look-back window: predecessors read per round trip
 constexpr int MAX_PASSES = SC_SORT_MAX_PASSES;
 constexpr uint32_t FLAG_AGG = 1u << 30;
 constexpr uint32_t FLAG_INC = 2u << 30;
@@ -195,9 +199,9 @@ __global__ void __launch_bounds__(SORT_THREADS, SortCfg<KeyT>::MINB)
 onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* __restrict__ keys_in,
                      const uint32_t* __restrict__ vals_in,
                      KeyT* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int nbits,
-                     const uint32_t* __restrict__ digit_offset /*[RADIX] exclusive*/,
+                     const uint32_t* __restrict__ digit_offset /*[RADIX] exclusive, or raw counts*/,
                      volatile uint32_t* __restrict__ lookback /*[tiles][RADIX]*/,
-                     uint32_t* __restrict__ ticket) {
+                     uint32_t* __restrict__ ticket, int hist_is_raw) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SortSmem<KeyT>& sm = *reinterpret_cast<SortSmem<KeyT>*>(smem_raw);
     constexpr int SORT_KPT = SortCfg<KeyT>::KPT;
@@ -260,8 +264,10 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
         }
         const uint32_t count = acc;
         // publish aggregate, then resolve exclusive prefix over previous tiles.  The walk reads
-        // FOUR predecessors per round trip (independent loads), consumes them in order and
-        // re-polls from the first one that is not published yet.
+        // LB_W predecessors per round trip (independent loads), consumes them in order and
+        // re-polls from the first one that is not published yet.  When all tiles of a small sort
+        // are resident at once, tile t resolves after ~t / (2 LB_W) round trips: the width of the
+        // window, not bandwidth, sets the duration of such a pass.
         volatile uint32_t* my = lookback + (size_t)tile * RADIX + d;
         uint32_t excl = 0;
         if (tile == 0) {
@@ -271,12 +277,12 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
             int64_t t = (int64_t)tile - 1;
             bool done = false;
             while (!done) {
-                uint32_t v[4];
+                uint32_t v[LB_W];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) v[u] = (t - u >= 0) ? lookback[(size_t)(t - u) * RADIX + d] : (2u << 30);
+                for (int u = 0; u < LB_W; ++u) v[u] = (t - u >= 0) ? lookback[(size_t)(t - u) * RADIX + d] : (2u << 30);
                 int used = 0;
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < LB_W; ++u) {
                     const uint32_t f = v[u] & FLAG_MASK;
                     if (!done && used == u && f != 0) {
                         excl += v[u] & VAL_MASK;
@@ -303,7 +309,26 @@ onesweep_pass_kernel(int64_t n, const int64_t* __restrict__ n_dev, const KeyT* _
             if (ww < w) wsum += sm.scan_tmp[ww];
         const uint32_t dstart = wsum + incl - count;
         sm.digit_start[d] = dstart;
-        sm.gbase[d] = (int64_t)digit_offset[d] + (int64_t)excl - (int64_t)dstart;
+        uint32_t goff = digit_offset[d];
+        if (hist_is_raw) {
+            // the caller handed the raw digit counts: exclusive scan over the digits here (saves the
+            // separate scan launch of the fused binning pipeline)
+            uint32_t hin = goff;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t2 = __shfl_up_sync(0xffffffffu, hin, o);
+                if (lane >= o) hin += t2;
+            }
+            __syncthreads();  // scan_tmp is re-used
+            if (lane == 31) sm.scan_tmp[w] = hin;
+            __syncthreads();
+            uint32_t hsum = 0;
+#pragma unroll
+            for (int ww = 0; ww < SORT_WARPS; ++ww)
+                if (ww < w) hsum += sm.scan_tmp[ww];
+            goff = hsum + hin - goff;
+        }
+        sm.gbase[d] = (int64_t)goff + (int64_t)excl - (int64_t)dstart;
     }
     __syncthreads();
 
@@ -350,15 +375,17 @@ int sort_histogram(int64_t n_max, const int64_t* n_dev, const KeyT* keys, const 
 // (even number of passes), negative on error.
 template <typename KeyT>
 int sort_run(int64_t n_max, const int64_t* n_dev, KeyT* keys_in, uint32_t* vals_in, KeyT* keys_out,
-             uint32_t* vals_out, const ScSortPlan& plan, void* workspace, cudaStream_t st) {
+             uint32_t* vals_out, const ScSortPlan& plan, void* workspace, cudaStream_t st, bool hist_raw = false) {
     if (n_max == 0) return 0;
     unsigned char* ws = (unsigned char*)workspace;
     uint32_t* hist = (uint32_t*)(ws + plan.hist_off);
     uint32_t* tickets = (uint32_t*)(ws + plan.ticket_off);
     uint32_t* lookback = (uint32_t*)(ws + plan.lookback_off);
     const int passes = plan.pp.passes;
-    sort_hist_scan_kernel<<<passes, RADIX, 0, st>>>(hist);
-    SC_CHECK_LAUNCH("sort_hist_scan_kernel");
+    if (!hist_raw) {
+        sort_hist_scan_kernel<<<passes, RADIX, 0, st>>>(hist);
+        SC_CHECK_LAUNCH("sort_hist_scan_kernel");
+    }
     static bool attr_set = false;  // one flag per KeyT instantiation
     if (!attr_set) {
         SC_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<KeyT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -372,7 +399,7 @@ int sort_run(int64_t n_max, const int64_t* n_dev, KeyT* keys_in, uint32_t* vals_
     for (int p = 0; p < passes; ++p) {
         onesweep_pass_kernel<KeyT><<<(unsigned)plan.tiles, SORT_THREADS, sizeof(SortSmem<KeyT>), st>>>(
             n_max, n_dev, kin, vin, kout, vout, plan.pp.shift[p], plan.pp.nbits[p], hist + p * RADIX,
-            lookback + (size_t)p * plan.tiles * RADIX, tickets + p);
+            lookback + (size_t)p * plan.tiles * RADIX, tickets + p, hist_raw ? 1 : 0);
         SC_CHECK_LAUNCH("onesweep_pass_kernel");
         KeyT* tk = kin; kin = kout; kout = tk;
         uint32_t* tv = vin; vin = vout; vout = tv;
@@ -438,8 +465,9 @@ int sc_sort_histogram_u64(int64_t n_max, const int64_t* n_dev, const uint64_t* k
     return sort_histogram<uint64_t>(n_max, n_dev, keys, plan, ws, st);
 }
 int sc_sort_run_u32(int64_t n_max, const int64_t* n_dev, uint32_t* keys_in, uint32_t* vals_in,
-                    uint32_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st) {
-    return sort_run<uint32_t>(n_max, n_dev, keys_in, vals_in, keys_out, vals_out, plan, ws, st);
+                    uint32_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st,
+                    bool hist_raw) {
+    return sort_run<uint32_t>(n_max, n_dev, keys_in, vals_in, keys_out, vals_out, plan, ws, st, hist_raw);
 }
 int sc_sort_run_u64(int64_t n_max, const int64_t* n_dev, uint64_t* keys_in, uint32_t* vals_in,
                     uint64_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st) {

@@ -36,7 +36,10 @@ int sc_sort_histogram_u64(int64_t n_max, const int64_t* n_dev, const uint64_t* k
 
 // scan the histograms and run the passes.  Returns 0 if the result is in keys_out/vals_out,
 // 1 if it is in keys_in/vals_in, < 0 on error.
+// hist_raw: the histograms in ws are raw counts accumulated by the caller's own kernel (the passes
+// scan them in their prologue; no scan launch).
 int sc_sort_run_u32(int64_t n_max, const int64_t* n_dev, uint32_t* keys_in, uint32_t* vals_in,
-                    uint32_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st);
+                    uint32_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st,
+                    bool hist_raw = false);
 int sc_sort_run_u64(int64_t n_max, const int64_t* n_dev, uint64_t* keys_in, uint32_t* vals_in,
                     uint64_t* keys_out, uint32_t* vals_out, const ScSortPlan& plan, void* ws, cudaStream_t st);

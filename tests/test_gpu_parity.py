@@ -25,7 +25,7 @@ pytestmark = pytest.mark.gpu
 
 IMG_TOL = 1e-4
 GRAD_RTOL = 1e-3
-IMAGE_OUTLIER_FRAC = 2e-5
+IMAGE_OUTLIER_FRAC = 2e-6   # measured: 8 of 3.5e7 compared values, every one on a threshold pair
 IMAGE_OUTLIER_MAX = 8e-3  # ~ 2/255 of a unit colour
 
 
@@ -44,23 +44,57 @@ def cuda(d, dev):
     return {k: v.to(dev) for k, v in d.items()}
 
 
-def assert_image_close(got, want, what, scale=1.0):
+MARGIN_TOL = 2e-3   # an outlier pixel must hold a pair within this RELATIVE distance of alpha = 1/255 or T = 1e-4
+GRAD_ELEM_ATOL = 1e-6   # x max|reference|: the absolute floor of the per-element relative gradient check
+GRAD_ELEM_BAD_FRAC = 1e-4
+
+
+def _record(kind, what, **kw):
+    """parity statistics of this session: printed by conftest's terminal summary, written to
+    gpurun_out/parity_stats.json (DESIGN.md section 2 quotes them)"""
+    test = os.environ.get("PYTEST_CURRENT_TEST", "").split(" ")[0].split("::")[-1]
+    getattr(pytest, "parity_stats", []).append(dict(kind=kind, test=test, what=what, **kw))
+
+
+def assert_image_close(got, want, what, scale=1.0, margin=None):
+    """1e-4 max-abs (north_star), except pixels that sit on a hard discontinuity of the algorithm: at most
+    IMAGE_OUTLIER_FRAC of the values, none above IMAGE_OUTLIER_MAX, and — when the oracle's `margin` map
+    ([C,H,W], oracle/gsplat_torch.py rasterize_to_pixels(return_margin=True)) is given — EVERY one of them on a
+    pixel that holds a (pixel, Gaussian) pair within MARGIN_TOL of the alpha = 1/255 or T = 1e-4 test."""
     diff = (got.cpu() - want).abs() / scale
     bad = diff > IMG_TOL
-    frac = bad.float().mean().item()
-    assert frac <= IMAGE_OUTLIER_FRAC, f"{what}: {bad.sum().item()} of {bad.numel()} values off by > {IMG_TOL}"
+    n_bad = int(bad.sum())
+    frac = n_bad / max(1, bad.numel())
+    off_margin = None
+    if margin is not None and n_bad:
+        m = margin
+        while m.dim() < bad.dim():
+            m = m[..., None]
+        off_margin = int((bad & ~(m.expand_as(bad) < MARGIN_TOL)).sum())
+    _record("image", what, n_bad=n_bad, numel=bad.numel(), max_diff=float(diff.max().detach()), off_margin=off_margin)
+    assert n_bad <= max(2, IMAGE_OUTLIER_FRAC * bad.numel()), f"{what}: {n_bad} of {bad.numel()} values off by > {IMG_TOL}"
     assert diff.max().item() <= IMAGE_OUTLIER_MAX, f"{what}: max diff {diff.max().item()}"
-    return int(bad.sum())
+    assert not off_margin, f"{what}: {off_margin} of {n_bad} outliers are NOT on an alpha/T threshold pair"
+    return n_bad
 
 
 def assert_grad_close(got, want, what, rtol=GRAD_RTOL):
+    """(1) global: max-abs and L2 error <= 1e-3 of the reference's scale; (2) PER ELEMENT (north_star's
+    "1e-3 relative"): |got - want| <= 1e-3 |want| + GRAD_ELEM_ATOL max|want| on all but GRAD_ELEM_BAD_FRAC of
+    the entries (fp32 sums of +- contributions in a different order cancel differently: both sides carry
+    rounding of ~1e-6 x the LARGEST partial sum, which the floor stands for)."""
     got = got.detach().cpu().double()
     want = want.detach().double()
     assert torch.isfinite(got).all(), what
     denom = want.abs().max().item() + 1e-30
     err = (got - want).abs().max().item() / denom
     l2 = ((got - want).norm() / (want.norm() + 1e-30)).item()
+    bad = (got - want).abs() > rtol * want.abs() + GRAD_ELEM_ATOL * denom
+    frac_bad = float(bad.double().mean()) if bad.numel() else 0.0
+    _record("grad", what, max_rel=err, l2_rel=l2, elem_bad=int(bad.sum()), numel=bad.numel())
     assert err <= rtol and l2 <= rtol, f"{what}: max-rel {err:.3e}, l2-rel {l2:.3e}"
+    assert int(bad.sum()) <= max(2, GRAD_ELEM_BAD_FRAC * bad.numel()), \
+        f"{what}: {int(bad.sum())} of {bad.numel()} entries miss the per-element bar"
 
 
 # ------------------------------------------------------------------------------ projection
@@ -283,10 +317,10 @@ def test_rasterize_forward(S, dev, n, W, H, scale):
     rc, ra = S.rasterize_to_pixels(a["means2d"], a["conics"], a["colors"], a["opacities"], W, H, 16,
                                    a["isect_offsets"], a["flatten_ids"], backgrounds=None, packed=False, absgrad=True)
     assert rc.shape == (1, H, W, 4) and ra.shape == (1, H, W, 1)
-    assert_image_close(rc[..., :3], rc_w[..., :3], "rgb")
-    assert_image_close(ra, ra_w, "alpha")
+    assert_image_close(rc[..., :3], rc_w[..., :3], "rgb", margin=aux["margin"])
+    assert_image_close(ra, ra_w, "alpha", margin=aux["margin"])
     dscale = float(aux["depths"].max())
-    assert_image_close(rc[..., 3], rc_w[..., 3], "depth-weighted", scale=max(1.0, dscale))
+    assert_image_close(rc[..., 3], rc_w[..., 3], "depth-weighted", scale=max(1.0, dscale), margin=aux["margin"])
     assert float(ra.max()) > 0.3
     # backgrounds
     bg = torch.tensor([[0.2, 0.4, 0.6, 0.0]])
@@ -389,9 +423,9 @@ def test_full_sequence_cfg1_forward_and_backward(S, dev, fused):
     aux = out["aux"]
     for k in ("radii", "tiles_per_gauss", "isect_ids", "flatten_ids", "isect_offsets"):
         assert torch.equal(aux[k].cpu(), aux_w[k]), f"{k} not bit-exact"
-    assert_image_close(out["render_colors"][..., :3], rc_w[..., :3].detach(), "rgb")
-    assert_image_close(out["render_alphas"], ra_w.detach(), "alpha")
-    assert_image_close(out["render_colors"][..., 3], rc_w[..., 3].detach(), "depth", scale=100.0)
+    assert_image_close(out["render_colors"][..., :3], rc_w[..., :3].detach(), "rgb", margin=aux_w["margin"])
+    assert_image_close(out["render_alphas"], ra_w.detach(), "alpha", margin=aux_w["margin"])
+    assert_image_close(out["render_colors"][..., 3], rc_w[..., 3].detach(), "depth", scale=100.0, margin=aux_w["margin"])
     ((out["render_colors"] * v_rc.to(dev)).sum() + (out["render_alphas"] * v_ra.to(dev)).sum()).backward()
     for k in ("means", "quats", "scales", "opacities", "shs"):
         assert_grad_close(c[k].grad, torch.nan_to_num(leaves[k].grad), f"v_{k}")
@@ -399,6 +433,35 @@ def test_full_sequence_cfg1_forward_and_backward(S, dev, fused):
     assert vp.grad is not None and vp.absgrad.shape == vp.shape      # retain_grad + absgrad side effect
     assert out["rgb"].shape == (3, H, W) and out["acc"].shape == (1, H, W) and out["depth"].shape == (1, H, W)
     assert out["visibility_filter"].dtype == torch.bool and out["radii"].dtype == torch.float32
+
+
+@pytest.mark.parametrize("yaw", [45.0, -45.0])
+def test_cfg4_side_camera_1920x886_vs_oracle(S, dev, yaw):
+    """BASELINE.json configs[3]: the Waymo SIDE cameras are 1920x886 — a height that is NOT a multiple of the
+    16-pixel tile (56 tile rows, the last one 6 pixels tall).  Whole fused path, forward + backward, against
+    the oracle at 100 k Gaussians."""
+    n, W, H, deg = 100000, 1920, 886, 3
+    s = make_gaussians(n, sh_degree=deg, seed=44)
+    V, K = make_camera(W, H, yaw_deg=yaw, z_shift=3.0)
+    leaves = {k: v.clone().requires_grad_(True) for k, v in s.items()}
+    rc_w, ra_w, aux_w = G.render_reference_sequence(leaves["means"], leaves["quats"], leaves["scales"],
+                                                    leaves["opacities"], leaves["shs"], V, K, W, H, deg, return_aux=True)
+    g = torch.Generator().manual_seed(4)
+    v_rc = torch.randn(1, H, W, 4, generator=g)
+    v_ra = torch.randn(1, H, W, 1, generator=g)
+    v_rc[..., 3] *= 0.02
+    ((rc_w * v_rc).sum() + (ra_w * v_ra).sum()).backward()
+    c, out = _pipeline_gpu(S, dev, s, V, K, W, H, deg, fused=True)
+    aux = out["aux"]
+    assert aux["isect_offsets"].shape == (1, 56, 120)
+    for k in ("radii", "tiles_per_gauss", "isect_ids", "flatten_ids", "isect_offsets"):
+        assert torch.equal(aux[k].cpu(), aux_w[k]), f"{k} not bit-exact"
+    assert_image_close(out["render_colors"][..., :3], rc_w[..., :3].detach(), "cfg4 rgb", margin=aux_w["margin"])
+    assert_image_close(out["render_alphas"], ra_w.detach(), "cfg4 alpha", margin=aux_w["margin"])
+    assert_image_close(out["render_colors"][..., 3], rc_w[..., 3].detach(), "cfg4 depth", scale=100.0, margin=aux_w["margin"])
+    ((out["render_colors"] * v_rc.to(dev)).sum() + (out["render_alphas"] * v_ra.to(dev)).sum()).backward()
+    for k in ("means", "quats", "scales", "opacities", "shs"):
+        assert_grad_close(c[k].grad, torch.nan_to_num(leaves[k].grad), f"cfg4 v_{k}")
 
 
 @pytest.mark.parametrize("deg,antialiasing", [(3, True), (1, True), (3, False)])
@@ -512,6 +575,21 @@ def test_rasterization_entry_matches_sequence(S, dev):
 
 
 # ------------------------------------------------------------------------------ size-independent properties
+def _assert_binning_equals_oracle(S, means2d, radii, depths, tile, W, H, tpg, ids, flat, off):
+    """FULL-SIZE bit-exact binning: the fused pipeline's sorted list against (1) the CPU oracle's isect_tiles /
+    isect_offset_encode on the same projected inputs and (2) a stable torch.sort on the device of this library's
+    own UNSORTED emission (a different set of kernels: count, 3-kernel scan, entry-order emit)"""
+    tw, th = math.ceil(W / float(tile)), math.ceil(H / float(tile))
+    w_tpg, w_ids, w_flat = G.isect_tiles(means2d.cpu(), radii.cpu(), depths.cpu(), tile, tw, th, n_cameras=radii.shape[0])
+    assert torch.equal(tpg.cpu(), w_tpg), "tiles_per_gauss"
+    assert torch.equal(ids.cpu(), w_ids), "sorted isect_ids"
+    assert torch.equal(flat.cpu(), w_flat), "flatten_ids"
+    assert torch.equal(off.cpu(), G.isect_offset_encode(w_ids, radii.shape[0], tw, th)), "isect_offsets"
+    _, ids_u, flat_u = S.isect_tiles(means2d, radii, depths, tile, tw, th, sort=False)
+    ids_s, order = torch.sort(ids_u, stable=True)
+    assert torch.equal(ids, ids_s) and torch.equal(flat, flat_u[order]), "stable sort of the unsorted emission"
+
+
 def test_cfg2_scale_properties(S, dev):
     """BASELINE.json configs[1] shape (2M Gaussians, 1920x1280): structural invariants +
     linearity in colour + determinism of the forward pass."""
@@ -536,6 +614,7 @@ def test_cfg2_scale_properties(S, dev):
     assert torch.equal((ids & 0xFFFFFFFF).to(torch.int32).view(torch.float32), aux["depths"][0][flat.long()])
     # checksum of the multiset of values survives the sort
     assert int(flat.long().sum()) == int((tpg[0].long() * torch.arange(n, device=dev)).sum())
+    _assert_binning_equals_oracle(S, aux["means2d"], aux["radii"], aux["depths"], 16, W, H, tpg, ids, flat, off)
     ra = out["render_alphas"]
     assert float(ra.min()) >= 0 and float(ra.max()) <= 1.0
     a = aux
@@ -756,6 +835,7 @@ def test_cfg3_lidar_frame_scale_properties(S, dev):
     offs = torch.cat([off.reshape(-1).long(), torch.tensor([I], device=dev)])
     assert torch.equal(torch.bincount(ids >> 32, minlength=off.numel()), offs[1:] - offs[:-1])
     assert bool((radii[0][flat.long()] > 0).all()), "only visible points are binned"
+    _assert_binning_equals_oracle(S, m2, radii, dep, 16, W, H, tpg, ids, flat, off)
     cols = torch.cat([rgb, dep[0][:, None]], -1)[None]
     op = torch.ones(1, P, device=dev)
     outs = {}
