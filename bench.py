@@ -299,8 +299,7 @@ def run_ours(args):
     timer = StageTimer()
     proxy = _LibProxy(_lib.lib)
     stage_fns = ["sc_projection_fwd_opacity", "sc_projection_bwd_opacity", "sc_sh_fwd_view", "sc_sh_bwd_view",
-                 "sc_isect_prepare",
-                 "sc_isect_emit_sorted", "sc_isect_offset_encode", "sc_rasterize_fwd_depth", "sc_rasterize_bwd"]
+                 "sc_bin_prepare", "sc_bin_finish", "sc_rasterize_fwd_depth", "sc_rasterize_bwd"]
     timer.wrap(proxy, stage_fns)
     rendering.lib = proxy
 
@@ -343,7 +342,8 @@ def run_ours(args):
         arena.zero_grad()
         for v in range(n_views):
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
-                                       dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks)
+                                       dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks,
+                                       aux_ids=False)
             torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc[v], v_ra[v]])
         if world > 1:
             allreduce_gradients(arena)
@@ -365,7 +365,7 @@ def run_ours(args):
         for v in range(n_views):
             Vd, Kd, Cd = cam_dev[v, 0:16].view(1, 4, 4), cam_dev[v, 16:25].view(1, 3, 3), cam_dev[v, 28:31]
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
-                                       Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks)
+                                       Vd, Kd, Cd, WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks, aux_ids=False)
             # the reference's training loss (train.py:183-186 without the LPIPS network):
             # 0.8 * L1 + 0.2 * (1 - SSIM), fused forward + backward on the compositor's output
             feeder.acquire(*staged_gt[v])
@@ -453,7 +453,7 @@ def run_ours(args):
             for v in range(n_views):
                 out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
                                            dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE, train=False)
-                I_total += out["aux"]["isect_ids"].numel()
+                I_total += out["aux"]["flatten_ids"].numel()
                 V_total += int(out["visibility_filter"].sum())
         rendering._STATS["buf"] = None
         torch.cuda.synchronize()
@@ -498,8 +498,9 @@ def run_ours(args):
             "sc_projection_fwd_opacity": 80.0 * n, "sc_sh_fwd_view": 204.0 * Vc + 12.0 * n,
             # prepare = count (28 N) + depth sort of the visible pairs (16 V, one logical pass) + scan (12 V);
             # emit_sorted = emit (28 V + 12 I) + tile sort (24 I, one logical pass)
-            "sc_isect_prepare": 28.0 * n + 28.0 * Vc, "sc_isect_emit_sorted": 28.0 * Vc + 36.0 * Ic,
-            "sc_isect_offset_encode": 8.0 * Ic,
+            # finish = emit (28 V + 12 I) + tile sort (24 I, one logical pass) + offset encode (8 I): the logical
+            # stages of SURVEY 8(d), whatever the implementation fuses
+            "sc_bin_prepare": 28.0 * n + 28.0 * Vc, "sc_bin_finish": 28.0 * Vc + 44.0 * Ic,
             "sc_sh_bwd_view": 216.0 * Vc + 192.0 * n, "sc_projection_bwd_opacity": 128.0 * n,
         }
         stage_table = {}

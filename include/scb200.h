@@ -16,6 +16,8 @@
  *   sc_knn3_mean_dist2         simple_knn._C.distCUDA2         submodules/simple-knn/spatial.cu:16-25,
  *                                                              simple_knn.cu:186-222
  *   sc_isect_prepare/emit_sorted   the same isect_tiles(sort=True) as two calls around its one host read-back
+ *   sc_bin_prepare/finish          isect_tiles(sort=True) + isect_offset_encode for ONE camera and a tile grid of
+ *                                  at most 128 x 128 (street_gaussian_renderer.py:243-253): the fast path
  *   sc_*_opacity, sc_sh_*_view     the kernels above with the renderer's glue folded in
  *                                  (street_gaussian_renderer.py:233-238, :256-266)
  *   sc_photometric_fwd/bwd     loss_utils.l1_loss + ssim       street_gaussian/utils/loss_utils.py:21-38, :96-131,
@@ -174,6 +176,29 @@ int sc_isect_emit_sorted(int64_t N, int C, const float* means2d, const int32_t* 
                          void* sort_workspace, int64_t sort_workspace_bytes, void* stream);
 int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, int tile_width,
                            int tile_height, int tile_n_bits, int32_t* offsets, void* stream);
+/* Fast binning path: ONE camera (C == 1) and a tile grid of at most 128 x 128 tiles — every
+ * configuration the reference renders (isect_tiles + isect_offset_encode,
+ * street_gaussian_renderer.py:243-253).  Same results bit for bit as the generic pipeline above.
+ *   sc_bin_supported: 1 when (C, tile grid) qualifies.
+ *   sc_bin_prepare: like sc_isect_prepare (same workspace; its first 24 bytes hold int64 {n_visible,
+ *     n_isects, n_items} once the stream has drained, n_items = sum of the tile-box widths), and
+ *     additionally the tile boxes of the visible Gaussians in depth order and the histograms of
+ *     their tile columns / rows.  ONE cooperative kernel (grid-wide barriers, one CTA per SM).
+ *   sc_bin_finish: emits the intersections in depth order and sorts them by tile column INSIDE the
+ *     emit kernel, sorts by tile row, writes flatten_ids[n_isects], isect_ids[n_isects] (nullable:
+ *     skipped when the caller only composites) and offsets[tile_height * tile_width].
+ *     sort_workspace >= sc_bin_sort_workspace_bytes(n_isects), 256-byte aligned. */
+int sc_bin_supported(int C, int tile_width, int tile_height);
+int sc_bin_prepare(int64_t N, const float* means2d, const int32_t* radii, const float* depths, int tile_size,
+                   int tile_width, int tile_height, int32_t* tiles_per_gauss, void* workspace,
+                   int64_t workspace_bytes, void* stream);
+int64_t sc_bin_sort_workspace_bytes(int64_t n_isects);
+/* byte offset, inside the prepare workspace, of 16 uint64 %globaltimer stamps that CTA 0 of the cooperative
+ * kernel leaves at its phase boundaries (measurement only: tools/bin_phases.py) */
+int64_t sc_bin_phase_stamps_offset(int64_t N, int tile_width, int tile_height);
+int sc_bin_finish(int64_t N, const float* depths, int tile_width, int tile_height, int64_t n_visible,
+                  int64_t n_isects, int64_t n_items, const void* prepare_workspace, int32_t* flatten_ids, int64_t* isect_ids,
+                  int32_t* offsets, void* sort_workspace, int64_t sort_workspace_bytes, void* stream);
 
 /* ---- A7/A8: compositing ---------------------------------------------------------------- */
 /* CH in 1..5; backgrounds[C,CH] nullable; max_hit 0 = unlimited.

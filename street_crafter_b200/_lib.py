@@ -59,6 +59,11 @@ SIGNATURES = {
     "sc_isect_emit_sorted": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i32, _i64, _i64,
                                     _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
     "sc_isect_offset_encode": (_i32, [_i64, _ptr, _i32, _i32, _i32, _i32, _ptr, _ptr]),
+    "sc_bin_supported": (_i32, [_i32, _i32, _i32]),
+    "sc_bin_prepare": (_i32, [_i64, _ptr, _ptr, _ptr, _i32, _i32, _i32, _ptr, _ptr, _i64, _ptr]),
+    "sc_bin_sort_workspace_bytes": (_i64, [_i64]),
+    "sc_bin_phase_stamps_offset": (_i64, [_i64, _i32, _i32]),
+    "sc_bin_finish": (_i32, [_i64, _ptr, _i32, _i32, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
     "sc_rasterize_fwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                 _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_rasterize_bwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
@@ -82,6 +87,13 @@ def _bind(path: str):
     return lib
 
 
+def _sources_newer_than(lib_path: str) -> bool:
+    t = os.path.getmtime(lib_path)
+    csrc = os.path.join(_HERE, "csrc")
+    deps = [os.path.join(csrc, f) for f in os.listdir(csrc)] + [os.path.join(_HERE, "..", "include", "scb200.h")]
+    return any(os.path.exists(d) and os.path.getmtime(d) > t for d in deps)
+
+
 def _load() -> C.CDLL:
     """dlopen the in-tree library, (re)building it first with nvcc when it is missing or older
     than its sources (nvcc cross-compiles sm_100a without a GPU).  Never a CPU fallback."""
@@ -89,9 +101,14 @@ def _load() -> C.CDLL:
     if not os.environ.get("SCB200_LIB"):
         try:
             build()  # incremental: a no-op when libscb200.so is newer than every source
-        except Exception:
-            if not os.path.exists(LIB_PATH):
+        except Exception as e:
+            # a box without nvcc may still carry an up-to-date library; a library OLDER than its sources
+            # must never be bound silently (tests / bench would exercise stale kernels)
+            if not os.path.exists(LIB_PATH) or _sources_newer_than(LIB_PATH):
                 raise
+            import warnings
+            warnings.warn(f"street_crafter_b200: rebuild skipped ({type(e).__name__}: {e}); "
+                          f"{LIB_PATH} is up to date with its sources")
     try:
         return _bind(LIB_PATH)
     except AttributeError as e:

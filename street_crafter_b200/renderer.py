@@ -21,7 +21,8 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
                          max_sh_degree: int, znear: float = 0.001, zfar: float = 1000.0,
                          tile_size: int = 16, use_depth: bool = True, absgrad: bool = True,
                          antialiasing: bool = True, train: bool = True,
-                         grad_sinks: Optional[Dict[str, Tensor]] = None, fused: bool = True) -> Dict[str, Tensor]:
+                         grad_sinks: Optional[Dict[str, Tensor]] = None, fused: bool = True,
+                         aux_ids: bool = True) -> Dict[str, Tensor]:
     """xyz3[N,3] rgb3[N,K,3] (SH) scale[N,3] quats[N,4] occ1[N,1] w2c[1,4,4] K[1,3,3]
     camera_center[3] -> the reference's result dict (rgb[3,H,W], acc, depth, viewspace_points,
     visibility_filter, radii) plus the raw render tensors.
@@ -29,12 +30,14 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
     fused=True (default) runs the same computation as ONE autograd node per camera
     (rendering.fused_view): the elementwise glue between the five ops (opacity * compensation,
     dirs, mask, +0.5 / clamp, cat with depth and their backward nodes) is folded into the
-    kernels.  fused=False issues the five ops exactly as the reference does (:219-280)."""
+    kernels.  fused=False issues the five ops exactly as the reference does (:219-280).
+    aux_ids=False (fused only): the sorted 64-bit isect_ids — an intermediate the reference's result
+    dict does not hold — are not written out; out["aux"]["isect_ids"] is then empty."""
     if fused and use_depth and rgb3.dim() == 3 and rgb3.shape[1] in (4, 16) and tile_size == 16:
         render_colors, render_alphas, meta = fused_view(
             xyz3, quats, scale, occ1[:, 0], rgb3, w2c, K, camera_center, width, height, max_sh_degree,
             near_plane=znear, far_plane=zfar, antialiased=antialiasing, tile_size=tile_size, absgrad=absgrad,
-            grad_sinks=grad_sinks)
+            grad_sinks=grad_sinks, need_isect_ids=aux_ids)
         radii, means2d = meta["radii"], meta["means2d"]
         rendered_color = render_colors[..., :-1]
         rendered_depth = meta["depth_norm"]  # render_colors[..., -1:] / render_alphas.clamp(min=1e-10), in-kernel

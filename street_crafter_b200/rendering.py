@@ -228,7 +228,7 @@ def _tile_n_bits(tile_width: int, tile_height: int) -> int:
     return int(math.floor(math.log2(tile_width * tile_height))) + 1
 
 
-# pinned landing buffers for the {n_visible, n_isects} read-back, one per (device, stream)
+# pinned landing buffers for the {n_visible, n_isects, n_items} read-back, one per (device, stream)
 _PINNED_TOTALS: Dict[Tuple[int, int], Tensor] = {}
 
 
@@ -237,45 +237,61 @@ def _isect_begin(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int,
     """phase 1 of the fused binning pipeline: compaction of the emitting entries + their stable
     depth order + scan (one C call), then an ASYNC copy of {n_visible, n_isects} to pinned host
     memory and an event.  The caller may enqueue independent GPU work before _isect_finish()
-    waits on the event, so the GPU stays busy across the host read-back."""
+    waits on the event, so the GPU stays busy across the host read-back.  One camera and a tile
+    grid of at most 128 x 128 take the fast path (sc_bin_*), anything else the generic one."""
     C, N = radii.shape
     CN = C * N
     dev = means2d.device
+    fast = bool(lib.sc_bin_supported(C, tile_width, tile_height))
     ws_bytes = int(lib.sc_isect_workspace_bytes(CN, tile_width, tile_height))
     ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-    check(lib.sc_isect_prepare(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width, tile_height,
-                               _p(tpg), _p(ws), ws_bytes, st), "sc_isect_prepare")
+    if fast:
+        check(lib.sc_bin_prepare(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width, tile_height,
+                                 _p(tpg), _p(ws), ws_bytes, st), "sc_bin_prepare")
+    else:
+        check(lib.sc_isect_prepare(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width, tile_height,
+                                   _p(tpg), _p(ws), ws_bytes, st), "sc_isect_prepare")
     key = (dev.index if dev.index is not None else torch.cuda.current_device(), st)
     host = _PINNED_TOTALS.get(key)
     if host is None:
-        host = _PINNED_TOTALS[key] = torch.empty(2, dtype=torch.int64).pin_memory()
-    host.copy_(ws[:16].view(torch.int64), non_blocking=True)
+        host = _PINNED_TOTALS[key] = torch.empty(3, dtype=torch.int64).pin_memory()
+    host.copy_(ws[:24].view(torch.int64), non_blocking=True)
     ev = torch.cuda.Event()
     ev.record()
-    return (means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, host, ev)
+    return (means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, host, ev, fast)
 
 
-def _isect_finish(state):
-    """phase 2: wait for the counts (the one host sync of the pipeline), then emit + tile sort on
-    the (camera, tile) bits (one C call)."""
-    means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, host, ev = state
+def _isect_finish(state, need_ids: bool = True):
+    """phase 2: wait for the counts (the one host sync of the pipeline), then emit + tile sort (one C
+    call).  -> (tiles_per_gauss, isect_ids | None, flatten_ids, isect_offsets | None): the fast path
+    also produces the tile offsets (and skips the 64-bit ids when `need_ids` is False)."""
+    means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, host, ev, fast = state
     C, N = radii.shape
     dev = means2d.device
     bits = _tile_n_bits(tile_width, tile_height)
     cam_bits = 0 if C == 1 else int(math.floor(math.log2(C))) + 1
     ev.synchronize()
-    n_visible, n_isects = host.tolist()
+    n_visible, n_isects, n_items = host.tolist()
+    if fast:
+        flat = torch.empty(n_isects, dtype=torch.int32, device=dev)
+        ids = torch.empty(n_isects, dtype=torch.int64, device=dev) if need_ids else None
+        offsets = torch.empty((1, tile_height, tile_width), dtype=torch.int32, device=dev)
+        sws_bytes = int(lib.sc_bin_sort_workspace_bytes(n_isects))
+        sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
+        check(lib.sc_bin_finish(N, _p(depths), tile_width, tile_height, n_visible, n_isects, n_items, _p(ws), _p(flat),
+                                _p(ids), _p(offsets), _p(sws), sws_bytes, st), "sc_bin_finish")
+        return tpg, ids, flat, offsets
     ids = torch.empty((2, n_isects), dtype=torch.int64, device=dev)
     flat = torch.empty((2, n_isects), dtype=torch.int32, device=dev)
     if n_isects == 0:
-        return tpg, ids[0], flat[0]
+        return tpg, ids[0], flat[0], None
     sws_bytes = int(lib.sc_sort_workspace_bytes(n_isects))
     sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
     check(lib.sc_isect_emit_sorted(N, C, _p(means2d), _p(radii), _p(depths), tile_size, tile_width,
                                    tile_height, bits, cam_bits, n_visible, n_isects, _p(ws),
                                    _p(ids[0]), _p(flat[0]), _p(ids[1]), _p(flat[1]), _p(sws),
                                    sws_bytes, st), "sc_isect_emit_sorted")
-    return tpg, ids[0], flat[0]
+    return tpg, ids[0], flat[0], None
 
 
 @torch.no_grad()
@@ -308,7 +324,7 @@ def isect_tiles(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int, 
         tpg = torch.empty((C, N), dtype=torch.int32, device=dev)
         if sort:
             state = _isect_begin(means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st)
-            return _isect_finish(state)
+            return _isect_finish(state)[:3]
         # unsorted (gsplat's sort=False): entry order, through the stand-alone entry points
         cum = torch.empty(CN + 1, dtype=torch.int64, device=dev)
         ws_bytes = int(lib.sc_scan_workspace_bytes(CN))
@@ -477,7 +493,7 @@ class _FusedView(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
-                eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, sinks):
+                eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, sinks, need_ids=True):
         means = _f32c(means, "means")
         quats = _f32c(quats, "quats")
         scales = _f32c(scales, "scales")
@@ -514,8 +530,11 @@ class _FusedView(torch.autograd.Function):
             # independent of the binning: runs on the GPU while the host waits for the counts
             check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(radii),
                                      _p(depths), _p(colors4), st), "sc_sh_fwd_view")
-            tpg, isect_ids, flatten_ids = _isect_finish(state)
-        isect_offsets = isect_offset_encode(isect_ids, 1, tile_width, tile_height)
+            tpg, isect_ids, flatten_ids, isect_offsets = _isect_finish(state, need_ids)
+        if isect_offsets is None:
+            isect_offsets = isect_offset_encode(isect_ids, 1, tile_width, tile_height)
+        if isect_ids is None:   # not materialised (need_ids=False): the compositor only reads flatten_ids
+            isect_ids = torch.empty(0, dtype=torch.int64, device=dev)
         with torch.cuda.device(dev):
             render_colors = torch.empty((1, height, width, 4), dtype=torch.float32, device=dev)
             render_alphas = torch.empty((1, height, width, 1), dtype=torch.float32, device=dev)
@@ -591,20 +610,23 @@ class _FusedView(torch.autograd.Function):
             if absgrad:
                 m2.absgrad = v_abs.view(1, N, 2)
         if sinks is not None:
-            return (None,) * 19
+            return (None,) * 20
         need = ctx.needs_input_grad
         return (g_means if need[0] else None, g_quats if need[1] else None, g_scales if need[2] else None,
-                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 14
+                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 15
 
 
 def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, shs: Tensor, viewmats: Tensor,
                Ks: Tensor, campos: Tensor, width: int, height: int, sh_degree: int, eps2d: float = 0.3,
                near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
                antialiased: bool = True, tile_size: int = 16, absgrad: bool = False,
-               grad_sinks: Optional[Dict[str, Tensor]] = None) -> Tuple[Tensor, Tensor, Dict]:
+               grad_sinks: Optional[Dict[str, Tensor]] = None, need_isect_ids: bool = True,
+               ) -> Tuple[Tensor, Tensor, Dict]:
     """One camera (viewmats[1,4,4], Ks[1,3,3], campos[3] on the device), SH colours with K = 4 or
     16 coefficients, RGB + depth channel: -> (render_colors[1,H,W,4], render_alphas[1,H,W,1], meta).
-    `meta["means2d"].grad` / `.absgrad` are filled by the backward pass."""
+    `meta["means2d"].grad` / `.absgrad` are filled by the backward pass.  `need_isect_ids=False`
+    leaves meta["isect_ids"] empty: the 64-bit keys are an intermediate of the binning that only the
+    op-by-op API hands out (the reference renderer's result dict does not hold them)."""
     import weakref
     assert viewmats.shape == (1, 4, 4) and Ks.shape == (1, 3, 3) and campos.shape == (3,)
     assert shs.dim() == 3 and shs.shape[1] in (4, 16) and (sh_degree + 1) ** 2 <= shs.shape[1]
@@ -612,7 +634,8 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
     if grad_sinks is not None:
         assert all(k in grad_sinks for k in ("means", "quats", "scales", "opacities", "shs"))
     out = _FusedView.apply(means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
-                           eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, grad_sinks)
+                           eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, grad_sinks,
+                           need_isect_ids)
     (rc, ra, depth_norm, radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets,
      vis, radii_norm) = out[:15]
     comps = out[15] if len(out) > 15 else None
