@@ -324,17 +324,21 @@ int sc_densify_move(int64_t N, const int32_t* flags /*[4N]*/, const int64_t* des
  * symmetry prior (:313-318, :347-350).  All table arrays are HOST arrays of device pointers.
  * sc_assemble_bwd writes the gradients of every segment's own arrays (v_xyz[s][n_s,3], v_rot[s][n_s,4]; NULL =
  * not wanted) and ACCUMULATES the tracked-pose gradients into v_pose_rot[s][4] / v_pose_trans[s][3] (NULL = pose
- * not optimised; the caller zeroes them). */
+ * not optimised; the caller zeroes them).
+ * host_shell (HOST float[n_segments][4] = centre xyz, 2 R; NULL or 2 R = 0: none): the sky model's shell
+ * projection of its positions, GaussianModelSky.get_xyz (street_gaussian/models/gaussian_model_sky.py:68-76):
+ * d = xyz - c, ratio = |d| / (2 R), xyz_w = c + d / ratio where ratio < 1 — plain segments only. */
 #define SC_ASSEMBLE_MAX_SEGMENTS 32
 int sc_assemble_fwd(int n_segments, const int64_t* host_seg_start /*[n_segments+1]*/, const float* const* host_xyz,
                     const float* const* host_rot, const float* const* host_pose_rot,
                     const float* const* host_pose_trans, const uint8_t* const* host_flip, int flip_axis,
-                    const float* host_flip_quat /*[4]*/, float* out_xyz /*[N,3]*/, float* out_rot /*[N,4]*/,
-                    void* stream);
+                    const float* host_flip_quat /*[4]*/, const float* host_shell /*[n_segments][4], nullable*/,
+                    float* out_xyz /*[N,3]*/, float* out_rot /*[N,4]*/, void* stream);
 int sc_assemble_bwd(int n_segments, const int64_t* host_seg_start, const float* const* host_xyz,
                     const float* const* host_rot, const float* const* host_pose_rot,
                     const float* const* host_pose_trans, const uint8_t* const* host_flip, int flip_axis,
-                    const float* host_flip_quat, const float* v_out_xyz /*[N,3]*/, const float* v_out_rot /*[N,4]*/,
+                    const float* host_flip_quat, const float* host_shell, const float* v_out_xyz /*[N,3]*/,
+                    const float* v_out_rot /*[N,4]*/,
                     float* const* host_v_xyz, float* const* host_v_rot, float* const* host_v_pose_rot,
                     float* const* host_v_pose_trans, void* stream);
 
@@ -378,6 +382,40 @@ int sc_knn3_mean_dist2(int64_t P, const float* points, float* mean_dist2, void* 
  * compositing kernels: every thread runs `iters` rounds of 8 independent dependent chains.
  * flops = grid*block*iters*16 (fma) ; ex2 ops = grid*block*iters*8.  sink[grid*block] out. */
 int sc_probe_fp32(int kind /*0 fma, 1 ex2*/, int grid, int block, int iters, float* sink, void* stream);
+
+/* ---- N1: LiDAR condition pipeline (street_gaussian/pointcloud_processor/waymo_processor.py:179-242) ---- */
+/* sc_lidar_gather: the point set of ONE condition frame from device-resident clouds.  segs_dev: n_segs (<= 512)
+ * records of sc_lidar_segment_bytes() bytes {int64 dst0, int64 count, const void* src, int32 is_f64,
+ * int32 has_pose, double pose[12]}: `count` rows of 6 values (xyz rgb; float32 world-space background clouds,
+ * float64 actor clouds posed by the 3x4 float64 object->world matrix exactly as base_processor.py:58-63) land
+ * at [dst0, dst0 + count).  Writes means[n,3], rgb[n,3] and the isotropic splat scales[n,3]: `scale`, or with
+ * use_ndc_scale scale * z / fx * 0.5 * min(H, W) (data_processor/utils/render_utils.py:116-122; w2c_row2 =
+ * third row of the float32 world->camera matrix).
+ * sc_lidar_pack: compositor output (rgb[H*W,3], alpha[H*W]) -> uint8 [H*W,4] = (x * 255).astype(uint8) of the
+ * reference's PNG pair (waymo_processor.py:237-242) and / or float [4,H*W] of the quantised values. */
+int64_t sc_lidar_segment_bytes(void);
+int sc_lidar_gather(int64_t n_points, int n_segs, const void* segs_dev, const float* w2c_row2, float scale, float fx,
+                    int height, int width, int use_ndc_scale, float* means, float* rgb, float* scales, void* stream);
+int sc_lidar_pack(int64_t n_pix, const float* rgb, const float* alpha, uint8_t* out_u8, float* out_f32, void* stream);
+
+/* ---- N4 / 8(e): optimiser step and checkpoint rows on the flat parameter arena ---------------------------- */
+/* sc_adam_step: torch.optim.Adam(lr per group, eps) as GaussianModel.training_setup configures it
+ * (street_gaussian/models/gaussian_model.py:293-305) over ONE flat fp32 buffer that holds every parameter
+ * group: host_group_start[n_groups+1] ascending element offsets (multiples of 4), host_lr[n_groups]; elements
+ * [lo, hi) (multiples of 4) are updated — the slice one rank owns after the gradient reduce-scatter.
+ * params / exp_avg / exp_avg_sq are updated in place; `step` is the 1-based step count of the bias
+ * correction.  n_groups <= 64. */
+int sc_adam_step(int n_groups, const int64_t* host_group_start, const float* host_lr, int64_t lo, int64_t hi,
+                 float* params, const float* grads, float* exp_avg, float* exp_avg_sq, float beta1, float beta2,
+                 float eps, int64_t step, void* stream);
+/* Row layout of GaussianModel.make_ply / load_ply (gaussian_model.py:82-99, :107-156, :328-342):
+ * x y z nx ny nz | f_dc (3) | f_rest (3 (K-1), channel-major) | opacity | scale (3) | rot (4) | semantic (S).
+ * xyz[N,3] f_dc[N,1,3] f_rest[N,K-1,3] opacity[N,1] scaling[N,3] rotation[N,4] semantic[N,S] <-> rows[N,width]. */
+int sc_ply_row_width(int K, int S);
+int sc_ply_pack(int64_t N, int K, int S, const float* xyz, const float* f_dc, const float* f_rest, const float* opacity,
+                const float* scaling, const float* rotation, const float* semantic, float* rows, void* stream);
+int sc_ply_unpack(int64_t N, int K, int S, const float* rows, float* xyz, float* f_dc, float* f_rest, float* opacity,
+                  float* scaling, float* rotation, float* semantic, void* stream);
 
 #ifdef __cplusplus
 }

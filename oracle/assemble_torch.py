@@ -27,7 +27,7 @@ def quaternion_raw_multiply(a, b):                                       # gener
 
 def assemble(segments, flip_quat, flip_axis=1):
     """segments: list of dicts with `xyz` [n,3], `rotation` [n,4] (raw) and, for actors, `pose_rot` [4] (raw),
-    `pose_trans` [3], optional `flip` [n] bool.  -> (xyz [N,3], rotation [N,4]) of the concatenated scene graph."""
+    `pose_trans` [3], optional `flip` [n] bool; the sky model adds `shell` = (centre [3], radius).  -> (xyz [N,3], rotation [N,4]) of the concatenated scene graph."""
     xyzs, rots = [], []
     for s in segments:
         x, q = s["xyz"], F.normalize(s["rotation"])                      # gaussian_model.py:229-235
@@ -41,6 +41,12 @@ def assemble(segments, flip_quat, flip_axis=1):
             a = s["pose_rot"].reshape(1, 4).expand(n, -1)                # :256
             x = torch.einsum('bij, bj -> bi', quaternion_to_matrix(a), x) + s["pose_trans"].reshape(1, 3)   # :351-352
             q = F.normalize(quaternion_raw_multiply(a, q))               # :319-320
+        elif s.get("shell") is not None:                                 # gaussian_model_sky.py:68-76
+            c, r = s["shell"]
+            c = torch.as_tensor(c, dtype=x.dtype).to(x.device)
+            dists = torch.linalg.norm(x - c, dim=1, keepdims=True)
+            ratios = dists / (2 * torch.as_tensor([float(r)], dtype=x.dtype).to(x.device))
+            x = torch.where(ratios < 1., c + (x - c) / ratios, x)
         xyzs.append(x)
         rots.append(q)
     return torch.cat(xyzs, 0), torch.cat(rots, 0)

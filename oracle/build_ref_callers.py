@@ -46,6 +46,14 @@ ENTRIES = [
     ("focal2fov", "street_gaussian/utils/graphics_utils.py", None, "focal2fov", True),
     ("RGB2SH", "street_gaussian/utils/sh_utils.py", None, "RGB2SH", True),
     ("inverse_sigmoid", "street_gaussian/utils/general_utils.py", None, "inverse_sigmoid", True),
+    # checkpoint / PLY formats and the optimizer set-up (row N4)
+    ("gm_state_dict", "street_gaussian/models/gaussian_model.py", "GaussianModel", "state_dict", True),
+    ("gm_load_state_dict", "street_gaussian/models/gaussian_model.py", "GaussianModel", "load_state_dict", True),
+    ("gm_training_setup", "street_gaussian/models/gaussian_model.py", "GaussianModel", "training_setup", True),
+    ("gm_make_ply", "street_gaussian/models/gaussian_model.py", "GaussianModel", "make_ply", True),
+    ("gm_load_ply", "street_gaussian/models/gaussian_model.py", "GaussianModel", "load_ply", True),
+    ("gm_construct_list_of_attributes", "street_gaussian/models/gaussian_model.py", "GaussianModel",
+     "construct_list_of_attributes", True),
     # LiDAR condition pipeline (row N1): aggregation of +-delta frames, actor posing
     ("make_lidar_ply", "street_gaussian/pointcloud_processor/base_processor.py", "BasePointCloudProcessor",
      "make_lidar_ply", True),

@@ -32,8 +32,9 @@ SIGNATURES = {
                                    _ptr]),
     "sc_densify_move": (_i32, [_i64, _ptr, _ptr, _i64, _i64, _i64, _i64, _i32, _ptr, _ptr, _ptr, _f32, _ptr, _i32, _ptr, _ptr,
                                _ptr, _ptr, _ptr]),
-    "sc_assemble_fwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr]),
-    "sc_assemble_bwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_assemble_fwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_assemble_bwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
+                               _ptr]),
     "sc_assemble_act_fwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_assemble_act_bwd": (_i32, [_i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_assemble_features_fwd": (_i32, [_i32, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
@@ -74,6 +75,13 @@ SIGNATURES = {
                                   _i64, _i32, _ptr]),
     "sc_knn_workspace_bytes": (_i64, [_i64]),
     "sc_knn3_mean_dist2": (_i32, [_i64, _ptr, _ptr, _ptr, _i64, _ptr]),
+    "sc_lidar_segment_bytes": (_i64, []),
+    "sc_lidar_gather": (_i32, [_i64, _i32, _ptr, _ptr, _f32, _f32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr]),
+    "sc_lidar_pack": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_adam_step": (_i32, [_i32, _ptr, _ptr, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _f32, _f32, _f32, _i64, _ptr]),
+    "sc_ply_row_width": (_i32, [_i32, _i32]),
+    "sc_ply_pack": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_ply_unpack": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_probe_fp32": (_i32, [_i32, _i32, _i32, _i32, _ptr, _ptr]),
 }
 

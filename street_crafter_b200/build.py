@@ -33,6 +33,8 @@ SOURCES = {
     "densify_cycle.cu": [],
     "assemble.cu": [],
     "compact.cu": [],
+    "lidar.cu": [],
+    "optim.cu": [],
     "probe.cu": ["--use_fast_math"],
 }
 

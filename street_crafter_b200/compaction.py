@@ -19,7 +19,7 @@ MAX_ARRAYS = 32
 
 
 @torch.no_grad()
-def compact_rows(keep: Tensor, tensors: Sequence[Tensor]) -> List[Tensor]:
+def compact_rows(keep: Tensor, tensors: Sequence[Tensor], alloc=None) -> List[Tensor]:
     """keep [N] bool; tensors: fp32 CUDA tensors whose first dimension is N (any trailing shape).
     -> new contiguous tensors holding the rows with keep == True, in order (== `t[keep]`)."""
     if not keep.is_cuda:
@@ -41,7 +41,10 @@ def compact_rows(keep: Tensor, tensors: Sequence[Tensor]) -> List[Tensor]:
         check(lib.sc_exclusive_scan_i32(N, k8.to(torch.int32).data_ptr(), dest.data_ptr(), dest.data_ptr() + 8 * N,
                                         ws.data_ptr(), ws_bytes, st), "sc_exclusive_scan_i32")
         n_keep = int(dest[N].item())  # sizes the outputs (the reference's boolean indexing syncs the same way)
-        outs = [torch.empty((n_keep,) + tuple(t.shape[1:]), dtype=torch.float32, device=dev) for t in srcs]
+        if alloc is None:
+            outs = [torch.empty((n_keep,) + tuple(t.shape[1:]), dtype=torch.float32, device=dev) for t in srcs]
+        else:   # alloc(i, shape): destination of output i (model_arena.SceneArena: views of a fresh flat arena)
+            outs = [alloc(i, (n_keep,) + tuple(t.shape[1:])) for i, t in enumerate(srcs)]
         for a in range(0, len(srcs), MAX_ARRAYS):
             part_s, part_d = srcs[a:a + MAX_ARRAYS], outs[a:a + MAX_ARRAYS]
             n = len(part_s)

@@ -6,6 +6,7 @@
 // concatenated Gaussian set, which write the projection kernel's `means` / `quats` inputs directly:
 //
 //   plain segment (background, sky):   xyz_w = xyz                    rot_w = normalize(rot)
+//   sky shell (gaussian_model_sky.py:68-76): d = xyz - c, ratio = |d| / (2 R); xyz_w = c + d / ratio where ratio < 1
 //   actor segment (rigid pose a, t):   x' = flip_axis-mirrored xyz where flip_mask      (:347-350)
 //                                      xyz_w = R(a / |a|) x' + t                         (:351-352)
 //                                      q  = normalize(rot); q = f (x) q where flip_mask  (:313-318)
@@ -27,6 +28,7 @@ struct SegTable {
     const float* pose_rot[SC_ASSEMBLE_MAX_SEGMENTS];    // null: plain segment
     const float* pose_trans[SC_ASSEMBLE_MAX_SEGMENTS];
     const uint8_t* flip[SC_ASSEMBLE_MAX_SEGMENTS];      // null: no flips
+    float shell[SC_ASSEMBLE_MAX_SEGMENTS][4];            // sky shell: centre xyz, 2 R (0 = none)
     int n;
     int flip_axis;
     float fq[4];
@@ -87,6 +89,14 @@ assemble_fwd_kernel(SegTable T, float* __restrict__ out_xyz, float* __restrict__
     const Quat raw = ldq(T.rot[s] + 4 * k);
     Quat q = qscale(raw, 1.f / qnorm_f(raw));
     if (T.pose_rot[s] == nullptr) {
+        if (T.shell[s][3] > 0.f) {
+            const float d[3] = {x[0] - T.shell[s][0], x[1] - T.shell[s][1], x[2] - T.shell[s][2]};
+            const float ratio = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]) / T.shell[s][3];
+            if (ratio < 1.f) {
+#pragma unroll
+                for (int c = 0; c < 3; ++c) x[c] = T.shell[s][c] + d[c] / ratio;
+            }
+        }
         out_xyz[3 * i] = x[0]; out_xyz[3 * i + 1] = x[1]; out_xyz[3 * i + 2] = x[2];
         reinterpret_cast<float4*>(out_rot)[i] = make_float4(q.w, q.x, q.y, q.z);
         return;
@@ -133,7 +143,20 @@ assemble_bwd_kernel(SegTable T, GradTable G, const float* __restrict__ v_out_xyz
         const float nq = qnorm_f(raw);
         const Quat q0 = qscale(raw, 1.f / nq);
         if (T.pose_rot[s] == nullptr) {
-            if (G.v_xyz[s]) { G.v_xyz[s][3 * k] = gx[0]; G.v_xyz[s][3 * k + 1] = gx[1]; G.v_xyz[s][3 * k + 2] = gx[2]; }
+            float gp[3] = {gx[0], gx[1], gx[2]};
+            if (T.shell[s][3] > 0.f) {
+                // y = c + d / ratio = c + 2R d / |d|  ->  v_d = (g - dhat (dhat . g)) / ratio
+                const float d[3] = {__ldg(T.xyz[s] + 3 * k) - T.shell[s][0], __ldg(T.xyz[s] + 3 * k + 1) - T.shell[s][1],
+                                    __ldg(T.xyz[s] + 3 * k + 2) - T.shell[s][2]};
+                const float dist = sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+                const float ratio = dist / T.shell[s][3];
+                if (ratio < 1.f) {
+                    const float dg = (d[0] * gx[0] + d[1] * gx[1] + d[2] * gx[2]) / (dist * dist);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) gp[c] = (gx[c] - d[c] * dg) / ratio;
+                }
+            }
+            if (G.v_xyz[s]) { G.v_xyz[s][3 * k] = gp[0]; G.v_xyz[s][3 * k + 1] = gp[1]; G.v_xyz[s][3 * k + 2] = gp[2]; }
             if (G.v_rot[s]) {
                 const Quat d = normalize_vjp(q0, go, nq);
                 reinterpret_cast<float4*>(G.v_rot[s])[k] = make_float4(d.w, d.x, d.y, d.z);
@@ -213,7 +236,7 @@ assemble_bwd_kernel(SegTable T, GradTable G, const float* __restrict__ v_out_xyz
 
 int fill_table(SegTable& T, int n_segments, const int64_t* seg_start, const float* const* xyz, const float* const* rot,
                const float* const* pose_rot, const float* const* pose_trans, const uint8_t* const* flip, int flip_axis,
-               const float* flip_quat) {
+               const float* flip_quat, const float* shell) {
     SC_CHECK_ARG(n_segments >= 1 && n_segments <= SC_ASSEMBLE_MAX_SEGMENTS, "segment count");
     SC_CHECK_ARG(seg_start && xyz && rot && pose_rot && pose_trans && flip, "null table");
     SC_CHECK_ARG(flip_axis >= 0 && flip_axis < 3 && flip_quat, "flip axis / quaternion");
@@ -231,6 +254,8 @@ int fill_table(SegTable& T, int n_segments, const int64_t* seg_start, const floa
         T.xyz[s] = in ? xyz[s] : nullptr; T.rot[s] = in ? rot[s] : nullptr;
         T.pose_rot[s] = in ? pose_rot[s] : nullptr; T.pose_trans[s] = in ? pose_trans[s] : nullptr;
         T.flip[s] = in ? flip[s] : nullptr;
+        for (int c = 0; c < 4; ++c) T.shell[s][c] = (in && shell) ? shell[4 * s + c] : 0.f;
+        SC_CHECK_ARG(!(in && shell && shell[4 * s + 3] > 0.f && pose_rot[s]), "the sky shell applies to a plain segment");
     }
     for (int s = 0; s <= SC_ASSEMBLE_MAX_SEGMENTS; ++s) T.start[s] = seg_start[s <= n_segments ? s : n_segments];
     return SC_OK;
@@ -456,10 +481,11 @@ int fill_feat_table(FeatTable& T, int n_segments, const int64_t* seg_start, int 
 
 extern "C" int sc_assemble_fwd(int n_segments, const int64_t* seg_start, const float* const* xyz,
                                const float* const* rot, const float* const* pose_rot, const float* const* pose_trans,
-                               const uint8_t* const* flip, int flip_axis, const float* flip_quat, float* out_xyz,
-                               float* out_rot, void* stream) {
+                               const uint8_t* const* flip, int flip_axis, const float* flip_quat,
+                               const float* host_shell, float* out_xyz, float* out_rot, void* stream) {
     SegTable T;
-    const int rc = fill_table(T, n_segments, seg_start, xyz, rot, pose_rot, pose_trans, flip, flip_axis, flip_quat);
+    const int rc = fill_table(T, n_segments, seg_start, xyz, rot, pose_rot, pose_trans, flip, flip_axis, flip_quat,
+                              host_shell);
     if (rc != SC_OK) return rc;
     const int64_t n = T.start[T.n] - T.start[0];
     if (n == 0) return SC_OK;
@@ -471,11 +497,11 @@ extern "C" int sc_assemble_fwd(int n_segments, const int64_t* seg_start, const f
 
 extern "C" int sc_assemble_bwd(int n_segments, const int64_t* seg_start, const float* const* xyz,
                                const float* const* rot, const float* const* pose_rot, const float* const* pose_trans,
-                               const uint8_t* const* flip, int flip_axis, const float* flip_quat,
+                               const uint8_t* const* flip, int flip_axis, const float* flip_quat, const float* host_shell,
                                const float* v_out_xyz, const float* v_out_rot, float* const* v_xyz, float* const* v_rot,
                                float* const* v_pose_rot, float* const* v_pose_trans, void* stream) {
     SegTable T;
-    const int rc = fill_table(T, n_segments, seg_start, xyz, rot, pose_rot, pose_trans, flip, flip_axis, flip_quat);
+    const int rc = fill_table(T, n_segments, seg_start, xyz, rot, pose_rot, pose_trans, flip, flip_axis, flip_quat, host_shell);
     if (rc != SC_OK) return rc;
     const int64_t n = T.start[T.n] - T.start[0];
     if (n == 0) return SC_OK;

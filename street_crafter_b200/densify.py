@@ -55,7 +55,7 @@ def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp
                       xyz_gradient_accum: Tensor, denom: Tensor, max_grad: float, min_opacity: float, extent: float,
                       max_screen_size, percent_dense: float = 0.01, percent_big_ws: float = 0.1, n_copies: int = 2,
                       noise: Optional[Tensor] = None, generator: Optional[torch.Generator] = None,
-                      grad_column: int = 0):
+                      grad_column: int = 0, alloc=None):
     """The reference's `GaussianModel.densify_and_prune(max_grad, min_opacity, prune_big_points, extent,
     max_screen_size)` (/root/reference/street_gaussian/models/gaussian_model.py:521-551: densify_and_clone
     :493-519, densify_and_split :452-491, cat_optimizer :384-408, prune_points :416-431) on plain tensors, as
@@ -68,6 +68,8 @@ def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp
     here with `torch.randn` on the device — the same Philox stream the reference's call consumes.
     `grad_column=1` takes the gradients from `xyz_gradient_accum[:, 1]` (the background / actor models'
     `densify_grad_abs_*` option, gaussian_model_bkgd.py:102-105).
+    `alloc(role, name, shape)` (role in params / exp_avg / exp_avg_sq; optional) supplies the destination of every
+    output array — model_arena.SceneArena hands out views of a fresh flat arena, so the move kernel writes there.
     -> (params, exp_avg, exp_avg_sq, stats, scalars): stats = the three zeroed statistics (:546-548),
     scalars = the reference's `scalar_dict` (points_total / clone / split / pruned)."""
     xyz, scaling, rotation, opacity = params["xyz"], params["scaling"], params["rotation"], params["opacity"]
@@ -114,7 +116,15 @@ def densify_and_prune(params: Dict[str, Tensor], exp_avg: Dict[str, Tensor], exp
         assert noise.is_cuda and noise.dtype == torch.float32 and tuple(noise.shape) == (n_copies * n_split, 3), noise.shape
         n_out = n_stay + n_clone + n_copies * n_child
         index_ws = torch.empty(max(1, n_clone + 2 * n_child), dtype=torch.int32, device=dev)
-        outs = [torch.empty((n_out,) + tuple(t.shape[1:]), dtype=torch.float32, device=dev) for t, _ in table]
+        roles = [("params", k) for k in names] + [("exp_avg", k) for k in names if k in exp_avg] + \
+                [("exp_avg_sq", k) for k in names if k in exp_avg_sq]
+        if alloc is None:
+            outs = [torch.empty((n_out,) + tuple(t.shape[1:]), dtype=torch.float32, device=dev) for t, _ in table]
+        else:
+            outs = [alloc(r, k, (n_out,) + tuple(t.shape[1:])) for (r, k), (t, _) in zip(roles, table)]
+            for o, (t, _) in zip(outs, table):
+                assert o.is_cuda and o.dtype == torch.float32 and o.is_contiguous() and \
+                    tuple(o.shape) == (n_out,) + tuple(t.shape[1:]), (o.shape, t.shape)
         for a in range(0, len(table), MAX_ARRAYS):
             part, part_o = table[a:a + MAX_ARRAYS], outs[a:a + MAX_ARRAYS]
             n = len(part)

@@ -17,26 +17,33 @@ MAX_SEGMENTS = 32      # SC_ASSEMBLE_MAX_SEGMENTS
 FLIP_QUAT_Y = (0.0, 0.0, 1.0, 0.0)   # matrix_to_quaternion(diag(-1, 1, -1)), street_gaussian_model.py:55-58
 
 
-def _tables(segs, starts, flip_quat):
+def _tables(segs, starts, flip_quat, shells):
     n = len(segs)
     ptr = lambda t: t.data_ptr() if t is not None and t.numel() else None
     arr = lambda xs: (C.c_void_p * n)(*xs)
+    shell = (C.c_float * (4 * n))(*[v for sh in shells for v in (sh if sh is not None else (0.0, 0.0, 0.0, 0.0))])
     return ((C.c_int64 * (n + 1))(*starts), arr([ptr(s[0]) for s in segs]), arr([ptr(s[1]) for s in segs]),
             arr([s[2].data_ptr() if s[2] is not None else None for s in segs]),
             arr([s[3].data_ptr() if s[3] is not None else None for s in segs]), arr([ptr(s[4]) for s in segs]),
-            (C.c_float * 4)(*flip_quat))
+            (C.c_float * 4)(*flip_quat), shell)
+
+
+def _segments_of(kinds, flips, tensors):
+    segs, it = [], iter(tensors)
+    for actor, flip in zip(kinds, flips):
+        xyz, rot = next(it), next(it)
+        pr, pt = (next(it), next(it)) if actor else (None, None)
+        segs.append((xyz, rot, pr, pt, flip))
+    return segs
 
 
 class _Assemble(torch.autograd.Function):
     @staticmethod
     def forward(ctx, meta, *tensors):
-        kinds, flips, flip_axis, flip_quat = meta
+        kinds, flips, flip_axis, flip_quat, shells = meta
         dev = tensors[0].device
-        segs, it = [], iter(tensors)
-        for actor, flip in zip(kinds, flips):
-            xyz, rot = next(it).contiguous(), next(it).contiguous()
-            pr, pt = (next(it).contiguous(), next(it).contiguous()) if actor else (None, None)
-            segs.append((xyz, rot, pr, pt, flip))
+        tensors = tuple(t.contiguous() for t in tensors)
+        segs = _segments_of(kinds, flips, tensors)
         starts = [0]
         for s in segs:
             starts.append(starts[-1] + s[0].shape[0])
@@ -47,16 +54,19 @@ class _Assemble(torch.autograd.Function):
         with torch.cuda.device(dev):
             for a in range(0, len(segs), MAX_SEGMENTS):
                 part = segs[a:a + MAX_SEGMENTS]
-                t = _tables(part, starts[a:a + len(part) + 1], flip_quat)
-                check(lib.sc_assemble_fwd(len(part), t[0], t[1], t[2], t[3], t[4], t[5], flip_axis, t[6],
+                t = _tables(part, starts[a:a + len(part) + 1], flip_quat, shells[a:a + len(part)])
+                check(lib.sc_assemble_fwd(len(part), t[0], t[1], t[2], t[3], t[4], t[5], flip_axis, t[6], t[7],
                                           out_xyz.data_ptr(), out_rot.data_ptr(), st), "sc_assemble_fwd")
-        ctx.segs, ctx.starts, ctx.meta = segs, starts, meta
+        # inputs go through save_for_backward (autograd's version counters guard against an in-place parameter
+        # or pose update between forward and backward); only pointer-free metadata stays on ctx
+        ctx.save_for_backward(*tensors)
+        ctx.starts, ctx.meta = starts, meta
         return out_xyz, out_rot
 
     @staticmethod
     def backward(ctx, v_xyz, v_rot):
-        kinds, flips, flip_axis, flip_quat = ctx.meta
-        segs, starts = ctx.segs, ctx.starts
+        kinds, flips, flip_axis, flip_quat, shells = ctx.meta
+        segs, starts = _segments_of(kinds, flips, ctx.saved_tensors), ctx.starts
         dev = segs[0][0].device
         v_xyz = (v_xyz if v_xyz is not None else torch.zeros((starts[-1], 3), device=dev)).float().contiguous()
         v_rot = (v_rot if v_rot is not None else torch.zeros((starts[-1], 4), device=dev)).float().contiguous()
@@ -84,9 +94,9 @@ class _Assemble(torch.autograd.Function):
             for a in range(0, len(segs), MAX_SEGMENTS):
                 part, gpart = segs[a:a + MAX_SEGMENTS], gsegs[a:a + MAX_SEGMENTS]
                 n = len(part)
-                t = _tables(part, starts[a:a + n + 1], flip_quat)
+                t = _tables(part, starts[a:a + n + 1], flip_quat, shells[a:a + n])
                 g = [(C.c_void_p * n)(*[ptr(gs[j]) for gs in gpart]) for j in range(4)]
-                check(lib.sc_assemble_bwd(n, t[0], t[1], t[2], t[3], t[4], t[5], flip_axis, t[6], v_xyz.data_ptr(),
+                check(lib.sc_assemble_bwd(n, t[0], t[1], t[2], t[3], t[4], t[5], flip_axis, t[6], t[7], v_xyz.data_ptr(),
                                           v_rot.data_ptr(), g[0], g[1], g[2], g[3], st), "sc_assemble_bwd")
         return tuple(grads)
 
@@ -96,13 +106,24 @@ def assemble_xyz_rotation(segments: Sequence[Dict[str, Optional[Tensor]]], flip_
     """segments, in scene-graph order (background, visible actors, sky — `parse_camera`,
     street_gaussian_model.py:216-243): dicts with `xyz` [n,3] and `rotation` [n,4] (the model's RAW `_rotation`);
     actors add `pose_rot` [4] (ActorPose.get_tracking_rotation, raw wxyz), `pose_trans` [3] and optionally `flip`
-    [n] bool (the training-time flip mask, :262-271).  -> (`get_xyz` [N,3], `get_rotation` [N,4]), differentiable
-    w.r.t. every float input (tracked poses included)."""
+    [n] bool (the training-time flip mask, :262-271); the sky model adds `shell` = (centre xyz, radius): its
+    positions inside twice that radius are pushed out onto the sphere of radius 2 R (GaussianModelSky.get_xyz,
+    gaussian_model_sky.py:68-76).  -> (`get_xyz` [N,3], `get_rotation` [N,4]), differentiable w.r.t. every float
+    input (tracked poses included)."""
     if not segments:
         raise ValueError("assemble_xyz_rotation needs at least one segment")
-    kinds, flips, tensors = [], [], []
+    kinds, flips, tensors, shells = [], [], [], []
     for s in segments:
         xyz, rot = s["xyz"], s["rotation"]
+        sh = s.get("shell")
+        if sh is not None:
+            c, r = sh
+            c = [float(v) for v in (c.tolist() if torch.is_tensor(c) else c)]
+            r = float(r.item() if torch.is_tensor(r) else r)
+            # 2 * sphere_radius as the reference forms it: a float32 product (gaussian_model_sky.py:73)
+            sh = (c[0], c[1], c[2], float(torch.tensor(r, dtype=torch.float32) * 2))
+            assert s.get("pose_rot") is None, "the sky shell applies to a plain (unposed) segment"
+        shells.append(sh)
         if not (xyz.is_cuda and rot.is_cuda):
             raise RuntimeError("assemble_xyz_rotation needs CUDA tensors: street_crafter_b200 has no CPU path")
         assert xyz.dtype == torch.float32 and rot.dtype == torch.float32 and xyz.shape[1:] == (3,) and \
@@ -120,7 +141,7 @@ def assemble_xyz_rotation(segments: Sequence[Dict[str, Optional[Tensor]]], flip_
                 flip = (flip if flip.dtype == torch.bool else flip != 0).reshape(-1).contiguous().view(torch.uint8)
                 assert flip.numel() == xyz.shape[0] and flip.is_cuda
         flips.append(flip)
-    meta = (tuple(kinds), tuple(flips), int(flip_axis), tuple(float(v) for v in flip_quat))
+    meta = (tuple(kinds), tuple(flips), int(flip_axis), tuple(float(v) for v in flip_quat), tuple(shells))
     return _Assemble.apply(meta, *tensors)
 
 
@@ -141,7 +162,8 @@ class _AssembleAct(torch.autograd.Function):
                 t = _AssembleAct._tables(segs[a:a + MAX_SEGMENTS], starts[a:a + MAX_SEGMENTS + 1], clamp_max[a:a + MAX_SEGMENTS])
                 check(lib.sc_assemble_act_fwd(t[0], t[1], t[2], t[3], t[4], out_s.data_ptr(), out_o.data_ptr(), st),
                       "sc_assemble_act_fwd")
-        ctx.segs, ctx.starts, ctx.clamp_max = segs, starts, clamp_max
+        ctx.save_for_backward(*[t for sg in segs for t in sg])   # version-counter checked (not ctx attributes)
+        ctx.starts, ctx.clamp_max = starts, clamp_max
         return out_s, out_o
 
     @staticmethod
@@ -153,7 +175,9 @@ class _AssembleAct(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, v_s, v_o):
-        segs, starts, clamp_max = ctx.segs, ctx.starts, ctx.clamp_max
+        saved = ctx.saved_tensors
+        segs = [(saved[i], saved[i + 1]) for i in range(0, len(saved), 2)]
+        starts, clamp_max = ctx.starts, ctx.clamp_max
         dev, N = segs[0][0].device, starts[-1]
         v_s = (v_s if v_s is not None else torch.zeros((N, 3), device=dev)).float().contiguous()
         v_o = (v_o if v_o is not None else torch.zeros((N, 1), device=dev)).float().contiguous()

@@ -235,3 +235,86 @@ def test_reference_create_from_pcd_over_the_shim(table, dev):
     assert m._features_dc.shape == (40000, 1, 3) and m._features_rest.shape == (40000, 15, 3)
     assert torch.allclose(m._features_dc[:, 0].detach().cpu(), (rgb - 0.5) / 0.28209479177387814, atol=1e-6)
     assert m.max_radii2D.shape == (40000,)
+
+
+# ------------------------------------------------------------------------------ N1: LiDAR condition pipeline
+def _synthetic_lidar_sequence(n_frames=31, n_bkgd=6000, seed=0):
+    """the reference's ply_dict / track_info layout (waymo_processor.py:39-97, :205-224) on a synthetic drive:
+    float64 world-space background clouds per frame, three actors with box-frame clouds (one with missing frames,
+    one never observed), boxes that move with the frame"""
+    rng = np.random.default_rng(seed)
+    ply = {"background": {}, "background_visible": {}}
+    for f in range(n_frames):
+        xyz = np.stack([rng.uniform(-30, 30, n_bkgd), rng.uniform(-3, 5, n_bkgd), rng.uniform(2, 90, n_bkgd) + 0.5 * f], -1)
+        ply["background"][f] = np.concatenate([xyz, rng.uniform(0, 1, (n_bkgd, 3))], -1)
+    track_info = {f"{f:06d}": {} for f in range(n_frames)}
+    objects = {}
+    for a, (tid, frames) in enumerate((("car_a", range(0, n_frames)), ("car_b", range(5, 20, 2)), ("ghost", range(0, 0)))):
+        objects[a] = {"track_id": tid, "object_id": a, "start_frame": 0 if tid != "car_b" else 5,
+                      "end_frame": n_frames - 1 if tid != "car_b" else 19}
+        if len(frames):
+            ply[tid] = {}
+        for f in frames:
+            m = 400 + 10 * a
+            pts = rng.normal(0, 1, (m, 3)) * np.array([2.0, 0.8, 0.7])
+            ply[tid][f] = np.concatenate([pts, rng.uniform(0, 1, (m, 3))], -1)
+        for f in range(n_frames):
+            track_info[f"{f:06d}"][tid] = {"lidar_box": {"heading": 0.3 * a + 0.01 * f, "center_x": 12.0 + 3 * a + 0.4 * f,
+                                                         "center_y": -2.0 + 4 * a, "center_z": 0.6}}
+    return ply, track_info, objects
+
+
+@pytest.mark.parametrize("frame,W,H", [(12, 512, 288), (2, 320, 176)])
+def test_lidar_condition_pipeline_vs_reference_render_condition(table, dev, monkeypatch, tmp_path, frame, W, H):
+    """row N1: the reference's WaymoPointCloudProcessor.render_condition (UNMODIFIED: NumPy aggregation of +-10
+    frames, float64 actor posing, its own splat wrapper over the shim, uint8 quantisation, cv2.imwrite) against
+    the device pipeline (clouds resident, one gather kernel, no host round trip, no PNG)"""
+    from street_crafter_b200.lidar_condition import LidarClouds, box_pose, render_condition
+    for k, m in easyvolcap_stub(table).items():
+        monkeypatch.setitem(sys.modules, k, m)
+    ply, track_info, objects = _synthetic_lidar_sequence()
+    written = {}
+    cv2_stub = types.SimpleNamespace(imwrite=lambda path, arr: written.__setitem__(path, np.array(arr)))
+    cfg = types.SimpleNamespace(diffusion=types.SimpleNamespace(force_render_condition=False, shuffle_actors=False),
+                                render=types.SimpleNamespace(scale=0.01, use_ndc_scale=True, use_knn_scale=False))
+    lns = lidar_ns(table)
+    import os as _os
+    ns = bind(table, ["make_lidar_ply", "transform_lidar_ply", "render_condition"],
+              {"torch": torch, "np": np, "os": _os, "cv2": cv2_stub, "cfg": cfg, "Camera": object,
+               "render_pointcloud_diff_point_rasterization": lns["render_pointcloud_diff_point_rasterization"]})
+    proc = types.SimpleNamespace(start_frame=0, end_frame=30, delta_frames=10, ply_dict=ply, track_info=track_info)
+    proc.make_lidar_ply = types.MethodType(ns["make_lidar_ply"], proc)
+    proc.transform_lidar_ply = types.MethodType(ns["transform_lidar_ply"], proc)
+    V, K = make_camera(W, H, yaw_deg=6.0, z_shift=0.5 * frame, x_shift=0.3)
+    K = K.clone()
+    K[0, 2], K[1, 2] = 0.48 * W, 0.53 * H
+    c2w = torch.linalg.inv(V.double())
+    ego = np.eye(4)
+    ego[:3, 3] = [0.2, 0.0, 0.5 * frame]
+    cam = types.SimpleNamespace(
+        meta={"guidance_rgb_path": str(tmp_path / "g" / "rgb.png"), "guidance_mask_path": str(tmp_path / "g" / "mask.png"),
+              "frame": frame, "ego_pose": ego},
+        image_height=H, image_width=W, get_extrinsic=lambda: c2w.float(), get_intrinsic=lambda: K)
+    ns["render_condition"](proc, cam, objects)
+    ref_rgb = written[cam.meta["guidance_rgb_path"]][..., [2, 1, 0]]      # the reference writes BGR
+    ref_mask = written[cam.meta["guidance_mask_path"]]
+    assert ref_rgb.shape == (H, W, 3) and ref_mask.shape == (H, W, 1) and ref_rgb.dtype == np.uint8
+    # device pipeline: clouds uploaded once, actors active at `frame` in the reference's order
+    clouds = LidarClouds(ply, dev)
+    s, e = max(0, frame - 10), min(30, frame + 10)
+    poses = [(o["track_id"], box_pose(ego, track_info[f"{frame:06d}"][o["track_id"]]["lidar_box"]))
+             for o in objects.values() if o["start_frame"] <= frame <= o["end_frame"]]
+    u8, f32 = render_condition(clouds, c2w.float().numpy(), K.numpy(), H, W, s, e, poses, scale=0.01, use_ndc_scale=True,
+                               out_uint8=True, out_float=True)
+    got = u8.cpu().numpy()
+    assert got.shape == (H, W, 4)
+    want = np.concatenate([ref_rgb, ref_mask], -1)
+    d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+    frac = float((d > 0).mean())
+    print(f"lidar condition frame {frame}: {int((d > 0).sum())} of {d.size} bytes differ (max {int(d.max())}), coverage "
+          f"{float((want[..., 3] > 0).mean()):.3f}")
+    assert (want[..., 3] > 127).mean() > 0.05, "the frame must show something"
+    # float32 view-space depth (sum order of a 3-term dot product) feeds the splat radius: a handful of splats move
+    # by one ulp, and truncation to uint8 turns a 1e-7 difference into one LSB on a boundary
+    assert frac < 2e-3 and int(d.max()) <= 2, (frac, int(d.max()))
+    assert torch.equal(f32.cpu(), torch.from_numpy(got).permute(2, 0, 1).float() / 255.0)

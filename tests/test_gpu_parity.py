@@ -1083,7 +1083,8 @@ def test_assemble_vs_oracle(S, dev, n_bkgd, n_actors, n_per_actor, n_sky):
                      "pose_trans": leaf(3, k=20.0),
                      "flip": None if a % 3 == 2 else (torch.rand(n, generator=g) < 0.5).to(dev)})
     if n_sky:
-        segs.append({"name": "sky", "xyz": leaf(n_sky, 3, k=100.0), "rotation": leaf(n_sky, 4)})
+        segs.append({"name": "sky", "xyz": leaf(n_sky, 3, k=100.0), "rotation": leaf(n_sky, 4),
+                     "shell": ([3.0, -2.0, 1.0], 60.0)})     # GaussianModelSky.get_xyz: ~half the points inside 2 R
     N = sum(s["xyz"].shape[0] for s in segs)
     w_xyz, w_rot = torch.randn(N, 3, generator=g).to(dev), torch.randn(N, 4, generator=g).to(dev)
     fq = torch.tensor(FLIP_QUAT_Y, device=dev)

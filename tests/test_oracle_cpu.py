@@ -361,6 +361,7 @@ def _assemble_golden_segments(z, to=lambda t: t, grad=True):
             s["idft_base"] = [float(v) for v in z["actor_idft_base"]]
         if name == "sky":
             s["scaling_clamp_max"] = float(z["sky_clamp_max"])
+            s["shell"] = ([float(v) for v in z["sky_center"]], float(z["sky_radius"]))
         if name.startswith("obj_"):
             s.update(pose_rot=mk("pose_rot"), pose_trans=mk("pose_trans"), flip=to(torch.from_numpy(z[f"{name}_flip"])))
         segs.append(s)

@@ -44,6 +44,11 @@ def load():
     assert len(fs) == 1
     fs[0].decorator_list, fs[0].name = [], "sky_get_scaling"
     exec(compile(ast.Module(body=fs, type_ignores=[]), src_sky, "exec"), ns)
+    # ... and its shell-projected get_xyz, gaussian_model_sky.py:68-76
+    fx = [n for n in sky.body if isinstance(n, ast.FunctionDef) and n.name == "get_xyz"]
+    assert len(fx) == 1
+    fx[0].decorator_list, fx[0].name = [], "sky_get_xyz"
+    exec(compile(ast.Module(body=fx, type_ignores=[]), src_sky, "exec"), ns)
     # the actor model's Fourier DC features (gaussian_model_actor.py:67-76) and the base model's get_features
     # (gaussian_model.py:238-241); IDFT from the reference's own sh_utils (imports on CPU)
     import importlib.util
@@ -116,10 +121,13 @@ if __name__ == "__main__":
     flips = {"obj_000": torch.rand(sizes["obj_000"], generator=g) < 0.5, "obj_001": torch.zeros(0, dtype=torch.bool),
              "obj_002": torch.zeros(sizes["obj_002"], dtype=torch.bool)}
     m.flip_mask = torch.cat([flips[k] for k in m.graph_obj_list], 0)
-    class Sky(Leaf):                                                          # gaussian_model_sky.py:63-66
+    class Sky(Leaf):                                                          # gaussian_model_sky.py:63-76
         scaling_activation = staticmethod(torch.exp)
-        sphere_radius = torch.tensor(0.45)
+        sphere_radius = torch.Tensor([0.45])                                  # :24, a [1] float tensor
+        sphere_center = torch.tensor([0.5, -0.3, 0.2])
         get_scaling = property(ns["sky_get_scaling"])
+        get_xyz = property(ns["sky_get_xyz"])
+    m.sky._xyz = (m.sky._xyz.detach() * 0.3).requires_grad_(True)            # some inside, some outside 2 R
     m.sky.__class__ = Sky
     xyz = ns["get_xyz"](m)
     rot = ns["get_rotation"](m)
@@ -137,7 +145,8 @@ if __name__ == "__main__":
            "flip_axis": np.array(m.flip_axis), "out_xyz": xyz.detach().numpy(), "out_rot": rot.detach().numpy(),
            "w_xyz": w_xyz.numpy(), "w_rot": w_rot.numpy(), "out_scaling": sca.detach().numpy(),
            "out_opacity": opa.detach().numpy(), "w_scaling": w_sca.numpy(), "w_opacity": w_opa.numpy(),
-           "sky_clamp_max": np.array(float(Sky.sphere_radius)), "out_features": fea.detach().numpy(),
+           "sky_clamp_max": np.array(float(Sky.sphere_radius)),
+           "sky_center": Sky.sphere_center.numpy(), "sky_radius": np.array(float(Sky.sphere_radius), dtype=np.float32), "out_features": fea.detach().numpy(),
            "w_features": w_fea.numpy(),
            "actor_idft_base": IDFT_REF(Actor.fourier_scale * (m.frame - Actor.start_frame) / (Actor.end_frame - Actor.start_frame),
                                        Actor.fourier_dim)[0].numpy()}
@@ -156,4 +165,6 @@ if __name__ == "__main__":
         out[f"{k}_v_pose_trans"] = (pose_trans[k].grad if pose_trans[k].grad is not None else z3).numpy()
         out[f"{k}_flip"] = flips[k].numpy()
     np.savez_compressed(os.path.join(ROOT, "tests", "golden", "assemble.npz"), **out)
+    d = (m.sky._xyz.detach() - Sky.sphere_center).norm(dim=1)
+    print("sky points inside / outside the 2R shell:", int((d < 0.9).sum()), int((d >= 0.9).sum()))
     print(len(out), "arrays;", n, "Gaussians; flip quaternion", out["flip_quat"], "; flipped", int(m.flip_mask.sum()))
