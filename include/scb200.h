@@ -404,10 +404,10 @@ int sc_lidar_pack(int64_t n_pix, const float* rgb, const float* alpha, uint8_t* 
  * group: host_group_start[n_groups+1] ascending element offsets (multiples of 4), host_lr[n_groups]; elements
  * [lo, hi) (multiples of 4) are updated — the slice one rank owns after the gradient reduce-scatter.
  * params / exp_avg / exp_avg_sq are updated in place; `step` is the 1-based step count of the bias
- * correction.  n_groups <= 64. */
+ * correction; beta1 / beta2 / eps are the Python doubles torch forms 1 - beta from.  n_groups <= 64. */
 int sc_adam_step(int n_groups, const int64_t* host_group_start, const float* host_lr, int64_t lo, int64_t hi,
-                 float* params, const float* grads, float* exp_avg, float* exp_avg_sq, float beta1, float beta2,
-                 float eps, int64_t step, void* stream);
+                 float* params, const float* grads, float* exp_avg, float* exp_avg_sq, double beta1, double beta2,
+                 double eps, int64_t step, void* stream);
 /* Row layout of GaussianModel.make_ply / load_ply (gaussian_model.py:82-99, :107-156, :328-342):
  * x y z nx ny nz | f_dc (3) | f_rest (3 (K-1), channel-major) | opacity | scale (3) | rot (4) | semantic (S).
  * xyz[N,3] f_dc[N,1,3] f_rest[N,K-1,3] opacity[N,1] scaling[N,3] rotation[N,4] semantic[N,S] <-> rows[N,width]. */

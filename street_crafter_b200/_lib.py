@@ -78,7 +78,8 @@ SIGNATURES = {
     "sc_lidar_segment_bytes": (_i64, []),
     "sc_lidar_gather": (_i32, [_i64, _i32, _ptr, _ptr, _f32, _f32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "sc_lidar_pack": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _ptr]),
-    "sc_adam_step": (_i32, [_i32, _ptr, _ptr, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _f32, _f32, _f32, _i64, _ptr]),
+    "sc_adam_step": (_i32, [_i32, _ptr, _ptr, _i64, _i64, _ptr, _ptr, _ptr, _ptr, C.c_double, C.c_double, C.c_double,
+                            _i64, _ptr]),
     "sc_ply_row_width": (_i32, [_i32, _i32]),
     "sc_ply_pack": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_ply_unpack": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),

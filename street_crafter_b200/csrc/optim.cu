@@ -112,7 +112,7 @@ int ply_cols(PlyCols& C, int K, int S) {
 
 extern "C" int sc_adam_step(int n_groups, const int64_t* host_group_start /*[n_groups+1]*/, const float* host_lr,
                             int64_t lo, int64_t hi, float* params, const float* grads, float* exp_avg,
-                            float* exp_avg_sq, float beta1, float beta2, float eps, int64_t step, void* stream) {
+                            float* exp_avg_sq, double beta1, double beta2, double eps, int64_t step, void* stream) {
     SC_CHECK_ARG(n_groups >= 1 && n_groups <= ADAM_MAX_GROUPS && host_group_start && host_lr, "groups");
     SC_CHECK_ARG(step >= 1 && lo >= 0 && hi >= lo, "step / range");
     SC_CHECK_ARG((lo & 3) == 0 && (hi & 3) == 0, "range must be a multiple of 4 elements");
@@ -123,8 +123,8 @@ extern "C" int sc_adam_step(int n_groups, const int64_t* host_group_start /*[n_g
     AdamGroups G;
     G.n = n_groups;
     // the scalars torch forms in Python doubles before the float32 tensor ops
-    const double bc1 = 1.0 - pow((double)beta1, (double)step);
-    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    const double bc1 = 1.0 - pow(beta1, (double)step);
+    const double bc2 = 1.0 - pow(beta2, (double)step);
     for (int s = 0; s <= ADAM_MAX_GROUPS; ++s) G.start[s] = host_group_start[s <= n_groups ? s : n_groups];
     for (int s = 0; s < ADAM_MAX_GROUPS; ++s) G.step_size[s] = s < n_groups ? (float)((double)host_lr[s] / bc1) : 0.f;
     for (int s = 0; s < n_groups; ++s)
@@ -133,8 +133,8 @@ extern "C" int sc_adam_step(int n_groups, const int64_t* host_group_start /*[n_g
     const int64_t n4 = (hi - lo) / 4;
     adam_step_kernel<<<(unsigned)sc_div_up(n4, 256), 256, 0, (cudaStream_t)stream>>>(
         G, lo / 4, hi / 4, reinterpret_cast<float4*>(params), reinterpret_cast<const float4*>(grads),
-        reinterpret_cast<float4*>(exp_avg), reinterpret_cast<float4*>(exp_avg_sq), (float)(1.0 - (double)beta1), beta2,
-        (float)(1.0 - (double)beta2), (float)sqrt(bc2), eps);
+        reinterpret_cast<float4*>(exp_avg), reinterpret_cast<float4*>(exp_avg_sq), (float)(1.0 - beta1), (float)beta2,
+        (float)(1.0 - beta2), (float)sqrt(bc2), (float)eps);
     SC_CHECK_LAUNCH("adam_step_kernel");
     return SC_OK;
 }

@@ -33,11 +33,15 @@ def arena_layout(n: int, k_sh: int):
 
 
 class GaussianArena:
-    def __init__(self, scene: Dict[str, Tensor], device):
+    def __init__(self, scene: Dict[str, Tensor], device, pad_to: int = 4):
+        """pad_to: the buffers' length is rounded up to a multiple of it (4 * world for ShardedAdam, whose
+        reduce-scatter / all-gather need equal shards of whole float4s)"""
         n = scene["means"].shape[0]
         k_sh = scene["shs"].shape[1]
         self.n, self.k_sh = n, k_sh
         self.layout, total = arena_layout(n, k_sh)
+        self.used = total
+        total = (total + pad_to - 1) // pad_to * pad_to
         self.params = torch.zeros(total, dtype=torch.float32, device=device)
         self.grads = torch.zeros(total, dtype=torch.float32, device=device)
         for name, off, numel, shape in self.layout:
@@ -114,3 +118,65 @@ class HostViewFeeder:
         cur.wait_event(ready)
         for t in dev_tensors:
             t.record_stream(cur)  # the caching allocator must not recycle them under the compute stream
+
+
+class ShardedAdam:
+    """Optimizer step of the view-sharded trainer without a replicated update: the gradient
+    arena is REDUCE-SCATTERED (half the traffic of the all-reduce), every rank runs the fused Adam kernel
+    (csrc/optim.cu: torch.optim.Adam semantics, one learning rate per attribute as
+    street_gaussian/models/gaussian_model.py:293-305) on its 1/world slice — exp_avg / exp_avg_sq exist only for
+    that slice — and the updated parameters are ALL-GATHERED, optionally on a side stream so that the transfer
+    runs under the next step's first kernels (`wait()` before the parameters are read).  With world == 1 it is a
+    plain fused Adam over the whole arena."""
+
+    def __init__(self, arena: GaussianArena, lrs: Dict[str, float], betas=(0.9, 0.999), eps: float = 1e-15, group=None):
+        self.arena, self.lrs, self.betas, self.eps, self.group = arena, dict(lrs), betas, float(eps), group
+        on = dist.is_available() and dist.is_initialized()
+        self.world = dist.get_world_size(group) if on else 1
+        self.rank = dist.get_rank(group) if on else 0
+        total = arena.params.numel()
+        if total % (4 * self.world):
+            raise ValueError(f"arena length {total} is not a multiple of 4 * world: build it with pad_to=4 * world")
+        self.per = total // self.world
+        self.lo, self.hi = self.rank * self.per, (self.rank + 1) * self.per
+        dev = arena.params.device
+        self.exp_avg = torch.zeros(self.per, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(self.per, dtype=torch.float32, device=dev)
+        self.t = 0
+        self.side = torch.cuda.Stream(dev) if dev.type == "cuda" else None
+        self._gathered = None
+        starts = [off for _, off, _, _ in arena.layout] + [total]
+        self._starts = starts
+        self._lr = [float(self.lrs.get(name, 0.0)) for name, *_ in arena.layout]
+
+    def step(self, async_gather: bool = False) -> None:
+        import ctypes as C
+        from ._lib import check, lib
+        a = self.arena
+        self.t += 1
+        if self.world > 1:
+            # in place: the reduced slice of rank r lands at its own offset of the gradient arena
+            dist.reduce_scatter_tensor(a.grads[self.lo:self.hi], a.grads, op=dist.ReduceOp.SUM, group=self.group)
+        n = len(self._lr)
+        st = torch.cuda.current_stream(a.params.device).cuda_stream
+        with torch.cuda.device(a.params.device):
+            # the moment buffers hold the slice only: hand the kernel their virtual base (element 0 of the arena)
+            check(lib.sc_adam_step(n, (C.c_int64 * (n + 1))(*self._starts), (C.c_float * n)(*self._lr), self.lo, self.hi,
+                                   a.params.data_ptr(), a.grads.data_ptr(), self.exp_avg.data_ptr() - 4 * self.lo,
+                                   self.exp_avg_sq.data_ptr() - 4 * self.lo, float(self.betas[0]), float(self.betas[1]),
+                                   self.eps, self.t, st), "sc_adam_step")
+        if self.world > 1:
+            if async_gather and self.side is not None:
+                self.side.wait_stream(torch.cuda.current_stream(a.params.device))
+                with torch.cuda.stream(self.side):
+                    dist.all_gather_into_tensor(a.params.detach(), a.params.detach()[self.lo:self.hi], group=self.group)
+                    self._gathered = torch.cuda.Event()
+                    self._gathered.record(self.side)
+            else:
+                dist.all_gather_into_tensor(a.params.detach(), a.params.detach()[self.lo:self.hi], group=self.group)
+
+    def wait(self) -> None:
+        """the compute stream waits for an asynchronous parameter all-gather"""
+        if self._gathered is not None:
+            torch.cuda.current_stream(self.arena.params.device).wait_event(self._gathered)
+            self._gathered = None

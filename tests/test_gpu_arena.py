@@ -167,7 +167,10 @@ def test_checkpoint_and_ply_vs_reference_methods(table, dev, tmp_path):
     for grp in m.optimizer.param_groups:
         a = arena.params("background")[grp["name"]]
         assert torch.allclose(a, grp["params"][0], rtol=1e-5, atol=1e-6), grp["name"]
-    # ---- PLY rows
+    # ---- PLY rows (on bit-identical parameters: the two optimizers above differ in the last bits)
+    with torch.no_grad():
+        for k, t in arena.model_tensors("background").items():
+            t.copy_(getattr(m, k))
     el_ref = m.make_ply()
     el = arena.make_ply("background")
     assert el.dtype == el_ref.dtype and el.shape == el_ref.shape

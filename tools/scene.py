@@ -26,7 +26,22 @@ def make_camera(width: int, height: int, yaw_deg: float = 0.0, z_shift: float = 
 
 
 def make_gaussians(n: int, sh_degree: int = 3, seed: int = 0, scale_mean: float = 0.08,
-                   box=((-40.0, 40.0), (-3.0, 6.0), (-10.0, 90.0))):
+                   box=((-40.0, 40.0), (-3.0, 6.0), (-10.0, 90.0)), device=None):
+    """device=None: the CPU generator (the stream every parity test is pinned to); a CUDA device draws the same
+    distributions there (fast for the 6 M-Gaussian bench scene; other values)"""
+    if device is not None:
+        g = torch.Generator(device=device).manual_seed(seed)
+        kw = dict(generator=g, device=device)
+        u = torch.rand(n, 3, **kw)
+        lo = torch.tensor([b[0] for b in box], device=device)
+        hi = torch.tensor([b[1] for b in box], device=device)
+        means = lo + u * (hi - lo)
+        scales = torch.exp(math.log(scale_mean) + 0.6 * torch.randn(n, 3, **kw))
+        quats = torch.randn(n, 4, **kw)
+        opacities = torch.sigmoid(2.0 * torch.randn(n, **kw))
+        K = (sh_degree + 1) ** 2
+        shs = torch.cat([(torch.rand(n, 1, 3, **kw) * 2 - 1) * 1.7, 0.1 * torch.randn(n, K - 1, 3, **kw)], 1)
+        return dict(means=means, quats=quats, scales=scales, opacities=opacities, shs=shs)
     g = torch.Generator().manual_seed(seed)
     u = torch.rand(n, 3, generator=g)
     lo = torch.tensor([b[0] for b in box])
