@@ -10,11 +10,13 @@ Prints one JSON line per measurement (CUDA events, 1 warm-up pass, max over rank
 from __future__ import annotations
 
 import json
+import time
 import math
 import os
 import sys
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
@@ -88,13 +90,70 @@ def sweep(dev):
 
 
 def knn(dev):
+    """distCUDA2 beside the REFERENCE's own simple_knn.cu (oracle/_ref/libsimpleknn_ref.so, compiled from
+    /root/reference/submodules/simple-knn where it lies; simple_knn.cu:186-222) on the same device and points"""
+    import ctypes
     from street_crafter_b200.knn import distCUDA2
-    P = 5_000_000
-    xyz, _ = make_lidar_points(P, seed=5)
-    xyz = xyz.to(dev)
-    distCUDA2(xyz)
-    ms = ev_ms(lambda: distCUDA2(xyz), 3)
-    print(json.dumps({"config": "configs[4] distCUDA2", "points": P, "ms": ms, "Mpoints_per_s": P / ms / 1e3}))
+    ref = None
+    path = os.path.join(ROOT, "oracle", "_ref", "libsimpleknn_ref.so")
+    if os.path.exists(path):
+        ref = ctypes.CDLL(path)
+        ref.ref_knn.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    for P in (100_000, 1_000_000, 5_000_000):
+        xyz, _ = make_lidar_points(P, seed=5)
+        xyz = xyz.to(dev).contiguous()
+        distCUDA2(xyz)
+        ms = ev_ms(lambda: distCUDA2(xyz), 3)
+        row = {"config": "configs[4] distCUDA2", "points": P, "ms": ms, "Mpoints_per_s": P / ms / 1e3,
+               "frac_of_64B_per_point_hbm_floor": 64.0 * P / (ms * 1e-3) / 6535.4e9}
+        if ref is not None:
+            out = torch.zeros(P, device=dev)
+            ref.ref_knn(P, xyz.data_ptr(), out.data_ptr())       # warm-up (the reference syncs inside)
+            t0 = time.perf_counter()
+            ref.ref_knn(P, xyz.data_ptr(), out.data_ptr())
+            torch.cuda.synchronize()
+            ms_ref = (time.perf_counter() - t0) * 1e3              # its two blocking cudaMemcpy make wall clock the honest timer
+            got = distCUDA2(xyz)
+            row.update({"reference_simple_knn_ms": ms_ref, "speedup_vs_reference_kernel": ms_ref / ms,
+                        "bit_identical_frac": float((got == out).float().mean())})
+        print(json.dumps(row))
+
+
+def lidar_pipeline(dev):
+    """configs[2] through the device pipeline of row N1 (street_crafter_b200/lidar_condition.py): 25 condition frames of
+    a 5 M-point aggregate (21 background frames + 2 actors), gather -> projection -> binning -> max_hit compositing ->
+    uint8 pack, nothing leaves the device"""
+    import numpy as np
+    from street_crafter_b200.lidar_condition import LidarClouds, render_condition
+    W, H, frames, n_frames = 1024, 576, 25, 45
+    per = 5_000_000 // 21
+    rng = np.random.default_rng(0)
+    ply = {"background": {}}
+    for f in range(n_frames):
+        xyz = np.stack([rng.uniform(-40, 40, per), rng.uniform(-3, 6, per), rng.uniform(1, 80, per) + 0.4 * f], -1)
+        ply["background"][f] = np.concatenate([xyz, rng.uniform(0, 1, (per, 3))], -1).astype(np.float32)
+    for a in range(2):
+        ply[f"car{a}"] = {f: np.concatenate([rng.normal(0, 1, (2000, 3)), rng.uniform(0, 1, (2000, 3))], -1) for f in range(n_frames)}
+    clouds = LidarClouds(ply, dev)
+    K = make_camera(W, H)[1].numpy()
+
+    def trajectory():
+        outs = []
+        for i in range(frames):
+            f = 10 + i
+            V, _ = make_camera(W, H, yaw_deg=-10.0 + 20.0 * i / (frames - 1), z_shift=0.4 * f, x_shift=0.05 * i)
+            c2w = torch.linalg.inv(V.double()).float().numpy()
+            poses = [(f"car{a}", np.array([[1, 0, 0, 3.0 * a], [0, 1, 0, 0.5], [0, 0, 1, 15.0 + 0.4 * f], [0, 0, 0, 1.0]])) for a in range(2)]
+            u8, _ = render_condition(clouds, c2w, K, H, W, f - 10, f + 10, poses, scale=0.01, use_ndc_scale=True)
+            outs.append(u8)
+        return outs
+
+    trajectory()
+    ms = ev_ms(trajectory)
+    cov = float((trajectory()[frames // 2][..., 3] > 0).float().mean())
+    print(json.dumps({"config": "configs[2] LiDAR condition pipeline on the device (N1)", "points_per_frame": 21 * per + 2 * 21 * 2000,
+                      "frames": frames, "size": [W, H], "ms_total": ms, "frames_per_s": frames / ms * 1e3,
+                      "mid_frame_coverage": cov}))
 
 
 def multiview(dev):
@@ -148,4 +207,4 @@ if __name__ == "__main__":
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
     torch.cuda.set_device(dev)
     for what in sys.argv[1:] or ["lidar", "sweep", "knn"]:
-        {"lidar": lidar, "sweep": sweep, "knn": knn, "multiview": multiview}[what](dev)
+        {"lidar": lidar, "lidar_pipeline": lidar_pipeline, "sweep": sweep, "knn": knn, "multiview": multiview}[what](dev)
