@@ -20,15 +20,19 @@ from torch import Tensor
 FIELDS = (("means", 3), ("quats", 4), ("scales", 3), ("opacities", 1))
 
 
-def arena_layout(n: int, k_sh: int):
+def arena_layout(n: int, k_sh: int, align: int = 4):
     """[(name, offset, numel, shape)] of the attribute-major arena; offsets are multiples of 4
-    floats so every view is 16-byte aligned (float4 kernels)."""
+    floats so every view is 16-byte aligned (float4 kernels).  The SH block starts (and the arena ends) on
+    a multiple of `align`: the geometric block [0, shs offset) and the SH block are then each divisible into
+    `align / 4` equal float4 slices (ShardedAdam shards and gathers them separately)."""
     out, off = [], 0
     for name, w in FIELDS:
         out.append((name, off, n * w, (n, w)))
         off += (n * w + 3) // 4 * 4
+    off = (off + align - 1) // align * align
     out.append(("shs", off, n * k_sh * 3, (n, k_sh, 3)))
-    off += (n * k_sh * 3 + 3) // 4 * 4
+    off += n * k_sh * 3
+    off = (off + align - 1) // align * align
     return out, off
 
 
@@ -39,9 +43,9 @@ class GaussianArena:
         n = scene["means"].shape[0]
         k_sh = scene["shs"].shape[1]
         self.n, self.k_sh = n, k_sh
-        self.layout, total = arena_layout(n, k_sh)
-        self.used = total
-        total = (total + pad_to - 1) // pad_to * pad_to
+        self.layout, total = arena_layout(n, k_sh, max(4, pad_to))
+        # [geometric block | SH block]: the two ranges ShardedAdam exchanges separately
+        self.blocks = [(0, self.layout[-1][1]), (self.layout[-1][1], total)]
         self.params = torch.zeros(total, dtype=torch.float32, device=device)
         self.grads = torch.zeros(total, dtype=torch.float32, device=device)
         for name, off, numel, shape in self.layout:
@@ -125,9 +129,11 @@ class ShardedAdam:
     arena is REDUCE-SCATTERED (half the traffic of the all-reduce), every rank runs the fused Adam kernel
     (csrc/optim.cu: torch.optim.Adam semantics, one learning rate per attribute as
     street_gaussian/models/gaussian_model.py:293-305) on its 1/world slice — exp_avg / exp_avg_sq exist only for
-    that slice — and the updated parameters are ALL-GATHERED, optionally on a side stream so that the transfer
-    runs under the next step's first kernels (`wait()` before the parameters are read).  With world == 1 it is a
-    plain fused Adam over the whole arena."""
+    that slice — and the updated parameters are ALL-GATHERED.  The arena's two blocks are exchanged separately:
+    the geometric block (means, quats, scales, opacities: 19 % of the bytes) is what the next step's projection and
+    binning read; the SH block (81 %) is first read by the SH kernel, so with `async_gather` its all-gather runs on
+    a side stream UNDER the projection + binning of the next step's views (rendering.prepare_view).  `wait_geometry()`
+    / `wait_sh()` make the compute stream wait for the respective gather.  world == 1: a plain fused Adam."""
 
     def __init__(self, arena: GaussianArena, lrs: Dict[str, float], betas=(0.9, 0.999), eps: float = 1e-15, group=None):
         self.arena, self.lrs, self.betas, self.eps, self.group = arena, dict(lrs), betas, float(eps), group
@@ -135,48 +141,66 @@ class ShardedAdam:
         self.world = dist.get_world_size(group) if on else 1
         self.rank = dist.get_rank(group) if on else 0
         total = arena.params.numel()
-        if total % (4 * self.world):
-            raise ValueError(f"arena length {total} is not a multiple of 4 * world: build it with pad_to=4 * world")
-        self.per = total // self.world
-        self.lo, self.hi = self.rank * self.per, (self.rank + 1) * self.per
+        self.ranges = []          # (block lo, block hi, my lo, my hi, offset of my slice inside the moment buffers)
+        mom = 0
+        for b0, b1 in arena.blocks:
+            if (b1 - b0) % (4 * self.world):
+                raise ValueError(f"arena block [{b0}, {b1}) is not a multiple of 4 * world: build the arena with "
+                                 f"pad_to=4 * world")
+            per = (b1 - b0) // self.world
+            self.ranges.append((b0, b1, b0 + self.rank * per, b0 + (self.rank + 1) * per, mom))
+            mom += per
         dev = arena.params.device
-        self.exp_avg = torch.zeros(self.per, dtype=torch.float32, device=dev)
-        self.exp_avg_sq = torch.zeros(self.per, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(max(mom, 4), dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(max(mom, 4), dtype=torch.float32, device=dev)
         self.t = 0
         self.side = torch.cuda.Stream(dev) if dev.type == "cuda" else None
-        self._gathered = None
-        starts = [off for _, off, _, _ in arena.layout] + [total]
-        self._starts = starts
+        self._ev = [None, None]
+        self._starts = [off for _, off, _, _ in arena.layout] + [total]
         self._lr = [float(self.lrs.get(name, 0.0)) for name, *_ in arena.layout]
 
     def step(self, async_gather: bool = False) -> None:
         import ctypes as C
         from ._lib import check, lib
         a = self.arena
+        dev = a.params.device
         self.t += 1
-        if self.world > 1:
-            # in place: the reduced slice of rank r lands at its own offset of the gradient arena
-            dist.reduce_scatter_tensor(a.grads[self.lo:self.hi], a.grads, op=dist.ReduceOp.SUM, group=self.group)
+        params = a.params.detach()
         n = len(self._lr)
-        st = torch.cuda.current_stream(a.params.device).cuda_stream
-        with torch.cuda.device(a.params.device):
-            # the moment buffers hold the slice only: hand the kernel their virtual base (element 0 of the arena)
-            check(lib.sc_adam_step(n, (C.c_int64 * (n + 1))(*self._starts), (C.c_float * n)(*self._lr), self.lo, self.hi,
-                                   a.params.data_ptr(), a.grads.data_ptr(), self.exp_avg.data_ptr() - 4 * self.lo,
-                                   self.exp_avg_sq.data_ptr() - 4 * self.lo, float(self.betas[0]), float(self.betas[1]),
-                                   self.eps, self.t, st), "sc_adam_step")
+        st = torch.cuda.current_stream(dev).cuda_stream
+        for b0, b1, lo, hi, mo in self.ranges:
+            if self.world > 1:
+                # in place: the reduced slice of rank r lands at its own offset of the gradient arena
+                dist.reduce_scatter_tensor(a.grads[lo:hi], a.grads[b0:b1], op=dist.ReduceOp.SUM, group=self.group)
+            with torch.cuda.device(dev):
+                # the moment buffers hold this rank's slices only: hand the kernel their virtual base
+                check(lib.sc_adam_step(n, (C.c_int64 * (n + 1))(*self._starts), (C.c_float * n)(*self._lr), lo, hi,
+                                       a.params.data_ptr(), a.grads.data_ptr(), self.exp_avg.data_ptr() + 4 * (mo - lo),
+                                       self.exp_avg_sq.data_ptr() + 4 * (mo - lo), float(self.betas[0]),
+                                       float(self.betas[1]), self.eps, self.t, st), "sc_adam_step")
         if self.world > 1:
-            if async_gather and self.side is not None:
-                self.side.wait_stream(torch.cuda.current_stream(a.params.device))
-                with torch.cuda.stream(self.side):
-                    dist.all_gather_into_tensor(a.params.detach(), a.params.detach()[self.lo:self.hi], group=self.group)
-                    self._gathered = torch.cuda.Event()
-                    self._gathered.record(self.side)
-            else:
-                dist.all_gather_into_tensor(a.params.detach(), a.params.detach()[self.lo:self.hi], group=self.group)
+            for i, (b0, b1, lo, hi, _) in enumerate(self.ranges):
+                if async_gather and self.side is not None:
+                    self.side.wait_stream(torch.cuda.current_stream(dev))
+                    with torch.cuda.stream(self.side):
+                        dist.all_gather_into_tensor(params[b0:b1], params[lo:hi], group=self.group)
+                        self._ev[i] = torch.cuda.Event()
+                        self._ev[i].record(self.side)
+                else:
+                    dist.all_gather_into_tensor(params[b0:b1], params[lo:hi], group=self.group)
+
+    def _wait(self, i: int) -> None:
+        if self._ev[i] is not None:
+            torch.cuda.current_stream(self.arena.params.device).wait_event(self._ev[i])
+            self._ev[i] = None
+
+    def wait_geometry(self) -> None:
+        """the compute stream waits for the asynchronous all-gather of the geometric block"""
+        self._wait(0)
+
+    def wait_sh(self) -> None:
+        self._wait(1)
 
     def wait(self) -> None:
-        """the compute stream waits for an asynchronous parameter all-gather"""
-        if self._gathered is not None:
-            torch.cuda.current_stream(self.arena.params.device).wait_event(self._gathered)
-            self._gathered = None
+        self._wait(0)
+        self._wait(1)

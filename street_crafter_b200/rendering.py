@@ -481,6 +481,63 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
                                     tile_size, isect_offsets, flatten_ids, absgrad, max_hit)
 
 
+def _project_begin(means, quats, scales, opacities, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
+                   radius_clip, antialiased, tile_size, st):
+    """projection (+ opacity * compensation, result packing) and the first half of the binning for ONE camera"""
+    N = means.shape[0]
+    dev = means.device
+    radii = torch.empty((1, N), dtype=torch.int32, device=dev)
+    means2d = torch.empty((1, N, 2), dtype=torch.float32, device=dev)
+    depths = torch.empty((1, N), dtype=torch.float32, device=dev)
+    conics = torch.empty((1, N, 3), dtype=torch.float32, device=dev)
+    comps = torch.empty((1, N), dtype=torch.float32, device=dev) if antialiased else None
+    op_c = torch.empty((1, N), dtype=torch.float32, device=dev)
+    # the renderer's result packing (row A11), written by the producing kernels
+    vis = torch.empty((1, N), dtype=torch.bool, device=dev)
+    radii_norm = torch.empty((1, N), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.sc_projection_fwd_opacity(N, 1, _p(means), _p(quats), _p(scales), _p(opacities),
+                                            _p(viewmats), _p(Ks), int(width), int(height), float(eps2d),
+                                            float(near_plane), float(far_plane), float(radius_clip),
+                                            _p(radii), _p(means2d), _p(depths), _p(conics), _p(comps),
+                                            _p(op_c), _p(vis), _p(radii_norm), st),
+              "sc_projection_fwd_opacity")
+        tile_width = math.ceil(width / float(tile_size))
+        tile_height = math.ceil(height / float(tile_size))
+        tpg = torch.empty((1, N), dtype=torch.int32, device=dev)
+        state = _isect_begin(means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st)
+    return dict(radii=radii, means2d=means2d, depths=depths, conics=conics, comps=comps, op_c=op_c, vis=vis,
+                radii_norm=radii_norm, state=state, tile_width=tile_width, tile_height=tile_height,
+                key=(N, int(width), int(height), int(tile_size), bool(antialiased)))
+
+
+def _project_finish(pb, need_ids):
+    dev = pb["radii"].device
+    with torch.cuda.device(dev):
+        tpg, isect_ids, flatten_ids, isect_offsets = _isect_finish(pb.pop("state"), need_ids)
+    if isect_offsets is None:
+        isect_offsets = isect_offset_encode(isect_ids, 1, pb["tile_width"], pb["tile_height"])
+    if isect_ids is None:   # not materialised (need_ids=False): the compositor only reads flatten_ids
+        isect_ids = torch.empty(0, dtype=torch.int64, device=dev)
+    pb.update(tpg=tpg, isect_ids=isect_ids, flatten_ids=flatten_ids, isect_offsets=isect_offsets)
+    return pb
+
+
+@torch.no_grad()
+def prepare_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, viewmats: Tensor, Ks: Tensor,
+                 width: int, height: int, eps2d: float = 0.3, near_plane: float = 0.01, far_plane: float = 1e10,
+                 radius_clip: float = 0.0, antialiased: bool = True, tile_size: int = 16, need_isect_ids: bool = False):
+    """Phase 1 of a camera pass — projection and the complete binning, everything that reads only the GEOMETRIC
+    parameters — as a state object for `fused_view(..., prepared=state)`.  A multi-view step can run phase 1 of all
+    its views first: the view-sharded trainer does, so that the all-gather of the SH coefficients (81 % of the
+    parameter bytes) travels under it (parallel.ShardedAdam).  Same kernels, same results."""
+    means, quats, scales = _f32c(means.detach(), "means"), _f32c(quats.detach(), "quats"), _f32c(scales.detach(), "scales")
+    opacities = _f32c(opacities.detach(), "opacities", 4)
+    pb = _project_begin(means, quats, scales, opacities, _f32c(viewmats, "viewmats"), _f32c(Ks, "Ks"), width, height, eps2d,
+                        near_plane, far_plane, radius_clip, antialiased, tile_size, _stream())
+    return _project_finish(pb, need_isect_ids)
+
+
 # ------------------------------------------------------------------------------------------
 # one camera pass as ONE autograd node (rows A1..A8b with A2/A5-prologue/A6 folded into kernels)
 # ------------------------------------------------------------------------------------------
@@ -493,7 +550,8 @@ class _FusedView(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
-                eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, sinks, need_ids=True):
+                eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, sinks, need_ids=True,
+                prepared=None):
         means = _f32c(means, "means")
         quats = _f32c(quats, "quats")
         scales = _f32c(scales, "scales")
@@ -505,36 +563,26 @@ class _FusedView(torch.autograd.Function):
         N, Kc = shs.shape[0], shs.shape[1]
         dev = means.device
         st = _stream()
-        radii = torch.empty((1, N), dtype=torch.int32, device=dev)
-        means2d = torch.empty((1, N, 2), dtype=torch.float32, device=dev)
-        depths = torch.empty((1, N), dtype=torch.float32, device=dev)
-        conics = torch.empty((1, N, 3), dtype=torch.float32, device=dev)
-        comps = torch.empty((1, N), dtype=torch.float32, device=dev) if antialiased else None
-        op_c = torch.empty((1, N), dtype=torch.float32, device=dev)
         colors4 = torch.empty((1, N, 4), dtype=torch.float32, device=dev)
-        # the renderer's result packing (row A11), written by the producing kernels
-        vis = torch.empty((1, N), dtype=torch.bool, device=dev)
-        radii_norm = torch.empty((1, N), dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
-            check(lib.sc_projection_fwd_opacity(N, 1, _p(means), _p(quats), _p(scales), _p(opacities),
-                                                _p(viewmats), _p(Ks), int(width), int(height), float(eps2d),
-                                                float(near_plane), float(far_plane), float(radius_clip),
-                                                _p(radii), _p(means2d), _p(depths), _p(conics), _p(comps),
-                                                _p(op_c), _p(vis), _p(radii_norm), st),
-                  "sc_projection_fwd_opacity")
-        tile_width = math.ceil(width / float(tile_size))
-        tile_height = math.ceil(height / float(tile_size))
-        with torch.cuda.device(dev):
-            tpg = torch.empty((1, N), dtype=torch.int32, device=dev)
-            state = _isect_begin(means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st)
-            # independent of the binning: runs on the GPU while the host waits for the counts
-            check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(radii),
-                                     _p(depths), _p(colors4), st), "sc_sh_fwd_view")
-            tpg, isect_ids, flatten_ids, isect_offsets = _isect_finish(state, need_ids)
-        if isect_offsets is None:
-            isect_offsets = isect_offset_encode(isect_ids, 1, tile_width, tile_height)
-        if isect_ids is None:   # not materialised (need_ids=False): the compositor only reads flatten_ids
-            isect_ids = torch.empty(0, dtype=torch.int64, device=dev)
+        if prepared is None:
+            pb = _project_begin(means, quats, scales, opacities, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
+                                radius_clip, antialiased, tile_size, st)
+            with torch.cuda.device(dev):
+                # independent of the binning: runs on the GPU while the host waits for the counts
+                check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(pb["radii"]),
+                                         _p(pb["depths"]), _p(colors4), st), "sc_sh_fwd_view")
+            pb = _project_finish(pb, need_ids)
+        else:
+            # two-phase schedule (prepare_view): projection + binning already ran — e.g. for every view of the
+            # step while the SH coefficients were still arriving from the other ranks
+            pb = prepared
+            assert pb["key"] == (N, int(width), int(height), int(tile_size), bool(antialiased)), "prepared for another view"
+            with torch.cuda.device(dev):
+                check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(pb["radii"]),
+                                         _p(pb["depths"]), _p(colors4), st), "sc_sh_fwd_view")
+        radii, means2d, depths, conics, comps, op_c, vis, radii_norm = (pb[k] for k in (
+            "radii", "means2d", "depths", "conics", "comps", "op_c", "vis", "radii_norm"))
+        tpg, isect_ids, flatten_ids, isect_offsets = (pb[k] for k in ("tpg", "isect_ids", "flatten_ids", "isect_offsets"))
         with torch.cuda.device(dev):
             render_colors = torch.empty((1, height, width, 4), dtype=torch.float32, device=dev)
             render_alphas = torch.empty((1, height, width, 1), dtype=torch.float32, device=dev)
@@ -610,10 +658,10 @@ class _FusedView(torch.autograd.Function):
             if absgrad:
                 m2.absgrad = v_abs.view(1, N, 2)
         if sinks is not None:
-            return (None,) * 20
+            return (None,) * 21
         need = ctx.needs_input_grad
         return (g_means if need[0] else None, g_quats if need[1] else None, g_scales if need[2] else None,
-                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 15
+                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 16
 
 
 def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, shs: Tensor, viewmats: Tensor,
@@ -621,7 +669,7 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
                near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
                antialiased: bool = True, tile_size: int = 16, absgrad: bool = False,
                grad_sinks: Optional[Dict[str, Tensor]] = None, need_isect_ids: bool = True,
-               ) -> Tuple[Tensor, Tensor, Dict]:
+               prepared: Optional[Dict] = None) -> Tuple[Tensor, Tensor, Dict]:
     """One camera (viewmats[1,4,4], Ks[1,3,3], campos[3] on the device), SH colours with K = 4 or
     16 coefficients, RGB + depth channel: -> (render_colors[1,H,W,4], render_alphas[1,H,W,1], meta).
     `meta["means2d"].grad` / `.absgrad` are filled by the backward pass.  `need_isect_ids=False`
@@ -635,7 +683,7 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
         assert all(k in grad_sinks for k in ("means", "quats", "scales", "opacities", "shs"))
     out = _FusedView.apply(means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
                            eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, grad_sinks,
-                           need_isect_ids)
+                           need_isect_ids, prepared)
     (rc, ra, depth_norm, radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets,
      vis, radii_norm) = out[:15]
     comps = out[15] if len(out) > 15 else None

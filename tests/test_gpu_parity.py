@@ -1185,3 +1185,39 @@ def test_assemble_features_vs_oracle_cfg2(S, dev, K):
         assert (a_dc - b_dc).abs().max() < 2e-6
         if b_r is not None and b_r.numel():
             assert torch.equal(a_r, b_r)
+
+
+def test_prepare_view_two_phase_equals_single_pass(S, dev):
+    """rendering.prepare_view (projection + binning first) + fused_view(prepared=...) == one fused_view call,
+    forward bit-equal, gradients to the rounding of the atomic accumulation; a state prepared for another image
+    size is refused"""
+    from street_crafter_b200.rendering import prepare_view
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    n, W, H, deg = 40000, 640, 400, 3
+    s = make_gaussians(n, sh_degree=deg, seed=8)
+    V, K = make_camera(W, H, yaw_deg=-12.0)
+    Vd, Kd = V[None].to(dev), K[None].to(dev)
+    cc = (-(V[:3, :3].T @ V[:3, 3])).to(dev)
+    g = torch.Generator().manual_seed(1)
+    v_rc, v_ra = torch.randn(1, H, W, 4, generator=g).to(dev), torch.randn(1, H, W, 1, generator=g).to(dev)
+    res = []
+    for two_phase in (False, True):
+        c = {k: v.to(dev).requires_grad_(True) for k, v in s.items()}
+        st = prepare_view(c["means"], c["quats"], c["scales"], c["opacities"], Vd, Kd, W, H, near_plane=0.001,
+                          far_plane=1000.0, need_isect_ids=True) if two_phase else None
+        out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None], Vd, Kd, cc, W, H,
+                                   deg, prepared=st)
+        torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc, v_ra])
+        res.append((c, out))
+    (c0, o0), (c1, o1) = res
+    for k in ("render_colors", "render_alphas", "depth", "radii", "visibility_filter"):
+        assert torch.equal(o0[k], o1[k]), k
+    for k in ("isect_ids", "flatten_ids", "isect_offsets", "tiles_per_gauss"):
+        assert torch.equal(o0["aux"][k], o1["aux"][k]), k
+    for k in c0:
+        assert torch.allclose(c0[k].grad, c1[k].grad, rtol=1e-4, atol=1e-6 * float(c0[k].grad.abs().max())), k
+    assert o1["viewspace_points"].absgrad is not None
+    with pytest.raises(AssertionError):
+        st = prepare_view(c0["means"], c0["quats"], c0["scales"], c0["opacities"], Vd, Kd, W, H)
+        render_kernel_gsplat(c0["means"], c0["shs"], c0["scales"], c0["quats"], c0["opacities"][:, None], Vd, Kd, cc, W // 2, H,
+                             deg, prepared=st)
