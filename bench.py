@@ -343,7 +343,8 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
     gradient arena, fused Adam on the rank's slice, all-gather of the parameters (parallel.ShardedAdam; at N = 1 a
     fused Adam over the whole arena).  Two-phase view schedule: projection + binning of all the rank's views first
     (they read only the geometric parameters), then SH + compositing + backward per view, so that the all-gather of
-    the SH coefficients (81 % of the bytes) of the PREVIOUS step's update travels under phase one."""
+    the SH coefficients (81 % of the bytes) of the PREVIOUS step's update travels under phase one; the projection
+    backward of all views runs LAST, under the reduce-scatter of the SH gradients."""
     import torch.distributed as dist
     from street_crafter_b200.parallel import ShardedAdam
     from street_crafter_b200.rendering import prepare_view
@@ -351,7 +352,8 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
     arena = GaussianArena(scene, dev, pad_to=4 * world)
     del scene
     sinks = arena.sinks()
-    opt = ShardedAdam(arena, {"means": 1.6e-4, "quats": 1e-3, "scales": 5e-3, "opacities": 5e-2, "shs": 2.5e-3})
+    opt = ShardedAdam(arena, {"means": 1.6e-4, "quats": 1e-3, "scales": 5e-3, "opacities": 5e-2, "shs": 2.5e-3},
+                      reserve_sms=int(os.environ.get("SCB200_RESERVE_SMS", "32")))
     views = []
     for f in range(CFG4_FRAMES):
         for (W, H, yaw) in CFG4_CAMS:
@@ -370,8 +372,19 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
         Vm, Km = make_camera(W, H, yaw_deg=yaw, z_shift=z)
         cams[v] = (Vm[None].to(dev), Km[None].to(dev), (-(Vm[:3, :3].T @ Vm[:3, 3])).to(dev))
 
+    marks = []   # CUDA events of the compute stream at the phase boundaries of the timed steps
+
+    def mark():
+        if marks is not None and len(marks) < 64:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            marks.append(e)
+
+    fill_stream = torch.cuda.Stream(dev)
+
     def step():
-        arena.zero_grad()
+        mark()
+        zeroed = arena.zero_grad(stream=fill_stream)   # under phase one, which does not touch the gradients
         opt.wait_geometry()
         prepared = []
         for v in mine:   # phase one: everything that reads only means / quats / scales / opacities
@@ -379,18 +392,27 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
             Vd, Kd, _ = cams[v]
             prepared.append(prepare_view(arena.means, arena.quats, arena.scales, arena.opacities, Vd, Kd, W, H,
                                          near_plane=0.001, far_plane=1000.0))
+        mark()
         opt.wait_sh()
+        deferred = []
         for v, st in zip(mine, prepared):
             W, H, _, _ = views[v]
             Vd, Kd, Cd = cams[v]
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities, Vd, Kd, Cd,
-                                       W, H, SH_DEGREE, grad_sinks=sinks, aux_ids=False, prepared=st)
+                                       W, H, SH_DEGREE, grad_sinks=sinks, aux_ids=False, prepared=st, deferred=deferred)
             torch.autograd.backward([out["render_colors"], out["render_alphas"]], list(up[(W, H)]))
         prepared.clear()
+        # the SH gradients are final: their reduce-scatter travels under the projection backward of all the views
+        opt.begin_sh_exchange()
+        for fn in deferred:
+            fn()
+        mark()
         opt.step(async_gather=True)
+        mark()
 
     for _ in range(2):
         step()
+    marks.clear()
     steps = max(2, min(args.steps, 4))
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -406,13 +428,22 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     pix = sum(W * H for (W, H, _, _) in views)
+    ph = [0.0, 0.0, 0.0]
+    for i in range(0, len(marks) - 3, 4):
+        for j in range(3):
+            ph[j] += marks[i + j].elapsed_time(marks[i + j + 1]) / steps
+    phases = {"projection_binning_all_views_ms": ph[0], "sh_compositing_backward_ms": ph[1],
+              "reduce_scatter_adam_ms": ph[2], "rank": rank,
+              "note": "compute-stream CUDA events of rank 0; the parameter all-gather runs on a side stream, what is "
+                      "left of ms_per_step is its exposed part plus rank skew"}
     del arena, sinks, opt
     torch.cuda.empty_cache()
     return {"workload": "cfg4: 6M Gaussians SH3, 40 views = 8 frames x (3 x 1920x1280 + 2 x 1920x886), view v on rank v mod "
                         "world; step = fwd + bwd of the rank's views + reduce-scatter of the gradient arena + fused Adam on "
                         "the rank's slice + all-gather of the parameters (N = 1: fused Adam on the whole arena)",
             "scaling": "strong", "gaussians": CFG4_GAUSS, "views": len(views), "views_per_gpu": len(mine), "steps": steps,
-            "ms_per_step": ms, "views_per_s": len(views) / (ms * 1e-3), "value": pix / (ms * 1e-3) / 1e6, "unit": "Mpix/s"}
+            "ms_per_step": ms, "views_per_s": len(views) / (ms * 1e-3), "value": pix / (ms * 1e-3) / 1e6, "unit": "Mpix/s",
+            "phases": phases}
 
 
 class _LibProxy:
@@ -441,7 +472,7 @@ def run_ours(args):
     import street_crafter_b200 as S
     from street_crafter_b200 import _lib, rendering
     from street_crafter_b200.losses import photometric_loss_render
-    from street_crafter_b200.parallel import GaussianArena, HostViewFeeder, allreduce_gradients
+    from street_crafter_b200.parallel import GaussianArena, HostViewFeeder, TwoPhaseAllReduce, allreduce_gradients
     from street_crafter_b200.renderer import render_kernel_gsplat
     from tools.scene import make_camera, make_gaussians
 
@@ -486,16 +517,23 @@ def run_ours(args):
 
     sinks = arena.sinks()  # projection / SH backward add straight into the flat gradient arena
 
+    exchange = TwoPhaseAllReduce(arena)
+
     def step_resident():
         """inputs already in HBM; upstream gradients fixed (loss-independent)"""
         arena.zero_grad()
+        deferred = [] if world > 1 else None
         for v in range(n_views):
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
                                        dev_V[v], dev_K[v], dev_C[v], WIDTH, HEIGHT, SH_DEGREE, grad_sinks=sinks,
-                                       aux_ids=False)
+                                       aux_ids=False, deferred=deferred)
             torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc[v], v_ra[v]])
         if world > 1:
-            allreduce_gradients(arena)
+            # all-reduce of the SH block (81 % of the arena) under the views' projection backward, then the rest
+            exchange.begin_sh()
+            for fn in deferred:
+                fn()
+            exchange.finish()
 
     feeder = HostViewFeeder(dev)
 
@@ -523,7 +561,8 @@ def run_ours(args):
             loss.backward()
             losses.append(loss.detach())
         if world > 1:
-            allreduce_gradients(arena)
+            exchange.begin_sh()
+            exchange.finish()
         # D2H read of the step's result: into pinned memory, then wait for it
         loss_host.copy_(torch.stack(losses), non_blocking=True)
         torch.cuda.current_stream().synchronize()

@@ -189,6 +189,9 @@ int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, in
  *     skipped when the caller only composites) and offsets[tile_height * tile_width].
  *     sort_workspace >= sc_bin_sort_workspace_bytes(n_isects), 256-byte aligned. */
 int sc_bin_supported(int C, int tile_width, int tile_height);
+/* leave n_sms SMs out of the cooperative grid of sc_bin_prepare (process-wide): a concurrent kernel that holds
+ * SMs — an NCCL collective on a side stream — would otherwise keep the cooperative launch waiting until it ends */
+int sc_bin_reserve_sms(int n_sms);
 int sc_bin_prepare(int64_t N, const float* means2d, const int32_t* radii, const float* depths, int tile_size,
                    int tile_width, int tile_height, int32_t* tiles_per_gauss, void* workspace,
                    int64_t workspace_bytes, void* stream);

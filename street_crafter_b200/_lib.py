@@ -61,6 +61,7 @@ SIGNATURES = {
                                     _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
     "sc_isect_offset_encode": (_i32, [_i64, _ptr, _i32, _i32, _i32, _i32, _ptr, _ptr]),
     "sc_bin_supported": (_i32, [_i32, _i32, _i32]),
+    "sc_bin_reserve_sms": (_i32, [_i32]),
     "sc_bin_prepare": (_i32, [_i64, _ptr, _ptr, _ptr, _i32, _i32, _i32, _ptr, _ptr, _i64, _ptr]),
     "sc_bin_sort_workspace_bytes": (_i64, [_i64]),
     "sc_bin_phase_stamps_offset": (_i64, [_i64, _i32, _i32]),

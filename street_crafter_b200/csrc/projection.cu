@@ -1802,10 +1802,12 @@ BinSortWs bin_sort_layout(int64_t n_isects) {
 }  // namespace
 
 namespace {
-// CTAs of the cooperative prepare kernel on the current device (one per SM), 0 when cooperative
-// launch is not available; cached per device
+int g_reserved_sms = 0;   // sc_bin_reserve_sms
+
+// CTAs of the cooperative prepare kernel on the current device (CP_CTAS_PER_SM per SM, minus the SMs left to
+// concurrent kernels), 0 when cooperative launch is not available; device properties cached per device
 int coop_grid_size() {
-    static int cached[64];
+    static int sms_of[64], per_sm_of[64];
     static bool known[64];
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
@@ -1814,12 +1816,23 @@ int coop_grid_size() {
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, bin_prepare_coop_kernel, CP_THREADS, 0);
-        cached[dev] = (coop && per_sm >= 1) ? std::min(sms * std::min(per_sm, CP_CTAS_PER_SM), CP_MAX_CTAS) : 0;
+        sms_of[dev] = (coop && per_sm >= 1) ? sms : 0;
+        per_sm_of[dev] = std::min(per_sm, CP_CTAS_PER_SM);
         known[dev] = true;
     }
-    return cached[dev];
+    const int sms = std::max(sms_of[dev] - g_reserved_sms, sms_of[dev] > 0 ? 8 : 0);
+    return std::min(sms * per_sm_of[dev], CP_MAX_CTAS);
 }
 }  // namespace
+
+// A cooperative launch needs all its CTAs resident at once: while another kernel (an NCCL collective on a side
+// stream) holds SMs, a grid sized for the whole device cannot start until that kernel ends — which would
+// serialise exactly the transfer it is meant to overlap.  Leaves `n_sms` SMs out of the cooperative grid.
+extern "C" int sc_bin_reserve_sms(int n_sms) {
+    SC_CHECK_ARG(n_sms >= 0 && n_sms < 1024, "n_sms");
+    g_reserved_sms = n_sms;
+    return SC_OK;
+}
 
 extern "C" int sc_bin_supported(int C, int tile_width, int tile_height) {
     return (C == 1 && tile_width <= FB_RADIX && tile_height <= FB_RADIX && coop_grid_size() > 0) ? 1 : 0;

@@ -65,18 +65,67 @@ class GaussianArena:
     def tensors(self) -> List[Tensor]:
         return [getattr(self, name) for name, *_ in self.layout]
 
-    def zero_grad(self):
-        self.grads.zero_()
+    def zero_grad(self, stream=None):
+        """stream: a side stream to run the fill on (ordered after the current stream's pending work) -> the event
+        to wait for before the first backward; the fill then overlaps whatever does not touch the gradients"""
+        ev = None
+        if stream is not None:
+            stream.wait_stream(torch.cuda.current_stream(self.grads.device))
+            with torch.cuda.stream(stream):
+                self.grads.zero_()
+                ev = torch.cuda.Event()
+                ev.record(stream)
+        else:
+            self.grads.zero_()
         for name, off, numel, shape in self.layout:
             p = getattr(self, name)
             if p.grad is None or p.grad.data_ptr() != self.grads.data_ptr() + 4 * off:
                 p.grad = self.grads[off:off + numel].view(shape)
+        return ev
 
 
 def allreduce_gradients(arena: GaussianArena, group=None) -> None:
     """one SUM all-reduce over the flat gradient arena (NCCL over NVLink on GPUs, gloo in tests)"""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(arena.grads, op=dist.ReduceOp.SUM, group=group)
+
+
+class TwoPhaseAllReduce:
+    """The all-reduce of the flat gradient arena in its two blocks: `begin_sh()` starts the SH block (81 % of the
+    bytes) on a side stream as soon as the last view's SH backward has run, `finish()` reduces the geometric block and
+    makes the compute stream wait for both.  Between the two the caller runs the deferred projection-backward
+    kernels of its views (rendering.fused_view(deferred=...)), which only write the geometric block."""
+
+    def __init__(self, arena: GaussianArena, group=None):
+        self.arena, self.group = arena, group
+        on = dist.is_available() and dist.is_initialized()
+        self.world = dist.get_world_size(group) if on else 1
+        self.side = torch.cuda.Stream(arena.grads.device) if arena.grads.is_cuda and self.world > 1 else None
+        self._ev = None
+
+    def begin_sh(self) -> None:
+        if self.world == 1:
+            return
+        a = self.arena
+        b0, b1 = a.blocks[1]
+        if self.side is None:
+            dist.all_reduce(a.grads[b0:b1], op=dist.ReduceOp.SUM, group=self.group)
+            return
+        self.side.wait_stream(torch.cuda.current_stream(a.grads.device))
+        with torch.cuda.stream(self.side):
+            dist.all_reduce(a.grads[b0:b1], op=dist.ReduceOp.SUM, group=self.group)
+            self._ev = torch.cuda.Event()
+            self._ev.record(self.side)
+
+    def finish(self) -> None:
+        if self.world == 1:
+            return
+        a = self.arena
+        b0, b1 = a.blocks[0]
+        dist.all_reduce(a.grads[b0:b1], op=dist.ReduceOp.SUM, group=self.group)
+        if self._ev is not None:
+            torch.cuda.current_stream(a.grads.device).wait_event(self._ev)
+            self._ev = None
 
 
 def shard_views(n_views: int, rank: int, world: int) -> List[int]:
@@ -135,11 +184,17 @@ class ShardedAdam:
     a side stream UNDER the projection + binning of the next step's views (rendering.prepare_view).  `wait_geometry()`
     / `wait_sh()` make the compute stream wait for the respective gather.  world == 1: a plain fused Adam."""
 
-    def __init__(self, arena: GaussianArena, lrs: Dict[str, float], betas=(0.9, 0.999), eps: float = 1e-15, group=None):
+    def __init__(self, arena: GaussianArena, lrs: Dict[str, float], betas=(0.9, 0.999), eps: float = 1e-15, group=None,
+                 reserve_sms: int = 32):
         self.arena, self.lrs, self.betas, self.eps, self.group = arena, dict(lrs), betas, float(eps), group
         on = dist.is_available() and dist.is_initialized()
         self.world = dist.get_world_size(group) if on else 1
         self.rank = dist.get_rank(group) if on else 0
+        if self.world > 1 and arena.params.is_cuda:
+            # the asynchronous parameter all-gather runs beside the next step's binning, whose cooperative kernel
+            # needs its whole grid resident: keep it off the SMs the collective's CTAs occupy
+            from ._lib import check, lib
+            check(lib.sc_bin_reserve_sms(int(reserve_sms)), "sc_bin_reserve_sms")
         total = arena.params.numel()
         self.ranges = []          # (block lo, block hi, my lo, my hi, offset of my slice inside the moment buffers)
         mom = 0
@@ -156,8 +211,23 @@ class ShardedAdam:
         self.t = 0
         self.side = torch.cuda.Stream(dev) if dev.type == "cuda" else None
         self._ev = [None, None]
+        self._rs_ev = None
         self._starts = [off for _, off, _, _ in arena.layout] + [total]
         self._lr = [float(self.lrs.get(name, 0.0)) for name, *_ in arena.layout]
+
+    def begin_sh_exchange(self) -> None:
+        """Reduce-scatter of the SH block on the side stream, to be called as soon as the SH gradients are final —
+        after the SH backward of the rank's last view, with the projection backward of its views still to run
+        (rendering.fused_view(deferred=...)): 81 % of the gradient bytes then travel under those kernels."""
+        if self.world == 1 or self.side is None:
+            return
+        a = self.arena
+        b0, b1, lo, hi, _ = self.ranges[1]
+        self.side.wait_stream(torch.cuda.current_stream(a.params.device))
+        with torch.cuda.stream(self.side):
+            dist.reduce_scatter_tensor(a.grads[lo:hi], a.grads[b0:b1], op=dist.ReduceOp.SUM, group=self.group)
+            self._rs_ev = torch.cuda.Event()
+            self._rs_ev.record(self.side)
 
     def step(self, async_gather: bool = False) -> None:
         import ctypes as C
@@ -168,10 +238,14 @@ class ShardedAdam:
         params = a.params.detach()
         n = len(self._lr)
         st = torch.cuda.current_stream(dev).cuda_stream
-        for b0, b1, lo, hi, mo in self.ranges:
+        for i, (b0, b1, lo, hi, mo) in enumerate(self.ranges):
             if self.world > 1:
-                # in place: the reduced slice of rank r lands at its own offset of the gradient arena
-                dist.reduce_scatter_tensor(a.grads[lo:hi], a.grads[b0:b1], op=dist.ReduceOp.SUM, group=self.group)
+                if i == 1 and self._rs_ev is not None:      # begin_sh_exchange already reduced this block
+                    torch.cuda.current_stream(dev).wait_event(self._rs_ev)
+                    self._rs_ev = None
+                else:
+                    # in place: the reduced slice of rank r lands at its own offset of the gradient arena
+                    dist.reduce_scatter_tensor(a.grads[lo:hi], a.grads[b0:b1], op=dist.ReduceOp.SUM, group=self.group)
             with torch.cuda.device(dev):
                 # the moment buffers hold this rank's slices only: hand the kernel their virtual base
                 check(lib.sc_adam_step(n, (C.c_int64 * (n + 1))(*self._starts), (C.c_float * n)(*self._lr), lo, hi,

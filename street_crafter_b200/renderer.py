@@ -22,7 +22,8 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
                          tile_size: int = 16, use_depth: bool = True, absgrad: bool = True,
                          antialiasing: bool = True, train: bool = True,
                          grad_sinks: Optional[Dict[str, Tensor]] = None, fused: bool = True,
-                         aux_ids: bool = True, prepared: Optional[Dict] = None) -> Dict[str, Tensor]:
+                         aux_ids: bool = True, prepared: Optional[Dict] = None,
+                         deferred: Optional[list] = None) -> Dict[str, Tensor]:
     """xyz3[N,3] rgb3[N,K,3] (SH) scale[N,3] quats[N,4] occ1[N,1] w2c[1,4,4] K[1,3,3]
     camera_center[3] -> the reference's result dict (rgb[3,H,W], acc, depth, viewspace_points,
     visibility_filter, radii) plus the raw render tensors.
@@ -39,7 +40,7 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
         render_colors, render_alphas, meta = fused_view(
             xyz3, quats, scale, occ1[:, 0], rgb3, w2c, K, camera_center, width, height, max_sh_degree,
             near_plane=znear, far_plane=zfar, antialiased=antialiasing, tile_size=tile_size, absgrad=absgrad,
-            grad_sinks=grad_sinks, need_isect_ids=aux_ids, prepared=prepared)
+            grad_sinks=grad_sinks, need_isect_ids=aux_ids, prepared=prepared, deferred=deferred)
         radii, means2d = meta["radii"], meta["means2d"]
         rendered_color = render_colors[..., :-1]
         rendered_depth = meta["depth_norm"]  # render_colors[..., -1:] / render_alphas.clamp(min=1e-10), in-kernel

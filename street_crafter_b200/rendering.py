@@ -551,7 +551,7 @@ class _FusedView(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
                 eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, sinks, need_ids=True,
-                prepared=None):
+                prepared=None, deferred=None):
         means = _f32c(means, "means")
         quats = _f32c(quats, "quats")
         scales = _f32c(scales, "scales")
@@ -600,6 +600,7 @@ class _FusedView(torch.autograd.Function):
         ctx.cfg = (int(width), int(height), int(tile_size), float(eps2d), bool(antialiased), bool(absgrad),
                    int(sh_degree))
         ctx.sinks = sinks
+        ctx.deferred = deferred
         ctx.means2d_ref = None  # weakref to the returned means2d: receives .grad / .absgrad in backward
         ctx.set_materialize_grads(False)  # no zero-filled "gradients" for the auxiliary outputs
         aux = (radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets, vis,
@@ -646,11 +647,20 @@ class _FusedView(torch.autograd.Function):
                                        _p(v_conics), _p(v_colors4), _p(v_opc), st), "sc_rasterize_bwd")
             check(lib.sc_sh_bwd_view(N, Kc, sh_degree, _p(means), _p(campos), _p(shs), _p(radii), _p(colors4),
                                      _p(v_colors4), _p(g_shs), _p(g_means), 1, st), "sc_sh_bwd_view")
-            check(lib.sc_projection_bwd_opacity(N, 1, _p(means), _p(quats), _p(scales), _p(opacities),
-                                                _p(viewmats), _p(Ks), width, height, eps2d, _p(radii),
-                                                _p(v_means2d), v_colors4.data_ptr() + 12, 4, _p(v_conics),
-                                                _p(v_opc), 1 if antialiased else 0, _p(g_means), _p(g_quats),
-                                                _p(g_scales), _p(g_op), 1, st), "sc_projection_bwd_opacity")
+
+            def projection_bwd(keep=(arena, means, quats, scales, opacities, viewmats, Ks, radii)):
+                with torch.cuda.device(dev):
+                    check(lib.sc_projection_bwd_opacity(N, 1, _p(means), _p(quats), _p(scales), _p(opacities),
+                                                        _p(viewmats), _p(Ks), width, height, eps2d, _p(radii),
+                                                        _p(v_means2d), v_colors4.data_ptr() + 12, 4, _p(v_conics),
+                                                        _p(v_opc), 1 if antialiased else 0, _p(g_means), _p(g_quats),
+                                                        _p(g_scales), _p(g_op), 1, _stream()), "sc_projection_bwd_opacity")
+            if ctx.deferred is not None and sinks is not None:
+                # gradient-arena mode only: the caller runs the projection backward of all its views LATER (so that
+                # the exchange of the SH gradients, final once the last view's SH backward has run, travels under them)
+                ctx.deferred.append(projection_bwd)
+            else:
+                projection_bwd()
         m2 = ctx.means2d_ref() if ctx.means2d_ref is not None else None
         if m2 is not None:
             # what the reference reads after backward (street_gaussian_model.py:504-508)
@@ -658,10 +668,10 @@ class _FusedView(torch.autograd.Function):
             if absgrad:
                 m2.absgrad = v_abs.view(1, N, 2)
         if sinks is not None:
-            return (None,) * 21
+            return (None,) * 22
         need = ctx.needs_input_grad
         return (g_means if need[0] else None, g_quats if need[1] else None, g_scales if need[2] else None,
-                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 16
+                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 17
 
 
 def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, shs: Tensor, viewmats: Tensor,
@@ -669,12 +679,14 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
                near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
                antialiased: bool = True, tile_size: int = 16, absgrad: bool = False,
                grad_sinks: Optional[Dict[str, Tensor]] = None, need_isect_ids: bool = True,
-               prepared: Optional[Dict] = None) -> Tuple[Tensor, Tensor, Dict]:
+               prepared: Optional[Dict] = None, deferred: Optional[list] = None) -> Tuple[Tensor, Tensor, Dict]:
     """One camera (viewmats[1,4,4], Ks[1,3,3], campos[3] on the device), SH colours with K = 4 or
     16 coefficients, RGB + depth channel: -> (render_colors[1,H,W,4], render_alphas[1,H,W,1], meta).
     `meta["means2d"].grad` / `.absgrad` are filled by the backward pass.  `need_isect_ids=False`
     leaves meta["isect_ids"] empty: the 64-bit keys are an intermediate of the binning that only the
-    op-by-op API hands out (the reference renderer's result dict does not hold them)."""
+    op-by-op API hands out (the reference renderer's result dict does not hold them).  `deferred` (a list, with
+    `grad_sinks` only): the backward appends its projection-backward launch to it instead of running it; the caller
+    calls the entries once the backward passes of all its views are through (parallel.ShardedAdam)."""
     import weakref
     assert viewmats.shape == (1, 4, 4) and Ks.shape == (1, 3, 3) and campos.shape == (3,)
     assert shs.dim() == 3 and shs.shape[1] in (4, 16) and (sh_degree + 1) ** 2 <= shs.shape[1]
@@ -683,7 +695,7 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
         assert all(k in grad_sinks for k in ("means", "quats", "scales", "opacities", "shs"))
     out = _FusedView.apply(means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
                            eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, grad_sinks,
-                           need_isect_ids, prepared)
+                           need_isect_ids, prepared, deferred)
     (rc, ra, depth_norm, radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets,
      vis, radii_norm) = out[:15]
     comps = out[15] if len(out) > 15 else None

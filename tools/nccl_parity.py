@@ -26,7 +26,7 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     from street_crafter_b200._lib import check, lib
     from street_crafter_b200.densify import densification_stats
-    from street_crafter_b200.parallel import (GaussianArena, ShardedAdam, allreduce_densification_stats, allreduce_gradients,
+    from street_crafter_b200.parallel import (GaussianArena, ShardedAdam, TwoPhaseAllReduce, allreduce_densification_stats,
                                               shard_views)
     from street_crafter_b200.renderer import render_kernel_gsplat
     from tools.scene import make_camera, make_gaussians
@@ -38,14 +38,14 @@ def main():
     ups = [(torch.randn(1, H, W, 4, generator=g).to(dev) * torch.tensor([1, 1, 1, 0.02], device=dev),
             torch.randn(1, H, W, 1, generator=g).to(dev)) for _ in range(n_views)]
 
-    def run_views(arena, views, stats=None):
+    def run_views(arena, views, stats=None, deferred=None):
         arena.zero_grad()
         sinks = arena.sinks()
         for v in views:
             Vm, Km = cams[v]
             cc = (-(Vm[:3, :3].T @ Vm[:3, 3])).to(dev)
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities, Vm[None].to(dev),
-                                       Km[None].to(dev), cc, W, H, deg, grad_sinks=sinks)
+                                       Km[None].to(dev), cc, W, H, deg, grad_sinks=sinks, deferred=deferred)
             torch.autograd.backward([out["render_colors"], out["render_alphas"]], list(ups[v]))
             if stats is not None:
                 densification_stats(out["viewspace_points"], out["visibility_filter"], out["radii"], W, H, *stats)
@@ -53,8 +53,14 @@ def main():
     # ---- 1. sharded + all-reduce == sequential
     arena = GaussianArena(scene, dev, pad_to=4 * world)
     stats = [torch.zeros(n, 2, device=dev), torch.zeros(n, 1, device=dev), torch.zeros(n, device=dev)]
-    run_views(arena, shard_views(n_views, rank, world), stats)
-    allreduce_gradients(arena)
+    # (the bench's schedule: projection backward of all views deferred, SH block reduced under it)
+    deferred = []
+    run_views(arena, shard_views(n_views, rank, world), stats, deferred)
+    exchange = TwoPhaseAllReduce(arena)
+    exchange.begin_sh()
+    for fn in deferred:
+        fn()
+    exchange.finish()
     allreduce_densification_stats(*stats)
     seq = GaussianArena(scene, dev, pad_to=4 * world)
     seq_stats = [torch.zeros(n, 2, device=dev), torch.zeros(n, 1, device=dev), torch.zeros(n, device=dev)]
@@ -91,7 +97,12 @@ def main():
     ref_p = {name: getattr(seq, name).detach().clone().requires_grad_(True) for name, *_ in seq.layout}
     ref_opt = torch.optim.Adam([{"params": [ref_p[k]], "lr": lrs[k]} for k in ref_p], lr=0.0, eps=1e-15)
     for it in range(3):
-        run_views(sharded, shard_views(n_views, rank, world))
+        deferred = [] if it != 0 else None
+        run_views(sharded, shard_views(n_views, rank, world), None, deferred)
+        if deferred is not None:
+            opt.begin_sh_exchange()
+            for fn in deferred:
+                fn()
         opt.step(async_gather=(it == 1))
         opt.wait()
         run_views(seq, range(n_views))
