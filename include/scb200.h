@@ -133,6 +133,17 @@ int sc_isect_gather_counts(int64_t CN, const uint32_t* order, const int32_t* til
 int64_t sc_scan_workspace_bytes(int64_t n);
 int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out, int64_t* total,
                           void* workspace, int64_t workspace_bytes, void* stream);
+/* Allocation-free variant of sc_exclusive_scan_i32.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernels, same results; the block-sum scratch is a file-scope
+ * `static __device__` array inside the library (64 KiB + 256 B, held by every GPU that loads the library until
+ * the process exits) instead of a caller workspace.  Calls no cudaMalloc, cudaFree or other allocating routine.
+ * Limit: n <= sc_exclusive_scan_i32_noalloc_max_n() = 2^24 elements; larger n returns SC_ERR_WORKSPACE with
+ * a message naming the limit.  Every call on a device shares the one array (it keeps the previous call's
+ * block sums; nothing needs clearing, each call overwrites what it reads): calls that OVERLAP on the same
+ * GPU (different streams, no ordering between them) race — order them on one stream or with events. */
+int64_t sc_exclusive_scan_i32_noalloc_max_n(void);
+int sc_exclusive_scan_i32_noalloc(int64_t n, const int32_t* in, int64_t* out, int64_t* total, void* stream);
 /* emits the row-major tile list of entry order[j] at cum_tiles[j] for j = 0..C*N-1
  * (order == NULL: identity, i.e. camera-major then Gaussian order, gsplat's unsorted output):
  * isect_ids = cam << (32+tile_n_bits) | tile << 32 | bits(depth); flatten_ids = cam*N + g.

@@ -50,6 +50,8 @@ SIGNATURES = {
     "sc_isect_gather_counts": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr]),
     "sc_scan_workspace_bytes": (_i64, [_i64]),
     "sc_exclusive_scan_i32": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
+    "sc_exclusive_scan_i32_noalloc_max_n": (_i64, []),
+    "sc_exclusive_scan_i32_noalloc": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr]),
     "sc_isect_emit": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _i32, _i32, _i64, _ptr,
                              _ptr, _ptr]),
     "sc_sort_workspace_bytes": (_i64, [_i64]),

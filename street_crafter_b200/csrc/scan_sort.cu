@@ -501,6 +501,69 @@ extern "C" int sc_exclusive_scan_i32(int64_t n, const int32_t* in, int64_t* out,
     return SC_OK;
 }
 
+// ---- allocation-free scan -------------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot
+// allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same three kernels
+// as sc_exclusive_scan_i32; the block-sum scratch is this file-scope array instead of a caller workspace.
+// Every GPU that loads the library holds the array (64 KiB + 256 B) until the process exits.
+#define SC_SCAN_NOALLOC_MAX_N (1ll << 24)
+constexpr int64_t SCAN_NOALLOC_MAX_BLOCKS = SC_SCAN_NOALLOC_MAX_N / SCAN_TILE;  // 8192 block sums
+static __device__ __align__(256) int64_t g_scan_noalloc_scratch[SCAN_NOALLOC_MAX_BLOCKS + 32];
+
+// In host code the array's NAME is only a handle for the runtime; the device address of the array is looked
+// up once per device, with that device current, and cached.
+static int scan_noalloc_scratch_ptr(int64_t** out) {
+    constexpr int MAX_DEVICES = 64;
+    static int64_t* ptr_of[MAX_DEVICES] = {};
+    int dev = -1;
+    SC_CUDA(cudaGetDevice(&dev));
+    SC_CHECK_ARG(dev >= 0 && dev < MAX_DEVICES, "device ordinal beyond 63");
+    int64_t* p = __atomic_load_n(&ptr_of[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        void* sym = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&sym, g_scan_noalloc_scratch);
+        if (e != cudaSuccess || !sym) {
+            sc_set_error("cudaGetSymbolAddress(g_scan_noalloc_scratch) on device %d: %s", dev, cudaGetErrorString(e));
+            return SC_ERR_CUDA;
+        }
+        p = static_cast<int64_t*>(sym);
+        __atomic_store_n(&ptr_of[dev], p, __ATOMIC_RELEASE);  // racing first calls look up the same address
+    }
+    *out = p;
+    return SC_OK;
+}
+
+extern "C" int64_t sc_exclusive_scan_i32_noalloc_max_n(void) { return SC_SCAN_NOALLOC_MAX_N; }
+
+extern "C" int sc_exclusive_scan_i32_noalloc(int64_t n, const int32_t* in, int64_t* out, int64_t* total,
+                                             void* stream) {
+    SC_CHECK_ARG(n >= 0, "n");
+    if (n > SC_SCAN_NOALLOC_MAX_N) {
+        sc_set_error("sc_exclusive_scan_i32_noalloc: n = %lld exceeds the built-in scratch (at most %lld elements); "
+                     "use sc_exclusive_scan_i32 with a caller workspace",
+                     (long long)n, (long long)SC_SCAN_NOALLOC_MAX_N);
+        return SC_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        if (total) SC_CUDA(cudaMemsetAsync(total, 0, 8, st));
+        return SC_OK;
+    }
+    SC_CHECK_ARG(in && out, "null pointer");
+    int64_t* block_sums = nullptr;
+    const int rc = scan_noalloc_scratch_ptr(&block_sums);
+    if (rc != SC_OK) return rc;
+    // nothing in the scratch has to start at zero: the first kernel writes block_sums[0, nb) before any read
+    const int64_t nb = sc_div_up(n, SCAN_TILE);
+    scan_block_sums_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(n, in, block_sums);
+    SC_CHECK_LAUNCH("scan_block_sums_kernel");
+    scan_spine_kernel<<<1, 1024, 0, st>>>(nb, block_sums, total);
+    SC_CHECK_LAUNCH("scan_spine_kernel");
+    scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(n, in, block_sums, out);
+    SC_CHECK_LAUNCH("scan_apply_kernel");
+    return SC_OK;
+}
+
 extern "C" int64_t sc_sort_workspace_bytes(int64_t n) { return sc_sort_make_plan(n, 0, 64, 0).total; }
 
 extern "C" int sc_radix_sort_pairs(int64_t n, uint64_t* keys_in, uint32_t* vals_in, uint64_t* keys_out,
