@@ -740,7 +740,7 @@ constexpr int FB_KPT = 16;
 constexpr int FB_TILE = FB_THREADS * FB_KPT;  // 4096 slots per CTA
 constexpr int FB_TILE_LOG2 = 12;
 constexpr int FB_RADIX = 128;
-constexpr int FB_LB_W = 8;
+constexpr int FB_LB_W = 4;  // measured on cfg2: window 16 / 8 / 4 -> finish half 0.724 / 0.733 / 0.683 ms per step
 static_assert(FB_TILE == (1 << FB_TILE_LOG2), "tile size");
 // item blocks of the emit kernel: an item is one (Gaussian, tile column) pair, i.e. a run of h
 // consecutive tile rows that lands contiguously in the column-sorted list
