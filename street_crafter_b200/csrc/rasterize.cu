@@ -71,6 +71,46 @@ __device__ __forceinline__ bool pair_test(const PairX& X, float c2, float h, flo
 }
 #define SC_DEAD_Y __int_as_float(0x7f800000)
 
+// ---- Blackwell packed FP32 (fma/add/sub/mul .f32x2 -> SASS FFMA2 / FADD2 / FMUL2) ------------------
+// One instruction works on the two halves of a 64-bit register pair: the SAME FLOP rate as scalar FFMA
+// (probe.cu: 65.1 vs 71.0 TFLOP/s) in HALF the issue slots, and the compositing kernels are bound by
+// instruction issue.  A lane's 8 pixels become 4 pairs (rows 2p and 2p+1 of its column); every
+// per-Gaussian operand is broadcast into both halves once per (lane, Gaussian).  Each half is rounded
+// exactly like the scalar instruction (.rn, .ftz under --use_fast_math), so the accept / reject
+// decisions and the results are those of the scalar build (SC_RASTER_F32X2=0 keeps it for comparison).
+#ifndef SC_RASTER_F32X2
+#define SC_RASTER_F32X2 1
+#endif
+typedef unsigned long long f2;
+__device__ __forceinline__ f2 pk2(float lo, float hi) { f2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ f2 bc2(float x) { return pk2(x, x); }
+__device__ __forceinline__ float lo2(f2 v) { float a, b; asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); return a; }
+__device__ __forceinline__ float hi2(f2 v) { float a, b; asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); return b; }
+__device__ __forceinline__ float half2of(f2 v, int half) { return half ? hi2(v) : lo2(v); }
+__device__ __forceinline__ void set_half(f2& v, int half, float x) { v = half ? pk2(lo2(v), x) : pk2(x, hi2(v)); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { f2 d; asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { f2 d; asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f2 sub2(f2 a, f2 b) { f2 d; asm("sub.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { f2 d; asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+// negation of both halves: ptxas folds it into the operand modifier of the consuming packed instruction
+// (plain neg.f32: the .ftz form --use_fast_math would pick is kept as a separate flushing FADD)
+__device__ __forceinline__ float negf(float x) { float r; asm("neg.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ f2 neg2(f2 a) { return pk2(negf(lo2(a)), negf(hi2(a))); }
+__device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+// per-Gaussian operands of the pair test, broadcast once per (lane, Gaussian)
+struct PairX2 { f2 y, c2, v, u, h; };
+__device__ __forceinline__ PairX2 pair_x2(const PairX& X, float y, float c2, float h) {
+    return {bc2(y), bc2(c2), bc2(X.v), bc2(X.u), bc2(h)};
+}
+// pair_test on two pixels: the same three roundings per half (dy, inner fma, outer fma, s2 - h)
+__device__ __forceinline__ void pair_test2(const PairX2& P, float h, f2 py, f2& dy, f2& s2, bool& ok_lo, bool& ok_hi) {
+    dy = sub2(P.y, py);
+    s2 = fma2(fma2(P.c2, dy, P.v), dy, P.u);
+    const f2 win = sub2(s2, P.h);
+    ok_lo = fabsf(lo2(win)) <= h;
+    ok_hi = fabsf(hi2(win)) <= h;
+}
+
 // minimum of f(t) = p t^2 + q t + r over [lo, hi], p > 0
 __device__ __forceinline__ float parabola_min(float p, float q, float r, float lo, float hi) {
     const float t = fminf(fmaxf(-0.5f * q / p, lo), hi);
@@ -247,20 +287,39 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
     const int range_start = isect_offsets[tslot];
     const int range_end = (tslot == n_slots - 1) ? (int)n_isects : isect_offsets[tslot + 1];
 
+#if SC_RASTER_F32X2
+    // pixel pair p = rows 2p, 2p+1 of the lane's column (low, high half)
+    f2 T2[PPT / 2], pix2[PPT / 2][CH], py2[PPT / 2];
+#define FWD_T(r) half2of(T2[(r) >> 1], (r) & 1)
+#define FWD_PIX(r, c) half2of(pix2[(r) >> 1][c], (r) & 1)
+#else
     float T[PPT], pix[PPT][CH], pyv[PPT];
+#define FWD_T(r) T[r]
+#define FWD_PIX(r, c) pix[r][c]
+#endif
     int hits[PPT];
     unsigned live = 0;          // bit r: pixel r still accumulating
     unsigned contributing = 0;  // STATS only
 #pragma unroll
     for (int r = 0; r < PPT; ++r) {
-        T[r] = 1.0f;
         hits[r] = 0;
         const bool in = j < width && i0 + r * ROW_STEP < height;
         if (in) live |= 1u << r;
-        pyv[r] = in ? (float)(i0 + r * ROW_STEP) + 0.5f : SC_DEAD_Y;
+        const float y = in ? (float)(i0 + r * ROW_STEP) + 0.5f : SC_DEAD_Y;
         sm.P[r][lane] = range_end - 1;
+#if SC_RASTER_F32X2
+        set_half(py2[r >> 1], r & 1, y);
+        if (r & 1) {
+            T2[r >> 1] = bc2(1.0f);
+#pragma unroll
+            for (int c = 0; c < CH; ++c) pix2[r >> 1][c] = 0ull;
+        }
+#else
+        T[r] = 1.0f;
+        pyv[r] = y;
 #pragma unroll
         for (int c = 0; c < CH; ++c) pix[r][c] = 0.f;
+#endif
     }
     const unsigned inside = live;
 
@@ -281,6 +340,84 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             const float hwin = 0.5f * (B.lo - LOG2_ALPHA_FLOOR);
             float col[CH];
             load_colors<CH>(sm.C, t, col);
+#if SC_RASTER_F32X2
+            // two halves of 4 row pairs (= 2 pixel pairs): one warp-uniform branch each, the chains inside are
+            // branch-free so that they interleave
+            const PairX2 P2 = pair_x2(X, A.y, B.c2, hwin);
+            const f2 lo_2 = bc2(B.lo);
+            f2 col2[CH];
+#pragma unroll
+            for (int c = 0; c < CH; ++c) col2[c] = bc2(col[c]);
+            auto halves = [&](auto nocap_tag) {
+            constexpr bool NOCAP = decltype(nocap_tag)::value;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if ((B.rmask >> (4 * h)) & 0xfu) {
+                    f2 s2[2], dy2;
+                    bool ok[4];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) pair_test2(P2, hwin, py2[2 * h + u], dy2, s2[u], ok[2 * u], ok[2 * u + 1]);
+                    if (__any_sync(FULL, ok[0] | ok[1] | ok[2] | ok[3])) {
+                        f2 a2[2], next_T2[2];
+                        bool any_stop = false;
+#pragma unroll
+                        for (int u = 0; u < 2; ++u) {
+                            const int p = 2 * h + u;
+                            // (an opacity below the cap can never reach it: ok implies s2 >= 0; warp-uniform)
+                            const f2 e2 = sub2(lo_2, s2[u]);
+                            const float au0 = exp2f(lo2(e2)), au1 = exp2f(hi2(e2));
+                            a2[u] = pk2(ok[2 * u] ? (NOCAP ? au0 : fminf(SC_ALPHA_CAP, au0)) : 0.f,
+                                        ok[2 * u + 1] ? (NOCAP ? au1 : fminf(SC_ALPHA_CAP, au1)) : 0.f);
+                            next_T2[u] = fma2(neg2(a2[u]), T2[p], T2[p]);
+                            // alpha == 0 leaves T (> 1e-4 for every pixel, live or not) unchanged
+                            any_stop |= (lo2(next_T2[u]) <= SC_T_STOP) | (hi2(next_T2[u]) <= SC_T_STOP);
+                            if (MAXHIT) any_stop |= (ok[2 * u] && hits[2 * p] + 1 >= max_hit) |
+                                                    (ok[2 * u + 1] && hits[2 * p + 1] + 1 >= max_hit);
+                        }
+                        if (!__any_sync(FULL, any_stop)) {
+#pragma unroll
+                            for (int u = 0; u < 2; ++u) {
+                                const int p = 2 * h + u;
+                                const f2 vis = mul2(a2[u], T2[p]);
+#pragma unroll
+                                for (int c = 0; c < CH; ++c) pix2[p][c] = fma2(col2[c], vis, pix2[p][c]);
+                                T2[p] = next_T2[u];
+                                if (STATS) contributing += (ok[2 * u] ? 1u : 0u) + (ok[2 * u + 1] ? 1u : 0u);
+                                if (MAXHIT) { hits[2 * p] += ok[2 * u] ? 1 : 0; hits[2 * p + 1] += ok[2 * u + 1] ? 1 : 0; }
+                            }
+                        } else {  // rare: some pixel saturates (or reaches max_hit) on this entry
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const int r = 4 * h + q, p = r >> 1, hf = r & 1;
+                                const float Tr = half2of(T2[p], hf);
+                                const float nT = half2of(next_T2[q >> 1], hf);
+                                const float a = half2of(a2[q >> 1], hf);
+                                const bool sat = nT <= SC_T_STOP;  // stops BEFORE using the entry
+                                const bool used = ok[q] && !sat;
+                                const float vis = used ? a * Tr : 0.f;
+#pragma unroll
+                                for (int c = 0; c < CH; ++c)
+                                    set_half(pix2[p][c], hf, fmaf(col[c], vis, half2of(pix2[p][c], hf)));
+                                set_half(T2[p], hf, used ? nT : Tr);
+                                if (STATS) contributing += used ? 1u : 0u;
+                                bool full = false;  // max_hit stops AFTER using the entry
+                                if (MAXHIT) {
+                                    hits[r] += used ? 1 : 0;
+                                    full = used && hits[r] >= max_hit;
+                                }
+                                if (sat || full) {
+                                    set_half(py2[p], hf, SC_DEAD_Y);
+                                    live &= ~(1u << r);
+                                    sm.P[r][lane] = full ? B.idx : B.idx - 1;
+                                }
+                            }
+                            done = !__any_sync(FULL, live != 0);
+                        }
+                    }
+                }
+            }
+            };
+#else
             // two halves of 4 row pairs: one warp-uniform branch each, the 4 pixel chains inside
             // are branch-free so that they interleave
             auto halves = [&](auto nocap_tag) {
@@ -349,6 +486,7 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                 }
             }
             };
+#endif
             if (B.lo <= LO_NOCAP) halves(std::true_type{}); else halves(std::false_type{});
         }
         __syncwarp();
@@ -357,25 +495,29 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
     for (int r = 0; r < PPT; ++r) {
         if (inside & (1u << r)) {
             const int64_t pix_id = ((int64_t)cam * height + (i0 + r * ROW_STEP)) * width + j;
-            render_alphas[pix_id] = 1.0f - T[r];
+            const float Tr = FWD_T(r);
+            float pixr[CH];
+#pragma unroll
+            for (int c = 0; c < CH; ++c) pixr[c] = FWD_PIX(r, c);
+            render_alphas[pix_id] = 1.0f - Tr;
             if constexpr (CH == 4) {
-                float4 o = make_float4(pix[r][0], pix[r][1], pix[r][2], pix[r][3]);
+                float4 o = make_float4(pixr[0], pixr[1], pixr[2], pixr[3]);
                 if (backgrounds) {
-                    o.x += T[r] * __ldg(backgrounds + cam * 4 + 0); o.y += T[r] * __ldg(backgrounds + cam * 4 + 1);
-                    o.z += T[r] * __ldg(backgrounds + cam * 4 + 2); o.w += T[r] * __ldg(backgrounds + cam * 4 + 3);
+                    o.x += Tr * __ldg(backgrounds + cam * 4 + 0); o.y += Tr * __ldg(backgrounds + cam * 4 + 1);
+                    o.z += Tr * __ldg(backgrounds + cam * 4 + 2); o.w += Tr * __ldg(backgrounds + cam * 4 + 3);
                 }
                 reinterpret_cast<float4*>(render_colors)[pix_id] = o;
                 // A11 fused: the renderer's depth map, render_colors[..., 3] / clamp(alpha, 1e-10)
                 // (street_gaussian_renderer.py:283), IEEE division like the torch op it replaces
-                if (depth_norm) depth_norm[pix_id] = __fdiv_rn(o.w, fmaxf(1.0f - T[r], 1e-10f));
+                if (depth_norm) depth_norm[pix_id] = __fdiv_rn(o.w, fmaxf(1.0f - Tr, 1e-10f));
             } else {
 #pragma unroll
                 for (int c = 0; c < CH; ++c)
                     render_colors[pix_id * CH + c] =
-                        backgrounds ? pix[r][c] + T[r] * __ldg(backgrounds + cam * CH + c) : pix[r][c];
+                        backgrounds ? pixr[c] + Tr * __ldg(backgrounds + cam * CH + c) : pixr[c];
             }
             if (last_ids) last_ids[pix_id] = sm.P[r][lane];
-            if (final_T) final_T[pix_id] = T[r];
+            if (final_T) final_T[pix_id] = Tr;
         }
     }
     if (STATS) {
@@ -400,6 +542,8 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             atomicAdd(stats + 1, c);
         }
     }
+#undef FWD_T
+#undef FWD_PIX
 }
 
 // ------------------------------------------------------------------------------- backward
@@ -460,34 +604,64 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 
     // per-pixel state: T (running transmittance, walking back), R = <v_rc, colour behind> -
     // T_final * v_ra (+ T_final * <bg, v_rc>), so that v_alpha = <v_rc,col> * T - R / (1-alpha)
+#if SC_RASTER_F32X2
+    // pixel pair p = rows 2p, 2p+1 of the lane's column (low, high half).
+    // Shared-memory layout of the upstream colour gradients (CH == 4): V[2p][lane] = (c0 lo, c0 hi, c1 lo, c1 hi),
+    // V[2p+1][lane] = (c2 lo, c2 hi, c3 lo, c3 hi) — two conflict-free LDS.128 deliver four aligned register pairs.
+    f2 T2[PPT / 2], R2[PPT / 2], py2[PPT / 2], v_rc2[VSM ? 1 : PPT / 2][CH];
+#else
     float T[PPT], R[PPT], v_rc[VSM ? 1 : PPT][CH], pyv[PPT];
+#endif
     int tile_last = -1;
 #pragma unroll
-    for (int r = 0; r < PPT; ++r) {
-        const int i = i0 + r * ROW_STEP;
-        const bool inside = (i < height) && (j < width);
-        const int64_t pix_id = ((int64_t)cam * height + min(i, height - 1)) * width + min(j, width - 1);
-        const float Tf = inside ? final_T[pix_id] : 1.0f;
-        const int binf = inside ? last_ids[pix_id] : -1;
-        sm.P[r][lane] = binf;
-        tile_last = max(tile_last, binf);
-        T[r] = Tf;
-        pyv[r] = SC_DEAD_Y;
-        float bg_dot = 0.f;
-        float vin[CH];
+    for (int p = 0; p < PPT / 2; ++p) {
+        float Tf2[2], Rr2[2], vin2[2][CH];
 #pragma unroll
-        for (int c = 0; c < CH; ++c) {
-            vin[c] = inside ? v_render_colors[pix_id * CH + c] : 0.f;
-            if (backgrounds) bg_dot += __ldg(backgrounds + cam * CH + c) * vin[c];
+        for (int u = 0; u < 2; ++u) {
+            const int r = 2 * p + u;
+            const int i = i0 + r * ROW_STEP;
+            const bool inside = (i < height) && (j < width);
+            const int64_t pix_id = ((int64_t)cam * height + min(i, height - 1)) * width + min(j, width - 1);
+            const float Tf = inside ? final_T[pix_id] : 1.0f;
+            const int binf = inside ? last_ids[pix_id] : -1;
+            sm.P[r][lane] = binf;
+            tile_last = max(tile_last, binf);
+            float bg_dot = 0.f;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+                vin2[u][c] = inside ? v_render_colors[pix_id * CH + c] : 0.f;
+                if (backgrounds) bg_dot += __ldg(backgrounds + cam * CH + c) * vin2[u][c];
+            }
+            const float v_ra = (inside && v_render_alphas) ? v_render_alphas[pix_id] : 0.f;  // nullable: zeros
+            Tf2[u] = Tf;
+            Rr2[u] = Tf * (bg_dot - v_ra);
         }
+#if SC_RASTER_F32X2
+        T2[p] = pk2(Tf2[0], Tf2[1]);
+        R2[p] = pk2(Rr2[0], Rr2[1]);
+        py2[p] = bc2(SC_DEAD_Y);
         if constexpr (VSM) {
-            sm.V[r][lane] = make_float4(vin[0], vin[1], vin[2], vin[3]);
+            sm.V[2 * p][lane] = make_float4(vin2[0][0], vin2[1][0], vin2[0][1], vin2[1][1]);
+            sm.V[2 * p + 1][lane] = make_float4(vin2[0][2], vin2[1][2], vin2[0][3], vin2[1][3]);
         } else {
 #pragma unroll
-            for (int c = 0; c < CH; ++c) v_rc[r][c] = vin[c];
+            for (int c = 0; c < CH; ++c) v_rc2[p][c] = pk2(vin2[0][c], vin2[1][c]);
         }
-        const float v_ra = (inside && v_render_alphas) ? v_render_alphas[pix_id] : 0.f;  // nullable: zeros
-        R[r] = Tf * (bg_dot - v_ra);
+#else
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            const int r = 2 * p + u;
+            T[r] = Tf2[u];
+            R[r] = Rr2[u];
+            pyv[r] = SC_DEAD_Y;
+            if constexpr (VSM) {
+                sm.V[r][lane] = make_float4(vin2[u][0], vin2[u][1], vin2[u][2], vin2[u][3]);
+            } else {
+#pragma unroll
+                for (int c = 0; c < CH; ++c) v_rc[r][c] = vin2[u][c];
+            }
+        }
+#endif
     }
     // the tile never used an entry past max(last id): start there
 #pragma unroll
@@ -534,7 +708,11 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                 for (int r = 0; r < PPT; ++r) {
                     const int b = sm.P[r][lane];
                     if (b >= B.idx) {
+#if SC_RASTER_F32X2
+                        set_half(py2[r >> 1], r & 1, (float)(i0 + r * ROW_STEP) + 0.5f);
+#else
                         pyv[r] = (float)(i0 + r * ROW_STEP) + 0.5f;
+#endif
                         sm.P[r][lane] = -1;
                     } else {
                         m = max(m, b);
@@ -551,10 +729,86 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             // dx is constant over a lane's 8 pixels, so of the moments of w = -au * v_alpha only
             // sum w, sum w dy, sum w dy^2 (and the two |.| sums, which are not linear) are
             // accumulated per pixel; the dx factors are applied once per (lane, Gaussian)
+            bool any_entry = false;
+            // A Gaussian whose opacity is below the cap can never reach it (ok implies s2 >= 0, so
+            // alpha <= opacity): its chains drop the clamp and the "not clamped" predicate.  The
+            // choice is per Gaussian, i.e. warp-uniform; both instances are the same code otherwise.
+#if SC_RASTER_F32X2
+            // dx is constant over a lane's 8 pixels, so of the moments of w = -au * v_alpha only sum w, sum w dy,
+            // sum w dy^2 (and the two |.| sums, which are not linear) are accumulated per pixel — here per HALF:
+            // the low halves sum the even rows, the high halves the odd rows, joined once per (lane, Gaussian).
+            const PairX2 P2 = pair_x2(X, A.y, B.c2, hwin);
+            const f2 lo_2 = bc2(B.lo), one2 = bc2(1.0f), b22 = bc2(A.b2), hx02 = bc2(hx0), c2x22 = bc2(c2x2);
+            f2 col2[CH], vc2[CH], sw2 = 0ull, swy2 = 0ull, swyy2 = 0ull;
+            float abx0 = 0.f, abx1 = 0.f, aby0 = 0.f, aby1 = 0.f;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) { col2[c] = bc2(col[c]); vc2[c] = 0ull; }
+            auto halves = [&](auto nocap_tag) {
+            constexpr bool NOCAP = decltype(nocap_tag)::value;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if ((B.rmask >> (4 * h)) & 0xfu) {
+                    f2 s2[2], dy2[2];
+                    bool ok[4];
+#pragma unroll
+                    for (int u = 0; u < 2; ++u)
+                        pair_test2(P2, hwin, py2[2 * h + u], dy2[u], s2[u], ok[2 * u], ok[2 * u + 1]);
+                    if (__any_sync(FULL, ok[0] | ok[1] | ok[2] | ok[3])) {
+                        any_entry = true;
+#pragma unroll
+                        for (int u = 0; u < 2; ++u) {
+                            const int p = 2 * h + u;
+                            const bool ok0 = ok[2 * u], ok1 = ok[2 * u + 1];
+                            // a dead pixel has dy = -inf: keep it out of the moment sums
+                            const f2 dy = pk2(ok0 ? lo2(dy2[u]) : 0.f, ok1 ? hi2(dy2[u]) : 0.f);
+                            const f2 e2 = sub2(lo_2, s2[u]);
+                            const float au0 = exp2f(lo2(e2)), au1 = exp2f(hi2(e2));
+                            const f2 a = pk2(ok0 ? (NOCAP ? au0 : fminf(SC_ALPHA_CAP, au0)) : 0.f,
+                                             ok1 ? (NOCAP ? au1 : fminf(SC_ALPHA_CAP, au1)) : 0.f);
+                            const f2 oma = sub2(one2, a);
+                            // MUFU.RCP; exactly 1 when the pair is not used
+                            const f2 ra = pk2(rcp_approx(lo2(oma)), rcp_approx(hi2(oma)));
+                            T2[p] = mul2(T2[p], ra);
+                            const f2 fac = mul2(a, T2[p]);
+                            f2 vr[CH];
+                            if constexpr (VSM) {
+                                const ulonglong2 v01 = *reinterpret_cast<const ulonglong2*>(&sm.V[2 * p][lane]);
+                                const ulonglong2 v23 = *reinterpret_cast<const ulonglong2*>(&sm.V[2 * p + 1][lane]);
+                                vr[0] = v01.x; vr[1] = v01.y; vr[2] = v23.x; vr[3] = v23.y;
+                            } else {
+#pragma unroll
+                                for (int c = 0; c < CH; ++c) vr[c] = v_rc2[p][c];
+                            }
+                            f2 d = mul2(col2[0], vr[0]);
+                            vc2[0] = fma2(fac, vr[0], vc2[0]);
+#pragma unroll
+                            for (int c = 1; c < CH; ++c) {
+                                d = fma2(col2[c], vr[c], d);
+                                vc2[c] = fma2(fac, vr[c], vc2[c]);
+                            }
+                            const f2 v_alpha = fma2(d, T2[p], neg2(mul2(R2[p], ra)));  // d T - R / (1 - alpha)
+                            R2[p] = fma2(d, fac, R2[p]);
+                            // a clamped alpha passes no gradient; unclamped: -alpha * v_alpha is already 0 when !ok
+                            const f2 w = NOCAP ? mul2(neg2(a), v_alpha)
+                                               : mul2(neg2(pk2((ok0 && au0 <= SC_ALPHA_CAP) ? au0 : 0.f,
+                                                               (ok1 && au1 <= SC_ALPHA_CAP) ? au1 : 0.f)), v_alpha);
+                            const f2 wdy = mul2(w, dy);
+                            sw2 = add2(sw2, w);
+                            swy2 = add2(swy2, wdy);
+                            swyy2 = fma2(wdy, dy, swyy2);
+                            const f2 ax = mul2(w, fma2(b22, dy, hx02));    // w * d s2 / d mean.x
+                            const f2 ay = mul2(w, fma2(c2x22, dy, P2.v));  // w * d s2 / d mean.y
+                            abx0 += fabsf(lo2(ax)); abx1 += fabsf(hi2(ax));
+                            aby0 += fabsf(lo2(ay)); aby1 += fabsf(hi2(ay));
+                        }
+                    }
+                }
+            }
+            };
+#else
             float vc[CH], sw = 0.f, swy = 0.f, swyy = 0.f, abx = 0.f, aby = 0.f;
 #pragma unroll
             for (int c = 0; c < CH; ++c) vc[c] = 0.f;
-            bool any_entry = false;
             // two halves of 4 row pairs: one warp-uniform branch each; the 4 pixel chains inside
             // are branch-free so that they interleave
             // A Gaussian whose opacity is below the cap can never reach it (ok implies s2 >= 0, so
@@ -615,11 +869,20 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                 }
             }
             };
+#endif
             if (B.lo <= LO_NOCAP) halves(std::true_type{}); else halves(std::false_type{});
             if (!any_entry) continue;  // warp-uniform
             float v[NRED];
+#if SC_RASTER_F32X2
+            // join the halves (even + odd rows)
+            const float sw = lo2(sw2) + hi2(sw2), swy = lo2(swy2) + hi2(swy2), swyy = lo2(swyy2) + hi2(swyy2);
+            const float abx = abx0 + abx1, aby = aby0 + aby1;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) v[c] = lo2(vc2[c]) + hi2(vc2[c]);
+#else
 #pragma unroll
             for (int c = 0; c < CH; ++c) v[c] = vc[c];
+#endif
 #pragma unroll
             for (int c = CH; c < 5; ++c) v[c] = 0.f;
             const float swx = sw * X.dx;       // sum w dx
