@@ -54,6 +54,14 @@ def parse():
     ap.add_argument("--gaussians", type=int, default=N_GAUSS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cfg4", action="store_true", help="skip the strong-scaled configs[3] record")
+    ap.add_argument("--schedule", default="graph", choices=["graph", "sequential", "pipeline"],
+                    help="graph (N=1 default): the whole multi-view step with the sync-free binning captured ONCE in a "
+                         "CUDA graph and replayed (street_crafter_b200.pipeline.GraphedStep); sequential: one eager "
+                         "camera pass after the other (N>1 always: its NCCL overlap lives there); pipeline: eager "
+                         "two-stream ViewPipeline")
+    ap.add_argument("--ahead", type=int, default=1, help="pipeline: views prepared before the first compositing kernel")
+    ap.add_argument("--no-pipe-sh", action="store_true")
+    ap.add_argument("--no-pipe-tail", action="store_true")
     return ap.parse_args()
 
 
@@ -519,9 +527,24 @@ def run_ours(args):
 
     exchange = TwoPhaseAllReduce(arena)
 
-    def step_resident():
+    from street_crafter_b200.pipeline import ViewPipeline
+    pipe = ViewPipeline(dev, ahead=args.ahead, pipeline_sh=not args.no_pipe_sh, pipeline_tail=not args.no_pipe_tail)
+    dev_views = list(zip(dev_V, dev_K, dev_C))
+
+    def pipe_backward(v, out):
+        torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc[v], v_ra[v]])
+
+    from street_crafter_b200.pipeline import GraphedStep
+    schedule = args.schedule if world == 1 else "sequential"
+
+    def step_sequential():
         """inputs already in HBM; upstream gradients fixed (loss-independent)"""
         arena.zero_grad()
+        if schedule == "pipeline":
+            # compositing on the compute stream, everything HBM-bound one view ahead / behind on a memory stream
+            pipe.step(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities, dev_views, WIDTH, HEIGHT,
+                      SH_DEGREE, sinks, pipe_backward)
+            return
         deferred = [] if world > 1 else None
         for v in range(n_views):
             out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities,
@@ -534,6 +557,19 @@ def run_ours(args):
             for fn in deferred:
                 fn()
             exchange.finish()
+
+    params_fn = lambda: (arena.means, arena.shs, arena.scales, arena.quats, arena.opacities)
+    graphed = None
+    if schedule == "graph":
+        # the same kernels on the same inputs, captured once: no launch gaps, no read-back bubbles, ~0 host work
+        graphed = GraphedStep(pipe, arena.zero_grad, params_fn, dev_views, WIDTH, HEIGHT, SH_DEGREE, lambda: sinks,
+                              pipe_backward)
+
+    def step_resident():
+        if graphed is not None:
+            graphed.replay()
+        else:
+            step_sequential()
 
     feeder = HostViewFeeder(dev)
 
@@ -567,6 +603,50 @@ def run_ours(args):
         loss_host.copy_(torch.stack(losses), non_blocking=True)
         torch.cuda.current_stream().synchronize()
         return loss_host
+
+    # ---- the same end-to-end step captured in a CUDA graph: the host -> device copies (pinned memory, a copy
+    # stream forked inside the capture so that view v+1's image travels under view v's render), the loss kernels
+    # and the device -> host copy of the losses are graph nodes; the host replays and waits for the loss
+    graphed_e2e = None
+    if schedule == "graph":
+        cam_static = torch.zeros(n_views, 32, device=dev)
+        gt_static = [torch.empty(3, HEIGHT, WIDTH, device=dev) for _ in range(n_views)]
+        loss_dev = torch.zeros(n_views, device=dev)
+        copy_stream = torch.cuda.Stream(dev)
+        gt_ready = [None] * n_views
+        e2e_views = [(cam_static[v, 0:16].view(1, 4, 4), cam_static[v, 16:25].view(1, 3, 3), cam_static[v, 28:31])
+                     for v in range(n_views)]
+
+        def e2e_before():
+            cur = torch.cuda.current_stream(dev)
+            copy_stream.wait_stream(cur)
+            with torch.cuda.stream(copy_stream):
+                cam_static.copy_(host_cams, non_blocking=True)
+                cam_ready = torch.cuda.Event()
+                cam_ready.record(copy_stream)
+                for v in range(n_views):
+                    gt_static[v].copy_(host_gt[v], non_blocking=True)
+                    gt_ready[v] = torch.cuda.Event()
+                    gt_ready[v].record(copy_stream)
+            cur.wait_event(cam_ready)
+
+        def e2e_backward(v, out):
+            torch.cuda.current_stream(dev).wait_event(gt_ready[v])
+            loss = photometric_loss_render(out["render_colors"], gt_static[v], None, 0.2, 1.0)[0]
+            loss.backward()
+            loss_dev[v].copy_(loss.detach())
+
+        def e2e_after():
+            loss_host.copy_(loss_dev, non_blocking=True)
+
+        graphed_e2e = GraphedStep(pipe, arena.zero_grad, params_fn, e2e_views, WIDTH, HEIGHT, SH_DEGREE, lambda: sinks,
+                                  e2e_backward, before=e2e_before, after=e2e_after)
+        step_e2e_eager = step_e2e
+
+        def step_e2e():
+            graphed_e2e.replay()
+            torch.cuda.current_stream().synchronize()
+            return loss_host
 
     h2d = host_cams.numel() * 4 + sum(t.numel() * 4 for t in host_gt)
     d2h = 4 * n_views
@@ -606,10 +686,27 @@ def run_ours(args):
     launches = _lib.launch_count() - l0
     clocks = sampler.stop()
     stages = timer.summary()
+    if graphed is not None:
+        torch.cuda.synchronize()
+        if graphed.overflowed():
+            raise RuntimeError(f"graphed step: views {graphed.overflowed()} outgrew their capacity {graphed.capacities}")
+        launches = graphed.launches_per_replay * args.steps   # launched by the replays (counted at capture)
+        # kernels inside a graph replay cannot be bracketed one by one: the dominant kernel's launch duration comes
+        # from the same number of EAGER sequential steps, bracketed on its stream, right here
+        for _ in range(2):
+            step_sequential()
+        timer.only = {"sc_rasterize_bwd"}
+        timer.reserve(2 * n_views * args.steps)
+        timer.enabled = True
+        ms_step_eager = timed(step_sequential, args.steps)
+        timer.enabled = False
+        stages = timer.summary()
+    else:
+        ms_step_eager = ms_step
     # ---- the same steps once more with EVERY stage bracketed: per-stage table only, not `value`
     timer.only = None
     timer.enabled = True
-    ms_step_instrumented = timed(step_resident, args.steps)
+    ms_step_instrumented = timed(step_sequential, args.steps)
     timer.enabled = False
     stages_all = timer.summary()
     stages_all["sc_rasterize_bwd"] = stages["sc_rasterize_bwd"]  # the live measurement is the one reported
@@ -618,6 +715,15 @@ def run_ours(args):
     for _ in range(2):
         step_e2e()
     ms_e2e = timed(step_e2e, args.steps)
+    e2e_check = None
+    if graphed_e2e is not None:
+        torch.cuda.synchronize()
+        if graphed_e2e.overflowed():
+            raise RuntimeError("graphed e2e step: a view outgrew its capacity")
+        l_graph = step_e2e().clone()
+        l_eager = step_e2e_eager().clone()
+        e2e_check = {"loss_graph": l_graph.tolist(), "loss_eager": l_eager.tolist()}
+        assert torch.allclose(l_graph, l_eager, rtol=1e-5, atol=1e-6), e2e_check
 
     cfg1 = run_cfg1(dev, render_kernel_gsplat, make_camera, make_gaussians) if rank == 0 else None
     cfg4 = None if args.no_cfg4 else run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gaussians,
@@ -730,11 +836,18 @@ def run_ours(args):
             "config": {"workload": WORKLOAD, "gaussians": n, "views_per_gpu": n_views,
                        "isects_per_step": I_total, "visible_per_step": V_total,
                        "l2_policy": "inputs larger than L2 (472 MB parameters + 0.9 GB/step intermediates)",
-                       "parallelism": f"view-sharded x{world}, flat-arena gradient all-reduce" if world > 1 else "single GPU"},
+                       "parallelism": f"view-sharded x{world}, flat-arena gradient all-reduce" if world > 1 else "single GPU",
+                       "schedule": {"graph": "whole step (3 camera passes, sync-free binning) captured once in a CUDA "
+                                             "graph, replayed per step", "sequential": "eager, one camera pass after "
+                                    "the other", "pipeline": "eager two-stream ViewPipeline"}[schedule],
+                       "ms_per_step_eager_sequential": ms_step_eager},
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h,
                     "what": "pinned host camera matrices + target images -> device (side stream), render, "
-                            "0.8*L1 + 0.2*(1-SSIM) loss (fused kernels), backward, loss -> host"},
+                            "0.8*L1 + 0.2*(1-SSIM) loss (fused kernels), backward, loss -> host"
+                            + ("; all of it nodes of one CUDA graph replayed per step, the host waits for the loss"
+                               if graphed_e2e is not None else ""),
+                    "graph_vs_eager_loss": e2e_check},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": roofline,

@@ -207,6 +207,15 @@ int sc_bin_prepare(int64_t N, const float* means2d, const int32_t* radii, const 
                    int tile_width, int tile_height, int32_t* tiles_per_gauss, void* workspace,
                    int64_t workspace_bytes, void* stream);
 int64_t sc_bin_sort_workspace_bytes(int64_t n_isects);
+/* Sync-free form of sc_bin_finish (same reference call, isect_tiles + isect_offset_encode): the counts
+ * {n_visible, n_isects, n_items} are NOT read back, they stay in the first 24 bytes of the prepare workspace;
+ * flatten_ids / isect_ids hold `capacity` entries and sort_workspace >= sc_bin_sort_workspace_bytes(capacity).
+ * A list longer than the capacity is DROPPED (all offsets 0, the view renders empty; no out-of-bounds access):
+ * compare the counts with the capacity once the stream has passed and re-run with a larger one.  With it a camera pass has no host
+ * dependency and can be captured in a CUDA graph (street_crafter_b200.pipeline). */
+int sc_bin_finish_dev(int64_t N, const float* depths, int tile_width, int tile_height, int64_t capacity,
+                      const void* prepare_workspace, int32_t* flatten_ids, int64_t* isect_ids, int32_t* offsets,
+                      void* sort_workspace, int64_t sort_workspace_bytes, void* stream);
 /* byte offset, inside the prepare workspace, of 16 uint64 %globaltimer stamps that CTA 0 of the cooperative
  * kernel leaves at its phase boundaries (measurement only: tools/bin_phases.py) */
 int64_t sc_bin_phase_stamps_offset(int64_t N, int tile_width, int tile_height);
@@ -235,6 +244,20 @@ int sc_rasterize_fwd_depth(int C, int64_t N, int64_t n_isects, int width, int he
                            const float* opacities, const int32_t* isect_offsets, const int32_t* flatten_ids,
                            float* render_colors, float* render_alphas, float* depth_norm, int32_t* last_ids,
                            float* final_T, uint64_t* stats, void* stream);
+/* the same behind sc_bin_finish_dev: flatten_ids holds `capacity` entries, the list length is read from the device
+ * (n_isects_dev = the second int64 of the prepare workspace; 0 when it exceeds the capacity).  (sc_rasterize_bwd needs
+ * no such form: it walks a tile's list from last_ids down to isect_offsets and never looks at the list's end;
+ * pass the capacity as its n_isects.) */
+int sc_rasterize_fwd_depth_dev(int C, int64_t N, int64_t capacity, const int64_t* n_isects_dev, int width, int height,
+                               int tile_size, const float* means2d, const float* conics, const float* colors4,
+                               const float* opacities, const int32_t* isect_offsets, const int32_t* flatten_ids,
+                               float* render_colors, float* render_alphas, float* depth_norm, int32_t* last_ids,
+                               float* final_T, uint64_t* stats, void* stream);
+
+/* Resident compositing warps per SM for all later sc_rasterize_* launches (0 = as many as fit: 16).  A smaller
+ * number leaves registers to the HBM-bound kernels a caller runs beside the compositing on another stream
+ * (street_crafter_b200.pipeline); no counterpart in the reference (a scheduling knob of this library). */
+int sc_rasterize_limit_warps(int warps_per_sm);
 
 /* gradient buffers must be ZEROED by the caller; v_means2d_abs nullable; v_render_alphas nullable
  * (= no gradient flows into the alpha map). */

@@ -42,6 +42,9 @@ SIGNATURES = {
     "sc_densification_stats": (_i32, [_i64, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _ptr, _ptr, _ptr, _ptr]),
     "sc_rasterize_fwd_depth": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                       _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
+    "sc_rasterize_limit_warps": (_i32, [_i32]),
+    "sc_rasterize_fwd_depth_dev": (_i32, [_i32, _i64, _i64, _ptr, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
+                                          _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_projection_bwd_opacity": (_i32, [_i64, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _i32, _i32, _f32, _ptr,
                                          _ptr, _ptr, _i32, _ptr, _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _i32, _ptr]),
     "sc_sh_fwd_view": (_i32, [_i64, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
@@ -68,6 +71,7 @@ SIGNATURES = {
     "sc_bin_sort_workspace_bytes": (_i64, [_i64]),
     "sc_bin_phase_stamps_offset": (_i64, [_i64, _i32, _i32]),
     "sc_bin_finish": (_i32, [_i64, _ptr, _i32, _i32, _i64, _i64, _i64, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
+    "sc_bin_finish_dev": (_i32, [_i64, _ptr, _i32, _i32, _i64, _ptr, _ptr, _ptr, _ptr, _ptr, _i64, _ptr]),
     "sc_rasterize_fwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,
                                 _ptr, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr]),
     "sc_rasterize_bwd": (_i32, [_i32, _i64, _i64, _i32, _i32, _i32, _i32, _ptr, _ptr, _ptr, _ptr, _ptr, _ptr,

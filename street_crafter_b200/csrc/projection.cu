@@ -785,7 +785,6 @@ namespace cg = cooperative_groups;
 #endif
 constexpr int CP_THREADS = SC_CP_THREADS;          // 512 x 2 CTAs per SM: one CTA's barrier waits overlap the other's work
 constexpr int CP_CTAS_PER_SM = 1024 / CP_THREADS;
-constexpr int CP_Q = CP_THREADS / 256;             // groups of 256 threads (one thread per digit each)
 constexpr int CP_WARPS = CP_THREADS / 32;
 constexpr int CP_KPT = 8;   // 4096 keys per CTA and tile: V up to 1.2 M sorts with one tile per CTA and pass
 constexpr int CP_TILE = CP_THREADS * CP_KPT;
@@ -1304,7 +1303,8 @@ struct FeSmem {
 
 // emit + first sorting pass (digit = tile column tx)
 __global__ void __launch_bounds__(FB_THREADS, 3)
-isect_emit_sort_tx_kernel(int64_t V, int64_t n_isects, const int64_t* __restrict__ cum /*[V+1]*/,
+isect_emit_sort_tx_kernel(int64_t V, int64_t n_isects, const int64_t* __restrict__ totals_dev,
+                          const int64_t* __restrict__ cum /*[V+1]*/,
                           const uint32_t* __restrict__ rect_s, const uint32_t* __restrict__ gid_s,
                           const uint32_t* __restrict__ first_entry, const uint32_t* __restrict__ hist_tx,
                           volatile uint32_t* __restrict__ lookback, uint32_t* __restrict__ ticket,
@@ -1312,6 +1312,10 @@ isect_emit_sort_tx_kernel(int64_t V, int64_t n_isects, const int64_t* __restrict
     extern __shared__ __align__(16) unsigned char fb_smem_raw[];
     FeSmem& sm = *reinterpret_cast<FeSmem*>(fb_smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (totals_dev) {  // sync-free mode: the counts stay on the device, `n_isects` is the capacity of the outputs
+        V = totals_dev[0];
+        n_isects = totals_dev[1] <= n_isects ? totals_dev[1] : 0;  // a list that does not fit is DROPPED (empty view)
+    }
     if (tid == 0) sm.tile_id = atomicAdd(ticket, 1u);
     for (int i = tid; i < FB_WARPS * FB_RADIX; i += FB_THREADS) (&sm.warp_hist[0][0])[i] = 0;
     for (int q = tid; q < FB_TILE / 2; q += FB_THREADS) reinterpret_cast<uint32_t*>(sm.owner)[q] = 0u;
@@ -1426,7 +1430,8 @@ isect_emit_sort_tx_kernel(int64_t V, int64_t n_isects, const int64_t* __restrict
 
 // second (final) sorting pass (digit = tile row ty): flatten_ids, isect_ids (nullable), offsets
 __global__ void __launch_bounds__(FB_THREADS, 3)
-isect_sort_ty_final_kernel(int64_t n_isects, const uint64_t* __restrict__ pairs_in,
+isect_sort_ty_final_kernel(int64_t n_isects, const int64_t* __restrict__ totals_dev,
+                           const uint64_t* __restrict__ pairs_in,
                            const uint32_t* __restrict__ hist_ty, volatile uint32_t* __restrict__ lookback,
                            uint32_t* __restrict__ ticket, const float* __restrict__ depths, int tw,
                            int32_t* __restrict__ flatten_ids, int64_t* __restrict__ isect_ids,
@@ -1434,6 +1439,7 @@ isect_sort_ty_final_kernel(int64_t n_isects, const uint64_t* __restrict__ pairs_
     extern __shared__ __align__(16) unsigned char fb_smem_raw[];
     FbSmem& sm = *reinterpret_cast<FbSmem*>(fb_smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (totals_dev) n_isects = totals_dev[1] <= n_isects ? totals_dev[1] : 0;
     if (tid == 0) sm.tile_id = atomicAdd(ticket, 1u);
     for (int i = tid; i < FB_WARPS * FB_RADIX; i += FB_THREADS) (&sm.warp_hist[0][0])[i] = 0;
     __syncthreads();
@@ -1494,7 +1500,9 @@ isect_offsets_fixup_kernel(int n_tiles, const int64_t* __restrict__ n_isects_dev
                            int32_t* __restrict__ offsets) {
     __shared__ int32_t s_min[1024];
     const int tid = threadIdx.x;
-    const int32_t total = (int32_t)(n_isects_dev ? *n_isects_dev : n_isects);
+    // with the device count, `n_isects` is the capacity of the list (a list that does not fit is dropped: all
+    // offsets 0, the view renders empty)
+    const int32_t total = (int32_t)(n_isects_dev ? (*n_isects_dev <= n_isects ? *n_isects_dev : 0) : n_isects);
     const int per = (n_tiles + 1023) / 1024;
     const int lo = tid * per, hi = min(lo + per, n_tiles);
     int32_t m = total;
@@ -1907,22 +1915,13 @@ extern "C" int64_t sc_bin_phase_stamps_offset(int64_t N, int tile_width, int til
 
 extern "C" int64_t sc_bin_sort_workspace_bytes(int64_t n_isects) { return bin_sort_layout(n_isects).total; }
 
-extern "C" int sc_bin_finish(int64_t N, const float* depths, int tile_width, int tile_height, int64_t n_visible,
-                             int64_t n_isects, int64_t n_items, const void* prepare_workspace, int32_t* flatten_ids,
-                             int64_t* isect_ids, int32_t* offsets, void* sort_workspace,
-                             int64_t sort_workspace_bytes, void* stream) {
-    SC_CHECK_ARG(N >= 0 && n_isects >= 0 && n_visible >= 0 && n_visible <= N, "sizes");
-    SC_CHECK_ARG(n_items >= n_visible && n_items <= n_isects, "n_items");
-    SC_CHECK_ARG(n_isects < (1ll << 30), "n_isects (must be < 2^30)");
-    SC_CHECK_ARG(tile_width > 0 && tile_height > 0 && tile_width <= FB_RADIX && tile_height <= FB_RADIX, "tile grid");
-    SC_CHECK_ARG(offsets, "null pointer");
-    cudaStream_t st = (cudaStream_t)stream;
+// shared body of sc_bin_finish (counts known on the host) and sc_bin_finish_dev (counts on the device, outputs and
+// workspace sized for `n_isects` = the caller's capacity)
+static int bin_finish_impl(int64_t N, const float* depths, int tile_width, int tile_height, int64_t n_visible,
+                           int64_t n_isects, bool dev_counts, const void* prepare_workspace, int32_t* flatten_ids,
+                           int64_t* isect_ids, int32_t* offsets, void* sort_workspace, int64_t sort_workspace_bytes,
+                           cudaStream_t st) {
     const int n_tiles = tile_width * tile_height;
-    if (n_isects == 0) {
-        SC_CUDA(cudaMemsetAsync(offsets, 0, sizeof(int32_t) * (size_t)n_tiles, st));
-        return SC_OK;
-    }
-    SC_CHECK_ARG(depths && prepare_workspace && flatten_ids && sort_workspace, "null pointer");
     const IsectWs L = isect_ws_layout(N, (int64_t)n_tiles);
     const BinSortWs B = bin_sort_layout(n_isects);
     SC_CHECK_ARG(B.tiles + 1 <= L.first_cap, "n_isects exceeds the entry table");
@@ -1945,23 +1944,58 @@ extern "C" int sc_bin_finish(int64_t N, const float* depths, int tile_width, int
     uint32_t* tickets = (uint32_t*)(sws + B.ticket_off);
     uint64_t* pairs = (uint64_t*)(sws + B.pairs_off);
     const uint32_t* hist_xy = (const uint32_t*)(pws + L.hist_xy_off);
+    const int64_t* totals_dev = dev_counts ? (const int64_t*)(pws + L.totals_off) : nullptr;
     // (an ITEM-wise variant of this kernel — one weighted rank per (Gaussian, tile column) run instead of one
     // per slot, every lane writing its run — measured 2x SLOWER: 254 us vs 120 us on 13.6 M intersections; its
     // scattered 8-byte stores and the divergent run loops cost more than the ranking work it saves)
     isect_emit_sort_tx_kernel<<<(unsigned)B.tiles, FB_THREADS, sizeof(FeSmem), st>>>(
-        n_visible, n_isects, (const int64_t*)(pws + L.cum_off), (const uint32_t*)(pws + L.rect_s_off),
+        n_visible, n_isects, totals_dev, (const int64_t*)(pws + L.cum_off), (const uint32_t*)(pws + L.rect_s_off),
         (const uint32_t*)(pws + L.gid_s_off), (const uint32_t*)(pws + L.first_off), hist_xy,
         (uint32_t*)(sws + B.lookback_off), tickets + 0, pairs);
     SC_CHECK_LAUNCH("isect_emit_sort_tx_kernel");
     isect_sort_ty_final_kernel<<<(unsigned)B.tiles, FB_THREADS, sizeof(FbSmem), st>>>(
-        n_isects, pairs, hist_xy + FB_RADIX, (uint32_t*)(sws + B.lookback2_off), tickets + 1, depths, tile_width,
-        flatten_ids, isect_ids, offsets);
+        n_isects, totals_dev, pairs, hist_xy + FB_RADIX, (uint32_t*)(sws + B.lookback2_off), tickets + 1, depths,
+        tile_width, flatten_ids, isect_ids, offsets);
     SC_CHECK_LAUNCH("isect_sort_ty_final_kernel");
-    isect_offsets_fixup_kernel<<<1, 1024, 0, st>>>(n_tiles, nullptr, n_isects, offsets);
+    isect_offsets_fixup_kernel<<<1, 1024, 0, st>>>(n_tiles, totals_dev ? totals_dev + 1 : nullptr, n_isects, offsets);
     SC_CHECK_LAUNCH("isect_offsets_fixup_kernel");
     return SC_OK;
 }
 
+extern "C" int sc_bin_finish(int64_t N, const float* depths, int tile_width, int tile_height, int64_t n_visible,
+                             int64_t n_isects, int64_t n_items, const void* prepare_workspace, int32_t* flatten_ids,
+                             int64_t* isect_ids, int32_t* offsets, void* sort_workspace,
+                             int64_t sort_workspace_bytes, void* stream) {
+    SC_CHECK_ARG(N >= 0 && n_isects >= 0 && n_visible >= 0 && n_visible <= N, "sizes");
+    SC_CHECK_ARG(n_items >= n_visible && n_items <= n_isects, "n_items");
+    SC_CHECK_ARG(n_isects < (1ll << 30), "n_isects (must be < 2^30)");
+    SC_CHECK_ARG(tile_width > 0 && tile_height > 0 && tile_width <= FB_RADIX && tile_height <= FB_RADIX, "tile grid");
+    SC_CHECK_ARG(offsets, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_isects == 0) {
+        SC_CUDA(cudaMemsetAsync(offsets, 0, sizeof(int32_t) * (size_t)(tile_width * tile_height), st));
+        return SC_OK;
+    }
+    SC_CHECK_ARG(depths && prepare_workspace && flatten_ids && sort_workspace, "null pointer");
+    return bin_finish_impl(N, depths, tile_width, tile_height, n_visible, n_isects, false, prepare_workspace, flatten_ids,
+                           isect_ids, offsets, sort_workspace, sort_workspace_bytes, st);
+}
+
+// Sync-free form: no host read-back between the two halves of the binning.  The counts {n_visible, n_isects,
+// n_items} stay in the first 24 bytes of the prepare workspace; `capacity` bounds the list the outputs (and the sort
+// workspace, sc_bin_sort_workspace_bytes(capacity)) can hold.  A list longer than the capacity is DROPPED (all tile
+// offsets 0: the view renders empty, nothing is accessed out of bounds): the caller compares the counts with its
+// capacity once the stream has passed — e.g. one step later — and re-runs with a larger one.  Nothing here depends on a value the
+// host has not got yet, so a camera pass built on it can be captured in a CUDA graph.
+extern "C" int sc_bin_finish_dev(int64_t N, const float* depths, int tile_width, int tile_height, int64_t capacity,
+                                 const void* prepare_workspace, int32_t* flatten_ids, int64_t* isect_ids,
+                                 int32_t* offsets, void* sort_workspace, int64_t sort_workspace_bytes, void* stream) {
+    SC_CHECK_ARG(N >= 0 && capacity >= 1 && capacity < (1ll << 30), "sizes (1 <= capacity < 2^30)");
+    SC_CHECK_ARG(tile_width > 0 && tile_height > 0 && tile_width <= FB_RADIX && tile_height <= FB_RADIX, "tile grid");
+    SC_CHECK_ARG(depths && prepare_workspace && flatten_ids && sort_workspace && offsets, "null pointer");
+    return bin_finish_impl(N, depths, tile_width, tile_height, 0, capacity, true, prepare_workspace, flatten_ids,
+                           isect_ids, offsets, sort_workspace, sort_workspace_bytes, (cudaStream_t)stream);
+}
 
 extern "C" int sc_isect_offset_encode(int64_t n_isects, const int64_t* isect_ids, int C, int tile_width,
                                       int tile_height, int tile_n_bits, int32_t* offsets, void* stream) {

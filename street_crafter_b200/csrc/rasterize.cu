@@ -27,6 +27,7 @@
 #include <stdlib.h>
 #include "common.cuh"
 
+#include <algorithm>
 #include <type_traits>
 
 namespace {
@@ -269,8 +270,10 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                      const int32_t* __restrict__ flatten_ids, int max_hit, float* __restrict__ render_colors,
                      float* __restrict__ render_alphas, int32_t* __restrict__ last_ids,
                      float* __restrict__ final_T, unsigned long long* __restrict__ stats,
-                     float* __restrict__ depth_norm) {
+                     float* __restrict__ depth_norm, const int64_t* __restrict__ n_isects_dev) {
     __shared__ __align__(16) WarpSmem<CH, false> smem[WARPS_PER_CTA];
+    // sync-free binning: `n_isects` is the capacity; a list that did not fit was dropped (all offsets 0)
+    if (n_isects_dev) n_isects = (*n_isects_dev <= n_isects) ? *n_isects_dev : 0;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t n_slots = (int64_t)n_cams * tile_w * tile_h;
     const int64_t tslot = (int64_t)blockIdx.x * WARPS_PER_CTA + wib;
@@ -550,7 +553,7 @@ rasterize_fwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 // Sum of NRED per-lane values over the warp, through shared memory: every lane stores its
 // values as a column of Rd[NRED][RED_STRIDE]; lane l then sums half (l & 1) of row (l >> 1)
 // with four LDS.128 (rows are 36 floats apart, so the 8 lanes of a quarter-warp hit 32
-// distinct banks) and one shuffle joins the halves: 13 STS + 4 LDS.128 + 17 FADD + 1 SHFL per
+// distinct banks) and one shuffle joins the halves: 13 STS + 4 LDS.128 + 17 FADD (7 FADD2 + 2 FADD packed) + 1 SHFL per
 // (tile, Gaussian) instead of 16 SHFL + 31 FADD + 30 selects for the register butterfly.
 // Lanes 2k and 2k+1 both return the total of value k (k < NRED; other lanes return 0).
 __device__ __forceinline__ float warp_reduce_rows(const float (&v)[NRED], float (*Rd)[RED_STRIDE], int lane) {
@@ -560,10 +563,18 @@ __device__ __forceinline__ float warp_reduce_rows(const float (&v)[NRED], float 
     const int k = lane >> 1;
     float r = 0.f;
     if (k < NRED) {
+#if SC_RASTER_F32X2
+        // 16 floats as 8 register pairs: 7 packed adds + 1 scalar add instead of 15 scalar adds
+        const ulonglong2* row = reinterpret_cast<const ulonglong2*>(&Rd[k][(lane & 1) * 16]);
+        const ulonglong2 a = row[0], b = row[1], c = row[2], d = row[3];
+        const f2 s = add2(add2(add2(a.x, a.y), add2(b.x, b.y)), add2(add2(c.x, c.y), add2(d.x, d.y)));
+        r = lo2(s) + hi2(s);
+#else
         const float4* row = reinterpret_cast<const float4*>(&Rd[k][(lane & 1) * 16]);
         const float4 a = row[0], b = row[1], c = row[2], d = row[3];
         r = ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w)) +
             (((c.x + c.y) + (c.z + c.w)) + ((d.x + d.y) + (d.z + d.w)));
+#endif
     }
     r += __shfl_xor_sync(FULL, r, 1);
     __syncwarp();  // the rows are rewritten by the next Gaussian
@@ -902,19 +913,32 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
     }
 }
 
+// Resident compositing warps per SM (0 = as many as fit, i.e. 16 at 128 registers).  The compositing kernels fill
+// the register file; a smaller number leaves registers to the HBM-bound kernels that pipeline.ViewPipeline runs
+// BESIDE them on its memory stream (projection, binning, SH of the neighbouring views).  Implemented as a dynamic
+// shared-memory request that makes only that many one-warp CTAs fit an SM.
+int g_warps_per_sm = 0;
+size_t occupancy_pad(size_t static_smem) {
+    if (g_warps_per_sm <= 0 || WARPS_PER_CTA != 1) return 0;
+    const size_t per_cta = (size_t)(228 * 1024) / (size_t)g_warps_per_sm;   // 1 KB of each CTA is the system's
+    const size_t want = (per_cta > static_smem + 1024 + 128) ? per_cta - static_smem - 1024 : 0;
+    return std::min<size_t>(want / 128 * 128, 40 * 1024);
+}
+
 template <int CH>
 int launch_fwd(int C, int64_t n_isects, int width, int height, const float* means2d, const float* conics,
                const float* colors, const float* opacities, const float* backgrounds,
                const int32_t* isect_offsets, const int32_t* flatten_ids, int max_hit, float* render_colors,
                float* render_alphas, int32_t* last_ids, float* final_T, unsigned long long* stats,
-               float* depth_norm, cudaStream_t st) {
+               float* depth_norm, const int64_t* n_isects_dev, cudaStream_t st) {
     const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
     const unsigned grid = (unsigned)sc_div_up((int64_t)C * tile_w * tile_h, WARPS_PER_CTA);
+    const size_t pad = occupancy_pad(sizeof(WarpSmem<CH, false>) * WARPS_PER_CTA);
 #define FWD_LAUNCH(ST, MH)                                                                              \
-    rasterize_fwd_kernel<CH, ST, MH><<<grid, WARPS_PER_CTA * 32, 0, st>>>(                              \
+    rasterize_fwd_kernel<CH, ST, MH><<<grid, WARPS_PER_CTA * 32, pad, st>>>(                            \
         n_isects, C, width, height, tile_w, tile_h, reinterpret_cast<const float2*>(means2d), conics,    \
         colors, opacities, backgrounds, isect_offsets, flatten_ids, max_hit, render_colors,             \
-        render_alphas, last_ids, final_T, stats, depth_norm)
+        render_alphas, last_ids, final_T, stats, depth_norm, n_isects_dev)
     if (stats) {
         if (max_hit > 0) FWD_LAUNCH(true, true); else FWD_LAUNCH(true, false);
     } else {
@@ -934,7 +958,8 @@ int launch_bwd(int C, int64_t n_isects, int width, int height, const float* mean
                cudaStream_t st) {
     const int tile_w = (width + TILE - 1) / TILE, tile_h = (height + TILE - 1) / TILE;
     const unsigned grid = (unsigned)sc_div_up((int64_t)C * tile_w * tile_h, WARPS_PER_CTA);
-    rasterize_bwd_kernel<CH><<<grid, WARPS_PER_CTA * 32, 0, st>>>(
+    const size_t pad = occupancy_pad(sizeof(WarpSmem<CH, true, BATCH_BWD>) * WARPS_PER_CTA);
+    rasterize_bwd_kernel<CH><<<grid, WARPS_PER_CTA * 32, pad, st>>>(
         n_isects, C, width, height, tile_w, tile_h, reinterpret_cast<const float2*>(means2d), conics, colors,
         opacities, backgrounds, isect_offsets, flatten_ids, final_T, last_ids, v_render_colors, v_render_alphas,
         v_means2d, v_means2d_abs, v_conics, v_colors, v_opacities);
@@ -944,12 +969,18 @@ int launch_bwd(int C, int64_t n_isects, int width, int height, const float* mean
 
 }  // namespace
 
+extern "C" int sc_rasterize_limit_warps(int warps_per_sm) {
+    SC_CHECK_ARG(warps_per_sm >= 0 && warps_per_sm <= 64, "warps_per_sm");
+    g_warps_per_sm = warps_per_sm;
+    return SC_OK;
+}
+
 static int rasterize_fwd_entry(int C, int64_t N, int64_t n_isects, int CH, int width, int height,
                                 int tile_size, const float* means2d, const float* conics, const float* colors,
                                 const float* opacities, const float* backgrounds, const int32_t* isect_offsets,
                                 const int32_t* flatten_ids, int max_hit, float* render_colors,
                                 float* render_alphas, int32_t* last_ids, float* final_T, uint64_t* stats,
-                                float* depth_norm, void* stream) {
+                                float* depth_norm, const int64_t* n_isects_dev, void* stream) {
     SC_CHECK_ARG(C >= 1 && N >= 0 && n_isects >= 0 && width > 0 && height > 0, "sizes");
     SC_CHECK_ARG(n_isects < (1ll << 31), "n_isects must fit int32");
     if (tile_size != TILE) {
@@ -963,7 +994,7 @@ static int rasterize_fwd_entry(int C, int64_t N, int64_t n_isects, int CH, int w
     cudaStream_t st = (cudaStream_t)stream;
 #define ARGS C, n_isects, width, height, means2d, conics, colors, opacities, backgrounds, isect_offsets, \
              flatten_ids, max_hit, render_colors, render_alphas, last_ids, final_T,                       \
-             reinterpret_cast<unsigned long long*>(stats), depth_norm, st
+             reinterpret_cast<unsigned long long*>(stats), depth_norm, n_isects_dev, st
     switch (CH) {
         case 1: return launch_fwd<1>(ARGS);
         case 2: return launch_fwd<2>(ARGS);
@@ -985,7 +1016,7 @@ extern "C" int sc_rasterize_fwd(int C, int64_t N, int64_t n_isects, int CH, int 
                                 void* stream) {
     return rasterize_fwd_entry(C, N, n_isects, CH, width, height, tile_size, means2d, conics, colors, opacities,
                                backgrounds, isect_offsets, flatten_ids, max_hit, render_colors, render_alphas,
-                               last_ids, final_T, stats, nullptr, stream);
+                               last_ids, final_T, stats, nullptr, nullptr, stream);
 }
 
 extern "C" int sc_rasterize_fwd_depth(int C, int64_t N, int64_t n_isects, int width, int height, int tile_size,
@@ -997,7 +1028,21 @@ extern "C" int sc_rasterize_fwd_depth(int C, int64_t N, int64_t n_isects, int wi
     SC_CHECK_ARG(depth_norm, "null pointer");
     return rasterize_fwd_entry(C, N, n_isects, 4, width, height, tile_size, means2d, conics, colors4, opacities,
                                nullptr, isect_offsets, flatten_ids, 0, render_colors, render_alphas, last_ids,
-                               final_T, stats, depth_norm, stream);
+                               final_T, stats, depth_norm, nullptr, stream);
+}
+
+// sc_rasterize_fwd_depth behind the sync-free binning (sc_bin_finish_dev): `capacity` = length of flatten_ids,
+// the actual list length is read from the device (`n_isects_dev`, the second count of the prepare workspace)
+extern "C" int sc_rasterize_fwd_depth_dev(int C, int64_t N, int64_t capacity, const int64_t* n_isects_dev, int width,
+                                          int height, int tile_size, const float* means2d, const float* conics,
+                                          const float* colors4, const float* opacities, const int32_t* isect_offsets,
+                                          const int32_t* flatten_ids, float* render_colors, float* render_alphas,
+                                          float* depth_norm, int32_t* last_ids, float* final_T, uint64_t* stats,
+                                          void* stream) {
+    SC_CHECK_ARG(depth_norm && n_isects_dev && capacity >= 1, "null pointer / capacity");
+    return rasterize_fwd_entry(C, N, capacity, 4, width, height, tile_size, means2d, conics, colors4, opacities,
+                               nullptr, isect_offsets, flatten_ids, 0, render_colors, render_alphas, last_ids,
+                               final_T, stats, depth_norm, n_isects_dev, stream);
 }
 
 extern "C" int sc_rasterize_bwd(int C, int64_t N, int64_t n_isects, int CH, int width, int height,

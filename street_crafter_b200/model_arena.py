@@ -162,21 +162,20 @@ class SceneArena:
                 runs.append((self.step[name], [name]))
         with torch.cuda.device(self.device):
             for step, chunk in runs:
-                if True:
-                    starts, lr = [], []
-                    for name in chunk:
-                        for a in ATTRS:
-                            starts.append(self.layout[name][a][0])
-                            lr.append(float(lrs.get(name, {}).get(a, 0.0)))
-                    starts.append(self.span(chunk[-1])[1])
-                    clo, chi = max(lo, starts[0]), min(hi, starts[-1])
-                    if chi <= clo:
-                        continue
-                    n = len(lr)
-                    check(lib.sc_adam_step(n, (C.c_int64 * (n + 1))(*starts), (C.c_float * n)(*lr), clo, chi,
-                                           b["params"].data_ptr(), b["grads"].data_ptr(), b["exp_avg"].data_ptr(),
-                                           b["exp_avg_sq"].data_ptr(), float(betas[0]), float(betas[1]), float(eps),
-                                           int(step), st), "sc_adam_step")
+                starts, lr = [], []
+                for name in chunk:
+                    for a in ATTRS:
+                        starts.append(self.layout[name][a][0])
+                        lr.append(float(lrs.get(name, {}).get(a, 0.0)))
+                starts.append(self.span(chunk[-1])[1])
+                clo, chi = max(lo, starts[0]), min(hi, starts[-1])
+                if chi <= clo:
+                    continue
+                n = len(lr)
+                check(lib.sc_adam_step(n, (C.c_int64 * (n + 1))(*starts), (C.c_float * n)(*lr), clo, chi,
+                                       b["params"].data_ptr(), b["grads"].data_ptr(), b["exp_avg"].data_ptr(),
+                                       b["exp_avg_sq"].data_ptr(), float(betas[0]), float(betas[1]), float(eps),
+                                       int(step), st), "sc_adam_step")
 
     # ------------------------------------------------------------------ densification on the arena (N4)
     def _begin_rebuild(self, name: str, new_n: int) -> None:

@@ -23,7 +23,7 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
                          antialiasing: bool = True, train: bool = True,
                          grad_sinks: Optional[Dict[str, Tensor]] = None, fused: bool = True,
                          aux_ids: bool = True, prepared: Optional[Dict] = None,
-                         deferred: Optional[list] = None) -> Dict[str, Tensor]:
+                         deferred: Optional[list] = None, defer_sh: bool = False) -> Dict[str, Tensor]:
     """xyz3[N,3] rgb3[N,K,3] (SH) scale[N,3] quats[N,4] occ1[N,1] w2c[1,4,4] K[1,3,3]
     camera_center[3] -> the reference's result dict (rgb[3,H,W], acc, depth, viewspace_points,
     visibility_filter, radii) plus the raw render tensors.
@@ -40,7 +40,8 @@ def render_kernel_gsplat(xyz3: Tensor, rgb3: Tensor, scale: Tensor, quats: Tenso
         render_colors, render_alphas, meta = fused_view(
             xyz3, quats, scale, occ1[:, 0], rgb3, w2c, K, camera_center, width, height, max_sh_degree,
             near_plane=znear, far_plane=zfar, antialiased=antialiasing, tile_size=tile_size, absgrad=absgrad,
-            grad_sinks=grad_sinks, need_isect_ids=aux_ids, prepared=prepared, deferred=deferred)
+            grad_sinks=grad_sinks, need_isect_ids=aux_ids, prepared=prepared, deferred=deferred,
+            defer_sh=defer_sh)
         radii, means2d = meta["radii"], meta["means2d"]
         rendered_color = render_colors[..., :-1]
         rendered_depth = meta["depth_norm"]  # render_colors[..., -1:] / render_alphas.clamp(min=1e-10), in-kernel

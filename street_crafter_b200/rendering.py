@@ -15,7 +15,7 @@ path: CPU tensors raise."""
 from __future__ import annotations
 
 import math
-from typing import Dict, Optional, Tuple
+from typing import Dict, List, Optional, Tuple
 
 import torch
 from torch import Tensor
@@ -233,7 +233,8 @@ _PINNED_TOTALS: Dict[Tuple[int, int], Tensor] = {}
 
 
 def _isect_begin(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int, tile_width: int,
-                 tile_height: int, tpg: Tensor, st: int):
+                 tile_height: int, tpg: Tensor, st: int, capacity: Optional[int] = None,
+                 counts_host: Optional[Tensor] = None):
     """phase 1 of the fused binning pipeline: compaction of the emitting entries + their stable
     depth order + scan (one C call), then an ASYNC copy of {n_visible, n_isects} to pinned host
     memory and an event.  The caller may enqueue independent GPU work before _isect_finish()
@@ -251,6 +252,15 @@ def _isect_begin(means2d: Tensor, radii: Tensor, depths: Tensor, tile_size: int,
     else:
         check(lib.sc_isect_prepare(CN, _p(means2d), _p(radii), _p(depths), tile_size, tile_width, tile_height,
                                    _p(tpg), _p(ws), ws_bytes, st), "sc_isect_prepare")
+    if capacity is not None:
+        # sync-free mode (fast path only): the counts stay on the device; a copy travels to the caller's pinned
+        # buffer for the capacity check it makes LATER (nothing waits for it here)
+        if not fast:
+            raise RuntimeError("sync-free binning needs the fast path (one camera, tile grid <= 128 x 128)")
+        counts = ws[:24].view(torch.int64).clone()
+        if counts_host is not None:
+            counts_host.copy_(counts, non_blocking=True)
+        return (means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, counts, int(capacity), fast)
     key = (dev.index if dev.index is not None else torch.cuda.current_device(), st)
     host = _PINNED_TOTALS.get(key)
     if host is None:
@@ -268,6 +278,16 @@ def _isect_finish(state, need_ids: bool = True):
     means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, ws, host, ev, fast = state
     C, N = radii.shape
     dev = means2d.device
+    if isinstance(ev, int):   # sync-free mode: (…, counts on the device, capacity, fast)
+        counts, capacity = host, ev
+        flat = torch.empty(capacity, dtype=torch.int32, device=dev)
+        ids = torch.empty(capacity, dtype=torch.int64, device=dev) if need_ids else None
+        offsets = torch.empty((1, tile_height, tile_width), dtype=torch.int32, device=dev)
+        sws_bytes = int(lib.sc_bin_sort_workspace_bytes(capacity))
+        sws = torch.empty(sws_bytes, dtype=torch.uint8, device=dev)
+        check(lib.sc_bin_finish_dev(N, _p(depths), tile_width, tile_height, capacity, _p(ws), _p(flat), _p(ids),
+                                    _p(offsets), _p(sws), sws_bytes, st), "sc_bin_finish_dev")
+        return tpg, ids, flat, offsets
     bits = _tile_n_bits(tile_width, tile_height)
     cam_bits = 0 if C == 1 else int(math.floor(math.log2(C))) + 1
     ev.synchronize()
@@ -482,7 +502,7 @@ def rasterize_to_pixels(means2d: Tensor, conics: Tensor, colors: Tensor, opaciti
 
 
 def _project_begin(means, quats, scales, opacities, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
-                   radius_clip, antialiased, tile_size, st):
+                   radius_clip, antialiased, tile_size, st, capacity=None, counts_host=None):
     """projection (+ opacity * compensation, result packing) and the first half of the binning for ONE camera"""
     N = means.shape[0]
     dev = means.device
@@ -505,10 +525,13 @@ def _project_begin(means, quats, scales, opacities, viewmats, Ks, width, height,
         tile_width = math.ceil(width / float(tile_size))
         tile_height = math.ceil(height / float(tile_size))
         tpg = torch.empty((1, N), dtype=torch.int32, device=dev)
-        state = _isect_begin(means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st)
-    return dict(radii=radii, means2d=means2d, depths=depths, conics=conics, comps=comps, op_c=op_c, vis=vis,
-                radii_norm=radii_norm, state=state, tile_width=tile_width, tile_height=tile_height,
-                key=(N, int(width), int(height), int(tile_size), bool(antialiased)))
+        state = _isect_begin(means2d, radii, depths, tile_size, tile_width, tile_height, tpg, st, capacity, counts_host)
+    pb = dict(radii=radii, means2d=means2d, depths=depths, conics=conics, comps=comps, op_c=op_c, vis=vis,
+              radii_norm=radii_norm, state=state, tile_width=tile_width, tile_height=tile_height,
+              key=(N, int(width), int(height), int(tile_size), bool(antialiased)))
+    if capacity is not None:
+        pb["counts"], pb["capacity"] = state[9], int(capacity)
+    return pb
 
 
 def _project_finish(pb, need_ids):
@@ -524,18 +547,66 @@ def _project_finish(pb, need_ids):
 
 
 @torch.no_grad()
+def prepare_view_begin(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, viewmats: Tensor, Ks: Tensor,
+                       width: int, height: int, eps2d: float = 0.3, near_plane: float = 0.01, far_plane: float = 1e10,
+                       radius_clip: float = 0.0, antialiased: bool = True, tile_size: int = 16,
+                       shs: Optional[Tensor] = None, campos: Optional[Tensor] = None, sh_degree: Optional[int] = None,
+                       capacity: Optional[int] = None, counts_host: Optional[Tensor] = None):
+    """First half of `prepare_view`: enqueues the projection, the first half of the binning and the asynchronous
+    read-back of its counts on the CURRENT stream and returns without waiting.  With `shs` / `campos` / `sh_degree`
+    the SH colours of the view are evaluated here too (they only need the projection's radii and depths), so that
+    `fused_view(..., prepared=state)` starts with the compositing.  `prepare_view_finish(state)` waits for the
+    counts and enqueues the second half of the binning (on the stream current THEN; use the same one).
+    `capacity` (an upper bound of the view's intersection count, e.g. 1.25 x the last step's) selects the SYNC-FREE
+    binning: nothing is read back, `prepare_view_finish` does not wait, a list beyond the capacity is DROPPED (the
+    view renders empty); the counts
+    land in `counts_host` (pinned int64[3]: visible, intersections, items) for `capacity_exceeded`.  Such a pass has
+    no host dependency: it can be captured in a CUDA graph (pipeline.GraphedStep)."""
+    means, quats, scales = _f32c(means.detach(), "means"), _f32c(quats.detach(), "quats"), _f32c(scales.detach(), "scales")
+    opacities = _f32c(opacities.detach(), "opacities", 4)
+    st = _stream()
+    pb = _project_begin(means, quats, scales, opacities, _f32c(viewmats, "viewmats"), _f32c(Ks, "Ks"), width, height, eps2d,
+                        near_plane, far_plane, radius_clip, antialiased, tile_size, st, capacity, counts_host)
+    if shs is not None:
+        shs = _f32c(shs.detach(), "shs")
+        campos = _f32c(campos, "camera centre", 4)
+        N, Kc = shs.shape[0], shs.shape[1]
+        colors4 = torch.empty((1, N, 4), dtype=torch.float32, device=means.device)
+        with torch.cuda.device(means.device):
+            check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(pb["radii"]),
+                                     _p(pb["depths"]), _p(colors4), st), "sc_sh_fwd_view")
+        pb["colors4"] = colors4
+        pb["sh_key"] = (Kc, int(sh_degree))
+    return pb
+
+
+@torch.no_grad()
+def prepare_view_finish(pb: Dict, need_isect_ids: bool = False) -> Dict:
+    return _project_finish(pb, need_isect_ids)
+
+
+def capacity_exceeded(counts_host: Tensor, capacity: int) -> bool:
+    """after the stream has passed a sync-free pass: did the view's intersection list fit its capacity?"""
+    return int(counts_host[1]) > int(capacity)
+
+
+def prepared_tensors(pb: Dict) -> List[Tensor]:
+    """the device tensors of a prepared state (for Tensor.record_stream when it crosses streams)"""
+    return [v for v in pb.values() if isinstance(v, Tensor) and v.is_cuda]
+
+
+@torch.no_grad()
 def prepare_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, viewmats: Tensor, Ks: Tensor,
                  width: int, height: int, eps2d: float = 0.3, near_plane: float = 0.01, far_plane: float = 1e10,
-                 radius_clip: float = 0.0, antialiased: bool = True, tile_size: int = 16, need_isect_ids: bool = False):
+                 radius_clip: float = 0.0, antialiased: bool = True, tile_size: int = 16, need_isect_ids: bool = False,
+                 shs: Optional[Tensor] = None, campos: Optional[Tensor] = None, sh_degree: Optional[int] = None):
     """Phase 1 of a camera pass — projection and the complete binning, everything that reads only the GEOMETRIC
     parameters — as a state object for `fused_view(..., prepared=state)`.  A multi-view step can run phase 1 of all
     its views first: the view-sharded trainer does, so that the all-gather of the SH coefficients (81 % of the
     parameter bytes) travels under it (parallel.ShardedAdam).  Same kernels, same results."""
-    means, quats, scales = _f32c(means.detach(), "means"), _f32c(quats.detach(), "quats"), _f32c(scales.detach(), "scales")
-    opacities = _f32c(opacities.detach(), "opacities", 4)
-    pb = _project_begin(means, quats, scales, opacities, _f32c(viewmats, "viewmats"), _f32c(Ks, "Ks"), width, height, eps2d,
-                        near_plane, far_plane, radius_clip, antialiased, tile_size, _stream())
-    return _project_finish(pb, need_isect_ids)
+    pb = prepare_view_begin(means, quats, scales, opacities, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
+                            radius_clip, antialiased, tile_size, shs, campos, sh_degree)
+    return prepare_view_finish(pb, need_isect_ids)
 
 
 # ------------------------------------------------------------------------------------------
@@ -551,7 +622,7 @@ class _FusedView(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
                 eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, sinks, need_ids=True,
-                prepared=None, deferred=None):
+                prepared=None, deferred=None, defer_sh=False):
         means = _f32c(means, "means")
         quats = _f32c(quats, "quats")
         scales = _f32c(scales, "scales")
@@ -563,7 +634,9 @@ class _FusedView(torch.autograd.Function):
         N, Kc = shs.shape[0], shs.shape[1]
         dev = means.device
         st = _stream()
-        colors4 = torch.empty((1, N, 4), dtype=torch.float32, device=dev)
+        colors4 = None
+        if prepared is None or "colors4" not in prepared:
+            colors4 = torch.empty((1, N, 4), dtype=torch.float32, device=dev)
         if prepared is None:
             pb = _project_begin(means, quats, scales, opacities, viewmats, Ks, width, height, eps2d, near_plane, far_plane,
                                 radius_clip, antialiased, tile_size, st)
@@ -577,9 +650,13 @@ class _FusedView(torch.autograd.Function):
             # step while the SH coefficients were still arriving from the other ranks
             pb = prepared
             assert pb["key"] == (N, int(width), int(height), int(tile_size), bool(antialiased)), "prepared for another view"
-            with torch.cuda.device(dev):
-                check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(pb["radii"]),
-                                         _p(pb["depths"]), _p(colors4), st), "sc_sh_fwd_view")
+            if colors4 is None:
+                assert pb["sh_key"] == (Kc, int(sh_degree)), "prepared with other SH settings"
+                colors4 = pb["colors4"]
+            else:
+                with torch.cuda.device(dev):
+                    check(lib.sc_sh_fwd_view(N, Kc, int(sh_degree), _p(means), _p(campos), _p(shs), _p(pb["radii"]),
+                                             _p(pb["depths"]), _p(colors4), st), "sc_sh_fwd_view")
         radii, means2d, depths, conics, comps, op_c, vis, radii_norm = (pb[k] for k in (
             "radii", "means2d", "depths", "conics", "comps", "op_c", "vis", "radii_norm"))
         tpg, isect_ids, flatten_ids, isect_offsets = (pb[k] for k in ("tpg", "isect_ids", "flatten_ids", "isect_offsets"))
@@ -589,11 +666,18 @@ class _FusedView(torch.autograd.Function):
             last_ids = torch.empty((1, height, width), dtype=torch.int32, device=dev)
             final_T = torch.empty((1, height, width), dtype=torch.float32, device=dev)
             depth_norm = torch.empty((1, height, width, 1), dtype=torch.float32, device=dev)
-            check(lib.sc_rasterize_fwd_depth(1, N, flatten_ids.numel(), width, height, tile_size, _p(means2d),
-                                             _p(conics), _p(colors4), _p(op_c), _p(isect_offsets),
-                                             _p(flatten_ids), _p(render_colors), _p(render_alphas),
-                                             _p(depth_norm), _p(last_ids), _p(final_T), _p(_STATS["buf"]), st),
-                  "sc_rasterize_fwd_depth")
+            if "capacity" in pb:   # sync-free binning: the list length is on the device
+                check(lib.sc_rasterize_fwd_depth_dev(1, N, flatten_ids.numel(), pb["counts"].data_ptr() + 8, width, height,
+                                                     tile_size, _p(means2d), _p(conics), _p(colors4), _p(op_c),
+                                                     _p(isect_offsets), _p(flatten_ids), _p(render_colors),
+                                                     _p(render_alphas), _p(depth_norm), _p(last_ids), _p(final_T),
+                                                     _p(_STATS["buf"]), st), "sc_rasterize_fwd_depth_dev")
+            else:
+                check(lib.sc_rasterize_fwd_depth(1, N, flatten_ids.numel(), width, height, tile_size, _p(means2d),
+                                                 _p(conics), _p(colors4), _p(op_c), _p(isect_offsets),
+                                                 _p(flatten_ids), _p(render_colors), _p(render_alphas),
+                                                 _p(depth_norm), _p(last_ids), _p(final_T), _p(_STATS["buf"]), st),
+                      "sc_rasterize_fwd_depth")
         ctx.save_for_backward(means, quats, scales, opacities, shs, viewmats, Ks, campos, radii, means2d, conics,
                               colors4, op_c, isect_offsets, flatten_ids, last_ids, final_T, render_alphas,
                               depth_norm)
@@ -601,6 +685,7 @@ class _FusedView(torch.autograd.Function):
                    int(sh_degree))
         ctx.sinks = sinks
         ctx.deferred = deferred
+        ctx.defer_sh = bool(defer_sh)
         ctx.means2d_ref = None  # weakref to the returned means2d: receives .grad / .absgrad in backward
         ctx.set_materialize_grads(False)  # no zero-filled "gradients" for the auxiliary outputs
         aux = (radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets, vis,
@@ -645,8 +730,10 @@ class _FusedView(torch.autograd.Function):
                                        _p(flatten_ids), _p(final_T), _p(last_ids), _p(v_render_colors),
                                        _p(v_render_alphas), _p(v_means2d), _p(v_abs) if absgrad else None,
                                        _p(v_conics), _p(v_colors4), _p(v_opc), st), "sc_rasterize_bwd")
-            check(lib.sc_sh_bwd_view(N, Kc, sh_degree, _p(means), _p(campos), _p(shs), _p(radii), _p(colors4),
-                                     _p(v_colors4), _p(g_shs), _p(g_means), 1, st), "sc_sh_bwd_view")
+            def sh_bwd(keep=(arena, means, campos, shs, radii, colors4)):
+                with torch.cuda.device(dev):
+                    check(lib.sc_sh_bwd_view(N, Kc, sh_degree, _p(means), _p(campos), _p(shs), _p(radii), _p(colors4),
+                                             _p(v_colors4), _p(g_shs), _p(g_means), 1, _stream()), "sc_sh_bwd_view")
 
             def projection_bwd(keep=(arena, means, quats, scales, opacities, viewmats, Ks, radii)):
                 with torch.cuda.device(dev):
@@ -655,12 +742,28 @@ class _FusedView(torch.autograd.Function):
                                                         _p(v_means2d), v_colors4.data_ptr() + 12, 4, _p(v_conics),
                                                         _p(v_opc), 1 if antialiased else 0, _p(g_means), _p(g_quats),
                                                         _p(g_scales), _p(g_op), 1, _stream()), "sc_projection_bwd_opacity")
-            if ctx.deferred is not None and sinks is not None:
-                # gradient-arena mode only: the caller runs the projection backward of all its views LATER (so that
-                # the exchange of the SH gradients, final once the last view's SH backward has run, travels under them)
-                ctx.deferred.append(projection_bwd)
-            else:
+
+            def tail(keep=(arena, means, quats, scales, opacities, viewmats, Ks, radii, campos, shs, colors4)):
+                # may run on ANOTHER stream than this backward (pipeline.ViewPipeline): tell the allocator
+                cur = torch.cuda.current_stream(dev)
+                for t in keep:
+                    t.record_stream(cur)
+                sh_bwd()
                 projection_bwd()
+            deferred_ok = ctx.deferred is not None and sinks is not None
+            if deferred_ok and ctx.defer_sh:
+                # gradient-arena mode, view pipeline: the two HBM-bound backward kernels run later, on the stream the
+                # caller chooses, beside the next view's compositing
+                ctx.deferred.append(tail)
+            else:
+                sh_bwd()
+                if deferred_ok:
+                    # gradient-arena mode only: the caller runs the projection backward of all its views LATER (so
+                    # that the exchange of the SH gradients, final once the last view's SH backward has run, travels
+                    # under them)
+                    ctx.deferred.append(projection_bwd)
+                else:
+                    projection_bwd()
         m2 = ctx.means2d_ref() if ctx.means2d_ref is not None else None
         if m2 is not None:
             # what the reference reads after backward (street_gaussian_model.py:504-508)
@@ -668,10 +771,10 @@ class _FusedView(torch.autograd.Function):
             if absgrad:
                 m2.absgrad = v_abs.view(1, N, 2)
         if sinks is not None:
-            return (None,) * 22
+            return (None,) * 23
         need = ctx.needs_input_grad
         return (g_means if need[0] else None, g_quats if need[1] else None, g_scales if need[2] else None,
-                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 17
+                g_op if need[3] else None, g_shs if need[4] else None) + (None,) * 18
 
 
 def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, shs: Tensor, viewmats: Tensor,
@@ -679,14 +782,16 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
                near_plane: float = 0.01, far_plane: float = 1e10, radius_clip: float = 0.0,
                antialiased: bool = True, tile_size: int = 16, absgrad: bool = False,
                grad_sinks: Optional[Dict[str, Tensor]] = None, need_isect_ids: bool = True,
-               prepared: Optional[Dict] = None, deferred: Optional[list] = None) -> Tuple[Tensor, Tensor, Dict]:
+               prepared: Optional[Dict] = None, deferred: Optional[list] = None,
+               defer_sh: bool = False) -> Tuple[Tensor, Tensor, Dict]:
     """One camera (viewmats[1,4,4], Ks[1,3,3], campos[3] on the device), SH colours with K = 4 or
     16 coefficients, RGB + depth channel: -> (render_colors[1,H,W,4], render_alphas[1,H,W,1], meta).
     `meta["means2d"].grad` / `.absgrad` are filled by the backward pass.  `need_isect_ids=False`
     leaves meta["isect_ids"] empty: the 64-bit keys are an intermediate of the binning that only the
     op-by-op API hands out (the reference renderer's result dict does not hold them).  `deferred` (a list, with
     `grad_sinks` only): the backward appends its projection-backward launch to it instead of running it; the caller
-    calls the entries once the backward passes of all its views are through (parallel.ShardedAdam)."""
+    calls the entries once the backward passes of all its views are through (parallel.ShardedAdam).  `defer_sh`: the
+    deferred entry also holds the SH backward (pipeline.ViewPipeline runs both on its memory stream)."""
     import weakref
     assert viewmats.shape == (1, 4, 4) and Ks.shape == (1, 3, 3) and campos.shape == (3,)
     assert shs.dim() == 3 and shs.shape[1] in (4, 16) and (sh_degree + 1) ** 2 <= shs.shape[1]
@@ -695,7 +800,7 @@ def fused_view(means: Tensor, quats: Tensor, scales: Tensor, opacities: Tensor, 
         assert all(k in grad_sinks for k in ("means", "quats", "scales", "opacities", "shs"))
     out = _FusedView.apply(means, quats, scales, opacities, shs, viewmats, Ks, campos, width, height, sh_degree,
                            eps2d, near_plane, far_plane, radius_clip, antialiased, tile_size, absgrad, grad_sinks,
-                           need_isect_ids, prepared, deferred)
+                           need_isect_ids, prepared, deferred, defer_sh)
     (rc, ra, depth_norm, radii, means2d, depths, conics, op_c, colors4, tpg, isect_ids, flatten_ids, isect_offsets,
      vis, radii_norm) = out[:15]
     comps = out[15] if len(out) > 15 else None
