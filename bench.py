@@ -56,9 +56,9 @@ def parse():
     ap.add_argument("--no-cfg4", action="store_true", help="skip the strong-scaled configs[3] record")
     ap.add_argument("--schedule", default="graph", choices=["graph", "sequential", "pipeline"],
                     help="graph (N=1 default): the whole multi-view step with the sync-free binning captured ONCE in a "
-                         "CUDA graph and replayed (street_crafter_b200.pipeline.GraphedStep); sequential: one eager "
-                         "camera pass after the other (N>1 always: its NCCL overlap lives there); pipeline: eager "
-                         "two-stream ViewPipeline")
+                         "CUDA graph and replayed (street_crafter_b200.pipeline.GraphedStep; N>1: two graphs, "
+                         "the SH-gradient all-reduce starts between them); sequential: one eager camera pass after the "
+                         "other; pipeline: eager two-stream ViewPipeline")
     ap.add_argument("--ahead", type=int, default=1, help="pipeline: views prepared before the first compositing kernel")
     ap.add_argument("--no-pipe-sh", action="store_true")
     ap.add_argument("--no-pipe-tail", action="store_true")
@@ -535,7 +535,7 @@ def run_ours(args):
         torch.autograd.backward([out["render_colors"], out["render_alphas"]], [v_rc[v], v_ra[v]])
 
     from street_crafter_b200.pipeline import GraphedStep
-    schedule = args.schedule if world == 1 else "sequential"
+    schedule = args.schedule
 
     def step_sequential():
         """inputs already in HBM; upstream gradients fixed (loss-independent)"""
@@ -563,13 +563,20 @@ def run_ours(args):
     if schedule == "graph":
         # the same kernels on the same inputs, captured once: no launch gaps, no read-back bubbles, ~0 host work
         graphed = GraphedStep(pipe, arena.zero_grad, params_fn, dev_views, WIDTH, HEIGHT, SH_DEGREE, lambda: sinks,
-                              pipe_backward)
+                              pipe_backward, split_projection_backward=world > 1)
 
     def step_resident():
-        if graphed is not None:
+        if graphed is None:
+            step_sequential()
+        elif world == 1:
             graphed.replay()
         else:
-            step_sequential()
+            # two graphs: the all-reduce of the SH block (81 % of the arena) travels under the second one (the views'
+            # projection backward), then the geometric block
+            graphed.replay_main()
+            exchange.begin_sh()
+            graphed.replay_tail()
+            exchange.finish()
 
     feeder = HostViewFeeder(dev)
 
@@ -645,6 +652,9 @@ def run_ours(args):
 
         def step_e2e():
             graphed_e2e.replay()
+            if world > 1:
+                exchange.begin_sh()
+                exchange.finish()
             torch.cuda.current_stream().synchronize()
             return loss_host
 

@@ -52,14 +52,16 @@ class ViewPipeline:
              views: Sequence[Tuple[Tensor, Tensor, Tensor]], width: int, height: int, sh_degree: int,
              grad_sinks: Dict[str, Tensor], backward: Callable[[int, Dict[str, Tensor]], None],
              znear: float = 0.001, zfar: float = 1000.0, antialiasing: bool = True, absgrad: bool = True,
-             capacities: Optional[Sequence[int]] = None,
-             counts_host: Optional[Sequence[Tensor]] = None) -> List[Dict[str, Tensor]]:
+             capacities: Optional[Sequence[int]] = None, counts_host: Optional[Sequence[Tensor]] = None,
+             collect_projection_backward: Optional[List] = None) -> List[Dict[str, Tensor]]:
         """views: (w2c[1,4,4], K[1,3,3], camera_center[3]) on the device.  `backward(v, out)` attaches the caller's loss
         to the render of view v and calls .backward() on it (on the compute stream = the current stream).  The gradient
         arena behind `grad_sinks` must have been zeroed on the current stream.  On return the compute stream is ordered
         after every kernel of the step.  `capacities` (one per view) selects the sync-free binning
         (rendering.prepare_view_begin): no host wait anywhere in the step; `counts_host[v]` (pinned int64[3]) receives
-        the view's counts for the capacity check."""
+        the view's counts for the capacity check.  `collect_projection_backward` (a list): the views' projection
+        backward launches are appended to it instead of being run — the view-sharded trainer runs them while the SH
+        gradients, final without them, are already being exchanged (parallel.TwoPhaseAllReduce / ShardedAdam)."""
         comp = torch.cuda.current_stream(self.device)
         mem = self.mem
         n = len(views)
@@ -102,14 +104,17 @@ class ViewPipeline:
             deferred: List = []
             out = render_kernel_gsplat(means, shs, scales, quats, op2, V, K, C, width, height, sh_degree, znear=znear,
                                        zfar=zfar, antialiasing=antialiasing, absgrad=absgrad, grad_sinks=grad_sinks,
-                                       aux_ids=False, prepared=pb, deferred=deferred, defer_sh=self.pipeline_tail)
+                                       aux_ids=False, prepared=pb, deferred=deferred,
+                                       defer_sh=self.pipeline_tail and collect_projection_backward is None)
             backward(v, out)
             outs.append(out)
             if pending is not None:
                 # the counts of the next view have long arrived: the compute stream holds RF + RB of this view
                 ready.append(finish(pending))
                 pending = None
-            if self.pipeline_tail:
+            if collect_projection_backward is not None:
+                collect_projection_backward.extend(deferred)
+            elif self.pipeline_tail:
                 done = torch.cuda.Event()
                 done.record(comp)
                 with torch.cuda.stream(mem):
@@ -138,14 +143,20 @@ class GraphedStep:
                  views: Sequence[Tuple[Tensor, Tensor, Tensor]], width: int, height: int, sh_degree: int,
                  grad_sinks: Callable[[], Dict[str, Tensor]], backward: Callable[[int, Dict[str, Tensor]], None],
                  margin: float = 1.25, before: Optional[Callable[[], None]] = None,
-                 after: Optional[Callable[[], None]] = None, **render_kwargs):
+                 after: Optional[Callable[[], None]] = None, split_projection_backward: bool = False,
+                 **render_kwargs):
         """params() -> (means, shs, scales, quats, opacities); zero_grad() clears the gradient arena on the current
         stream; before() / after() (optional) are captured in front of / behind the views (host -> device copies of
-        the step's inputs from pinned memory; the optimiser step on the arena, the loss read-back)."""
+        the step's inputs from pinned memory; the optimiser step on the arena, the loss read-back).
+        split_projection_backward: TWO graphs — `replay_main()` ends with the last view's SH backward (the SH
+        gradients, 81 % of the arena, are final), `replay_tail()` holds the views' projection backward: a
+        multi-GPU step starts the exchange of the SH gradients between the two."""
         self.pipe, self.zero_grad, self.params, self.views = pipe, zero_grad, params, list(views)
         self.width, self.height, self.sh_degree = int(width), int(height), int(sh_degree)
         self.grad_sinks, self.backward, self.margin, self.after = grad_sinks, backward, float(margin), after
         self.before = before
+        self.split = bool(split_projection_backward)
+        self.graph_tail: Optional[torch.cuda.CUDAGraph] = None
         self.render_kwargs = render_kwargs
         self.counts_host = [torch.zeros(3, dtype=torch.int64).pin_memory() for _ in self.views]
         self.capacities: List[int] = []
@@ -161,12 +172,20 @@ class GraphedStep:
         # first used on; the caller's tensors may have met the default stream, which a capture must not wait for
         # (gradients go to the sinks, the accumulators stay empty)
         means, shs, scales, quats, opacities = (p.detach().requires_grad_(True) for p in self.params())
+        self._tail = [] if self.split else None
         outs = self.pipe.step(means, shs, scales, quats, opacities, self.views, self.width, self.height, self.sh_degree,
                               self.grad_sinks(), self.backward, capacities=self.capacities,
-                              counts_host=self.counts_host, **self.render_kwargs)
-        if self.after is not None:
+                              counts_host=self.counts_host, collect_projection_backward=self._tail,
+                              **self.render_kwargs)
+        if not self.split and self.after is not None:
             self.after()
         return outs
+
+    def _run_tail(self):
+        for fn in self._tail:
+            fn()
+        if self.after is not None:
+            self.after()
 
     def measure(self) -> List[int]:
         """intersection counts of the views as they are now (one eager, synchronising projection + binning each)"""
@@ -193,6 +212,8 @@ class GraphedStep:
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
             self._run()
+            if self.split:
+                self._run_tail()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         from ._lib import launch_count
@@ -200,8 +221,14 @@ class GraphedStep:
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             outs = self._run()
+        g2 = None
+        if self.split:
+            g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2, pool=g.pool()):
+                self._run_tail()
+            self._tail = None
         self.launches_per_replay = int(launch_count() - l0)   # this library's kernels inside one replay
-        self.graph, self.outs = g, outs
+        self.graph, self.graph_tail, self.outs = g, g2, outs
 
     def overflowed(self) -> List[int]:
         """views whose list outgrew its capacity in the LAST COMPLETED replay (synchronise first)"""
@@ -209,4 +236,13 @@ class GraphedStep:
 
     def replay(self) -> List[Dict[str, Tensor]]:
         self.graph.replay()
+        if self.graph_tail is not None:
+            self.graph_tail.replay()
         return self.outs
+
+    def replay_main(self) -> List[Dict[str, Tensor]]:
+        self.graph.replay()
+        return self.outs
+
+    def replay_tail(self) -> None:
+        self.graph_tail.replay()

@@ -145,6 +145,20 @@ def test_graphed_step_equals_eager_and_reports_overflow():
             assert torch.equal(o["render_colors"], r)
         for k in ref:
             assert (sinks[k] - ref[k]).abs().max().item() <= 1e-4 * ref[k].abs().max().item(), k
+    # two graphs (what the multi-GPU step replays around the start of its SH-gradient exchange)
+    gs2 = GraphedStep(ViewPipeline(dev), arena.zero_grad,
+                      lambda: (arena.means, arena.shs, arena.scales, arena.quats, arena.opacities), views, W, H, deg,
+                      lambda: sinks, bwd, split_projection_backward=True)
+    for _ in range(2):
+        gs2.replay_main()
+        torch.cuda.synchronize()
+        assert (sinks["shs"] - ref["shs"]).abs().max().item() <= 1e-4 * ref["shs"].abs().max().item()   # final already
+        assert float(sinks["quats"].abs().max()) == 0.0   # the projection backward has not run yet
+        gs2.replay_tail()
+        torch.cuda.synchronize()
+        for k in ref:
+            assert (sinks[k] - ref[k]).abs().max().item() <= 1e-4 * ref[k].abs().max().item(), k
+    del gs2
     # the camera moves (static tensors rewritten in place): same graph, new image; a view that sees much more than
     # the capacity allows is reported
     V2, K2 = make_camera(W, H, yaw_deg=10.0)
