@@ -355,7 +355,7 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
     backward of all views runs LAST, under the reduce-scatter of the SH gradients."""
     import torch.distributed as dist
     from street_crafter_b200.parallel import ShardedAdam
-    from street_crafter_b200.rendering import prepare_view
+    from street_crafter_b200.rendering import prepare_view, prepare_view_begin, prepare_view_finish
     scene = make_gaussians(CFG4_GAUSS, sh_degree=SH_DEGREE, seed=4, device=dev)
     arena = GaussianArena(scene, dev, pad_to=4 * world)
     del scene
@@ -389,31 +389,76 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
             marks.append(e)
 
     fill_stream = torch.cuda.Stream(dev)
+    state = {"prepared": [], "deferred": []}
+    caps, hosts = {}, {}    # graph schedule: capacity of every view's intersection list, pinned landing of its counts
+
+    def phase_one():   # everything that reads only means / quats / scales / opacities
+        for v in mine:
+            W, H, _, _ = views[v]
+            Vd, Kd, _ = cams[v]
+            if caps:
+                pb = prepare_view_begin(arena.means, arena.quats, arena.scales, arena.opacities, Vd, Kd, W, H,
+                                        near_plane=0.001, far_plane=1000.0, capacity=caps[v], counts_host=hosts[v])
+                state["prepared"].append(prepare_view_finish(pb, False))
+            else:
+                state["prepared"].append(prepare_view(arena.means, arena.quats, arena.scales, arena.opacities, Vd, Kd, W, H,
+                                                      near_plane=0.001, far_plane=1000.0))
+
+    def phase_two():   # SH + compositing + backward per view; the projection backward is deferred
+        # (fresh leaves: a captured backward must not meet gradient accumulators tied to another stream)
+        P = [p.detach().requires_grad_(True) for p in (arena.means, arena.shs, arena.scales, arena.quats, arena.opacities)]
+        for v, st in zip(mine, state["prepared"]):
+            W, H, _, _ = views[v]
+            Vd, Kd, Cd = cams[v]
+            out = render_kernel_gsplat(P[0], P[1], P[2], P[3], P[4], Vd, Kd, Cd, W, H, SH_DEGREE, grad_sinks=sinks,
+                                       aux_ids=False, prepared=st, deferred=state["deferred"])
+            torch.autograd.backward([out["render_colors"], out["render_alphas"]], list(up[(W, H)]))
+        state["prepared"] = []
+
+    def phase_three():
+        for fn in state["deferred"]:
+            fn()
+        state["deferred"] = []
+
+    graphs = None
+    if args.schedule == "graph":
+        # the three phases as three CUDA graphs (sync-free binning); the collectives and the waits for them stay
+        # eager calls between the replays
+        for v in mine:
+            W, H, _, _ = views[v]
+            pb = prepare_view(arena.means, arena.quats, arena.scales, arena.opacities, cams[v][0], cams[v][1], W, H,
+                              near_plane=0.001, far_plane=1000.0)
+            caps[v] = int(1.25 * pb["flatten_ids"].numel()) + 4096
+            hosts[v] = torch.zeros(3, dtype=torch.int64).pin_memory()
+            del pb
+        arena.zero_grad()
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):   # warm-up outside the capture
+            phase_one(); phase_two(); phase_three()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize()
+        gA, gB, gC = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gA):
+            phase_one()
+        with torch.cuda.graph(gB, pool=gA.pool()):
+            phase_two()
+        with torch.cuda.graph(gC, pool=gA.pool()):
+            phase_three()
+        graphs = (gA, gB, gC)
 
     def step():
         mark()
         zeroed = arena.zero_grad(stream=fill_stream)   # under phase one, which does not touch the gradients
         opt.wait_geometry()
-        prepared = []
-        for v in mine:   # phase one: everything that reads only means / quats / scales / opacities
-            W, H, _, _ = views[v]
-            Vd, Kd, _ = cams[v]
-            prepared.append(prepare_view(arena.means, arena.quats, arena.scales, arena.opacities, Vd, Kd, W, H,
-                                         near_plane=0.001, far_plane=1000.0))
+        graphs[0].replay() if graphs else phase_one()
         mark()
         opt.wait_sh()
-        deferred = []
-        for v, st in zip(mine, prepared):
-            W, H, _, _ = views[v]
-            Vd, Kd, Cd = cams[v]
-            out = render_kernel_gsplat(arena.means, arena.shs, arena.scales, arena.quats, arena.opacities, Vd, Kd, Cd,
-                                       W, H, SH_DEGREE, grad_sinks=sinks, aux_ids=False, prepared=st, deferred=deferred)
-            torch.autograd.backward([out["render_colors"], out["render_alphas"]], list(up[(W, H)]))
-        prepared.clear()
+        torch.cuda.current_stream(dev).wait_event(zeroed)
+        graphs[1].replay() if graphs else phase_two()
         # the SH gradients are final: their reduce-scatter travels under the projection backward of all the views
         opt.begin_sh_exchange()
-        for fn in deferred:
-            fn()
+        graphs[2].replay() if graphs else phase_three()
         mark()
         opt.step(async_gather=True)
         mark()
@@ -440,18 +485,25 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
     for i in range(0, len(marks) - 3, 4):
         for j in range(3):
             ph[j] += marks[i + j].elapsed_time(marks[i + j + 1]) / steps
+    if graphs:
+        torch.cuda.synchronize()
+        over = [v for v in mine if int(hosts[v][1]) > caps[v]]
+        if over:
+            raise RuntimeError(f"cfg4 graph schedule: views {over} outgrew their capacity")
     phases = {"projection_binning_all_views_ms": ph[0], "sh_compositing_backward_ms": ph[1],
               "reduce_scatter_adam_ms": ph[2], "rank": rank,
               "note": "compute-stream CUDA events of rank 0; the parameter all-gather runs on a side stream, what is "
                       "left of ms_per_step is its exposed part plus rank skew"}
-    del arena, sinks, opt
+    del arena, sinks, opt, graphs, state
     torch.cuda.empty_cache()
     return {"workload": "cfg4: 6M Gaussians SH3, 40 views = 8 frames x (3 x 1920x1280 + 2 x 1920x886), view v on rank v mod "
                         "world; step = fwd + bwd of the rank's views + reduce-scatter of the gradient arena + fused Adam on "
                         "the rank's slice + all-gather of the parameters (N = 1: fused Adam on the whole arena)",
             "scaling": "strong", "gaussians": CFG4_GAUSS, "views": len(views), "views_per_gpu": len(mine), "steps": steps,
             "ms_per_step": ms, "views_per_s": len(views) / (ms * 1e-3), "value": pix / (ms * 1e-3) / 1e6, "unit": "Mpix/s",
-            "phases": phases}
+            "phases": phases,
+            "schedule": "three CUDA graphs per step (projection + binning | SH + compositing + backward | projection "
+                        "backward), collectives between the replays" if args.schedule == "graph" else "eager"}
 
 
 class _LibProxy:
