@@ -438,14 +438,27 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
             phase_one(); phase_two(); phase_three()
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize()
-        gA, gB, gC = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-        with torch.cuda.graph(gA):
-            phase_one()
-        with torch.cuda.graph(gB, pool=gA.pool()):
-            phase_two()
-        with torch.cuda.graph(gC, pool=gA.pool()):
-            phase_three()
-        graphs = (gA, gB, gC)
+        try:
+            gA, gB, gC = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gA):
+                phase_one()
+            with torch.cuda.graph(gB, pool=gA.pool()):
+                phase_two()
+            with torch.cuda.graph(gC, pool=gA.pool()):
+                phase_three()
+            graphs = (gA, gB, gC)
+        except Exception as e:
+            print(f"cfg4: graph capture failed ({type(e).__name__}: {str(e)[:160]}); eager schedule", file=sys.stderr)
+            torch.cuda.synchronize()
+            graphs = None
+            state["prepared"], state["deferred"] = [], []
+            caps.clear()
+        if world > 1:
+            ok = torch.tensor([1 if graphs is not None else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                graphs = None
+                caps.clear()
 
     def step():
         mark()
@@ -485,6 +498,7 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
     for i in range(0, len(marks) - 3, 4):
         for j in range(3):
             ph[j] += marks[i + j].elapsed_time(marks[i + j + 1]) / steps
+    used_graphs = graphs is not None
     if graphs:
         torch.cuda.synchronize()
         over = [v for v in mine if int(hosts[v][1]) > caps[v]]
@@ -503,7 +517,7 @@ def run_cfg4(args, dev, rank, world, render_kernel_gsplat, make_camera, make_gau
             "ms_per_step": ms, "views_per_s": len(views) / (ms * 1e-3), "value": pix / (ms * 1e-3) / 1e6, "unit": "Mpix/s",
             "phases": phases,
             "schedule": "three CUDA graphs per step (projection + binning | SH + compositing + backward | projection "
-                        "backward), collectives between the replays" if args.schedule == "graph" else "eager"}
+                        "backward), collectives between the replays" if used_graphs else "eager"}
 
 
 class _LibProxy:
@@ -612,10 +626,22 @@ def run_ours(args):
 
     params_fn = lambda: (arena.means, arena.shs, arena.scales, arena.quats, arena.opacities)
     graphed = None
+    schedule_note = None
     if schedule == "graph":
         # the same kernels on the same inputs, captured once: no launch gaps, no read-back bubbles, ~0 host work
-        graphed = GraphedStep(pipe, arena.zero_grad, params_fn, dev_views, WIDTH, HEIGHT, SH_DEGREE, lambda: sinks,
-                              pipe_backward, split_projection_backward=world > 1)
+        try:
+            graphed = GraphedStep(pipe, arena.zero_grad, params_fn, dev_views, WIDTH, HEIGHT, SH_DEGREE, lambda: sinks,
+                                  pipe_backward, split_projection_backward=world > 1)
+        except Exception as e:   # a driver / torch that cannot capture: the eager schedule of the SAME kernels, said so
+            schedule_note = f"graph capture failed ({type(e).__name__}: {str(e)[:160]}); eager sequential schedule timed"
+            print(schedule_note, file=sys.stderr)
+            torch.cuda.synchronize()
+            schedule, graphed = "sequential", None
+        if world > 1:   # every rank must run the same schedule (the collectives pair up)
+            ok = torch.tensor([1 if graphed is not None else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                schedule, graphed = "sequential", None
 
     def step_resident():
         if graphed is None:
@@ -698,17 +724,31 @@ def run_ours(args):
         def e2e_after():
             loss_host.copy_(loss_dev, non_blocking=True)
 
-        graphed_e2e = GraphedStep(pipe, arena.zero_grad, params_fn, e2e_views, WIDTH, HEIGHT, SH_DEGREE, lambda: sinks,
-                                  e2e_backward, before=e2e_before, after=e2e_after)
+        try:
+            graphed_e2e = GraphedStep(pipe, arena.zero_grad, params_fn, e2e_views, WIDTH, HEIGHT, SH_DEGREE,
+                                      lambda: sinks, e2e_backward, before=e2e_before, after=e2e_after)
+        except Exception as e:
+            schedule_note = f"e2e graph capture failed ({type(e).__name__}: {str(e)[:160]}); eager e2e step timed"
+            print(schedule_note, file=sys.stderr)
+            torch.cuda.synchronize()
+            graphed_e2e = None
+        if world > 1:
+            ok = torch.tensor([1 if graphed_e2e is not None else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                graphed_e2e = None
         step_e2e_eager = step_e2e
 
-        def step_e2e():
+        def step_e2e_graph():
             graphed_e2e.replay()
             if world > 1:
                 exchange.begin_sh()
                 exchange.finish()
             torch.cuda.current_stream().synchronize()
             return loss_host
+
+        if graphed_e2e is not None:
+            step_e2e = step_e2e_graph
 
     h2d = host_cams.numel() * 4 + sum(t.numel() * 4 for t in host_gt)
     d2h = 4 * n_views
@@ -902,7 +942,7 @@ def run_ours(args):
                        "schedule": {"graph": "whole step (3 camera passes, sync-free binning) captured once in a CUDA "
                                              "graph, replayed per step", "sequential": "eager, one camera pass after "
                                     "the other", "pipeline": "eager two-stream ViewPipeline"}[schedule],
-                       "ms_per_step_eager_sequential": ms_step_eager},
+                       "ms_per_step_eager_sequential": ms_step_eager, "schedule_note": schedule_note},
             "e2e": {"value": e2e_value, "unit": "Mpix/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h,
                     "what": "pinned host camera matrices + target images -> device (side stream), render, "

@@ -178,3 +178,27 @@ def test_graphed_step_equals_eager_and_reports_overflow():
     gs.replay()
     torch.cuda.synchronize()
     assert gs.overflowed() == [0, 1, 2]
+
+
+def test_compositing_occupancy_limit_changes_nothing_but_residency():
+    """sc_rasterize_limit_warps (a dynamic shared-memory request that caps the resident one-warp CTAs per SM):
+    same images, same gradients to atomic rounding"""
+    from street_crafter_b200._lib import check, lib
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    dev = torch.device("cuda:0")
+    scene, views, W, H, deg = _scene_views(dev, n=30000)
+    V, K, C = views[1]
+    res = []
+    try:
+        for warps in (0, 6, 12):
+            check(lib.sc_rasterize_limit_warps(warps), "sc_rasterize_limit_warps")
+            c = {k: v.to(dev).requires_grad_(True) for k, v in scene.items()}
+            out = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], c["opacities"][:, None], V, K, C, W, H, deg)
+            (out["render_colors"].sum() + out["render_alphas"].sum()).backward()
+            res.append((out["render_colors"].detach().clone(), c["means"].grad.clone()))
+    finally:
+        lib.sc_rasterize_limit_warps(0)
+    assert lib.sc_rasterize_limit_warps(65) == -1
+    for img, g in res[1:]:
+        assert torch.equal(img, res[0][0])
+        assert (g - res[0][1]).abs().max().item() <= 1e-4 * res[0][1].abs().max().item()
