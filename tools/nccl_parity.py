@@ -4,8 +4,9 @@
 
   1. N-rank sharded views + ONE all-reduce of the flat gradient arena == one rank rendering every view sequentially;
   2. all-reduced densification statistics leave every rank with IDENTICAL clone / split / prune flags;
-  3. reduce-scatter + sharded fused Adam + all-gather == all-reduce + torch.optim.Adam on the full arena.
-Exit code 0 and "nccl parity ok" on rank 0 when all three hold."""
+  3. reduce-scatter + sharded fused Adam + all-gather == all-reduce + torch.optim.Adam on the full arena;
+  4. the sharded step replayed from two CUDA graphs around the start of the SH-block all-reduce == sequential.
+Exit code 0 and "nccl parity ok" on rank 0 when all four hold."""
 import os
 import sys
 
@@ -119,6 +120,39 @@ def main():
         if rank == 0:
             print(f"adam {name:10s} max |param diff| {d:.2e} (parameters moved by up to {moved:.2e})")
         ok &= d <= 2e-3 * moved + 1e-6
+    # ---- 4. the step as TWO CUDA graphs with the SH-block all-reduce started between them (bench.py's N > 1 schedule)
+    from street_crafter_b200.pipeline import GraphedStep, ViewPipeline
+    garena = GaussianArena(scene, dev, pad_to=4 * world)
+    gsinks = garena.sinks()
+    mine = list(shard_views(n_views, rank, world))
+    gviews = []
+    for v in mine:
+        Vm, Km = cams[v]
+        gviews.append((Vm[None].to(dev), Km[None].to(dev), (-(Vm[:3, :3].T @ Vm[:3, 3])).to(dev)))
+
+    def gbwd(i, out):
+        torch.autograd.backward([out["render_colors"], out["render_alphas"]], list(ups[mine[i]]))
+
+    gstep = GraphedStep(ViewPipeline(dev), garena.zero_grad,
+                        lambda: (garena.means, garena.shs, garena.scales, garena.quats, garena.opacities), gviews, W, H, deg,
+                        lambda: gsinks, gbwd, split_projection_backward=True)
+    gex = TwoPhaseAllReduce(garena)
+    seq = GaussianArena(scene, dev, pad_to=4 * world)   # (the Adam check above moved the old one's parameters)
+    run_views(seq, range(n_views))
+    for _ in range(2):
+        gstep.replay_main()
+        gex.begin_sh()
+        gstep.replay_tail()
+        gex.finish()
+        torch.cuda.synchronize()
+        ok &= gstep.overflowed() == []
+        for name, off, numel, _ in garena.layout:
+            a, b = garena.grads[off:off + numel].double(), seq.grads[off:off + numel].double()
+            err = float((a - b).abs().max() / (b.abs().max() + 1e-30))
+            ok &= err <= GRAD_RTOL
+            if rank == 0:
+                print(f"graph {name:10s} max-rel {err:.2e}")
+    del gstep
     t = torch.tensor([1.0 if ok else 0.0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.barrier()
