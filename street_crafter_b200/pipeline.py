@@ -50,12 +50,13 @@ class ViewPipeline:
 
     def step(self, means: Tensor, shs: Tensor, scales: Tensor, quats: Tensor, opacities: Tensor,
              views: Sequence[Tuple[Tensor, Tensor, Tensor]], width: int, height: int, sh_degree: int,
-             grad_sinks: Dict[str, Tensor], backward: Callable[[int, Dict[str, Tensor]], None],
+             grad_sinks: Optional[Dict[str, Tensor]], backward: Optional[Callable[[int, Dict[str, Tensor]], None]],
              znear: float = 0.001, zfar: float = 1000.0, antialiasing: bool = True, absgrad: bool = True,
              capacities: Optional[Sequence[int]] = None, counts_host: Optional[Sequence[Tensor]] = None,
              collect_projection_backward: Optional[List] = None) -> List[Dict[str, Tensor]]:
         """views: (w2c[1,4,4], K[1,3,3], camera_center[3]) on the device.  `backward(v, out)` attaches the caller's loss
-        to the render of view v and calls .backward() on it (on the compute stream = the current stream).  The gradient
+        to the render of view v and calls .backward() on it (on the compute stream = the current stream); None (with
+        `grad_sinks=None`, under torch.no_grad()): a render-only pass (evaluation: colours clamped to [0, 1]).  The gradient
         arena behind `grad_sinks` must have been zeroed on the current stream.  On return the compute stream is ordered
         after every kernel of the step.  `capacities` (one per view) selects the sync-free binning
         (rendering.prepare_view_begin): no host wait anywhere in the step; `counts_host[v]` (pinned int64[3]) receives
@@ -104,9 +105,10 @@ class ViewPipeline:
             deferred: List = []
             out = render_kernel_gsplat(means, shs, scales, quats, op2, V, K, C, width, height, sh_degree, znear=znear,
                                        zfar=zfar, antialiasing=antialiasing, absgrad=absgrad, grad_sinks=grad_sinks,
-                                       aux_ids=False, prepared=pb, deferred=deferred,
+                                       aux_ids=False, prepared=pb, deferred=deferred, train=backward is not None,
                                        defer_sh=self.pipeline_tail and collect_projection_backward is None)
-            backward(v, out)
+            if backward is not None:
+                backward(v, out)
             outs.append(out)
             if pending is not None:
                 # the counts of the next view have long arrived: the compute stream holds RF + RB of this view
@@ -139,14 +141,17 @@ class GraphedStep:
     Camera matrices, upstream tensors etc. are STATIC tensors: write new values into them before `replay()`.
     Re-capture after every densification (the parameter tensors change)."""
 
-    def __init__(self, pipe: ViewPipeline, zero_grad: Callable[[], None], params: Callable[[], Tuple[Tensor, ...]],
+    def __init__(self, pipe: ViewPipeline, zero_grad: Optional[Callable[[], None]],
+                 params: Callable[[], Tuple[Tensor, ...]],
                  views: Sequence[Tuple[Tensor, Tensor, Tensor]], width: int, height: int, sh_degree: int,
-                 grad_sinks: Callable[[], Dict[str, Tensor]], backward: Callable[[int, Dict[str, Tensor]], None],
+                 grad_sinks: Optional[Callable[[], Dict[str, Tensor]]],
+                 backward: Optional[Callable[[int, Dict[str, Tensor]], None]],
                  margin: float = 1.25, before: Optional[Callable[[], None]] = None,
                  after: Optional[Callable[[], None]] = None, split_projection_backward: bool = False,
                  **render_kwargs):
         """params() -> (means, shs, scales, quats, opacities); zero_grad() clears the gradient arena on the current
-        stream; before() / after() (optional) are captured in front of / behind the views (host -> device copies of
+        stream; `zero_grad = grad_sinks = backward = None`: a RENDER-ONLY graph (trajectory / novel-view rendering:
+        rewrite the camera tensors, replay, read `outs[v]["rgb"]`); before() / after() (optional) are captured in front of / behind the views (host -> device copies of
         the step's inputs from pinned memory; the optimiser step on the arena, the loss read-back).
         split_projection_backward: TWO graphs — `replay_main()` ends with the last view's SH backward (the SH
         gradients, 81 % of the arena, are final), `replay_tail()` holds the views' projection backward: a
@@ -167,6 +172,12 @@ class GraphedStep:
     def _run(self):
         if self.before is not None:
             self.before()
+        if self.backward is None:   # render only
+            with torch.no_grad():
+                means, shs, scales, quats, opacities = (p.detach() for p in self.params())
+                return self.pipe.step(means, shs, scales, quats, opacities, self.views, self.width, self.height,
+                                      self.sh_degree, None, None, capacities=self.capacities,
+                                      counts_host=self.counts_host, **self.render_kwargs)
         self.zero_grad()
         # fresh leaves over the same storage: autograd ties a leaf's gradient accumulator to the stream the leaf was
         # first used on; the caller's tensors may have met the default stream, which a capture must not wait for

@@ -202,3 +202,32 @@ def test_compositing_occupancy_limit_changes_nothing_but_residency():
     for img, g in res[1:]:
         assert torch.equal(img, res[0][0])
         assert (g - res[0][1]).abs().max().item() <= 1e-4 * res[0][1].abs().max().item()
+
+
+def test_render_only_graph_equals_eager_eval():
+    """GraphedStep without a backward: a trajectory render replays ONE graph per batch of views; the camera tensors
+    are rewritten in place"""
+    from street_crafter_b200.pipeline import GraphedStep, ViewPipeline
+    from street_crafter_b200.renderer import render_kernel_gsplat
+    dev = torch.device("cuda:0")
+    scene, views, W, H, deg = _scene_views(dev)
+    c = {k: v.to(dev) for k, v in scene.items()}
+    occ1 = c["opacities"][:, None]
+    gs = GraphedStep(ViewPipeline(dev), None, lambda: (c["means"], c["shs"], c["scales"], c["quats"], occ1), views, W, H,
+                     deg, None, None)
+    for shift in (0.0, 4.0):
+        if shift:
+            V2, K2 = make_camera(W, H, yaw_deg=5.0, z_shift=shift)
+            views[2][0].copy_(V2[None]); views[2][2].copy_(-(V2[:3, :3].T @ V2[:3, 3]))
+        outs = gs.replay()
+        torch.cuda.synchronize()
+        if gs.overflowed():
+            gs.recapture()
+            outs = gs.replay()
+            torch.cuda.synchronize()
+        for (V, K, C), o in zip(views, outs):
+            with torch.no_grad():
+                ref = render_kernel_gsplat(c["means"], c["shs"], c["scales"], c["quats"], occ1, V, K, C, W, H, deg, train=False)
+            for k in ("rgb", "acc", "depth", "radii", "visibility_filter"):
+                assert torch.equal(o[k], ref[k]), k
+            assert float(o["rgb"].max()) <= 1.0

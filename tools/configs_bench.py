@@ -83,9 +83,18 @@ def sweep(dev):
 
         views()
         ms = ev_ms(views, 3) / len(cams)
+        # the same three views as ONE render-only CUDA graph (sync-free binning): what a trajectory render replays
+        from street_crafter_b200.pipeline import GraphedStep, ViewPipeline
+        gs = GraphedStep(ViewPipeline(dev), None, lambda: (sc["means"], sc["shs"], sc["scales"], sc["quats"], occ1), cams,
+                         W, H, 3, None, None)
+        gs.replay()
+        ms_g = ev_ms(gs.replay, 5) / len(cams)
+        torch.cuda.synchronize()
+        assert gs.overflowed() == []
         print(json.dumps({"config": "configs[4] render-only sweep", "gaussians": N, "size": [W, H],
-                          "ms_per_view": ms, "views_per_s": 1e3 / ms, "Mpix_per_s": W * H / ms / 1e3}))
-        del sc
+                          "ms_per_view": ms, "views_per_s": 1e3 / ms, "Mpix_per_s": W * H / ms / 1e3,
+                          "graph_ms_per_view": ms_g, "graph_views_per_s": 1e3 / ms_g}))
+        del sc, gs
         torch.cuda.empty_cache()
 
 
