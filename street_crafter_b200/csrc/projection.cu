@@ -740,7 +740,14 @@ constexpr int FB_KPT = 16;
 constexpr int FB_TILE = FB_THREADS * FB_KPT;  // 4096 slots per CTA
 constexpr int FB_TILE_LOG2 = 12;
 constexpr int FB_RADIX = 128;
-constexpr int FB_LB_W = 4;  // measured on cfg2: window 16 / 8 / 4 -> finish half 0.724 / 0.733 / 0.683 ms per step
+#ifndef SC_FB_MIN_CTAS
+#define SC_FB_MIN_CTAS 4   // measured 2 / 3 / 4 CTAs per SM: finish half 0.701 / 0.683 / 0.659 ms per cfg2 step
+#endif
+constexpr int FB_MIN_CTAS = SC_FB_MIN_CTAS;   // resident CTAs per SM the two sorting kernels are compiled for
+#ifndef SC_FB_LB_W
+#define SC_FB_LB_W 2   // measured on cfg2: look-back window 16 / 8 / 4 -> finish half 0.724 / 0.733 / 0.683 ms per step; at 4 CTAs per SM: 4 / 2 -> 0.660 / 0.630
+#endif
+constexpr int FB_LB_W = SC_FB_LB_W;
 static_assert(FB_TILE == (1 << FB_TILE_LOG2), "tile size");
 // item blocks of the emit kernel: an item is one (Gaussian, tile column) pair, i.e. a run of h
 // consecutive tile rows that lands contiguously in the column-sorted list
@@ -1302,7 +1309,7 @@ struct FeSmem {
 };
 
 // emit + first sorting pass (digit = tile column tx)
-__global__ void __launch_bounds__(FB_THREADS, 3)
+__global__ void __launch_bounds__(FB_THREADS, FB_MIN_CTAS)
 isect_emit_sort_tx_kernel(int64_t V, int64_t n_isects, const int64_t* __restrict__ totals_dev,
                           const int64_t* __restrict__ cum /*[V+1]*/,
                           const uint32_t* __restrict__ rect_s, const uint32_t* __restrict__ gid_s,
@@ -1429,7 +1436,7 @@ isect_emit_sort_tx_kernel(int64_t V, int64_t n_isects, const int64_t* __restrict
 }
 
 // second (final) sorting pass (digit = tile row ty): flatten_ids, isect_ids (nullable), offsets
-__global__ void __launch_bounds__(FB_THREADS, 3)
+__global__ void __launch_bounds__(FB_THREADS, FB_MIN_CTAS)
 isect_sort_ty_final_kernel(int64_t n_isects, const int64_t* __restrict__ totals_dev,
                            const uint64_t* __restrict__ pairs_in,
                            const uint32_t* __restrict__ hist_ty, volatile uint32_t* __restrict__ lookback,
