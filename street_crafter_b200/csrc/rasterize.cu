@@ -64,13 +64,17 @@ __device__ __forceinline__ PairX pair_x(const StagedA& A, float px) {
 //          <=> 0 <= s2 <= thr,  s2 = sigma * log2(e),  thr = log2(opacity) - log2(1/255)
 //          <=> |s2 - h| <= h,   h = thr / 2            (one add + one compare).
 // A DEAD pixel (saturated in the forward, not yet reached in the backward, or outside the
-// image) holds y = +inf: s2 becomes +inf or NaN and fails the window, so liveness costs no
+// image) holds y = SC_DEAD_Y: s2 becomes huge (or +inf) and fails the window, so liveness costs no
 // instruction in the per-pair chain.
 __device__ __forceinline__ bool pair_test(const PairX& X, float c2, float h, float dy, float& s2) {
     s2 = fmaf(fmaf(c2, dy, X.v), dy, X.u);  // sigma * log2e
     return fabsf(s2 - h) <= h;
 }
-#define SC_DEAD_Y __int_as_float(0x7f800000)
+// (a large FINITE value, not +inf: dy = -1e18 makes s2 = c2 * 1e36 -> far outside any window (c2 > 0: the 2D
+// covariance carries eps2d on its diagonal; non-positive or NaN conics fail the window as well), while every
+// product of the backward's moment sums with the pixel's zero weight stays an exact 0 instead of 0 * inf = NaN —
+// so the backward needs no per-pixel select on dy)
+#define SC_DEAD_Y 1e18f
 
 // ---- Blackwell packed FP32 (fma/add/sub/mul .f32x2 -> SASS FFMA2 / FADD2 / FMUL2) ------------------
 // One instruction works on the two halves of a 64-bit register pair: the SAME FLOP rate as scalar FFMA
@@ -97,6 +101,8 @@ __device__ __forceinline__ f2 mul2(f2 a, f2 b) { f2 d; asm("mul.rn.ftz.f32x2 %0,
 // (plain neg.f32: the .ftz form --use_fast_math would pick is kept as a separate flushing FADD)
 __device__ __forceinline__ float negf(float x) { float r; asm("neg.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 __device__ __forceinline__ f2 neg2(f2 a) { return pk2(negf(lo2(a)), negf(hi2(a))); }
+__device__ __forceinline__ float absf_(float x) { float r; asm("abs.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ f2 abs2(f2 a) { return pk2(absf_(lo2(a)), absf_(hi2(a))); }
 __device__ __forceinline__ float rcp_approx(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 // per-Gaussian operands of the pair test, broadcast once per (lane, Gaussian)
 struct PairX2 { f2 y, c2, v, u, h; };
@@ -584,7 +590,7 @@ __device__ __forceinline__ float warp_reduce_rows(const float (&v)[NRED], float 
 // Slots of the reduced vector: 0..4 v_colors, 5..7 second moments (w dx dx, w dx dy, w dy dy),
 // 8..9 sum w*h (h = d s2 / d mean), 10..11 the same with |.|, 12 sum w;  w = -au * v_alpha.
 // A pixel joins the walk when the list position reaches its last_ids entry (a rare event,
-// handled in its own warp-uniform branch: until then its y is +inf and every test fails).
+// handled in its own warp-uniform branch: until then its y is SC_DEAD_Y and every test fails).
 template <int CH>
 __global__ void __launch_bounds__(WARPS_PER_CTA * 32, BWD_MIN_CTAS)
 rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int tile_w, int tile_h,
@@ -751,7 +757,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
             const PairX2 P2 = pair_x2(X, A.y, B.c2, hwin);
             const f2 lo_2 = bc2(B.lo), one2 = bc2(1.0f), b22 = bc2(A.b2), hx02 = bc2(hx0), c2x22 = bc2(c2x2);
             f2 col2[CH], vc2[CH], sw2 = 0ull, swy2 = 0ull, swyy2 = 0ull;
-            float abx0 = 0.f, abx1 = 0.f, aby0 = 0.f, aby1 = 0.f;
+            f2 abx2 = 0ull, aby2 = 0ull;
 #pragma unroll
             for (int c = 0; c < CH; ++c) { col2[c] = bc2(col[c]); vc2[c] = 0ull; }
             auto halves = [&](auto nocap_tag) {
@@ -770,8 +776,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                         for (int u = 0; u < 2; ++u) {
                             const int p = 2 * h + u;
                             const bool ok0 = ok[2 * u], ok1 = ok[2 * u + 1];
-                            // a dead pixel has dy = -inf: keep it out of the moment sums
-                            const f2 dy = pk2(ok0 ? lo2(dy2[u]) : 0.f, ok1 ? hi2(dy2[u]) : 0.f);
+                            const f2 dy = dy2[u];   // finite for dead pixels too; their weight w is an exact 0
                             const f2 e2 = sub2(lo_2, s2[u]);
                             const float au0 = exp2f(lo2(e2)), au1 = exp2f(hi2(e2));
                             const f2 a = pk2(ok0 ? (NOCAP ? au0 : fminf(SC_ALPHA_CAP, au0)) : 0.f,
@@ -809,8 +814,8 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
                             swyy2 = fma2(wdy, dy, swyy2);
                             const f2 ax = mul2(w, fma2(b22, dy, hx02));    // w * d s2 / d mean.x
                             const f2 ay = mul2(w, fma2(c2x22, dy, P2.v));  // w * d s2 / d mean.y
-                            abx0 += fabsf(lo2(ax)); abx1 += fabsf(hi2(ax));
-                            aby0 += fabsf(lo2(ay)); aby1 += fabsf(hi2(ay));
+                            abx2 = add2(abx2, abs2(ax));   // |.| is a folded operand modifier of the packed add
+                            aby2 = add2(aby2, abs2(ay));
                         }
                     }
                 }
@@ -844,7 +849,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 #pragma unroll
                         for (int q = 0; q < 4; ++q) {
                             const int r = 4 * h + q;
-                            // a dead pixel has dy = -inf: keep it out of the moment sums
+                            // (scalar build) keep the pixels that fail the test out of the moment sums
                             const float dy = ok[q] ? dyq[q] : 0.f;
                             const float au = exp2f(B.lo - s2[q]);
                             const float a = ok[q] ? (NOCAP ? au : fminf(SC_ALPHA_CAP, au)) : 0.f;
@@ -887,7 +892,7 @@ rasterize_bwd_kernel(int64_t n_isects, int n_cams, int width, int height, int ti
 #if SC_RASTER_F32X2
             // join the halves (even + odd rows)
             const float sw = lo2(sw2) + hi2(sw2), swy = lo2(swy2) + hi2(swy2), swyy = lo2(swyy2) + hi2(swyy2);
-            const float abx = abx0 + abx1, aby = aby0 + aby1;
+            const float abx = lo2(abx2) + hi2(abx2), aby = lo2(aby2) + hi2(aby2);
 #pragma unroll
             for (int c = 0; c < CH; ++c) v[c] = lo2(vc2[c]) + hi2(vc2[c]);
 #else

@@ -15,6 +15,7 @@ print(sys.argv[1], "graph ms/step", round(d["ms_per_step"], 4), "eager", round(d
 PY
 }
 run default
+shopt -s nullglob
 for so in street_crafter_b200/_variants/libscb200_*.so; do
   name=$(basename $so .so); name=${name#libscb200_}
   SCB200_LIB=$PWD/$so run $name
