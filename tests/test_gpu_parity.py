@@ -674,6 +674,26 @@ def test_knn_vs_compiled_reference(S, dev):
     assert exact > 0.99, f"only {exact:.4f} bit-identical to the reference kernel"
 
 
+def test_cfg5_knn_5m_vs_compiled_reference_full_size(S, dev):
+    """BASELINE configs[4]: distCUDA2 on 5 M points against the reference's own kernel on ALL of them (the subset test
+    above checks 512 queries against brute force)"""
+    import ctypes
+    path = os.path.join(os.path.dirname(os.path.dirname(__file__)), "oracle", "_ref", "libsimpleknn_ref.so")
+    if not os.path.exists(path):
+        pytest.skip("oracle/_ref not built")
+    ref = ctypes.CDLL(path)
+    ref.ref_knn.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    xyz, _ = make_lidar_points(5_000_000, seed=5)
+    p = xyz.to(dev).contiguous()
+    want = torch.zeros(p.shape[0], device=dev)
+    torch.cuda.synchronize()
+    ref.ref_knn(p.shape[0], p.data_ptr(), want.data_ptr())
+    torch.cuda.synchronize()
+    got = S.distCUDA2(p)
+    assert torch.allclose(got, want, rtol=1e-6, atol=0), (got - want).abs().max()
+    assert (got == want).float().mean().item() > 0.99
+
+
 # ------------------------------------------------------------------------------ LiDAR point splat
 def test_point_rasterizer_max_hit(S, dev):
     N, W, H = 20000, 256, 144
