@@ -29,6 +29,14 @@
  *   sc_assemble_features_fwd/bwd  StreetGaussianModel.get_features (Fourier DC of the actors)  street_gaussian/models/street_gaussian_model.py:366-386
  *   sc_assemble_act_fwd/bwd    StreetGaussianModel.get_scaling / get_opacity  street_gaussian/models/street_gaussian_model.py:273-294, :389-407
  *   sc_densify_classify/move   densify_and_prune (clone + split + prune)  street_gaussian/models/gaussian_model.py:433-551
+ *   sc_bin_finish_dev, sc_rasterize_fwd_depth_dev   the second half of isect_tiles(sort=True) and the compositing forward
+ *                                  WITHOUT the host read-back of n_isects (street_gaussian_renderer.py:243-280): counts stay on
+ *                                  the device, outputs sized by a capacity — a camera pass that can be captured in a CUDA graph
+ *   sc_adam_step               torch.optim.Adam.step() as set up by GaussianModel.training_setup   gaussian_model.py:287-305
+ *   sc_ply_pack/unpack         GaussianModel.make_ply / load_ply row layout   gaussian_model.py:82-156
+ *   sc_lidar_gather/pack       make_lidar_ply / transform_lidar_ply / the uint8 packing of render_condition
+ *                              street_gaussian/pointcloud_processor/base_processor.py:32-63, waymo_processor.py:179-242
+ *   sc_rasterize_limit_warps, sc_exclusive_scan_i32_noalloc   no counterpart in the reference (scheduling knob; allocation-free scan)
  *
  * Conventions: all pointers are DEVICE pointers unless named host_*; row-major contiguous
  * fp32 / int32 / int64 arrays; `stream` is a cudaStream_t passed as void*; nothing here
