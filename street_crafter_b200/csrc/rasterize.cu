@@ -254,7 +254,8 @@ constexpr int BWD_MIN_CTAS = SC_BWD_MIN_CTAS;
 #define SC_BWD_VRC_SMEM 1  // the backward keeps the per-pixel upstream colour gradient in shared memory (32 registers
                            // freed for the scheduler; one conflict-free LDS.128 per contributing pixel pair)
 #endif
-constexpr int BATCH_BWD = SC_BWD_BATCH;
+constexpr int BATCH_BWD = SC_BWD_BATCH;   // 64 (128 measured slower: 1.281 -> 1.357 ms per cfg2 step)
+static_assert(BATCH_BWD >= ROUND && BATCH >= ROUND, "a staging batch holds at least one round of candidates");
 constexpr bool BWD_VRC_SMEM = SC_BWD_VRC_SMEM != 0;
 
 template <int CH, bool WITH_GID, int NBATCH = BATCH>
