@@ -1505,8 +1505,8 @@ isect_sort_ty_final_kernel(int64_t n_isects, const int64_t* __restrict__ totals_
 __global__ void __launch_bounds__(1024)
 isect_offsets_fixup_kernel(int n_tiles, const int64_t* __restrict__ n_isects_dev, int64_t n_isects,
                            int32_t* __restrict__ offsets) {
-    __shared__ int32_t s_min[1024];
-    const int tid = threadIdx.x;
+    __shared__ int32_t s_warp[32];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     // with the device count, `n_isects` is the capacity of the list (a list that does not fit is dropped: all
     // offsets 0, the view renders empty)
     const int32_t total = (int32_t)(n_isects_dev ? (*n_isects_dev <= n_isects ? *n_isects_dev : 0) : n_isects);
@@ -1514,16 +1514,22 @@ isect_offsets_fixup_kernel(int n_tiles, const int64_t* __restrict__ n_isects_dev
     const int lo = tid * per, hi = min(lo + per, n_tiles);
     int32_t m = total;
     for (int i = hi - 1; i >= lo; --i) m = min(m, offsets[i]);
-    s_min[tid] = m;
-    __syncthreads();
-    // suffix minimum over the per-thread minima
-    for (int d = 1; d < 1024; d <<= 1) {
-        const int32_t o = (tid + d < 1024) ? s_min[tid + d] : total;
-        __syncthreads();
-        s_min[tid] = min(s_min[tid], o);
-        __syncthreads();
+    // suffix minimum over the per-thread minima: inside the warp by shuffles, across the 32 warps through one
+    // shared-memory exchange (two barriers instead of twenty)
+    int32_t suf = m;   // min over threads tid .. end of the warp
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int32_t o = __shfl_down_sync(0xffffffffu, suf, d);
+        if (lane + d < 32) suf = min(suf, o);
     }
-    int32_t run = (tid + 1 < 1024) ? s_min[tid + 1] : total;
+    if (lane == 0) s_warp[w] = suf;
+    __syncthreads();
+    int32_t later = total;   // min over the warps behind this one
+    for (int ww = w + 1; ww < 32; ++ww) later = min(later, s_warp[ww]);
+    // what follows this thread: the rest of its warp, then the later warps
+    int32_t next_in_warp = __shfl_down_sync(0xffffffffu, suf, 1);
+    if (lane == 31) next_in_warp = total;
+    int32_t run = min(next_in_warp, later);
     for (int i = hi - 1; i >= lo; --i) {
         run = min(run, offsets[i]);
         offsets[i] = run;
