@@ -946,7 +946,10 @@ size_t occupancy_pad(size_t static_smem) {
     if (g_warps_per_sm <= 0 || WARPS_PER_CTA != 1) return 0;
     const size_t per_cta = (size_t)(228 * 1024) / (size_t)g_warps_per_sm;   // 1 KB of each CTA is the system's
     const size_t want = (per_cta > static_smem + 1024 + 128) ? per_cta - static_smem - 1024 : 0;
-    return std::min<size_t>(want / 128 * 128, 40 * 1024);
+    // static + dynamic stay below the 48 KB a launch may use without opting in (so fewer than 5 warps per SM
+    // cannot be enforced this way: the request saturates)
+    const size_t cap = (size_t)(48 * 1024) - static_smem - 128;
+    return std::min<size_t>(want, cap) / 128 * 128;
 }
 
 template <int CH>
