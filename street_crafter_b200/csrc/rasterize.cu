@@ -252,6 +252,8 @@ constexpr int BWD_MIN_CTAS = SC_BWD_MIN_CTAS;
 #endif
 #ifndef SC_BWD_TEST_FIRST
 #define SC_BWD_TEST_FIRST 1   // window tests of all 8 pixels before the two half-tile bodies: 1.275 -> 1.233 ms per cfg2 step
+                              // (also hoisting the eight ex2 measured no better: 1.244 -> 1.253; reading entry t + 1's
+                              // staged record during entry t in the FORWARD measured worse, 0.616 -> 0.682: registers)
 #endif
 #ifndef SC_BWD_VRC_SMEM
 #define SC_BWD_VRC_SMEM 1  // the backward keeps the per-pixel upstream colour gradient in shared memory (32 registers
